@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz from the REAL reference (run in the build container only).
+
+Imports /root/reference/src/{gp,mpc,experiments} through a ``sys.modules`` shim that bypasses
+``src/__init__.py`` (which needs the absent third-party ``simdyn``) and ``src/mpc/__init__.py``
+(which needs CasADi), and drives the reference's own code on seeded inputs.  The QP assembler
+(osqp_rti.py) is run with a stub ``osqp`` module that only records what ``setup`` receives.
+Outputs are small fixtures; the committed files are what the tests (and the GPU box) read --
+/root/reference itself does not travel.
+
+    python -m oracle.gen_golden
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+os.environ["PYTHONDONTWRITEBYTECODE"] = "1"
+sys.dont_write_bytecode = True
+
+import numpy as np
+
+REF = "/root/reference/src"
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def install_shim():
+    for name in ("src", "src.mpc", "src.experiments"):
+        pkg = types.ModuleType(name)
+        pkg.__path__ = [os.path.join(REF, *name.split(".")[1:])]
+        sys.modules[name] = pkg
+
+    class _StubOSQP:  # records the arguments of the reference's call sites (osqp_rti.py:464-478)
+        last = None
+
+        def setup(self, **kw):
+            _StubOSQP.last = kw
+
+        def update(self, **kw):
+            pass
+
+        def warm_start(self, **kw):
+            pass
+
+    osqp = types.ModuleType("osqp")
+    osqp.OSQP = _StubOSQP
+    sys.modules["osqp"] = osqp
+    return _StubOSQP
+
+
+def gp_fixture(n=1000, seed=0):
+    """SURVEY section 8(d) config 1 synthetic residual data."""
+    rng = np.random.default_rng(seed)
+    m = rng.uniform(1.2, 2, n); alt = rng.uniform(0, 40, n)
+    y = rng.normal(0, 3, n); z = rng.normal(0, 3, n)
+    vx = rng.normal(-3, 1, n); vy = rng.normal(0, .5, n); vz = rng.normal(0, .5, n)
+    X = np.stack([m, alt, y, z, vx, vy, vz], 1)
+    U = np.stack([rng.uniform(.3, 5, n), rng.uniform(-1, 1, n), rng.uniform(-1, 1, n)], 1)
+    rho = 1.225 * np.exp(-alt / 8500)
+    v = X[:, 4:7]; sp = np.linalg.norm(v, axis=1)
+    D = -0.5 * rho[:, None] * 0.5 * 0.5 * sp[:, None] * v / m[:, None] + rng.normal(0, 0.01, (n, 3))
+    return X, U, D
+
+
+def query_fixture(X, U, nq, seed):
+    rng = np.random.default_rng(seed)
+    idx = rng.integers(0, X.shape[0], nq)
+    return X[idx] + rng.normal(0, 0.05, (nq, 7)), U[idx] + rng.normal(0, 0.05, (nq, 3))
+
+
+def main():
+    Stub = install_shim()
+    import src.gp as G
+    from src.gp.fast_gp import FastGPPredictor
+    os.makedirs(OUT, exist_ok=True)
+    save = lambda name, **kw: np.savez_compressed(os.path.join(OUT, name), **kw)
+
+    # ---- 1. kernels ------------------------------------------------------------------
+    rng = np.random.default_rng(10)
+    D = 11
+    X1 = rng.normal(0, 1, (37, D)); X2 = rng.normal(0, 1, (23, D))
+    ls = rng.uniform(0.5, 2.0, D); sv = 1.7
+    out = dict(X1=X1, X2=X2, ls=ls, sv=sv)
+    for name, cls in (("se", G.SquaredExponentialARD), ("m32", G.Matern32), ("m52", G.Matern52)):
+        k = cls(D, signal_variance=sv, lengthscales=ls)
+        out[f"{name}_self"] = k(X1); out[f"{name}_cross"] = k(X1, X2); out[f"{name}_diag"] = k.diagonal(X1)
+    gr = G.SquaredExponentialARD(D, sv, ls).gradients(X1, X2)
+    out["se_grad_names"] = np.array(list(gr.keys()))
+    out["se_grad"] = np.stack(list(gr.values()))
+    out["se_params"] = G.SquaredExponentialARD(D, sv, ls).get_params()
+    save("kernels.npz", **out)
+
+    # ---- 2. Simple3DoFGP exact, n=1000, noise 1e-4 (default, cond~9e6) and 1e-2 ----------
+    X, U, Dres = gp_fixture()
+    Xq, Uq = query_fixture(X, U, 64, 1)
+    out = dict(X=X, U=U, D=Dres, Xq=Xq, Uq=Uq)
+    for tag, noise in (("n1e-4", 1e-4), ("n1e-2", 1e-2)):
+        gp = G.Simple3DoFGP(use_sparse=False, noise_variance=noise)
+        gp.add_data(X, U, Dres); gp.fit()
+        means = np.zeros((64, 3)); vars_ = np.zeros((64, 3))
+        for i in range(64):
+            means[i], vars_[i] = gp.predict(Xq[i], Uq[i])
+        out[f"{tag}_mean"] = means; out[f"{tag}_var"] = vars_
+        out[f"{tag}_alpha"] = np.stack([g._alpha for g in gp.gp.gps])
+        out[f"{tag}_ymean"] = np.array([g._y_mean for g in gp.gp.gps])
+        out[f"{tag}_ystd"] = np.array([g._y_std for g in gp.gp.gps])
+        out[f"{tag}_lml"] = np.array([g.log_marginal_likelihood for g in gp.gp.gps])
+        out[f"{tag}_Ldiag"] = np.diag(gp.gp.gps[0]._L).copy()
+        out[f"{tag}_Lrow999"] = gp.gp.gps[0]._L[999].copy()
+        out[f"{tag}_Lcol0"] = gp.gp.gps[0]._L[:, 0].copy()
+    out["Z_train"] = gp.feature_extractor.extract_batch(X, U)
+    out["Z_query"] = gp.feature_extractor.extract_batch(Xq, Uq)
+    save("simple3dof_exact.npz", **out)
+
+    # ---- 3. ExactGP with each kernel, n=200 (+ return_cov, no-normalise) ------------------
+    rng = np.random.default_rng(3)
+    n = 200
+    Xs = rng.normal(0, 1, (n, 5)); ys = np.sin(Xs[:, 0]) + 0.3 * Xs[:, 1] ** 2 + rng.normal(0, 0.05, n)
+    Xt = rng.normal(0, 1, (17, 5)); ls5 = rng.uniform(0.7, 1.8, 5)
+    out = dict(X=Xs, y=ys, Xt=Xt, ls=ls5, sv=0.8, noise=1e-3)
+    for name, cls in (("se", G.SquaredExponentialARD), ("m32", G.Matern32), ("m52", G.Matern52)):
+        gp = G.ExactGP(cls(5, 0.8, ls5), noise_variance=1e-3).fit(Xs, ys)
+        pr = gp.predict(Xt)
+        mc, cov = gp.predict(Xt, return_cov=True)
+        out.update({f"{name}_mean": pr.mean, f"{name}_var": pr.variance, f"{name}_std": pr.std, f"{name}_cov": cov,
+                    f"{name}_alpha": gp._alpha, f"{name}_L": gp._L, f"{name}_lml": gp.log_marginal_likelihood,
+                    f"{name}_ymean": gp._y_mean, f"{name}_ystd": gp._y_std})
+    gp = G.ExactGP(G.SquaredExponentialARD(5, 0.8, ls5), noise_variance=1e-3, normalize_y=False).fit(Xs, ys)
+    pr = gp.predict(Xt)
+    out.update(se_nonorm_mean=pr.mean, se_nonorm_var=pr.variance, se_nonorm_lml=gp.log_marginal_likelihood)
+    # jitter escalation: duplicated inputs + tiny noise make K + noise*I numerically singular
+    Xd = np.vstack([Xs[:40], Xs[:40]]); yd = np.concatenate([ys[:40], ys[:40]])
+    gpj = G.ExactGP(G.SquaredExponentialARD(5, 0.8, ls5 * 50), noise_variance=1e-18).fit(Xd, yd)
+    prj = gpj.predict(Xt)
+    out.update(jit_X=Xd, jit_y=yd, jit_ls=ls5 * 50, jit_noise=1e-18, jit_mean=prj.mean, jit_var=prj.variance,
+               jit_Ldiag=np.diag(gpj._L).copy(), jit_lml=gpj.log_marginal_likelihood)
+    save("exact_gp.npz", **out)
+
+    # ---- 4. SparseGP FITC / VFE with injected inducing points -------------------------------
+    rng = np.random.default_rng(4)
+    n, M = 300, 40
+    Xs = rng.normal(0, 1, (n, 6)); ys = np.cos(Xs[:, 0]) * Xs[:, 2] + rng.normal(0, 0.05, n)
+    Z = Xs[rng.choice(n, M, replace=False)].copy(); Xt = rng.normal(0, 1, (19, 6)); ls6 = rng.uniform(0.8, 1.6, 6)
+    out = dict(X=Xs, y=ys, Z=Z, Xt=Xt, ls=ls6, sv=1.3, noise=1e-3)
+    for method in ("fitc", "vfe"):
+        gp = G.SparseGP(G.SquaredExponentialARD(6, 1.3, ls6), n_inducing=M, noise_variance=1e-3, method=method,
+                        inducing_points=Z.copy()).fit(Xs, ys)
+        pr = gp.predict(Xt)
+        out.update({f"{method}_mean": pr.mean, f"{method}_var": pr.variance, f"{method}_alpha": gp._alpha,
+                    f"{method}_Luu": gp._L_uu, f"{method}_LB": gp._L_B, f"{method}_lml": gp.log_marginal_likelihood})
+    out["fitc_Lambda"] = G.SparseGP(G.SquaredExponentialARD(6, 1.3, ls6), M, 1e-3, "fitc", Z.copy()).fit(Xs, ys)._Lambda_diag
+    # Simple3DoFGP sparse path with shared injected Z (seed global np.random before kmeans2 is NOT relied on)
+    X, U, Dres = gp_fixture(400, 7)
+    Xq, Uq = query_fixture(X, U, 16, 8)
+    gp = G.Simple3DoFGP(n_inducing=50, use_sparse=True)
+    gp.add_data(X, U, Dres)
+    Zf = gp.feature_extractor.extract_batch(X, U)
+    Zi = Zf[np.random.default_rng(9).choice(400, 50, replace=False)].copy()
+    for g in gp.gp.gps:                       # bypass MultiOutputSparseGP.fit's random re-draw (sparse_gp.py:448-451)
+        g._Z = Zi.copy(); g.fit(Zf, Dres[:, gp.gp.gps.index(g)])
+    gp._is_fitted = True
+    ms = np.zeros((16, 3)); vs = np.zeros((16, 3))
+    for i in range(16):
+        ms[i], vs[i] = gp.predict(Xq[i], Uq[i])
+    out.update(s3_X=X, s3_U=U, s3_D=Dres, s3_Z=Zi, s3_Xq=Xq, s3_Uq=Uq, s3_mean=ms, s3_var=vs)
+    save("sparse_gp.npz", **out)
+
+    # ---- 5. FastGPPredictor (profiler.benchmark_gp_prediction shapes, reduced) ---------------
+    rng = np.random.default_rng(5)
+    Xs = rng.normal(0, 1, (200, 17)); Ys = rng.normal(0, 1, (200, 6)); Xt = rng.normal(0, 1, (31, 17))
+    ls17 = rng.uniform(2.0, 4.0, 17)
+    fg = FastGPPredictor(); fg.fit(Xs, Ys, ls17, 1.2, 0.01)
+    mean, var = fg.predict(Xt)
+    save("fast_gp.npz", X=Xs, Y=Ys, Xt=Xt, ls=ls17, variance=1.2, noise=0.01, mean=mean, var=var, alpha=fg._alpha,
+         Ldiag=np.diag(fg._L).copy())
+
+    # ---- 6. features -------------------------------------------------------------------------
+    rng = np.random.default_rng(6)
+    X14 = rng.normal(0, 1, (50, 14)); X14[:, 0] = rng.uniform(1, 2, 50); X14[:, 1] = rng.uniform(0, 500, 50)
+    X14[:, 4:7] *= 5; q = rng.normal(0, 1, (50, 4)); X14[:, 7:11] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    X14[3, 4:7] = 0.0                                   # speed <= 1e-3 branch (features.py:224-231)
+    U3 = rng.normal(0, 2, (50, 3))
+    f3 = G.Simple3DoFFeatureExtractor(); ft = G.TranslationalFeatureExtractor(); fr = G.RotationalFeatureExtractor()
+    save("features.npz", X14=X14, U=U3, f3=f3.extract_batch(X14[:, :7], U3), ft=ft.extract_batch(X14, U3),
+         fr=fr.extract_batch(X14, U3))
+
+    # ---- 7. StructuredRocketGP (exact, 6 outputs) ----------------------------------------------
+    rng = np.random.default_rng(7)
+    n = 150
+    Xs = X14[rng.integers(0, 50, n)] + rng.normal(0, 0.1, (n, 14))
+    Xs[:, 7:11] /= np.linalg.norm(Xs[:, 7:11], axis=1, keepdims=True)
+    Us = rng.normal(0, 2, (n, 3)); Dv = rng.normal(0, 0.1, (n, 3)); Dw = rng.normal(0, 0.05, (n, 3))
+    sg = G.StructuredRocketGP(G.StructuredGPConfig(use_sparse=False, noise_variance=1e-3))
+    sg.add_data(Xs, Us, Dv, Dw); sg.fit()
+    res = [sg.predict(Xs[i] + 0.01, Us[i] - 0.01) for i in range(12)]
+    save("structured_gp.npz", X=Xs, U=Us, Dv=Dv, Dw=Dw, dv_mean=np.stack([r[0] for r in res]),
+         dw_mean=np.stack([r[1] for r in res]), dv_var=np.stack([r[2] for r in res]), dw_var=np.stack([r[3] for r in res]))
+
+    # ---- 8. QP assembly through the reference's own osqp_rti.py (stub osqp) ----------------------
+    from oracle.mpc import EulerDynamics
+    import src.mpc.osqp_rti as R
+    out = {}
+    x0 = np.array([2.0, 30, 0, 0, -3, 0, 0]); xt = np.array([2.0, 0, 0, 0, 0, 0, 0])
+    for tag, cls, N in (("fast20", R.FastRTI3DoF, 20), ("fast15", R.FastRTI3DoF, 15), ("fd20", R.OSQPRTIMPC, 20)):
+        ctl = cls(EulerDynamics(), R.OSQPRTIConfig(N=N))
+        ctl.initialize(x0, xt)
+        kw = Stub.last
+        out[f"{tag}_P"] = kw["P"].toarray(); out[f"{tag}_q"] = kw["q"]; out[f"{tag}_A"] = kw["A"].toarray()
+        out[f"{tag}_l"] = kw["l"]; out[f"{tag}_u"] = kw["u"]
+        out[f"{tag}_nnzA"] = kw["A"].nnz; out[f"{tag}_nnzP"] = kw["P"].nnz
+        out[f"{tag}_settings"] = np.array([kw["max_iter"], kw["eps_abs"], kw["eps_rel"], kw["scaling"],
+                                           float(kw["polish"]), float(kw["warm_start"])])
+        # a second build at a generic linearisation point (all thrust components non-zero)
+        rng = np.random.default_rng(20 + N)
+        Xl = ctl._X_lin + rng.normal(0, 0.3, ctl._X_lin.shape); Xl[:, 0] = np.linspace(2.0, 1.8, N + 1)
+        Ul = np.stack([rng.uniform(0.5, 4, N), rng.uniform(-1, 1, N), rng.uniform(-1, 1, N)], 1)
+        xc = x0 + rng.normal(0, 0.1, 7)
+        A2, l2, u2 = ctl._build_constraint_matrix(Xl, Ul, xc)
+        out.update({f"{tag}_Xl": Xl, f"{tag}_Ul": Ul, f"{tag}_xc": xc, f"{tag}_A2": A2.toarray(), f"{tag}_l2": l2,
+                    f"{tag}_u2": u2, f"{tag}_nnzA2": A2.nnz})
+    out["x0"] = x0; out["xt"] = xt
+    save("qp_assembly.npz", **out)
+
+    # ---- 9. UncertaintyPropagator (reference class, 14-state embedding of the 7-state model) ------
+    import src.mpc.uncertainty_prop as UP
+    from oracle.mpc import Rocket3DoFParams, linearize_3dof, step_3dof
+    X, U, Dres = gp_fixture(300, 11)
+    gp = G.Simple3DoFGP(use_sparse=False, noise_variance=1e-3); gp.add_data(X, U, Dres); gp.fit()
+    p = Rocket3DoFParams()
+
+    class Dyn14:
+        params = p
+
+        def step(self, x, u, dt):
+            xn = x.copy(); xn[:7] = step_3dof(x[:7], u, dt, p); return xn
+
+        def linearize(self, x, u, dt=None):
+            A = np.eye(14); B = np.zeros((14, 3)); A[:7, :7], B[:7] = linearize_3dof(x[:7], u, dt, p); return A, B
+
+    class GP14:
+        def predict(self, x, u):
+            m, v = gp.predict(x[:7], u); return m, np.zeros(3), v, np.zeros(3)
+
+    x0_14 = np.zeros(14); x0_14[:7] = [1.9, 25, 1, -2, -3.2, 0.3, -0.1]; x0_14[7] = 1.0
+    rng = np.random.default_rng(12)
+    Useq = np.stack([rng.uniform(1.5, 2.5, 20), rng.uniform(-.3, .3, 20), rng.uniform(-.3, .3, 20)], 1)
+    pu = UP.UncertaintyPropagator(Dyn14(), GP14()).propagate(x0_14, Useq, np.eye(14) * 1e-6, dt=0.1)
+    save("propagation.npz", X=X, U=U, D=Dres, noise=1e-3, x0=x0_14[:7], Useq=Useq, means=pu.means[:, :7],
+         covs=pu.covariances[:, :7, :7])
+
+    # ---- 10. Monte Carlo initial conditions / termination (reference MonteCarloSimulator) ------------
+    import src.experiments.monte_carlo as MC
+    cfg = MC.SimulationConfig(dt=0.1, max_time=30.0, altitude_mean=30.0, altitude_std=5.0, horizontal_std=3.0,
+                              velocity_mean=np.array([-3.0, 0.0, 0.0]), velocity_std=np.array([1.0, 0.5, 0.5]))
+    sim = MC.MonteCarloSimulator(EulerDynamics(), controller=None, config=cfg)
+    ics = np.stack([sim.sample_initial_condition(seed=42 + i) for i in range(64)])
+    lc = MC.LandingConstraints()
+    rng = np.random.default_rng(13)
+    states = rng.normal(0, 1, (200, 7)) * np.array([0.3, 1.0, 4, 4, 2, 1, 1]) + np.array([1.6, 0.3, 0, 0, -1, 0, 0])
+    ok = np.array([lc.check_landing(s, 2.0)[0] for s in states])
+    save("monte_carlo.npz", ics=ics, states=states, landing_ok=ok)
+    print("golden fixtures written to", os.path.abspath(OUT))
+    for f in sorted(os.listdir(OUT)):
+        print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")
+
+
+if __name__ == "__main__":
+    main()
