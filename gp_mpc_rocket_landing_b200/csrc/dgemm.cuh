@@ -1,0 +1,212 @@
+// FP64 tensor-core GEMM  C(M,N) = alpha * A(M,K) * B(N,K)^T + beta * C   ("NT": both operands k-contiguous, row-major)
+// for sm_100a.  FP64 has no tcgen05 kind, so the math is warp-level DMMA.8x8x4 (mma.sync m8n8k4) on register
+// fragments, operands staged global->shared by a 3-stage cp.async (LDGSTS) pipeline with 16-byte copies and a
+// (BK+4)-double row pitch that makes the 8-byte fragment loads bank-conflict free.
+//
+// All dimensions are padded by the caller: M % BM == 0, N % BN == 0, K % 16 == 0, leading dimensions even and
+// base pointers 16-byte aligned -- no bounds checks in the main loop.
+//
+// Used by: blocked Cholesky (panel TRSM, trailing SYRK), the blocked triangular solve behind the GP predictive
+// variance (reference exact_gp.py:260-261), the sparse-GP M x M products (sparse_gp.py:203,226).
+#pragma once
+#include "common.cuh"
+
+namespace gpmpc {
+
+constexpr int GEMM_BK = 16;
+constexpr int GEMM_PITCH = GEMM_BK + 4;  // doubles; (g*20 + t) mod 16 distinct over a half-warp
+constexpr int GEMM_STAGES = 3;
+constexpr int GEMM_THREADS = 256;
+
+enum GemmEpilogue : int {
+  EPI_STORE = 0,         // C = alpha*acc + beta*C
+  EPI_STORE_SUMSQ = 1,   // C = alpha*acc (+beta*C) and sumsq[n] += sum_m (alpha*acc)^2   (one M tile only)
+};
+
+struct GemmParams {
+  const double* A; long lda; long strideA;   // A[m*lda + k]
+  const double* B; long ldb; long strideB;   // B[n*ldb + k]
+  double* C; long ldc; long strideC;         // C[m*ldc + n]  (or C[n*ldc + m] when c_trans)
+  double* sumsq; long strideS;               // EPI_STORE_SUMSQ: per-column accumulator (length N)
+  int M, N, K;
+  double alpha, beta;
+  int epi;
+  int c_trans;      // store transposed
+  int k_tri;        // A is lower-triangular in (m,k): limit the k loop to k < m0 + BM
+  int lower_only;   // skip tiles strictly above the block diagonal (n0 >= m0 + BM)
+  int row_min;      // rows  m < row_min are computed but not stored
+  int col_min;      // cols  n < col_min are computed but not stored
+};
+
+template <int BM, int BN>
+struct GemmSmem {
+  double a[GEMM_STAGES][BM * GEMM_PITCH];
+  double b[GEMM_STAGES][BN * GEMM_PITCH];
+};
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) dgemm_nt_kernel(GemmParams p) {
+  static_assert(WARPS_M * WARPS_N * 32 == GEMM_THREADS, "8 warps");
+  constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
+  constexpr int MT = WM / 8, NT = WN / 8;
+  static_assert(WM % 8 == 0 && WN % 8 == 0, "warp tile multiple of 8");
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  GemmSmem<BM, BN>& sm = *reinterpret_cast<GemmSmem<BM, BN>*>(smem_raw);
+
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  if (p.lower_only && n0 >= m0 + BM) return;
+  const int bz = blockIdx.z;
+  const double* __restrict__ A = p.A + bz * p.strideA + (long)m0 * p.lda;
+  const double* __restrict__ B = p.B + bz * p.strideB + (long)n0 * p.ldb;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int wm = warp / WARPS_N, wn = warp % WARPS_N;
+
+  int K = p.K;
+  if (p.k_tri) K = min(K, m0 + BM);
+  const int nk = K / GEMM_BK;
+
+  double acc[MT][NT][2];
+#pragma unroll
+  for (int i = 0; i < MT; ++i)
+#pragma unroll
+    for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+  auto load_tile = [&](int stage, int kt) {
+    const int k0 = kt * GEMM_BK;
+    // A: BM rows x 16 doubles = BM*8 chunks of 16 B
+#pragma unroll
+    for (int c = tid; c < BM * 8; c += GEMM_THREADS) {
+      int r = c >> 3, kc = (c & 7) * 2;
+      cp_async16(&sm.a[stage][r * GEMM_PITCH + kc], A + (long)r * p.lda + k0 + kc);
+    }
+#pragma unroll
+    for (int c = tid; c < BN * 8; c += GEMM_THREADS) {
+      int r = c >> 3, kc = (c & 7) * 2;
+      cp_async16(&sm.b[stage][r * GEMM_PITCH + kc], B + (long)r * p.ldb + k0 + kc);
+    }
+  };
+
+#pragma unroll
+  for (int s = 0; s < GEMM_STAGES - 1; ++s) {
+    if (s < nk) load_tile(s, s);
+    cp_async_commit();
+  }
+
+  for (int kt = 0; kt < nk; ++kt) {
+    cp_async_wait<GEMM_STAGES - 2>();
+    __syncthreads();
+    {
+      int nxt = kt + GEMM_STAGES - 1;
+      if (nxt < nk) load_tile(nxt % GEMM_STAGES, nxt);
+      cp_async_commit();
+    }
+    const double* as = sm.a[kt % GEMM_STAGES] + (wm * WM + g) * GEMM_PITCH + t;
+    const double* bs = sm.b[kt % GEMM_STAGES] + (wn * WN + g) * GEMM_PITCH + t;
+#pragma unroll
+    for (int kk = 0; kk < GEMM_BK; kk += 4) {
+      double af[MT], bf[NT];
+#pragma unroll
+      for (int i = 0; i < MT; ++i) af[i] = as[i * 8 * GEMM_PITCH + kk];
+#pragma unroll
+      for (int j = 0; j < NT; ++j) bf[j] = bs[j * 8 * GEMM_PITCH + kk];
+#pragma unroll
+      for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();  // all operand reads (incl. in-place B == C) are complete before any store
+
+  // ---- epilogue -------------------------------------------------------------------------------------------
+  double* __restrict__ C = p.C + bz * p.strideC;
+  const double alpha = p.alpha, beta = p.beta;
+  double colsq[NT][2];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) colsq[j][0] = colsq[j][1] = 0.0;
+
+#pragma unroll
+  for (int i = 0; i < MT; ++i) {
+    const int m = m0 + wm * WM + i * 8 + g;
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      const int n = n0 + wn * WN + j * 8 + 2 * t;
+      double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
+      const bool row_ok = (m >= p.row_min);
+      if (!p.c_trans) {
+        double* cp = C + (long)m * p.ldc + n;
+        if (beta != 0.0) {
+          double2 old = *reinterpret_cast<const double2*>(cp);
+          v0 += beta * old.x;
+          v1 += beta * old.y;
+        }
+        if (row_ok) {
+          if (n >= p.col_min && n + 1 >= p.col_min) {
+            *reinterpret_cast<double2*>(cp) = make_double2(v0, v1);
+          } else if (n + 1 >= p.col_min) {
+            cp[1] = v1;
+          }
+        }
+      } else {
+        double* cp0 = C + (long)n * p.ldc + m;
+        double* cp1 = cp0 + p.ldc;
+        if (beta != 0.0) {
+          v0 += beta * (*cp0);
+          v1 += beta * (*cp1);
+        }
+        if (row_ok) {
+          if (n >= p.col_min) *cp0 = v0;
+          if (n + 1 >= p.col_min) *cp1 = v1;
+        }
+      }
+      colsq[j][0] += v0 * v0;
+      colsq[j][1] += v1 * v1;
+    }
+  }
+
+  if (p.epi == EPI_STORE_SUMSQ) {
+    // reduce over the 8 row-groups of the warp (lanes with equal t), then across the WARPS_M warps via shared memory
+    __shared__ double red[WARPS_M][BN];
+#pragma unroll
+    for (int j = 0; j < NT; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        double v = colsq[j][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (g == 0) red[wm][wn * WN + j * 8 + 2 * t + e] = v;
+      }
+    __syncthreads();
+    double* ss = p.sumsq + bz * p.strideS;
+    for (int c = tid; c < BN; c += GEMM_THREADS) {
+      double v = 0.0;
+#pragma unroll
+      for (int w = 0; w < WARPS_M; ++w) v += red[w][c];
+      ss[n0 + c] += v;
+    }
+  }
+}
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream) {
+  if (p.M % BM || p.N % BN || p.K % GEMM_BK || (p.lda & 1) || (p.ldb & 1)) {
+    gpmpc_set_error("dgemm_nt: dimensions must be padded (M%BM, N%BN, K%16, even ld)");
+    return GPMPC_ERR_ARG;
+  }
+  if (p.M == 0 || p.N == 0) return GPMPC_OK;
+  auto kern = dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>;
+  const int smem = (int)sizeof(GemmSmem<BM, BN>);
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    configured = true;
+  }
+  dim3 grid(p.N / BN, p.M / BM, batch);
+  kern<<<grid, GEMM_THREADS, smem, stream>>>(p);
+  return gpmpc_check_launch("dgemm_nt");
+}
+
+}  // namespace gpmpc

@@ -1,0 +1,361 @@
+// Batched FP64 dense linear algebra for the GP fit / predict path on sm_100a:
+//   * blocked right-looking Cholesky (64-wide panels; panel TRSM and trailing SYRK on DMMA via dgemm.cuh)
+//     -- replaces np.linalg.cholesky at reference exact_gp.py:164,170 / sparse_gp.py:187,205,228 / fast_gp.py:153
+//   * cho_solve for a few right-hand sides (exact_gp.py:179, sparse_gp.py:210,232)
+//   * blocked lower-triangular solve with MANY right-hand sides + fused column sum-of-squares
+//     -- replaces solve_triangular + np.sum(v**2, axis=0) at exact_gp.py:260-261 (never materialises a separate v)
+//   * small-M triangular solves for the sparse GP (sparse_gp.py:190,293,296)
+// Layout: row-major, lower triangle, dimensions padded to a multiple of 128 with a unit diagonal in the padding.
+#include <math.h>
+#include <stdio.h>
+
+#include "dgemm.cuh"
+#include "gpmpc_b200.h"
+
+using namespace gpmpc;
+
+// ------------------------------------------------------------------------------------------------ error state
+static thread_local char g_err[512] = "";
+extern "C" void gpmpc_set_error(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg); }
+extern "C" const char* gpmpc_last_error(void) { return g_err; }
+int gpmpc_check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return GPMPC_ERR_CUDA;
+  }
+  return GPMPC_OK;
+}
+extern "C" int gpmpc_version(void) { return 100; }
+
+// ------------------------------------------------------------------------------------------------ potrf diag 64
+// One CTA factors a 64x64 diagonal block in shared memory and also forms its inverse W = L11^{-1}; W turns the
+// panel solve and every later triangular solve against this block into a tensor-core GEMM.
+__global__ void __launch_bounds__(256) potrf_diag64_kernel(double* __restrict__ Abase, long lda, long strideA,
+                                                           double* __restrict__ Wbase, long strideW,
+                                                           int* __restrict__ info, int k0) {
+  extern __shared__ double potrf_sm[];
+  double(*S)[65] = reinterpret_cast<double(*)[65]>(potrf_sm);
+  double(*Wi)[65] = reinterpret_cast<double(*)[65]>(potrf_sm + 64 * 65);
+  const int b = blockIdx.x, tid = threadIdx.x;
+  double* A = Abase + b * strideA + (long)k0 * lda + k0;
+  double* W = Wbase + b * strideW;
+  for (int idx = tid; idx < 4096; idx += 256) {
+    int i = idx >> 6, k = idx & 63;
+    S[i][k] = A[(long)i * lda + k];
+    Wi[i][k] = 0.0;
+  }
+  __syncthreads();
+  for (int j = 0; j < 64; ++j) {
+    double d = S[j][j];
+    if (!(d > 0.0)) {  // uniform: every thread reads the same value
+      if (tid == 0 && info[b] == 0) info[b] = k0 + j + 1;  // LAPACK: order of the first non-PD leading minor
+      d = 1.0;  // keep going on finite numbers; the host checks info and retries with jitter
+    }
+    d = sqrt(d);
+    const double rd = 1.0 / d;
+    __syncthreads();
+    if (tid == 0) S[j][j] = d;
+    for (int i = j + 1 + tid; i < 64; i += 256) S[i][j] *= rd;
+    __syncthreads();
+    for (int idx = tid; idx < 4096; idx += 256) {
+      int i = idx >> 6, k = idx & 63;
+      if (k > j && k <= i) S[i][k] -= S[i][j] * S[k][j];
+    }
+    __syncthreads();
+  }
+  // inverse of the lower-triangular block, one column per thread
+  if (tid < 64) {
+    const int j = tid;
+    Wi[j][j] = 1.0 / S[j][j];
+    for (int i = j + 1; i < 64; ++i) {
+      double s = 0.0;
+      for (int k = j; k < i; ++k) s += S[i][k] * Wi[k][j];
+      Wi[i][j] = -s / S[i][i];
+    }
+  }
+  __syncthreads();
+  for (int idx = tid; idx < 4096; idx += 256) {
+    int i = idx >> 6, k = idx & 63;
+    A[(long)i * lda + k] = (k <= i) ? S[i][k] : 0.0;
+    W[idx] = Wi[i][k];
+  }
+}
+
+__global__ void zero_upper_kernel(double* __restrict__ A, int n, long lda, long strideA) {
+  double* a = A + blockIdx.z * strideA;
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  int i = blockIdx.y;
+  if (j < n && j > i) a[(long)i * lda + j] = 0.0;
+}
+
+extern "C" int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int batch, double* Winv, int* info,
+                           void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad > 0 && n_pad % 128 == 0, "gpmpc_potrf: n_pad must be a positive multiple of 128");
+  GPMPC_REQUIRE((lda & 1) == 0 && lda >= n_pad, "gpmpc_potrf: lda must be even and >= n_pad");
+  const long strideW = (long)(n_pad / 64) * 4096;
+  cudaMemsetAsync(info, 0, sizeof(int) * batch, stream);
+  const size_t diag_smem = sizeof(double) * 2 * 64 * 65;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(potrf_diag64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
+    configured = true;
+  }
+  for (int k0 = 0; k0 < n_pad; k0 += 64) {
+    double* W = Winv + (long)(k0 / 64) * 4096;
+    potrf_diag64_kernel<<<batch, 256, diag_smem, stream>>>(A, lda, strideA, W, strideW, info, k0);
+    int rc = gpmpc_check_launch("potrf_diag64");
+    if (rc) return rc;
+    if (k0 + 64 >= n_pad) break;
+    const int o = ((k0 + 64) / 128) * 128;  // 128-aligned tile origin; rows/cols below k0+64 are masked
+    GemmParams p{};
+    p.A = A + (long)o * lda + k0; p.lda = lda; p.strideA = strideA;
+    p.B = W; p.ldb = 64; p.strideB = strideW;
+    p.C = A + (long)o * lda + k0; p.ldc = lda; p.strideC = strideA;
+    p.M = n_pad - o; p.N = 64; p.K = 64; p.alpha = 1.0; p.beta = 0.0; p.epi = EPI_STORE;
+    p.row_min = k0 + 64 - o;
+    rc = launch_dgemm_nt<128, 64, 4, 2>(p, batch, stream);  // L21 = A21 * W^T  (in place)
+    if (rc) return rc;
+    GemmParams s{};
+    s.A = A + (long)o * lda + k0; s.lda = lda; s.strideA = strideA;
+    s.B = s.A; s.ldb = lda; s.strideB = strideA;
+    s.C = A + (long)o * lda + o; s.ldc = lda; s.strideC = strideA;
+    s.M = n_pad - o; s.N = n_pad - o; s.K = 64; s.alpha = -1.0; s.beta = 1.0; s.epi = EPI_STORE;
+    s.lower_only = 1; s.row_min = k0 + 64 - o; s.col_min = k0 + 64 - o;
+    rc = launch_dgemm_nt<128, 128, 2, 4>(s, batch, stream);  // A22 -= L21 * L21^T (lower tiles)
+    if (rc) return rc;
+  }
+  dim3 grid((n_pad + 255) / 256, n_pad, batch);
+  zero_upper_kernel<<<grid, 256, 0, stream>>>(A, n_pad, lda, strideA);
+  return gpmpc_check_launch("zero_upper");
+}
+
+// ------------------------------------------------------------------------------------------------ potrs (few RHS)
+// One CTA per (factor, rhs): y = L^{-1} b by 64-blocks (GEMV against the already-solved part, then the 64x64
+// inverse block), then a = L^{-T} y.  The solution vector lives in shared memory.
+__global__ void __launch_bounds__(256) potrs_kernel(const double* __restrict__ Lbase, int n_pad, long lda,
+                                                    long strideL, const double* __restrict__ Wbase,
+                                                    double* __restrict__ Bbase, int nrhs) {
+  extern __shared__ double sh[];
+  double* y = sh;               // n_pad
+  double* r = sh + n_pad;       // 64
+  double* part = r + 64;        // 4*64
+  const int f = blockIdx.x / nrhs;
+  const double* L = Lbase + f * strideL;
+  const double* Wf = Wbase + (long)f * (n_pad / 64) * 4096;
+  double* b = Bbase + (long)blockIdx.x * n_pad;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nb = n_pad / 64;
+  for (int i = tid; i < n_pad; i += 256) y[i] = b[i];
+  __syncthreads();
+  // forward
+  for (int ib = 0; ib < nb; ++ib) {
+    const int i0 = ib * 64;
+    for (int rr = warp; rr < 64; rr += 8) {
+      const double* row = L + (long)(i0 + rr) * lda;
+      double s = 0.0;
+      for (int k = lane; k < i0; k += 32) s += row[k] * y[k];
+      s = warp_sum(s);
+      if (lane == 0) r[rr] = y[i0 + rr] - s;
+    }
+    __syncthreads();
+    if (tid < 64) {
+      const double* w = Wf + (long)ib * 4096 + tid * 64;
+      double s = 0.0;
+      for (int k = 0; k <= tid; ++k) s += w[k] * r[k];
+      y[i0 + tid] = s;
+    }
+    __syncthreads();
+  }
+  // backward: a_i = W_i^T (y_i - sum_{k > block i} L[k, block i]^T a_k)
+  for (int ib = nb - 1; ib >= 0; --ib) {
+    const int i0 = ib * 64;
+    const int c = tid & 63, kp = tid >> 6;
+    double s = 0.0;
+    for (int k = i0 + 64 + kp; k < n_pad; k += 4) s += L[(long)k * lda + i0 + c] * y[k];
+    part[kp * 64 + c] = s;
+    __syncthreads();
+    if (tid < 64) r[tid] = y[i0 + tid] - (part[tid] + part[64 + tid] + part[128 + tid] + part[192 + tid]);
+    __syncthreads();
+    if (tid < 64) {
+      const double* w = Wf + (long)ib * 4096;
+      double s2 = 0.0;
+      for (int k = tid; k < 64; ++k) s2 += w[k * 64 + tid] * r[k];
+      y[i0 + tid] = s2;
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < n_pad; i += 256) b[i] = y[i];
+}
+
+extern "C" int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B,
+                           int nrhs, int batch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad % 128 == 0 && n_pad > 0, "gpmpc_potrs: n_pad must be a multiple of 128");
+  size_t smem = sizeof(double) * (n_pad + 64 + 256);
+  GPMPC_REQUIRE(smem <= 200 * 1024, "gpmpc_potrs: n_pad too large for the shared-memory solve");
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(potrs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    configured = true;
+  }
+  potrs_kernel<<<batch * nrhs, 256, smem, stream>>>(L, n_pad, lda, strideL, Winv, B, nrhs);
+  return gpmpc_check_launch("potrs");
+}
+
+// ------------------------------------------------------------------------------------------------ targets / LML
+// exact_gp.py:141-146: y_mean = mean(y), y_std = std(y) (population), y_std<1e-10 -> 1; Yn[p][i] = (y - mean)/std.
+__global__ void __launch_bounds__(256) normalize_targets_kernel(const double* __restrict__ Y, int n, int P, long ldy,
+                                                                int n_pad, int normalize, double* __restrict__ Yn,
+                                                                double* __restrict__ ymean, double* __restrict__ ystd) {
+  __shared__ double red[8];
+  __shared__ double s_val;
+  const int p = blockIdx.x, tid = threadIdx.x;
+  auto block_sum = [&](double v) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = v;
+    __syncthreads();
+    if (tid == 0) {
+      double t = 0.0;
+      for (int w = 0; w < 8; ++w) t += red[w];
+      s_val = t;
+    }
+    __syncthreads();
+    return s_val;
+  };
+  double mean = 0.0, sd = 1.0;
+  if (normalize) {
+    double s = 0.0;
+    for (int i = tid; i < n; i += 256) s += Y[(long)i * ldy + p];
+    mean = block_sum(s) / n;
+    double q = 0.0;
+    for (int i = tid; i < n; i += 256) {
+      double d = Y[(long)i * ldy + p] - mean;
+      q += d * d;
+    }
+    sd = sqrt(block_sum(q) / n);
+    if (sd < 1e-10) sd = 1.0;
+  }
+  for (int i = tid; i < n_pad; i += 256)
+    Yn[(long)p * n_pad + i] = (i < n) ? (Y[(long)i * ldy + p] - mean) / sd : 0.0;
+  if (tid == 0) {
+    ymean[p] = mean;
+    ystd[p] = sd;
+  }
+}
+
+extern "C" int gpmpc_normalize_targets(const double* Y, int n, int P, long ldy, int n_pad, int normalize, double* Yn,
+                                       double* ymean, double* ystd, void* stream) {
+  normalize_targets_kernel<<<P, 256, 0, (cudaStream_t)stream>>>(Y, n, P, ldy, n_pad, normalize, Yn, ymean, ystd);
+  return gpmpc_check_launch("normalize_targets");
+}
+
+// exact_gp.py:186-204: lml = -0.5 y^T alpha - sum log diag(L) - n/2 log(2 pi), one CTA per (factor, rhs).
+__global__ void __launch_bounds__(256) lml_kernel(const double* __restrict__ Lbase, int n, int n_pad, long lda,
+                                                  long strideL, const double* __restrict__ Yn,
+                                                  const double* __restrict__ alpha, int nrhs,
+                                                  double* __restrict__ lml) {
+  __shared__ double red[8];
+  const int f = blockIdx.x / nrhs, tid = threadIdx.x;
+  const double* L = Lbase + f * strideL;
+  const double* y = Yn + (long)blockIdx.x * n_pad;
+  const double* a = alpha + (long)blockIdx.x * n_pad;
+  double s = 0.0;
+  for (int i = tid; i < n; i += 256) s += -0.5 * y[i] * a[i] - log(L[(long)i * lda + i]);
+  s = warp_sum(s);
+  if ((tid & 31) == 0) red[tid >> 5] = s;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    lml[blockIdx.x] = t - 0.5 * n * log(2.0 * M_PI);
+  }
+}
+
+extern "C" int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strideL, const double* Yn,
+                         const double* alpha, int nrhs, int batch, double* lml, void* stream) {
+  lml_kernel<<<batch * nrhs, 256, 0, (cudaStream_t)stream>>>(L, n, n_pad, lda, strideL, Yn, alpha, nrhs, lml);
+  return gpmpc_check_launch("lml");
+}
+
+// ------------------------------------------------------------------------------------------------ TRSM, many RHS
+// V = L^{-1} Ks^T for Q right-hand sides stored as rows of Ks (Q_pad x n_pad, row-major) -- solved IN PLACE, block
+// row by block row (64 wide):   R_i = Ks_i - L[i, :i] V[:i]   (DMMA GEMM, K = 64 i)
+//                               V_i = W_i R_i                (DMMA GEMM, K = 64) + sumsq[q] += sum_rows V_i^2
+// Same arithmetic as a blocked dtrsm; the fused column sum of squares is exact_gp.py:261.
+extern "C" int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad,
+                                long ldk, double* sumsq, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0, "gpmpc_trsm_sumsq: n_pad and q_pad must be multiples of 128");
+  cudaMemsetAsync(sumsq, 0, sizeof(double) * q_pad, stream);
+  for (int ib = 0; ib < n_pad / 64; ++ib) {
+    const int i0 = ib * 64;
+    if (ib > 0) {
+      GemmParams p{};
+      p.A = L + (long)i0 * lda; p.lda = lda;
+      p.B = Ks; p.ldb = ldk;
+      p.C = Ks + i0; p.ldc = ldk; p.c_trans = 1;
+      p.M = 64; p.N = q_pad; p.K = i0; p.alpha = -1.0; p.beta = 1.0; p.epi = EPI_STORE;
+      int rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
+      if (rc) return rc;
+    }
+    GemmParams s{};
+    s.A = Winv + (long)ib * 4096; s.lda = 64;
+    s.B = Ks + i0; s.ldb = ldk;
+    s.C = Ks + i0; s.ldc = ldk; s.c_trans = 1;
+    s.M = 64; s.N = q_pad; s.K = 64; s.alpha = 1.0; s.beta = 0.0; s.epi = EPI_STORE_SUMSQ;
+    s.sumsq = sumsq;
+    int rc = launch_dgemm_nt<64, 128, 2, 4>(s, 1, stream);
+    if (rc) return rc;
+  }
+  return GPMPC_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ small-M TRSM
+// X = L^{-1} B for a small lower-triangular L (M <= 128, e.g. the sparse GP's L_uu / L_B, sparse_gp.py:190,293,296)
+// and many columns: L in shared memory, one column per thread (broadcast reads), optional column sum of squares.
+__global__ void __launch_bounds__(128) trsm_small_kernel(const double* __restrict__ L, int M, long ldl,
+                                                         double* __restrict__ B, long ldb, int ncols, int b_colmajor,
+                                                         double* __restrict__ sumsq, double sumsq_sign) {
+  extern __shared__ double sL[];  // M*(M+1)
+  for (int idx = threadIdx.x; idx < M * M; idx += blockDim.x) sL[(idx / M) * (M + 1) + idx % M] = L[(long)(idx / M) * ldl + idx % M];
+  __syncthreads();
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncols) return;
+  // element (i, c): column-major storage B[c*ldb + i] (rows of a (ncols x M) matrix) or row-major B[i*ldb + c]
+  auto at = [&](int i) -> double& { return b_colmajor ? B[(long)c * ldb + i] : B[(long)i * ldb + c]; };
+  double ss = 0.0;
+  for (int i = 0; i < M; ++i) {
+    double s = at(i);
+    for (int k = 0; k < i; ++k) s -= sL[i * (M + 1) + k] * at(k);
+    s /= sL[i * (M + 1) + i];
+    at(i) = s;
+    ss += s * s;
+  }
+  if (sumsq) sumsq[c] += sumsq_sign * ss;
+}
+
+extern "C" int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, long ldb, int ncols, int b_colmajor,
+                                double* sumsq, double sumsq_sign, void* stream) {
+  GPMPC_REQUIRE(M > 0 && M <= 144, "gpmpc_trsm_small: M must be in 1..144");
+  size_t smem = sizeof(double) * M * (M + 1);
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(trsm_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024);
+    configured = true;
+  }
+  trsm_small_kernel<<<(ncols + 127) / 128, 128, smem, (cudaStream_t)stream>>>(L, M, ldl, B, ldb, ncols, b_colmajor,
+                                                                            sumsq, sumsq_sign);
+  return gpmpc_check_launch("trsm_small");
+}
+
+// ------------------------------------------------------------------------------------------------ plain GEMM entry
+extern "C" int gpmpc_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc, int M, int N,
+                              int K, double alpha, double beta, int lower_only, void* stream) {
+  GemmParams p{};
+  p.A = A; p.lda = lda; p.B = B; p.ldb = ldb; p.C = C; p.ldc = ldc;
+  p.M = M; p.N = N; p.K = K; p.alpha = alpha; p.beta = beta; p.epi = EPI_STORE; p.lower_only = lower_only;
+  return launch_dgemm_nt<128, 128, 2, 4>(p, 1, (cudaStream_t)stream);
+}

@@ -1,0 +1,182 @@
+/* gpmpc_b200.h -- C ABI of the B200-native GP-MPC hot path (libgpmpc_b200.so).
+ *
+ * The reference (shiivashaakeri/gp-mpc-rocket-landing) is pure Python and has no FFI; the boundary its hot path
+ * sits behind is a set of duck-typed Python objects.  Each entry point below replaces the
+ * numeric body of the reference method it cites; `gp_mpc_rocket_landing_b200/` (and the `src.gp` / `src.mpc`
+ * alias package) is the Python side that binds them with ctypes -- INTEGRATION.md shows the binding.
+ *
+ * Conventions: every function returns 0 on success, <0 on error (text via gpmpc_last_error(), no exceptions cross
+ * the boundary); all pointers are DEVICE pointers to row-major FP64 unless a name ends in `_host`; the caller owns
+ * every buffer; the last argument is a cudaStream_t (passed as void*); kernels are stream-ordered and re-entrant
+ * on different streams.  "pad" sizes are multiples of 128 (rows) / 4 (feature columns) and padding is zero.
+ */
+#ifndef GPMPC_B200_H
+#define GPMPC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPMPC_KERNEL_SE 0        /* src/gp/kernels.py:130-379  SquaredExponentialARD */
+#define GPMPC_KERNEL_MATERN32 1  /* src/gp/kernels.py:482-576  Matern32 */
+#define GPMPC_KERNEL_MATERN52 2  /* src/gp/kernels.py:579-668  Matern52 */
+
+#define GPMPC_FEATURES_3DOF 0        /* src/gp/features.py:403-444 (11 features) */
+#define GPMPC_FEATURES_6DOF_TRANS 1  /* src/gp/features.py:194-258 (13 features) */
+#define GPMPC_FEATURES_6DOF_ROT 2    /* src/gp/features.py:305-354 (12 features) */
+
+int gpmpc_version(void);
+const char* gpmpc_last_error(void);
+
+/* ---- GP: Gram / fit / predict primitives -------------------------------------------------------------------- */
+
+/* Xs = X / lengthscales (n_pad x DP, zero padded), sq[i] = sum_d Xs[i,d]^2 in numpy's pairwise order.
+ * Replaces kernels.py:223-229 (SE-ARD), :522-526 (Matern32), :615-619 (Matern52). */
+int gpmpc_scale_inputs(const double* X, int n, int D, long ldx, const double* lengthscales, double* Xs, int n_pad,
+                       int DP, double* sq, void* stream);
+
+/* K[i,j] = k(x1_i, x2_j) (+ diag_add where i == j); rows >= n1_valid / cols >= n2_valid are written as zero (or the
+ * identity when pad_identity).  lower_only skips 128x128 tiles strictly above the diagonal.
+ * Replaces Kernel.__call__: kernels.py:238-262, :532-545, :625-638 and the `+ noise*I` at exact_gp.py:160. */
+int gpmpc_gram(int kind, const double* Xs1, const double* sq1, int n1_valid, int n1_pad, const double* Xs2,
+               const double* sq2, int n2_valid, int n2_pad, int DP, double signal_var, double diag_add,
+               int pad_identity, int lower_only, double* K, long ldk, void* stream);
+
+/* G = K * (x1_dim - x2_dim)^2 / l_dim^2  (SE-ARD gradient w.r.t. log lengthscale `dim`), kernels.py:310-316. */
+int gpmpc_gram_grad_lengthscale(const double* Xs1, const double* sq1, int n1_valid, int n1_pad, const double* Xs2,
+                                const double* sq2, int n2_valid, int n2_pad, int DP, double signal_var, int dim,
+                                double* G, long ldg, void* stream);
+
+/* In-place batched lower Cholesky (A = L L^T, upper triangle zeroed) + inverses of the 64x64 diagonal blocks
+ * (Winv: batch x n_pad/64 x 64 x 64).  info[b] = 0 or the order of the first non-positive pivot.
+ * Replaces np.linalg.cholesky at exact_gp.py:164,170, sparse_gp.py:187,205,228, fast_gp.py:153,158. */
+int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int batch, double* Winv, int* info, void* stream);
+
+/* B[(f*nrhs + r)*n_pad + i] <- (L_f L_f^T)^{-1} b : cho_solve at exact_gp.py:179, sparse_gp.py:210,232 and the two
+ * solve_triangular calls at fast_gp.py:163-165. */
+int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B, int nrhs, int batch,
+                void* stream);
+
+/* Target normalisation, exact_gp.py:141-150: Yn[p*n_pad + i] = (Y[i*ldy + p] - mean_p) / std_p. */
+int gpmpc_normalize_targets(const double* Y, int n, int P, long ldy, int n_pad, int normalize, double* Yn,
+                            double* ymean, double* ystd, void* stream);
+
+/* Log marginal likelihood, exact_gp.py:186-204; one value per (factor, rhs). */
+int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strideL, const double* Yn, const double* alpha,
+              int nrhs, int batch, double* lml, void* stream);
+
+/* Ks (q_pad x n_pad) <- (L^{-1} Ks^T)^T in place and sumsq[q] = sum_i v_iq^2: solve_triangular + np.sum(v**2, axis=0)
+ * at exact_gp.py:260-261 / fast_gp.py:194-199, as a blocked DMMA TRSM. */
+int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad, long ldk,
+                     double* sumsq, void* stream);
+
+/* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
+ * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
+int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, long ldb, int ncols, int b_colmajor, double* sumsq,
+                     double sumsq_sign, void* stream);
+
+/* mean[q, col0+p] = (sum_j Ks[q,j] alpha[p,j]) * ystd[p] + ymean[p]  (exact_gp.py:240-245, sparse_gp.py:281-284). */
+int gpmpc_predict_mean(const double* Ks, long ldk, int Q, int n, const double* alpha, int n_pad, int P,
+                       const double* ymean, const double* ystd, double* mean, long ldm, int col0, void* stream);
+
+/* var[q, col0+p] = max(prior - sumsq[q] (+ plus[q]), floor) * ystd[p]^2  (exact_gp.py:259-263, sparse_gp.py:299-300). */
+int gpmpc_predict_var(const double* sumsq, const double* plus, int Q, int P, double prior, double floor_,
+                      const double* ystd, double* var, long ldv, int col0, void* stream);
+
+/* C = alpha * A * B^T + beta * C on FP64 tensor cores (M,N multiples of 128, K of 16): sparse_gp.py:203,226. */
+int gpmpc_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc, int M, int N, int K,
+                   double alpha, double beta, int lower_only, void* stream);
+
+/* Feature extraction, features.py extract()/extract_batch(): X (B x ldx), U (B x ldu) -> Z (B x ldz). */
+int gpmpc_features(int which, const double* X, long ldx, const double* U, long ldu, int B, double* Z, long ldz,
+                   void* stream);
+
+
+/* ---- MPC: dynamics, horizon rollout / propagation, QP assembly, ADMM ---------------------------------------------- */
+
+/* OSQP status codes (osqp constants; the reference tests result.info.status, osqp_rti.py:532). */
+#define GPMPC_QP_SOLVED 1
+#define GPMPC_QP_SOLVED_INACCURATE 2
+#define GPMPC_QP_MAX_ITER -2
+#define GPMPC_QP_PRIMAL_INFEASIBLE -3
+#define GPMPC_QP_PRIMAL_INFEASIBLE_INACCURATE 3
+#define GPMPC_QP_DUAL_INFEASIBLE -4
+#define GPMPC_QP_DUAL_INFEASIBLE_INACCURATE 4
+#define GPMPC_QP_UNSOLVED -10
+
+/* Solver settings: the keyword arguments of osqp.OSQP.setup at osqp_rti.py:465-478 plus the OSQP 0.6 defaults the
+ * reference leaves untouched.  adaptive_rho_interval is iteration based (OSQP's default is timing based). */
+typedef struct GpmpcAdmmSettings {
+  double rho, sigma, alpha;
+  double eps_abs, eps_rel, eps_prim_inf, eps_dual_inf;
+  double adaptive_rho_tolerance;
+  int max_iter, scaling, check_every;
+  int adaptive_rho, adaptive_rho_interval;
+  int warm_x, warm_y;      /* use x / y buffers as warm start (osqp_rti.py:522-524) */
+  int rho_from_input;      /* start from rho[b] when > 0 (OSQP keeps its adapted rho between solves) */
+} GpmpcAdmmSettings;
+
+/* 3-DoF Euler model parameters (nominal_mpc.py:579-605, rocket_3dof.py:33-65). */
+typedef struct GpmpcDyn3 {
+  double alpha;   /* 1 / (I_sp g0) */
+  double g[3];    /* gravity vector g_I */
+  double dt;
+} GpmpcDyn3;
+
+/* Exact-GP model handle for the fused horizon kernels: P outputs sharing ONE kernel / factor (the
+ * MultiOutputExactGP default, exact_gp.py:464-474). All device pointers. */
+typedef struct GpmpcExactModel {
+  int kind, n, n_pad, D, DP, P;
+  double signal_var;
+  const double* lengthscales; /* D */
+  const double* Xs;           /* n_pad x DP scaled training inputs */
+  const double* sq;           /* n_pad */
+  const double* alpha;        /* P x n_pad */
+  const double* ymean;        /* P */
+  const double* ystd;         /* P */
+  const double* L;            /* n_pad x n_pad */
+  const double* Winv;         /* n_pad/64 x 64 x 64 */
+} GpmpcExactModel;
+
+/* Batched ADMM solve of B stage-structured QPs (see csrc/admm.cu): replaces osqp.OSQP.setup/update/warm_start/solve,
+ * osqp_rti.py:464-478,496,517,524,527.  AB: B x N x nx x (nx+nu) row-major stage blocks [A_k | B_k]; beq: B x nx(N+1)
+ * right-hand sides [x_init ; b_0 .. b_{N-1}]; q: B x n; Pdiag, lb, ub: n (shared by all scenarios; +-1e30 = infinite).
+ * x (B x n) and y (B x m): warm start in, solution out.  rho (B): in (when rho_from_input) / out.
+ * active (B ints or NULL): scenarios with 0 are skipped. */
+int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const double* beq, const double* q,
+                     const double* Pdiag, const double* lb, const double* ub, const GpmpcAdmmSettings* settings,
+                     const int* active, double* x, double* y, double* rho, int* status, int* iters, double* obj,
+                     double* pri_res, double* dua_res, void* stream);
+
+/* GP-augmented horizon rollout for B scenarios (gp_mpc.py:277-281 + _predict_with_gp :139-175, 7-state model):
+ * X[b,0]=x0[b]; X[b,k+1] = step(X[b,k],U[b,k]) + [0,0,0,0, d_mean*dt].  Also writes the cross-covariance rows
+ * Ks[(b*N+k), :] (consumed by gpmpc_trsm_sumsq for the variances) and dmean (B x N x 3).  model==NULL: nominal. */
+int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3* dyn, int B, int N, const double* x0,
+                       const double* U, double* X, double* dmean, double* Ks, long ldk, const int* active,
+                       void* stream);
+
+/* Linear covariance propagation (uncertainty_prop.py:117-177, 7-state): Sigma_{k+1} = A_k Sigma_k A_k' + diag(var)dt^2
+ * on the velocity block, A_k = analytic discrete Jacobian at (X[b,k],U[b,k]).  covs: B x (N+1) x 7 x 7. */
+int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U, const double* dvar,
+                             double sigma0, double* covs, const int* active, void* stream);
+
+/* QP assembly in the reference layout (osqp_rti.py:203-372): stage blocks AB (entries with |.|<=1e-10 dropped as at
+ * :301,309), beq, q.  lin_mode 0 = analytic Jacobians (FastRTI3DoF._linearize :656-710), 1 = finite differences
+ * (OSQPRTIMPC._linearize :374-401).  rhs_mode 0 = reference RTI rows (l=u=+c_k, :338-344), 1 = GP-MPC deviation form
+ * (gp_mpc.py:402-411).  c_gp (B x N x 3 GP means, may be NULL) enters as the affine term [0,0,0,0,d*dt]. */
+int gpmpc_qp_assemble_3dof(const GpmpcDyn3* dyn, int B, int N, int lin_mode, int rhs_mode, const double* X_lin,
+                           const double* U_lin, const double* x_init, const double* x_ref, long ldxref,
+                           const double* c_gp, const double* Qdiag, const double* Qfdiag, double* AB, double* beq,
+                           double* q, const int* active, void* stream);
+
+/* Unpack QP solutions z -> (X, U), SQP convergence test (gp_mpc.py:336-345), cost, fallback handling and the shifted
+ * warm start (osqp_rti.py:532-552).  See csrc/mpc.cu for the exact semantics of `mode`. */
+int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp_status, const double* x_ref,
+                          long ldxref, const double* Qdiag, const double* Qfdiag, const double* Rdiag, double* X,
+                          double* U, double* X_prev, double* U_prev, double* cost, int* converged, int* active,
+                          int* n_iter, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPMPC_B200_H */
