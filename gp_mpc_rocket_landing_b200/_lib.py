@@ -1,0 +1,136 @@
+"""ctypes binding of libgpmpc_b200.so (include/gpmpc_b200.h).
+
+The library is the product: there is no CPU fallback.  Importing this module fails loudly when the shared
+library has not been built (``python -m gp_mpc_rocket_landing_b200.build``), and every compute entry point
+fails loudly when no CUDA device is present.  torch is used only for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgpmpc_b200.so")
+
+c_dp = C.c_void_p  # device pointers travel as integers
+c_int, c_long, c_double = C.c_int, C.c_long, C.c_double
+
+
+class AdmmSettings(C.Structure):
+    """GpmpcAdmmSettings: osqp.OSQP.setup keywords (osqp_rti.py:465-478) + untouched OSQP 0.6 defaults."""
+    _fields_ = [
+        ("rho", c_double), ("sigma", c_double), ("alpha", c_double),
+        ("eps_abs", c_double), ("eps_rel", c_double), ("eps_prim_inf", c_double), ("eps_dual_inf", c_double),
+        ("adaptive_rho_tolerance", c_double),
+        ("max_iter", c_int), ("scaling", c_int), ("check_every", c_int),
+        ("adaptive_rho", c_int), ("adaptive_rho_interval", c_int),
+        ("warm_x", c_int), ("warm_y", c_int), ("rho_from_input", c_int),
+    ]
+
+    @classmethod
+    def reference_defaults(cls, **over):
+        s = cls(rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-4, eps_rel=1e-4, eps_prim_inf=1e-4, eps_dual_inf=1e-4,
+                adaptive_rho_tolerance=5.0, max_iter=50, scaling=3, check_every=25, adaptive_rho=1,
+                adaptive_rho_interval=25, warm_x=0, warm_y=0, rho_from_input=0)
+        for k, v in over.items():
+            setattr(s, k, v)
+        return s
+
+
+class Dyn3(C.Structure):
+    """GpmpcDyn3: Euler 3-DoF parameters (nominal_mpc.py:579-605, rocket_3dof.py:33-65)."""
+    _fields_ = [("alpha", c_double), ("g", c_double * 3), ("dt", c_double)]
+
+
+class ExactModel(C.Structure):
+    """GpmpcExactModel: P outputs sharing one kernel / Cholesky factor (exact_gp.py:464-474)."""
+    _fields_ = [
+        ("kind", c_int), ("n", c_int), ("n_pad", c_int), ("D", c_int), ("DP", c_int), ("P", c_int),
+        ("signal_var", c_double),
+        ("lengthscales", c_dp), ("Xs", c_dp), ("sq", c_dp), ("alpha", c_dp), ("ymean", c_dp), ("ystd", c_dp),
+        ("L", c_dp), ("Winv", c_dp),
+    ]
+
+
+_PROTOS = {
+    "gpmpc_version": (c_int, []),
+    "gpmpc_last_error": (C.c_char_p, []),
+    "gpmpc_scale_inputs": (c_int, [c_dp, c_int, c_int, c_long, c_dp, c_dp, c_int, c_int, c_dp, c_dp]),
+    "gpmpc_gram": (c_int, [c_int, c_dp, c_dp, c_int, c_int, c_dp, c_dp, c_int, c_int, c_int, c_double, c_double,
+                           c_int, c_int, c_dp, c_long, c_dp]),
+    "gpmpc_gram_grad_lengthscale": (c_int, [c_dp, c_dp, c_int, c_int, c_dp, c_dp, c_int, c_int, c_int, c_double,
+                                            c_int, c_dp, c_long, c_dp]),
+    "gpmpc_potrf": (c_int, [c_dp, c_int, c_long, c_long, c_int, c_dp, c_dp, c_dp]),
+    "gpmpc_potrs": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp]),
+    "gpmpc_normalize_targets": (c_int, [c_dp, c_int, c_int, c_long, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_lml": (c_int, [c_dp, c_int, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp, c_dp]),
+    "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_trsm_small": (c_int, [c_dp, c_int, c_long, c_dp, c_long, c_int, c_int, c_dp, c_double, c_dp]),
+    "gpmpc_predict_mean": (c_int, [c_dp, c_long, c_int, c_int, c_dp, c_int, c_int, c_dp, c_dp, c_dp, c_long, c_int,
+                                   c_dp]),
+    "gpmpc_predict_var": (c_int, [c_dp, c_dp, c_int, c_int, c_double, c_double, c_dp, c_dp, c_long, c_int, c_dp]),
+    "gpmpc_dgemm_nt": (c_int, [c_dp, c_long, c_dp, c_long, c_dp, c_long, c_int, c_int, c_int, c_double, c_double,
+                               c_int, c_dp]),
+    "gpmpc_features": (c_int, [c_int, c_dp, c_long, c_dp, c_long, c_int, c_dp, c_long, c_dp]),
+    "gpmpc_admm_solve": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                 C.POINTER(AdmmSettings), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_rollout_3dof": (c_int, [C.POINTER(ExactModel), C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_dp,
+                                   c_dp, c_long, c_dp, c_dp]),
+    "gpmpc_propagate_cov_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_double, c_dp, c_dp,
+                                         c_dp]),
+    "gpmpc_qp_assemble_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long,
+                                       c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_mpc_update_3dof": (c_int, [c_int, c_int, c_int, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                      c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+}
+
+EXPORTED_SYMBOLS = tuple(_PROTOS)
+
+
+class GpmpcError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m gp_mpc_rocket_landing_b200.build` "
+            "(the CUDA library is the product; there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _PROTOS.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise GpmpcError(f"{what} failed ({rc}): {lib.gpmpc_last_error().decode()}")
+
+
+def require_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        raise GpmpcError("gp_mpc_rocket_landing_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    return torch
+
+
+def ptr(t):
+    """Device pointer of a CUDA tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "expected a contiguous CUDA tensor"
+    return t.data_ptr()
+
+
+def stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name: str, *args) -> None:
+    check(getattr(lib, name)(*args), name)

@@ -1,0 +1,431 @@
+// MPC-side kernels of the 3-DoF GP-MPC hot path (7 states [m, r(3), v(3)], 3 controls):
+//   * GP-augmented horizon rollout            reference gp_mpc.py:277-281 + _predict_with_gp :139-175
+//   * linear covariance propagation           reference uncertainty_prop.py:117-177
+//   * QP assembly in the OSQP-RTI layout      reference osqp_rti.py:203-372, linearisation :374-401 / :656-710
+//   * SQP / RTI bookkeeping after the QP      reference gp_mpc.py:336-345, osqp_rti.py:532-552
+// The dynamics are the in-repo Euler statement (nominal_mpc.py:586-605); `simdyn` is third-party and absent.
+// This file is compiled with -fmad=false so that the element-wise model arithmetic rounds like the numpy
+// restatement; the one hot loop (the GP cross-covariance row) uses explicit fma().
+#include <math.h>
+
+#include "common.cuh"
+#include "gpmpc_b200.h"
+
+using namespace gpmpc;
+
+namespace {
+
+constexpr int NX = 7, NU = 3, NS = 10;
+
+// Euler step, nominal_mpc.py:586-605:  m+ = m - dt*alpha*|u| ; r+ = r + dt v ; v+ = v + dt (u/m + g)
+__device__ __forceinline__ void step3(const double* x, const double* u, const GpmpcDyn3& p, double* xn) {
+  const double T = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+  xn[0] = x[0] + p.dt * (-p.alpha * T);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    xn[1 + i] = x[1 + i] + p.dt * x[4 + i];
+    xn[4 + i] = x[4 + i] + p.dt * (u[i] / x[0] + p.g[i]);
+  }
+}
+
+// Analytic discrete Jacobians, osqp_rti.py:682-708 (T_mag carries the reference's +1e-10).
+__device__ __forceinline__ void jac3_analytic(const double* x, const double* u, const GpmpcDyn3& p, double A[NX][NX],
+                                              double Bm[NX][NU]) {
+  const double m = x[0];
+  const double T = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]) + 1e-10;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {
+#pragma unroll
+    for (int j = 0; j < NX; ++j) A[i][j] = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+    for (int j = 0; j < NU; ++j) Bm[i][j] = 0.0;
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    A[1 + i][4 + i] = p.dt;
+    A[4 + i][0] = -u[i] / (m * m) * p.dt;
+    Bm[0][i] = -p.alpha * u[i] / T * p.dt;
+    Bm[4 + i][i] = p.dt / m;
+  }
+}
+
+// Forward finite differences with eps = 1e-6, osqp_rti.py:374-401.
+__device__ __forceinline__ void jac3_fd(const double* x, const double* u, const GpmpcDyn3& p, double A[NX][NX],
+                                        double Bm[NX][NU]) {
+  const double eps = 1e-6;
+  double f0[NX], f1[NX], xp[NX], up[NU];
+  step3(x, u, p, f0);
+  for (int i = 0; i < NX; ++i) {
+    for (int d = 0; d < NX; ++d) xp[d] = x[d];
+    xp[i] += eps;
+    step3(xp, u, p, f1);
+    for (int r = 0; r < NX; ++r) A[r][i] = (f1[r] - f0[r]) / eps;
+  }
+  for (int i = 0; i < NU; ++i) {
+    for (int d = 0; d < NU; ++d) up[d] = u[d];
+    up[i] += eps;
+    step3(x, up, p, f1);
+    for (int r = 0; r < NX; ++r) Bm[r][i] = (f1[r] - f0[r]) / eps;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ rollout
+// One warp per scenario; the horizon is a dependency chain (x_{k+1} needs the GP mean at x_k), so the parallelism
+// is scenarios x training points: each lane evaluates n/32 cross-covariances per stage, writes them as one
+// coalesced row of Ks (kept for the variance TRSM) and accumulates the P posterior means on the fly.
+constexpr int ROLL_WARPS = 8;
+constexpr int MAXP = 6, MAXDP = 64;
+
+template <int DP_T>  // DP_T > 0: compile-time padded feature dimension (registers); 0: runtime (shared memory)
+__global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactModel M, int has_model, GpmpcDyn3 dyn,
+                                                                   int nbatch, int N, const double* __restrict__ x0,
+                                                                   const double* __restrict__ U,
+                                                                   double* __restrict__ X, double* __restrict__ dmean,
+                                                                   double* __restrict__ Ks, long ldk,
+                                                                   const int* __restrict__ active) {
+  __shared__ double zs_sm[ROLL_WARPS][MAXDP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * ROLL_WARPS + warp;
+  if (b >= nbatch) return;
+  const bool act = (active == nullptr) || active[b] != 0;
+  const int DP = DP_T > 0 ? DP_T : M.DP;
+  double* zs = zs_sm[warp];
+  double x[NX], xn[NX], u[NU];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) x[d] = x0[(long)b * NX + d];
+  if (act && lane < NX) X[(long)b * (N + 1) * NX + lane] = x[lane];
+  for (int k = 0; k < N; ++k) {
+    const long row = (long)b * N + k;
+    if (!act) {  // keep the rows of skipped scenarios finite for the variance TRSM that follows
+      if (has_model && Ks)
+        for (int j = lane; j < M.n_pad; j += 32) Ks[row * ldk + j] = 0.0;
+      continue;
+    }
+#pragma unroll
+    for (int d = 0; d < NU; ++d) u[d] = U[row * NU + d];
+    double dm[MAXP];
+#pragma unroll
+    for (int p = 0; p < MAXP; ++p) dm[p] = 0.0;
+    if (has_model) {
+      // features (features.py:403-444), scaling and row norm (kernels.py:223-229)
+      double z[11], sqv[11];
+      features_3dof_dev(x, u, z);
+#pragma unroll
+      for (int d = 0; d < 11; ++d) {
+        z[d] = z[d] / M.lengthscales[d];
+        sqv[d] = z[d] * z[d];
+      }
+      const double sqz = numpy_pairwise_sum_small(sqv, 11);
+      __syncwarp();
+      if (lane == 0) {
+#pragma unroll
+        for (int d = 0; d < 11; ++d) zs[d] = z[d];
+        for (int d = 11; d < DP; ++d) zs[d] = 0.0;
+      }
+      __syncwarp();
+      double zr[DP_T > 0 ? DP_T : 1];
+      if (DP_T > 0) {
+#pragma unroll
+        for (int d = 0; d < DP_T; ++d) zr[d] = zs[d];
+      }
+      double acc[MAXP];
+#pragma unroll
+      for (int p = 0; p < MAXP; ++p) acc[p] = 0.0;
+      for (int j = lane; j < M.n_pad; j += 32) {
+        double kv = 0.0;
+        if (j < M.n) {
+          const double* xr = M.Xs + (long)j * DP;
+          double dot = 0.0;
+          if (DP_T > 0) {
+#pragma unroll
+            for (int d = 0; d < DP_T; d += 4) {
+              const double4 t = *reinterpret_cast<const double4*>(xr + d);
+              dot = fma(zr[d], t.x, dot);
+              dot = fma(zr[d + 1], t.y, dot);
+              dot = fma(zr[d + 2], t.z, dot);
+              dot = fma(zr[d + 3], t.w, dot);
+            }
+          } else {
+            for (int d = 0; d < DP; ++d) dot = fma(zs[d], __ldg(xr + d), dot);
+          }
+          const double d2 = (sqz + __ldg(M.sq + j)) - 2.0 * dot;
+          kv = kernel_value(M.kind, d2, M.signal_var);
+#pragma unroll
+          for (int p = 0; p < MAXP; ++p)
+            if (p < M.P) acc[p] = fma(kv, __ldg(M.alpha + (long)p * M.n_pad + j), acc[p]);
+        }
+        if (Ks) Ks[row * ldk + j] = kv;
+      }
+#pragma unroll
+      for (int p = 0; p < MAXP; ++p)
+        if (p < M.P) dm[p] = warp_sum(acc[p]) * M.ystd[p] + M.ymean[p];  // exact_gp.py:240-245
+    }
+    step3(x, u, dyn, xn);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dm[i] * dyn.dt;  // gp_mpc.py:165-167
+    if (lane < NX) X[((long)b * (N + 1) + k + 1) * NX + lane] = xn[lane];
+    if (dmean && lane < 3) dmean[row * 3 + lane] = dm[lane];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) x[d] = xn[d];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ covariance
+// One thread per scenario, Sigma (7x7) in registers; A_k = I + E_k with 6 off-diagonal entries, so A Sigma A' is two
+// sparse row/column updates (same products as the dense form of uncertainty_prop.py:166, zeros skipped).
+__global__ void __launch_bounds__(128) propagate_cov3_kernel(GpmpcDyn3 dyn, int nbatch, int N,
+                                                             const double* __restrict__ X,
+                                                             const double* __restrict__ U,
+                                                             const double* __restrict__ dvar, double sigma0,
+                                                             double* __restrict__ covs,
+                                                             const int* __restrict__ active) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  double S[NX][NX], Mx[NX][NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i)
+#pragma unroll
+    for (int j = 0; j < NX; ++j) S[i][j] = (i == j) ? sigma0 : 0.0;
+  double* out = covs + (long)b * (N + 1) * NX * NX;
+#pragma unroll
+  for (int i = 0; i < NX; ++i)
+#pragma unroll
+    for (int j = 0; j < NX; ++j) out[i * NX + j] = S[i][j];
+  for (int k = 0; k < N; ++k) {
+    const double* x = X + ((long)b * (N + 1) + k) * NX;
+    const double* u = U + ((long)b * N + k) * NU;
+    const double m = x[0];
+    double a[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) a[i] = -u[i] / (m * m) * dyn.dt;
+    // Mx = A S
+#pragma unroll
+    for (int j = 0; j < NX; ++j) {
+      Mx[0][j] = S[0][j];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        Mx[1 + i][j] = S[1 + i][j] + dyn.dt * S[4 + i][j];
+        Mx[4 + i][j] = a[i] * S[0][j] + S[4 + i][j];
+      }
+    }
+    // S = Mx A'
+#pragma unroll
+    for (int r = 0; r < NX; ++r) {
+      S[r][0] = Mx[r][0];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        S[r][1 + i] = Mx[r][1 + i] + Mx[r][4 + i] * dyn.dt;
+        S[r][4 + i] = Mx[r][0] * a[i] + Mx[r][4 + i];
+      }
+    }
+    if (dvar) {
+      const double* v = dvar + ((long)b * N + k) * 3;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) S[4 + i][4 + i] = S[4 + i][4 + i] + v[i] * (dyn.dt * dyn.dt);  // :157-160
+    }
+    double* o = out + (long)(k + 1) * NX * NX;
+#pragma unroll
+    for (int i = 0; i < NX; ++i)
+#pragma unroll
+      for (int j = 0; j < NX; ++j) o[i * NX + j] = S[i][j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ QP assembly
+// One thread per (scenario, stage); stage N writes the initial-state rows and the terminal cost vector.
+__global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nbatch, int N, int lin_mode, int rhs_mode,
+                                                           const double* __restrict__ X_lin,
+                                                           const double* __restrict__ U_lin,
+                                                           const double* __restrict__ x_init,
+                                                           const double* __restrict__ x_ref, long ldxref,
+                                                           const double* __restrict__ c_gp,
+                                                           const double* __restrict__ Qd,
+                                                           const double* __restrict__ Qfd, double* __restrict__ AB,
+                                                           double* __restrict__ beq, double* __restrict__ q,
+                                                           const int* __restrict__ active) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nbatch * (N + 1)) return;
+  const int b = idx / (N + 1), k = idx - b * (N + 1);
+  if (active && !active[b]) return;
+  const int n = N * NS + NX, neq = NX * (N + 1);
+  const double* xr = x_ref + (long)b * ldxref + (long)k * NX;
+  double* qb = q + (long)b * n + (long)k * NS;
+  if (k == N) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      qb[i] = -(Qfd[i] * xr[i]);                       // osqp_rti.py:254-256
+      beq[(long)b * neq + i] = x_init[(long)b * NX + i];  // :286-288
+    }
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < NX; ++i) qb[i] = -(Qd[i] * xr[i]);  // :249-252
+#pragma unroll
+  for (int i = 0; i < NU; ++i) qb[NX + i] = 0.0;
+  double x[NX], u[NU], A[NX][NX], Bm[NX][NU];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) x[d] = X_lin[((long)b * (N + 1) + k) * NX + d];
+#pragma unroll
+  for (int d = 0; d < NU; ++d) u[d] = U_lin[((long)b * N + k) * NU + d];
+  if (lin_mode == 0) jac3_analytic(x, u, dyn, A, Bm);
+  else jac3_fd(x, u, dyn, A, Bm);
+  // affine term
+  double c[NX];
+  if (rhs_mode == 0) {
+    step3(x, u, dyn, c);  // c_k = f(x_lin,u_lin) - A x_lin - B u_lin   (:338-344, sign as the reference writes it)
+  } else {
+#pragma unroll
+    for (int d = 0; d < NX; ++d) c[d] = X_lin[((long)b * (N + 1) + k + 1) * NX + d];  // gp_mpc.py:402-411
+  }
+#pragma unroll
+  for (int r = 0; r < NX; ++r) {
+    double ax = 0.0, bu = 0.0;
+#pragma unroll
+    for (int j = 0; j < NX; ++j) ax += A[r][j] * x[j];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) bu += Bm[r][j] * u[j];
+    c[r] = (c[r] - ax) - bu;
+  }
+  if (c_gp) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) c[4 + i] = c[4 + i] + c_gp[((long)b * N + k) * 3 + i] * dyn.dt;
+  }
+  double* be = beq + (long)b * neq + NX + (long)k * NX;
+#pragma unroll
+  for (int r = 0; r < NX; ++r) be[r] = (rhs_mode == 0) ? c[r] : -c[r];
+  double* ab = AB + ((long)b * N + k) * NX * NS;
+#pragma unroll
+  for (int r = 0; r < NX; ++r) {
+#pragma unroll
+    for (int j = 0; j < NX; ++j) ab[r * NS + j] = (fabs(A[r][j]) > 1e-10) ? A[r][j] : 0.0;  // :301
+#pragma unroll
+    for (int j = 0; j < NU; ++j) ab[r * NS + NX + j] = (fabs(Bm[r][j]) > 1e-10) ? Bm[r][j] : 0.0;  // :309
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ post-QP update
+// One warp per scenario.  mode 0 = RTI (osqp_rti.py:532-552), mode 1 = GP-MPC SQP iteration (gp_mpc.py:336-345).
+__global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int mode, const double* __restrict__ z,
+                                                          const int* __restrict__ qp_status,
+                                                          const double* __restrict__ x_ref, long ldxref,
+                                                          const double* __restrict__ Qd,
+                                                          const double* __restrict__ Qfd,
+                                                          const double* __restrict__ Rd, double* __restrict__ X,
+                                                          double* __restrict__ U, double* __restrict__ X_prev,
+                                                          double* __restrict__ U_prev, double* __restrict__ cost,
+                                                          int* __restrict__ converged, int* __restrict__ active,
+                                                          int* __restrict__ n_iter) {
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  const int n = N * NS + NX;
+  const bool solved = qp_status[b] == GPMPC_QP_SOLVED;
+  const double* zb = z + (long)b * n;
+  double* Xb = X + (long)b * (N + 1) * NX;
+  double* Ub = U + (long)b * N * NU;
+  double dmaxx = 0.0, dmaxu = 0.0, cs = 0.0;
+  if (solved) {
+    for (int j = lane; j < n; j += 32) {
+      const int k = j / NS, i = j - k * NS;
+      const double v = zb[j];
+      if (i < NX) {
+        double* dst = Xb + k * NX + i;
+        dmaxx = fmax(dmaxx, fabs(v - *dst));
+        const double e = v - x_ref[(long)b * ldxref + (long)k * NX + i];
+        cs += ((k == N) ? Qfd[i] : Qd[i]) * (e * e);
+        *dst = v;
+        if (X_prev) {  // shifted warm start: X_prev[k-1] = X[k], X_prev[N] = X[N]
+          double* xp = X_prev + (long)b * (N + 1) * NX;
+          if (k >= 1) xp[(k - 1) * NX + i] = v;
+          if (k == N) xp[N * NX + i] = v;
+        }
+      } else {
+        double* dst = Ub + k * NU + (i - NX);
+        dmaxu = fmax(dmaxu, fabs(v - *dst));
+        cs += Rd[i - NX] * (v * v);
+        *dst = v;
+        if (U_prev) {
+          double* up = U_prev + (long)b * N * NU;
+          if (k >= 1) up[(k - 1) * NU + (i - NX)] = v;
+          if (k == N - 1) up[(N - 1) * NU + (i - NX)] = v;
+        }
+      }
+    }
+  }
+  dmaxx = warp_max(dmaxx);
+  dmaxu = warp_max(dmaxu);
+  cs = warp_sum(cs);
+  if (lane == 0) {
+    cost[b] = solved ? cs : INFINITY;
+    if (mode == 0) {
+      converged[b] = solved ? 1 : 0;
+    } else {
+      const int conv = (dmaxx < 1e-4 && dmaxu < 1e-4) ? 1 : 0;
+      converged[b] = conv;
+      if (n_iter) n_iter[b] += 1;
+      if (conv && active) active[b] = 0;
+    }
+  }
+}
+
+}  // namespace
+
+// ================================================================================================== C ABI
+extern "C" int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3* dyn, int B, int N, const double* x0,
+                                  const double* U, double* X, double* dmean, double* Ks, long ldk, const int* active,
+                                  void* stream) {
+  GPMPC_REQUIRE(dyn != nullptr && B >= 0 && N >= 1, "gpmpc_rollout_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  GpmpcExactModel M{};
+  int has_model = 0;
+  if (model) {
+    M = *model;
+    has_model = 1;
+    GPMPC_REQUIRE(M.D == 11 && M.DP >= 12 && M.DP <= MAXDP && M.DP % 4 == 0, "gpmpc_rollout_3dof: model must have D=11, DP%4==0");
+    GPMPC_REQUIRE(M.P >= 3 && M.P <= MAXP, "gpmpc_rollout_3dof: model must have 3..6 outputs");
+    GPMPC_REQUIRE(Ks == nullptr || ldk >= M.n_pad, "gpmpc_rollout_3dof: ldk < n_pad");
+  }
+  const int grid = (B + ROLL_WARPS - 1) / ROLL_WARPS;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (has_model && M.DP == 12)
+    rollout3_kernel<12><<<grid, ROLL_WARPS * 32, 0, s>>>(M, has_model, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
+  else
+    rollout3_kernel<0><<<grid, ROLL_WARPS * 32, 0, s>>>(M, has_model, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
+  return gpmpc_check_launch("rollout_3dof");
+}
+
+extern "C" int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U,
+                                        const double* dvar, double sigma0, double* covs, const int* active,
+                                        void* stream) {
+  GPMPC_REQUIRE(dyn != nullptr && B >= 0 && N >= 1, "gpmpc_propagate_cov_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  propagate_cov3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, B, N, X, U, dvar, sigma0, covs, active);
+  return gpmpc_check_launch("propagate_cov_3dof");
+}
+
+extern "C" int gpmpc_qp_assemble_3dof(const GpmpcDyn3* dyn, int B, int N, int lin_mode, int rhs_mode,
+                                      const double* X_lin, const double* U_lin, const double* x_init,
+                                      const double* x_ref, long ldxref, const double* c_gp, const double* Qdiag,
+                                      const double* Qfdiag, double* AB, double* beq, double* q, const int* active,
+                                      void* stream) {
+  GPMPC_REQUIRE(dyn != nullptr && B >= 0 && N >= 1, "gpmpc_qp_assemble_3dof: bad arguments");
+  GPMPC_REQUIRE(lin_mode >= 0 && lin_mode <= 1 && rhs_mode >= 0 && rhs_mode <= 1, "gpmpc_qp_assemble_3dof: bad mode");
+  if (B == 0) return GPMPC_OK;
+  const int total = B * (N + 1);
+  qp_assemble3_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      *dyn, B, N, lin_mode, rhs_mode, X_lin, U_lin, x_init, x_ref, ldxref, c_gp, Qdiag, Qfdiag, AB, beq, q, active);
+  return gpmpc_check_launch("qp_assemble_3dof");
+}
+
+extern "C" int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp_status,
+                                     const double* x_ref, long ldxref, const double* Qdiag, const double* Qfdiag,
+                                     const double* Rdiag, double* X, double* U, double* X_prev, double* U_prev,
+                                     double* cost, int* converged, int* active, int* n_iter, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && N >= 1 && (mode == 0 || mode == 1), "gpmpc_mpc_update_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  mpc_update3_kernel<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream>>>(B, N, mode, z, qp_status, x_ref, ldxref, Qdiag,
+                                                                     Qfdiag, Rdiag, X, U, X_prev, U_prev, cost,
+                                                                     converged, active, n_iter);
+  return gpmpc_check_launch("mpc_update_3dof");
+}

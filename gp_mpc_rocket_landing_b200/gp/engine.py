@@ -1,0 +1,212 @@
+"""Device-side GP engine: thin Python over the C-ABI (include/gpmpc_b200.h).
+
+Everything numeric happens in libgpmpc_b200.so; torch only owns the HBM buffers.  Layout conventions
+(DESIGN.md "Data layout"): FP64 row-major; training/query counts padded to multiples of 128 rows, feature
+dimension padded to a multiple of 4 with zeros; the Cholesky factor carries a unit diagonal in the padding.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from .. import _lib
+from .._lib import call, ptr, stream
+
+SE, M32, M52 = 0, 1, 2
+
+
+def torch_():
+    return _lib.require_cuda()
+
+
+def pad_to(n: int, m: int) -> int:
+    return ((max(n, 1) + m - 1) // m) * m
+
+
+def to_dev(a, dtype=None):
+    """numpy / sequence -> contiguous CUDA tensor (float64 by default); CUDA tensors pass through."""
+    torch = torch_()
+    if isinstance(a, torch.Tensor):
+        t = a if a.is_cuda else a.cuda()
+        if dtype is not None and t.dtype != dtype:
+            t = t.to(dtype)
+        return t.contiguous()
+    arr = np.ascontiguousarray(np.asarray(a, dtype=np.float64 if dtype is None else None))
+    t = torch.from_numpy(arr).cuda()
+    if dtype is not None:
+        t = t.to(dtype)
+    return t
+
+
+def scale_inputs(X, ls, n_pad=None, DP=None):
+    """kernels.py:223-229: Xs = X / l (zero padded) and numpy-order row sums of squares."""
+    torch = torch_()
+    n, D = X.shape
+    n_pad = pad_to(n, 128) if n_pad is None else n_pad
+    DP = pad_to(D, 4) if DP is None else DP
+    Xs = torch.empty((n_pad, DP), dtype=torch.float64, device=X.device)
+    sq = torch.empty((n_pad,), dtype=torch.float64, device=X.device)
+    call("gpmpc_scale_inputs", ptr(X), n, D, X.stride(0), ptr(ls), ptr(Xs), n_pad, DP, ptr(sq), stream())
+    return Xs, sq
+
+
+def gram_scaled(kind, Xs1, sq1, n1, Xs2, sq2, n2, sv, diag_add=0.0, pad_identity=0, lower_only=0, out=None):
+    torch = torch_()
+    n1_pad, DP = Xs1.shape
+    n2_pad = Xs2.shape[0]
+    K = out if out is not None else torch.empty((n1_pad, n2_pad), dtype=torch.float64, device=Xs1.device)
+    call("gpmpc_gram", int(kind), ptr(Xs1), ptr(sq1), n1, n1_pad, ptr(Xs2), ptr(sq2), n2, n2_pad, DP, float(sv),
+         float(diag_add), int(pad_identity), int(lower_only), ptr(K), K.stride(0), stream())
+    return K
+
+
+def gram(kind, X1, X2, ls, sv):
+    """Kernel.__call__ (kernels.py:238-262, :532-545, :625-638) on the device -> (N1, N2) CUDA tensor."""
+    X1 = to_dev(np.atleast_2d(X1) if not hasattr(X1, "is_cuda") else X1)
+    lsd = to_dev(ls)
+    Xs1, sq1 = scale_inputs(X1, lsd)
+    if X2 is None:
+        Xs2, sq2, n2 = Xs1, sq1, X1.shape[0]
+    else:
+        X2 = to_dev(np.atleast_2d(X2) if not hasattr(X2, "is_cuda") else X2)
+        Xs2, sq2 = scale_inputs(X2, lsd)
+        n2 = X2.shape[0]
+    K = gram_scaled(kind, Xs1, sq1, X1.shape[0], Xs2, sq2, n2, sv)
+    return K[: X1.shape[0], :n2]
+
+
+def gram_grad_lengthscale(X1, X2, ls, sv, dim):
+    """SE-ARD dK/dlog(l_dim), kernels.py:310-316."""
+    torch = torch_()
+    X1 = to_dev(np.atleast_2d(X1))
+    lsd = to_dev(ls)
+    Xs1, sq1 = scale_inputs(X1, lsd)
+    if X2 is None:
+        Xs2, sq2, n2 = Xs1, sq1, X1.shape[0]
+    else:
+        X2 = to_dev(np.atleast_2d(X2))
+        Xs2, sq2 = scale_inputs(X2, lsd)
+        n2 = X2.shape[0]
+    G = torch.empty((Xs1.shape[0], Xs2.shape[0]), dtype=torch.float64, device=X1.device)
+    call("gpmpc_gram_grad_lengthscale", ptr(Xs1), ptr(sq1), X1.shape[0], Xs1.shape[0], ptr(Xs2), ptr(sq2), n2,
+         Xs2.shape[0], Xs1.shape[1], float(sv), int(dim), ptr(G), G.stride(0), stream())
+    return G[: X1.shape[0], :n2]
+
+
+def features(which, X, U):
+    """features.py extract_batch on the device: (B,nx),(B,3) -> (B, 11|13|12)."""
+    torch = torch_()
+    X, U = to_dev(X), to_dev(U)
+    nf = {0: 11, 1: 13, 2: 12}[which]
+    Z = torch.empty((X.shape[0], nf), dtype=torch.float64, device=X.device)
+    call("gpmpc_features", which, ptr(X), X.stride(0), ptr(U), U.stride(0), X.shape[0], ptr(Z), Z.stride(0), stream())
+    return Z
+
+
+def potrf(A, batch=1):
+    """In-place batched Cholesky of (batch, n_pad, n_pad) (or (n_pad, n_pad)); returns (Winv, info)."""
+    torch = torch_()
+    n_pad = A.shape[-1]
+    Winv = torch.empty((batch, n_pad // 64, 64, 64), dtype=torch.float64, device=A.device)
+    info = torch.empty((batch,), dtype=torch.int32, device=A.device)
+    call("gpmpc_potrf", ptr(A), n_pad, A.stride(-2), n_pad * A.stride(-2), batch, ptr(Winv), ptr(info), stream())
+    return Winv, info
+
+
+class ExactFactor:
+    """K = k(X,X) + (noise+jitter) I = L L^T for one hyper-parameter set (exact_gp.py:157-175)."""
+
+    def __init__(self, kind, ls, sv, noise):
+        self.kind, self.sv, self.noise = int(kind), float(sv), float(noise)
+        self.ls_host = np.asarray(ls, dtype=np.float64).copy()
+        self.jitter = 0.0
+
+    def fit(self, X, jitters=(0.0, 1e-6, 1e-5, 1e-4, 1e-3, 1e-2, 1e-1)):
+        torch = torch_()
+        self.X = to_dev(X)
+        self.n, self.D = self.X.shape
+        self.ls = to_dev(self.ls_host)
+        self.Xs, self.sq = scale_inputs(self.X, self.ls)
+        self.n_pad, self.DP = self.Xs.shape
+        L = torch.empty((self.n_pad, self.n_pad), dtype=torch.float64, device=self.X.device)
+        for jit in jitters:  # exact_gp.py:163-175: retry chol(K_noise + jitter I), jitter = 1e-6 * 10^j < 1
+            gram_scaled(self.kind, self.Xs, self.sq, self.n, self.Xs, self.sq, self.n, self.sv,
+                        diag_add=self.noise + jit, pad_identity=1, lower_only=1, out=L)
+            self.Winv, info = potrf(L)
+            if int(info.item()) == 0:
+                self.L, self.jitter = L, jit
+                return self
+        raise ValueError("Kernel matrix is not positive definite even with jitter")
+
+    def solve(self, Bm):
+        """cho_solve for the rows of Bm (nrhs, n_pad), in place."""
+        call("gpmpc_potrs", ptr(self.L), self.n_pad, self.L.stride(0), 0, ptr(self.Winv), ptr(Bm), Bm.shape[0], 1,
+             stream())
+        return Bm
+
+    def cross(self, Xq, out=None):
+        """K* rows for queries Xq (Q,D): returns (Ks (q_pad, n_pad), Q)."""
+        Q = Xq.shape[0]
+        Xqs, sqq = scale_inputs(Xq, self.ls, DP=self.DP)
+        return gram_scaled(self.kind, Xqs, sqq, Q, self.Xs, self.sq, self.n, self.sv, out=out), Q
+
+    def sumsq_inplace(self, Ks):
+        """v = L^{-1} K*^T in place (row-wise) and sum_i v_i^2 per query (exact_gp.py:260-261)."""
+        torch = torch_()
+        sumsq = torch.empty((Ks.shape[0],), dtype=torch.float64, device=Ks.device)
+        call("gpmpc_trsm_sumsq", ptr(self.L), self.n_pad, self.L.stride(0), ptr(self.Winv), ptr(Ks), Ks.shape[0],
+             Ks.stride(0), ptr(sumsq), stream())
+        return sumsq
+
+
+class ExactModelDev:
+    """P outputs on one ExactFactor: alpha, y normalisation, LML (exact_gp.py:118-204) and predict (:213-268)."""
+
+    def __init__(self, factor: ExactFactor):
+        self.f = factor
+
+    def fit_targets(self, Y, normalize=True):
+        torch = torch_()
+        f = self.f
+        Y = to_dev(Y)
+        if Y.dim() == 1:
+            Y = Y[:, None].contiguous()
+        self.P = Y.shape[1]
+        dev = Y.device
+        self.Yn = torch.empty((self.P, f.n_pad), dtype=torch.float64, device=dev)
+        self.ymean = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        self.ystd = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        call("gpmpc_normalize_targets", ptr(Y), f.n, self.P, Y.stride(0), f.n_pad, int(normalize), ptr(self.Yn),
+             ptr(self.ymean), ptr(self.ystd), stream())
+        self.alpha = f.solve(self.Yn.clone())
+        self.lml = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        call("gpmpc_lml", ptr(f.L), f.n, f.n_pad, f.L.stride(0), 0, ptr(self.Yn), ptr(self.alpha), self.P, 1,
+             ptr(self.lml), stream())
+        return self
+
+    def predict(self, Xq, want_var=True, chunk=65536):
+        """-> mean (Q,P), var (Q,P) CUDA tensors."""
+        torch = torch_()
+        f = self.f
+        Xq = to_dev(Xq)
+        Q = Xq.shape[0]
+        mean = torch.empty((Q, self.P), dtype=torch.float64, device=Xq.device)
+        var = torch.empty((Q, self.P), dtype=torch.float64, device=Xq.device) if want_var else None
+        for s in range(0, Q, chunk):
+            e = min(Q, s + chunk)
+            Ks, q = f.cross(Xq[s:e])
+            call("gpmpc_predict_mean", ptr(Ks), Ks.stride(0), q, f.n, ptr(self.alpha), f.n_pad, self.P,
+                 ptr(self.ymean), ptr(self.ystd), ptr(mean[s:e]), mean.stride(0), 0, stream())
+            if want_var:
+                sumsq = f.sumsq_inplace(Ks)
+                call("gpmpc_predict_var", ptr(sumsq), None, q, self.P, f.sv, 1e-10, ptr(self.ystd), ptr(var[s:e]),
+                     var.stride(0), 0, stream())
+        return mean, var
+
+    def struct(self):
+        """GpmpcExactModel for the fused horizon kernels (keeps the tensors alive through self)."""
+        f = self.f
+        return _lib.ExactModel(kind=f.kind, n=f.n, n_pad=f.n_pad, D=f.D, DP=f.DP, P=self.P, signal_var=f.sv,
+                               lengthscales=ptr(f.ls), Xs=ptr(f.Xs), sq=ptr(f.sq), alpha=ptr(self.alpha),
+                               ymean=ptr(self.ymean), ystd=ptr(self.ystd), L=ptr(f.L), Winv=ptr(f.Winv))

@@ -1,0 +1,143 @@
+"""Device-side MPC engine: thin Python over the MPC entry points of the C-ABI (include/gpmpc_b200.h).
+
+QP layout (reference osqp_rti.py): z = [x_0,u_0,...,x_{N-1},u_{N-1},x_N], n = 10N+7,
+rows = [x_0 = x_init (7) | A_k x_k + B_k u_k - x_{k+1} = b_k (7N) | l <= I z <= u (n)], m = 7(N+1)+n.
+The dynamics blocks are stored dense per stage (AB: B x N x 7 x 10, explicit zeros = fixed superset pattern).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from .. import _lib
+from .._lib import AdmmSettings, Dyn3, call, ptr, stream
+from ..gp.engine import to_dev, torch_
+
+NX, NU, NS = 7, 3, 10
+INF = 1e30
+
+# osqp_rti.py:168-201 cost weights and box bounds
+Q_DIAG = np.array([0.0, 10.0, 10.0, 10.0, 1.0, 1.0, 1.0])
+QF_DIAG = Q_DIAG * 10.0
+R_DIAG = np.ones(3) * 0.01
+X_MIN = np.array([-np.inf, -100.0, -100.0, -100.0, -50.0, -50.0, -50.0])
+X_MAX = np.array([np.inf, 500.0, 100.0, 100.0, 50.0, 50.0, 50.0])
+U_MIN = np.array([0.3, -5.0, -5.0])
+U_MAX = np.array([5.0, 5.0, 5.0])
+
+
+def qp_dims(N):
+    n = N * NS + NX
+    return n, NX * (N + 1) + n
+
+
+def make_dyn(alpha, g_vec, dt):
+    d = Dyn3()
+    d.alpha = float(alpha)
+    for i in range(3):
+        d.g[i] = float(g_vec[i])
+    d.dt = float(dt)
+    return d
+
+
+def stage_vector(N, xpart, upart):
+    """Tile per-stage (7,) and (3,) vectors into the z ordering (n,)."""
+    n, _ = qp_dims(N)
+    v = np.zeros(n)
+    for k in range(N):
+        v[k * NS:k * NS + NX] = xpart
+        v[k * NS + NX:(k + 1) * NS] = upart
+    v[N * NS:] = xpart
+    return v
+
+
+@dataclass
+class QPData:
+    """Shared (scenario-independent) QP data on the device."""
+    N: int
+    Pdiag: object
+    lb: object
+    ub: object
+    Qd: object
+    Qfd: object
+    Rd: object
+
+    @classmethod
+    def reference(cls, N, Q=Q_DIAG, Qf=QF_DIAG, R=R_DIAG, x_min=X_MIN, x_max=X_MAX, u_min=U_MIN, u_max=U_MAX):
+        n, _ = qp_dims(N)
+        P = stage_vector(N, Q, R)
+        P[N * NS:] = Qf
+        lb = np.maximum(stage_vector(N, x_min, u_min), -INF)
+        ub = np.minimum(stage_vector(N, x_max, u_max), INF)
+        return cls(N, to_dev(P), to_dev(lb), to_dev(ub), to_dev(Q), to_dev(Qf), to_dev(R))
+
+
+class AdmmWorkspace:
+    """Per-scenario solver state that OSQP keeps between solves (x, y, rho) + per-solve outputs."""
+
+    def __init__(self, B, N, device=None):
+        torch = torch_()
+        n, m = qp_dims(N)
+        kw = dict(dtype=torch.float64, device=device or "cuda")
+        self.B, self.N, self.n, self.m = B, N, n, m
+        self.x = torch.zeros((B, n), **kw)
+        self.y = torch.zeros((B, m), **kw)
+        self.rho = torch.zeros((B,), **kw)
+        self.obj = torch.zeros((B,), **kw)
+        self.pri = torch.zeros((B,), **kw)
+        self.dua = torch.zeros((B,), **kw)
+        self.status = torch.zeros((B,), dtype=torch.int32, device=kw["device"])
+        self.iters = torch.zeros((B,), dtype=torch.int32, device=kw["device"])
+
+
+def admm_solve(qp: QPData, AB, beq, q, settings: AdmmSettings, ws: AdmmWorkspace, active=None):
+    call("gpmpc_admm_solve", NX, NU, qp.N, ws.B, ptr(AB), ptr(beq), ptr(q), ptr(qp.Pdiag), ptr(qp.lb), ptr(qp.ub),
+         C.byref(settings), ptr(active), ptr(ws.x), ptr(ws.y), ptr(ws.rho), ptr(ws.status), ptr(ws.iters),
+         ptr(ws.obj), ptr(ws.pri), ptr(ws.dua), stream())
+    return ws
+
+
+def rollout(model_struct, dyn, x0, U, X, dmean=None, Ks=None, active=None):
+    B, N = U.shape[0], U.shape[1]
+    call("gpmpc_rollout_3dof", C.byref(model_struct) if model_struct is not None else None, C.byref(dyn), B, N,
+         ptr(x0), ptr(U), ptr(X), ptr(dmean), ptr(Ks), Ks.stride(0) if Ks is not None else 0, ptr(active), stream())
+
+
+def propagate_cov(dyn, X, U, dvar, covs, sigma0=1e-6, active=None):
+    B, N = U.shape[0], U.shape[1]
+    call("gpmpc_propagate_cov_3dof", C.byref(dyn), B, N, ptr(X), ptr(U), ptr(dvar), float(sigma0), ptr(covs),
+         ptr(active), stream())
+
+
+def qp_assemble(dyn, qp: QPData, X_lin, U_lin, x_init, x_ref, AB, beq, q, c_gp=None, lin_mode=0, rhs_mode=0,
+                active=None):
+    """x_ref: (N+1,7) shared by all scenarios or (B,N+1,7)."""
+    B, N = U_lin.shape[0], U_lin.shape[1]
+    ldxref = 0 if x_ref.dim() == 2 else x_ref.stride(0)
+    call("gpmpc_qp_assemble_3dof", C.byref(dyn), B, N, lin_mode, rhs_mode, ptr(X_lin), ptr(U_lin), ptr(x_init),
+         ptr(x_ref), ldxref, ptr(c_gp), ptr(qp.Qd), ptr(qp.Qfd), ptr(AB), ptr(beq), ptr(q), ptr(active), stream())
+
+
+def mpc_update(qp: QPData, mode, z, qp_status, x_ref, X, U, X_prev, U_prev, cost, converged, active=None, n_iter=None):
+    B, N = U.shape[0], U.shape[1]
+    ldxref = 0 if x_ref.dim() == 2 else x_ref.stride(0)
+    call("gpmpc_mpc_update_3dof", B, N, mode, ptr(z), ptr(qp_status), ptr(x_ref), ldxref, ptr(qp.Qd), ptr(qp.Qfd),
+         ptr(qp.Rd), ptr(X), ptr(U), ptr(X_prev), ptr(U_prev), ptr(cost), ptr(converged), ptr(active), ptr(n_iter),
+         stream())
+
+
+def dense_constraints(N, AB, beq, lb, ub):
+    """Host helper (tests / debugging): dense (A, l, u) of one scenario from the stage-block storage."""
+    n, m = qp_dims(N)
+    A = np.zeros((m, n)); l = np.zeros(m); u = np.zeros(m)
+    A[:NX, :NX] = np.eye(NX)
+    for k in range(N):
+        r = NX + k * NX
+        A[r:r + NX, k * NS:(k + 1) * NS] = AB[k]
+        A[r:r + NX, (k + 1) * NS:(k + 1) * NS + NX] = -np.eye(NX)
+    A[NX * (N + 1):] = np.eye(n)
+    l[:NX * (N + 1)] = u[:NX * (N + 1)] = beq
+    l[NX * (N + 1):] = lb; u[NX * (N + 1):] = ub
+    return A, l, u

@@ -1,0 +1,43 @@
+"""CPU: the C-ABI library loads without a GPU and exports every symbol include/gpmpc_b200.h declares;
+compute entry points refuse to run without a CUDA device (no CPU fallback)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+def _declared():
+    txt = open(os.path.join(ROOT, "include", "gpmpc_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(gpmpc_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_declared_symbol():
+    from gp_mpc_rocket_landing_b200 import _lib
+    names = _declared()
+    assert len(names) >= 20
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for nm in names:
+        assert hasattr(raw, nm), f"{nm} declared in include/gpmpc_b200.h but not exported"
+        assert nm in _lib.EXPORTED_SYMBOLS, f"{nm} has no ctypes prototype"
+    assert _lib.lib.gpmpc_version() >= 100
+
+
+def test_struct_layouts_match_header():
+    from gp_mpc_rocket_landing_b200 import _lib
+    assert ctypes.sizeof(_lib.AdmmSettings) == 8 * 8 + 8 * 4
+    assert ctypes.sizeof(_lib.Dyn3) == 5 * 8
+    assert ctypes.sizeof(_lib.ExactModel) == 6 * 4 + 8 + 8 * 8
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from gp_mpc_rocket_landing_b200 import _lib
+    from gp_mpc_rocket_landing_b200.gp import engine
+    with pytest.raises(_lib.GpmpcError):
+        engine.gram(0, [[0.0]], None, [1.0], 1.0)

@@ -1,0 +1,135 @@
+"""GPU parity: GP kernels through the C-ABI (libgpmpc_b200.so) against the oracle and the golden vectors
+generated from the real reference.  FP64 tolerances are written next to each check; the 1e-9 relative bar of
+north_star applies on well-conditioned fixtures and is scaled by cond(K)/1e6 on the reference-default one
+(sigma_n^2 = 1e-4, cond ~ 9e6; even numpy-vs-numpy differs by 1.07e-9 there -- SURVEY H1)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+KINDS = {"se": 0, "m32": 1, "m52": 2}
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from gp_mpc_rocket_landing_b200.gp import engine
+    engine.torch_()
+    return engine
+
+
+def test_gram_matches_reference(eng):
+    g = load_golden("kernels.npz")
+    sv = float(g["sv"])
+    for name, kind in KINDS.items():
+        K = eng.gram(kind, g["X1"], None, g["ls"], sv).cpu().numpy()
+        Kc = eng.gram(kind, g["X1"], g["X2"], g["ls"], sv).cpu().numpy()
+        # same operation order as kernels.py:205-262; only the 11-term dot differs (DMMA vs BLAS): few ulp
+        np.testing.assert_allclose(K, g[f"{name}_self"], rtol=4e-15, atol=4e-15)
+        np.testing.assert_allclose(Kc, g[f"{name}_cross"], rtol=4e-15, atol=4e-15)
+    for i, nm in enumerate(g["se_grad_names"]):
+        nm = str(nm)
+        if nm == "log_signal_variance":
+            G = eng.gram(0, g["X1"], g["X2"], g["ls"], sv).cpu().numpy()
+        else:
+            G = eng.gram_grad_lengthscale(g["X1"], g["X2"], g["ls"], sv, int(nm.split("_")[-1])).cpu().numpy()
+        np.testing.assert_allclose(G, g["se_grad"][i], rtol=1e-13, atol=1e-15)
+
+
+def test_gram_large_and_ragged(eng):
+    """Sizes that are not multiples of the 128 tile, empty-ish inputs, and symmetry / unit diagonal."""
+    from oracle import gp as ogp
+    rng = np.random.default_rng(3)
+    for n1, n2, D in ((1, 1, 1), (129, 257, 11), (300, 5, 13), (1000, 640, 12)):
+        X1, X2 = rng.normal(size=(n1, D)), rng.normal(size=(n2, D))
+        ls = rng.uniform(0.5, 2.0, D)
+        for kind in (0, 1, 2):
+            K = eng.gram(kind, X1, X2, ls, 1.7).cpu().numpy()
+            np.testing.assert_allclose(K, ogp.gram(kind, X1, X2, ls, 1.7), rtol=1e-13, atol=1e-15)
+    X = rng.normal(size=(500, 11))
+    K = eng.gram(0, X, None, np.ones(11), 1.0).cpu().numpy()
+    assert np.array_equal(K, K.T) or np.max(np.abs(K - K.T)) < 1e-15
+    assert np.max(np.abs(np.diag(K) - 1.0)) < 1e-14
+
+
+def test_features_match_reference(eng):
+    g = load_golden("features.npz")
+    f3 = eng.features(0, g["X14"][:, :7].copy(), g["U"]).cpu().numpy()
+    ft = eng.features(1, g["X14"], g["U"]).cpu().numpy()
+    fr = eng.features(2, g["X14"], g["U"]).cpu().numpy()
+    # element-wise double arithmetic in the reference order; exp/atan2/asin may differ from libm by 1-2 ulp
+    np.testing.assert_allclose(f3, g["f3"], rtol=2e-15, atol=1e-17)
+    np.testing.assert_allclose(ft, g["ft"], rtol=2e-15, atol=1e-16)
+    np.testing.assert_allclose(fr, g["fr"], rtol=2e-15, atol=1e-16)
+
+
+def test_exact_fit_predict_all_kernels(eng):
+    g = load_golden("exact_gp.npz")
+    n = g["X"].shape[0]
+    for name, kind in KINDS.items():
+        f = eng.ExactFactor(kind, g["ls"], float(g["sv"]), float(g["noise"])).fit(g["X"])
+        assert f.jitter == 0.0
+        m = eng.ExactModelDev(f).fit_targets(g["y"])
+        L = f.L.cpu().numpy()
+        np.testing.assert_allclose(L[:n, :n], g[f"{name}_L"], rtol=1e-9, atol=1e-12)
+        assert np.array_equal(L[n:, :n], np.zeros_like(L[n:, :n])) and np.array_equal(L[n:, n:], np.eye(L.shape[0] - n))
+        assert relerr(m.alpha.cpu().numpy()[0, :n], g[f"{name}_alpha"]) < 1e-7   # alpha ~ cond * eps
+        assert relerr(m.lml.cpu().numpy()[0], g[f"{name}_lml"]) < 1e-11
+        assert m.ymean.item() == pytest.approx(float(g[f"{name}_ymean"]), rel=1e-15)
+        assert m.ystd.item() == pytest.approx(float(g[f"{name}_ystd"]), rel=1e-15)
+        mean, var = m.predict(g["Xt"])
+        assert relerr(mean.cpu().numpy()[:, 0], g[f"{name}_mean"]) < 1e-9
+        assert relerr(var.cpu().numpy()[:, 0], g[f"{name}_var"]) < 1e-9
+    f = eng.ExactFactor(0, g["ls"], float(g["sv"]), float(g["noise"])).fit(g["X"])
+    m = eng.ExactModelDev(f).fit_targets(g["y"], normalize=False)
+    mean, var = m.predict(g["Xt"])
+    assert relerr(mean.cpu().numpy()[:, 0], g["se_nonorm_mean"]) < 1e-9
+    assert relerr(var.cpu().numpy()[:, 0], g["se_nonorm_var"]) < 1e-9
+    assert relerr(m.lml.cpu().numpy()[0], g["se_nonorm_lml"]) < 1e-11
+
+
+def test_exact_fit_jitter_escalation(eng):
+    """exact_gp.py:163-175: the fixture is not PD at noise alone; the same jitter step must be selected."""
+    from oracle import gp as ogp
+    g = load_golden("exact_gp.npz")
+    fo = ogp.exact_fit(ogp.SE, g["jit_X"], g["jit_y"], g["jit_ls"], float(g["sv"]), float(g["jit_noise"]))
+    f = eng.ExactFactor(0, g["jit_ls"], float(g["sv"]), float(g["jit_noise"])).fit(g["jit_X"])
+    assert f.jitter == fo.jitter > 0.0
+    m = eng.ExactModelDev(f).fit_targets(g["jit_y"])
+    n = g["jit_X"].shape[0]
+    np.testing.assert_allclose(np.diag(f.L.cpu().numpy())[:n], g["jit_Ldiag"], rtol=1e-6)
+    assert relerr(m.lml.cpu().numpy()[0], g["jit_lml"]) < 1e-6
+
+
+@pytest.mark.parametrize("tag,noise,tol", [("n1e-2", 1e-2, 1e-9), ("n1e-4", 1e-4, 1e-8)])
+def test_simple3dof_exact_1000pt(eng, tag, noise, tol):
+    """BASELINE config 1 GP: 1000 synthetic residual points, 3 outputs sharing one factor."""
+    g = load_golden("simple3dof_exact.npz")
+    Z = eng.features(0, g["X"], g["U"])
+    np.testing.assert_allclose(Z.cpu().numpy(), g["Z_train"], rtol=2e-15, atol=1e-17)
+    f = eng.ExactFactor(0, np.ones(11), 1.0, noise).fit(Z)
+    m = eng.ExactModelDev(f).fit_targets(g["D"])
+    Zq = eng.features(0, g["Xq"], g["Uq"])
+    mean, var = m.predict(Zq)
+    assert relerr(mean.cpu().numpy(), g[f"{tag}_mean"]) < tol
+    assert relerr(var.cpu().numpy(), g[f"{tag}_var"]) < tol
+    assert relerr(m.lml.cpu().numpy(), g[f"{tag}_lml"]) < 1e-10
+    np.testing.assert_allclose(np.diag(f.L.cpu().numpy())[:1000], g[f"{tag}_Ldiag"], rtol=1e-9)
+    np.testing.assert_allclose(f.L.cpu().numpy()[999, :1000], g[f"{tag}_Lrow999"], rtol=1e-7, atol=1e-12)
+
+
+def test_predict_batch_equals_singles_and_variance_floor(eng):
+    """batch = loop of singles (bitwise: every query row is solved independently), floor 1e-10 * y_std^2."""
+    rng = np.random.default_rng(5)
+    X = rng.normal(size=(300, 11)); Y = rng.normal(size=(300, 3))
+    f = eng.ExactFactor(0, np.ones(11), 1.0, 1e-6).fit(X)
+    m = eng.ExactModelDev(f).fit_targets(Y)
+    Xq = np.vstack([X[:5], rng.normal(size=(200, 11))])
+    mean, var = m.predict(Xq)
+    mean, var = mean.cpu().numpy(), var.cpu().numpy()
+    for i in (0, 3, 77, 204):
+        m1, v1 = m.predict(Xq[i:i + 1])
+        assert np.array_equal(m1.cpu().numpy()[0], mean[i]) and np.array_equal(v1.cpu().numpy()[0], var[i])
+    ystd = m.ystd.cpu().numpy()
+    assert np.all(var >= 1e-10 * ystd**2 * (1 - 1e-15))

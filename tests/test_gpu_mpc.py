@@ -1,0 +1,243 @@
+"""GPU parity: MPC-side kernels through the C-ABI against the oracle (oracle/mpc.py) and the golden vectors the
+real reference assembler / propagator produced (tests/golden/qp_assembly.npz, propagation.npz)."""
+import numpy as np
+import pytest
+
+from conftest import load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def E():
+    from gp_mpc_rocket_landing_b200.gp import engine as ge
+    from gp_mpc_rocket_landing_b200.mpc import engine as me
+    ge.torch_()
+    return ge, me
+
+
+def _dyn(me, dt=0.1):
+    from oracle import mpc as ompc
+    p = ompc.Rocket3DoFParams()
+    return me.make_dyn(p.alpha, p.g_vec, dt), p
+
+
+def _assemble(ge, me, N, X_lin, U_lin, x_init, x_ref, lin_mode=0, rhs_mode=0, c_gp=None):
+    import torch
+    dyn, _ = _dyn(me)
+    qp = me.QPData.reference(N)
+    B = X_lin.shape[0]
+    n, m = me.qp_dims(N)
+    AB = torch.zeros((B, N, 7, 10), dtype=torch.float64, device="cuda")
+    beq = torch.zeros((B, 7 * (N + 1)), dtype=torch.float64, device="cuda")
+    q = torch.zeros((B, n), dtype=torch.float64, device="cuda")
+    me.qp_assemble(dyn, qp, ge.to_dev(X_lin), ge.to_dev(U_lin), ge.to_dev(x_init), ge.to_dev(x_ref), AB, beq, q,
+                   c_gp=None if c_gp is None else ge.to_dev(c_gp), lin_mode=lin_mode, rhs_mode=rhs_mode)
+    return qp, AB, beq, q
+
+
+def test_qp_assembly_matches_reference(E):
+    ge, me = E
+    g = load_golden("qp_assembly.npz")
+    x0, xt = g["x0"], g["xt"]
+    for tag, N, lin in (("fast20", 20, 0), ("fast15", 15, 0), ("fd20", 20, 1)):
+        X_lin = np.array([(1 - k / N) * x0 + (k / N) * xt for k in range(N + 1)])
+        U_lin = np.zeros((N, 3)); U_lin[:, 0] = x0[0] * 1.0
+        x_ref = np.tile(xt, (N + 1, 1))
+        cases = [(X_lin, U_lin, x0, "A", "l", "u"), (g[f"{tag}_Xl"], g[f"{tag}_Ul"], g[f"{tag}_xc"], "A2", "l2", "u2")]
+        for Xl, Ul, xc, kA, kl, ku in cases:
+            qp, AB, beq, q = _assemble(ge, me, N, Xl[None], Ul[None], xc[None], x_ref, lin_mode=lin)
+            A, l, u = me.dense_constraints(N, AB[0].cpu().numpy(), beq[0].cpu().numpy(), qp.lb.cpu().numpy(), qp.ub.cpu().numpy())
+            # matrix entries: same scalar formulas, same |.|>1e-10 filter -> identical pattern, values to 1 ulp
+            assert np.array_equal(A != 0, g[f"{tag}_{kA}"] != 0)
+            np.testing.assert_allclose(A, g[f"{tag}_{kA}"], rtol=3e-16, atol=0)
+            lr = np.maximum(g[f"{tag}_{kl}"], -1e30); ur = np.minimum(g[f"{tag}_{ku}"], 1e30)
+            # right-hand sides c_k = f - A x - B u: 10-term sums in a different association than numpy's matmul
+            np.testing.assert_allclose(l, lr, rtol=0, atol=2e-13)
+            np.testing.assert_allclose(u, ur, rtol=0, atol=2e-13)
+            np.testing.assert_array_equal(q[0].cpu().numpy(), g[f"{tag}_q"])
+        np.testing.assert_array_equal(qp.Pdiag.cpu().numpy(), np.diag(g[f"{tag}_P"]))
+
+
+def _oracle_qp(N, x0, xt, seed=0, perturb=0.0):
+    from oracle import mpc as ompc
+    rng = np.random.default_rng(seed)
+    p = ompc.Rocket3DoFParams()
+    X_lin = np.array([(1 - k / N) * x0 + (k / N) * xt for k in range(N + 1)]) + perturb * rng.normal(size=(N + 1, 7))
+    U_lin = np.zeros((N, 3)); U_lin[:, 0] = x0[0]
+    U_lin += perturb * rng.normal(size=(N, 3))
+    Pd, q = ompc.build_cost(N, np.tile(xt, (N + 1, 1)))
+    A, l, u = ompc.build_constraints(N, X_lin, U_lin, x0, 0.1, p, "analytic")
+    return Pd, q, A, l, u, X_lin, U_lin
+
+
+@pytest.mark.parametrize("max_iter", [50, 4000])
+def test_admm_matches_osqp_restatement(E, max_iter):
+    """Same algorithm, different linear algebra (block-tridiagonal reduced KKT vs dense LU): statuses, iteration
+    counts and rho histories must agree, iterates to ~1e-7 relative."""
+    import torch
+    from oracle import mpc as ompc
+    ge, me = E
+    N = 20
+    cfg = ompc.SimConfig()
+    x0s = np.stack([ompc.sample_initial_condition(42 + i, cfg) for i in range(6)])
+    x0s = np.vstack([x0s, [[2.0, 500, 50, 0, -75, 10, 0]]])  # README x0: violates the velocity box -> infeasible
+    B = x0s.shape[0]
+    xts = np.zeros_like(x0s); xts[:, 0] = x0s[:, 0]
+    Xl = np.zeros((B, N + 1, 7)); Ul = np.zeros((B, N, 3)); ref = []
+    for b in range(B):
+        Pd, q, A, l, u, Xl[b], Ul[b] = _oracle_qp(N, x0s[b], xts[b], seed=b, perturb=0.01)
+        s = ompc.OSQPSettings(max_iter=max_iter)
+        ref.append((Pd, q, A, l, u, ompc.OSQPOracle(Pd, q, A, l, u, s).solve()))
+    x_ref = np.stack([np.tile(xts[b], (N + 1, 1)) for b in range(B)])
+    qp, AB, beq, q = _assemble(ge, me, N, Xl, Ul, x0s, x_ref)
+    ws = me.AdmmWorkspace(B, N)
+    S = me.AdmmSettings.reference_defaults(max_iter=max_iter)
+    me.admm_solve(qp, AB, beq, q, S, ws)
+    torch.cuda.synchronize()
+    st, it = ws.status.cpu().numpy(), ws.iters.cpu().numpy()
+    x, y, rho = ws.x.cpu().numpy(), ws.y.cpu().numpy(), ws.rho.cpu().numpy()
+    for b in range(B):
+        r = ref[b][5]
+        assert st[b] == r.status, (b, st[b], r.status)
+        assert it[b] == r.iters, (b, it[b], r.iters)
+        assert rho[b] == pytest.approx(r.rho, rel=1e-6)
+        scale = max(1.0, np.max(np.abs(r.x)))
+        assert np.max(np.abs(x[b] - r.x)) < 1e-6 * scale
+        assert np.max(np.abs(y[b] - r.y)) < 1e-6 * max(1.0, np.max(np.abs(r.y)))
+        assert ws.obj[b].item() == pytest.approx(r.obj_val, rel=1e-6, abs=1e-6)
+    if max_iter == 4000:
+        assert (st[:6] == 1).all() and st[6] in (-3, 3)
+        # independent check: u0 within OSQP tolerance of the exact KKT solution on the identified active set
+        for b in range(6):
+            Pd, qv, A, l, u, r = ref[b]
+            xs, lo, up, _ = ompc.kkt_active_set_solve(Pd, qv, A, np.maximum(l, -1e30), np.minimum(u, 1e30), x[b], y[b])
+            tol = 1e-4 + 1e-4 * np.max(np.abs(xs))
+            assert np.max(np.abs(x[b][7:10] - xs[7:10])) < 10 * tol
+            # same active set as the CPU restatement (identified from the multipliers, OSQP convention:
+            # y < 0 lower bound active, y > 0 upper bound active)
+            ytol = 1e-6 * max(1.0, np.max(np.abs(r.y)))
+            assert np.array_equal(y[b] < -ytol, r.y < -ytol) and np.array_equal(y[b] > ytol, r.y > ytol)
+            ineq = ~((u - l) < 1e-9)
+            assert np.array_equal((y[b] < -ytol) & ineq, lo & ineq) and np.array_equal((y[b] > ytol) & ineq, up & ineq)
+
+
+def test_admm_warm_start_and_inactive(E):
+    """x/y/rho persist across solves like the OSQP object does (osqp_rti.py:522-527); inactive scenarios are
+    untouched."""
+    import torch
+    from oracle import mpc as ompc
+    ge, me = E
+    N = 15
+    x0 = np.array([2.0, 30.0, 1.0, -2.0, -3.0, 0.2, 0.1]); xt = np.array([2.0, 0, 0, 0, 0, 0, 0.0])
+    Pd, q, A, l, u, Xl, Ul = _oracle_qp(N, x0, xt)
+    s = ompc.OSQPSettings(max_iter=200)
+    o = ompc.OSQPOracle(Pd, q, A, l, u, s)
+    r1 = o.solve()
+    o.warm_start(x=r1.x)
+    r2 = o.solve()
+    qp, AB, beq, qd = _assemble(ge, me, N, np.stack([Xl, Xl]), np.stack([Ul, Ul]), np.stack([x0, x0]), np.tile(xt, (N + 1, 1)))
+    ws = me.AdmmWorkspace(2, N)
+    S = me.AdmmSettings.reference_defaults(max_iter=200)
+    me.admm_solve(qp, AB, beq, qd, S, ws)
+    assert ws.iters.cpu().tolist() == [r1.iters, r1.iters]
+    S2 = me.AdmmSettings.reference_defaults(max_iter=200, warm_x=1, warm_y=1, rho_from_input=1)
+    active = torch.tensor([1, 0], dtype=torch.int32, device="cuda")
+    x_before = ws.x.clone()
+    me.admm_solve(qp, AB, beq, qd, S2, ws, active=active)
+    assert ws.iters[0].item() == r2.iters and ws.status[0].item() == r2.status
+    assert np.max(np.abs(ws.x[0].cpu().numpy() - r2.x)) < 1e-6 * max(1, np.max(np.abs(r2.x)))
+    assert torch.equal(ws.x[1], x_before[1])
+
+
+def test_rollout_and_propagation_match_reference(E):
+    """gp_mpc.py:277-281 rollout + uncertainty_prop.py:117-177 against the golden output of the reference's own
+    UncertaintyPropagator (14-state embedding) and the oracle."""
+    import torch
+    from oracle import gp as ogp, mpc as ompc
+    ge, me = E
+    g = load_golden("propagation.npz")
+    dyn, p = _dyn(me)
+    Z = ge.features(0, g["X"], g["U"])
+    f = ge.ExactFactor(0, np.ones(11), 1.0, float(g["noise"])).fit(Z)
+    model = ge.ExactModelDev(f).fit_targets(g["D"])
+    N = g["Useq"].shape[0]
+    rng = np.random.default_rng(0)
+    B = 9
+    x0 = np.tile(g["x0"], (B, 1)); U = np.tile(g["Useq"], (B, 1, 1))
+    x0[1:] += 0.05 * rng.normal(size=(B - 1, 7)); U[1:] += 0.05 * rng.normal(size=(B - 1, N, 3))
+    X = torch.zeros((B, N + 1, 7), dtype=torch.float64, device="cuda")
+    dmean = torch.zeros((B, N, 3), dtype=torch.float64, device="cuda")
+    q_pad = ge.pad_to(B * N, 128)
+    Ks = torch.zeros((q_pad, f.n_pad), dtype=torch.float64, device="cuda")
+    ms = model.struct()
+    me.rollout(ms, dyn, ge.to_dev(x0), ge.to_dev(U), X, dmean, Ks)
+    sumsq = f.sumsq_inplace(Ks)
+    dvar = torch.zeros((q_pad, 3), dtype=torch.float64, device="cuda")
+    ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, B * N, 3, f.sv, 1e-10, ge.ptr(model.ystd), ge.ptr(dvar), 3, 0, ge.stream())
+    covs = torch.zeros((B, N + 1, 7, 7), dtype=torch.float64, device="cuda")
+    me.propagate_cov(dyn, X, ge.to_dev(U), dvar[: B * N].contiguous(), covs)
+    Xh, covh = X.cpu().numpy(), covs.cpu().numpy()
+    np.testing.assert_allclose(Xh[0], g["means"], rtol=1e-9, atol=1e-11)
+    np.testing.assert_allclose(covh[0], g["covs"], rtol=1e-8, atol=1e-18)
+    o = ogp.Simple3DoFGPOracle(noise_variance=float(g["noise"]))
+    o.add_data(g["X"], g["U"], g["D"]); o.fit()
+    for b in (1, 5, 8):
+        means, cv, dm, dv = ompc.propagate_linear(x0[b], U[b], np.eye(7) * 1e-6, 0.1, p, o.predict)
+        np.testing.assert_allclose(Xh[b], means, rtol=1e-9, atol=1e-11)
+        np.testing.assert_allclose(covh[b], cv, rtol=1e-8, atol=1e-18)
+        np.testing.assert_allclose(dmean[b].cpu().numpy(), dm, rtol=1e-8, atol=1e-11)
+        np.testing.assert_allclose(dvar[b * N:(b + 1) * N].cpu().numpy(), dv, rtol=1e-8)
+    # nominal rollout (no model) = plain Euler steps
+    Xn = torch.zeros_like(X)
+    me.rollout(None, dyn, ge.to_dev(x0), ge.to_dev(U), Xn)
+    xs = x0[3].copy()
+    for k in range(N):
+        xs = ompc.step_3dof(xs, U[3, k], 0.1, p)
+    np.testing.assert_allclose(Xn[3, N].cpu().numpy(), xs, rtol=1e-15, atol=1e-15)
+
+
+def test_mpc_update_semantics(E):
+    """mode 1: gp_mpc.py:336-345 (+ :478-482 failure -> nominal, which 'converges' with cost=inf);
+    mode 0: osqp_rti.py:532-552 (accept + shift, or keep everything)."""
+    import torch
+    ge, me = E
+    N = 5
+    n, _ = me.qp_dims(N)
+    qp = me.QPData.reference(N)
+    rng = np.random.default_rng(1)
+    B = 4
+    X = rng.normal(size=(B, N + 1, 7)); U = rng.normal(size=(B, N, 3))
+    z = np.zeros((B, n))
+    for b in range(B):
+        for k in range(N):
+            z[b, k * 10:k * 10 + 7] = X[b, k]; z[b, k * 10 + 7:k * 10 + 10] = U[b, k]
+        z[b, N * 10:] = X[b, N]
+    z[1] += 1e-5; z[2] += 1e-3
+    status = np.array([1, 1, 1, -2], dtype=np.int32)
+    x_ref = np.zeros((N + 1, 7))
+    t = lambda a, dt=None: ge.to_dev(a, dt)
+    Xd, Ud = t(X), t(U)
+    Xp, Up = torch.zeros_like(Xd), torch.zeros_like(Ud)
+    cost = torch.zeros(B, dtype=torch.float64, device="cuda")
+    conv = torch.zeros(B, dtype=torch.int32, device="cuda"); act = torch.ones(B, dtype=torch.int32, device="cuda")
+    nit = torch.zeros(B, dtype=torch.int32, device="cuda")
+    me.mpc_update(qp, 1, t(z), t(status, torch.int32), t(x_ref), Xd, Ud, Xp, Up, cost, conv, act, nit)
+    assert conv.cpu().tolist() == [1, 1, 0, 1] and act.cpu().tolist() == [0, 0, 1, 0] and nit.cpu().tolist() == [1] * 4
+    c = cost.cpu().numpy()
+    assert np.isinf(c[3]) and np.isfinite(c[:3]).all()
+    Xn, Un = z[0][: N * 10].reshape(N, 10)[:, :7], z[0][: N * 10].reshape(N, 10)[:, 7:]
+    expect = np.sum(me.Q_DIAG * Xn**2) + np.sum(me.R_DIAG * Un**2) + np.sum(me.QF_DIAG * z[0][N * 10:] ** 2)
+    assert c[0] == pytest.approx(expect, rel=1e-13)
+    np.testing.assert_allclose(Xd[2].cpu().numpy(), X[2] + 1e-3, rtol=0, atol=1e-15)
+    np.testing.assert_array_equal(Xd[3].cpu().numpy(), X[3])
+    # shifted warm start of a solved scenario
+    np.testing.assert_array_equal(Xp[2, :-1].cpu().numpy(), Xd[2, 1:].cpu().numpy())
+    np.testing.assert_array_equal(Xp[2, -1].cpu().numpy(), Xd[2, -1].cpu().numpy())
+    np.testing.assert_array_equal(Up[2, :-1].cpu().numpy(), Ud[2, 1:].cpu().numpy())
+    np.testing.assert_array_equal(Up[2, -1].cpu().numpy(), Ud[2, -1].cpu().numpy())
+    # mode 0: failure keeps X, U, X_prev
+    Xd2, Xp2 = t(X), t(X * 2)
+    me.mpc_update(qp, 0, t(z), t(status, torch.int32), t(x_ref), Xd2, t(U), Xp2, t(U), cost, conv, None, None)
+    assert conv.cpu().tolist() == [1, 1, 1, 0]
+    np.testing.assert_array_equal(Xd2[3].cpu().numpy(), X[3]); np.testing.assert_array_equal(Xp2[3].cpu().numpy(), 2 * X[3])
