@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py -- GP-MPC solves/sec (3-DoF, N=20, 1000-point exact GP, B=4096 scenarios per GPU) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--batch B] [--sqp-iters S]
+
+A "step" is one closed-loop control step of the Monte Carlo batch: `GPMPC.solve_batch` for every local scenario
+(GP rollout + GP variance + covariance propagation + S x (QP assembly + ADMM + update)), the plant step and the
+termination / respawn bookkeeping.  A "solve" is one scenario x one control step.  `value` is timed with the scenario
+states resident in HBM; `e2e` repeats the loop through the public numpy API (host buffers in, host results out).
+`--impl reference` times the CPU restatement of the same path (oracle/, the reference's algorithm on numpy/scipy --
+the reference's own GPMPC cannot run: CasADi/IPOPT/simdyn are absent) on all host cores.
+See DESIGN.md "Measurement" for the roofline arithmetic.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
+METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=4096, help="scenarios per GPU (weak scaling)")
+    ap.add_argument("--sqp-iters", type=int, default=1, help="SQP iterations per solve (1 = RTI; reference loop: 10)")
+    ap.add_argument("--qp-max-iter", type=int, default=1000)
+    ap.add_argument("--cpu-scenarios", type=int, default=0, help="reference arm: scenarios per step (default: #cores)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ====================================================================================================== CPU baseline
+def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
+    """One host process = one scenario in closed loop on the oracle (numpy/scipy restatement of the reference path)."""
+    from threadpoolctl import threadpool_limits
+    threadpool_limits(1)   # one BLAS thread per process: the parallelism is one process per scenario
+    from gp_mpc_rocket_landing_b200 import workloads
+    from oracle import gp as ogp, mpc as ompc
+    gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
+    gp.X, gp.U, gp.D, gp.fits = fits_blob
+    ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
+                           max_sqp_iter=sqp_iters)
+    X0, XT = workloads.sample_initial_conditions(idx, 1)
+    x, xt = X0[0], XT[0]
+    p = ompc.Rocket3DoFParams()
+
+    def one():
+        nonlocal x
+        r = ctl.solve(x, xt)
+        x = ompc.step_3dof(x, r.U_opt[0], DT, p)
+
+    for _ in range(warmup):
+        one()
+    conn.send("ready")
+    conn.recv()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    conn.send(time.perf_counter() - t0)
+    conn.close()
+
+
+def cpu_reference_run(n_scen, warmup, steps, sqp_iters, qp_max_iter):
+    """Closed loop of `n_scen` scenarios, one process each (scenarios are independent), `steps` control steps.
+    Returns (solves/s, wall seconds, cores used)."""
+    import multiprocessing as mp
+    from gp_mpc_rocket_landing_b200 import workloads
+    from oracle import gp as ogp
+    X, U, D = workloads.residual_dataset(N_TRAIN, seed=0)
+    gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
+    gp.add_data(X, U, D)
+    gp.fit()
+    blob = (gp.X, gp.U, gp.D, gp.fits)
+    ctx = mp.get_context("fork")
+    procs = []
+    for i in range(n_scen):
+        a, b = ctx.Pipe()
+        pr = ctx.Process(target=_cpu_worker, args=(i, b, blob, warmup, steps, sqp_iters, qp_max_iter))
+        pr.start()
+        procs.append((pr, a))
+    for _, a in procs:
+        a.recv()
+    t0 = time.perf_counter()
+    for _, a in procs:
+        a.send("go")
+    for _, a in procs:
+        a.recv()
+    wall = time.perf_counter() - t0
+    for pr, _ in procs:
+        pr.join()
+    return n_scen * steps / wall, wall, n_scen
+
+
+def config_dict(args, world):
+    return {"workload": "BASELINE configs[1]: 3-DoF GP-MPC Monte Carlo batch, perturbed initial states "
+                        "(sample_initial_condition seed 42+i), closed loop with respawn",
+            "scenarios_per_gpu": args.batch, "scenarios_total": args.batch * world, "horizon_N": N_HORIZON, "dt": DT,
+            "gp": f"Simple3DoFGP exact, n={N_TRAIN} synthetic residual points, SE-ARD, noise {NOISE}",
+            "sqp_iters_per_solve": args.sqp_iters, "qp": f"OSQP-form QP n=207 m=354, ADMM max_iter {args.qp_max_iter}, "
+            "eps 1e-4, warm start", "parallelism": f"scenario sharding x{world} (no data-path collective)",
+            "l2": "working set per step (K* rows 0.67 GB + QP state) exceeds the 126 MB L2; no explicit flush"}
+
+
+def run_reference_arm(args):
+    """`--impl reference`: the CPU restatement of the path on all host cores; rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_scen = args.cpu_scenarios or max(1, min(cores, 64))
+    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 3))
+    # bound the run: one oracle solve costs ~0.3-1 s; keep the whole arm within a few minutes
+    steps = min(steps, 20)
+    sps, wall, used = cpu_reference_run(n_scen, warmup, steps, args.sqp_iters, args.qp_max_iter)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": sps, "unit": "solves/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": wall / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config_dict(args, args.gpus),
+        "cpu_baseline": {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
+                         "sample": f"{n_scen} scenarios x {steps} closed-loop control steps, one process per scenario "
+                                   "(numpy/scipy oracle of the reference algorithm; the reference's own GPMPC needs "
+                                   "CasADi/IPOPT/simdyn, absent)"},
+        "e2e": {"value": sps, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ====================================================================================================== clocks
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return None
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in open(self.path).read().splitlines():
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.path)
+        if not sm:
+            return None
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ====================================================================================================== GPU arm
+def fp64_peak_tflops(torch):
+    """cuBLAS DGEMM 8192^3 (best of 5): the FP64 tensor ceiling for the DMMA kernels.  MEASURED_PEAKS.json holds only
+    HBM GB/s and bf16 TF/s, so the FP64 denominator is measured here, in the same run."""
+    n = 8192
+    a = torch.randn((n, n), dtype=torch.float64, device="cuda")
+    b = torch.randn((n, n), dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    best = 1e9
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, b); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del a, b
+    return 2.0 * n**3 / (best * 1e-3) / 1e12
+
+
+def build_problem(args, rank):
+    from gp_mpc_rocket_landing_b200 import workloads
+    from gp_mpc_rocket_landing_b200.dynamics import Rocket3DoFDynamics
+    from gp_mpc_rocket_landing_b200.gp import Simple3DoFGP
+    from gp_mpc_rocket_landing_b200.monte_carlo import BatchedMonteCarlo
+    from gp_mpc_rocket_landing_b200.mpc import GPMPC, GPMPCConfig
+    X, U, D = workloads.residual_dataset(N_TRAIN, seed=0)
+    gp = Simple3DoFGP(noise_variance=NOISE, use_sparse=False)
+    gp.add_data(X, U, D)
+    gp.fit()
+    dyn = Rocket3DoFDynamics()
+    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter)
+    ctl = GPMPC(dyn, gp, cfg)
+    ctl.setup()
+    mc = BatchedMonteCarlo(dyn, ctl, drag_cda=0.25, respawn=True)
+    mc.reset(first=rank * args.batch, count=args.batch, seed=42)
+    return dyn, gp, ctl, mc
+
+
+def run_b200_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # before CUDA is initialised in this process (the workers are forked)
+        cores = os.cpu_count() or 1
+        n_scen = max(1, min(cores, 32))
+        sps, wall, used = cpu_reference_run(n_scen, 1, 6, args.sqp_iters, args.qp_max_iter)
+        cpu_base = {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
+                    "sample": f"{n_scen} scenarios x 6 closed-loop control steps of the same workload, one process per "
+                              f"scenario, {wall:.1f} s wall (numpy/scipy oracle of the reference algorithm)"}
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from gp_mpc_rocket_landing_b200.mpc import engine as me
+    dyn, gp, ctl, mc = build_problem(args, rank)
+    B, K, W = args.batch, args.steps, max(args.warmup, 3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident loop ---------------------------------------------------------------------------------
+    for _ in range(W):
+        mc.step()
+    peak64 = fp64_peak_tflops(torch) if rank == 0 else None
+    ctl.timers = me.PhaseTimers()
+    clocks = ClockSampler(local)
+    qp_it, launches = 0.0, 0
+    barrier()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        sol = mc.step()
+        launches += ctl.last_kernel_launches + 1
+        qp_it += float(sol.qp_iterations.sum().item())
+    e1.record()
+    barrier()
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1)
+    phases = ctl.timers.totals()
+    ctl.timers = None
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * B * K / (ms * 1e-3)
+    stats = mc.counts.clone()
+    if world > 1:   # per-step statistics gather (the only collective of the path; tens of bytes)
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+
+    # ---- end-to-end loop through the public numpy API ------------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        from gp_mpc_rocket_landing_b200 import workloads
+        X0, XT = workloads.sample_initial_conditions(rank * B, B)
+        ctl.reset_warm_start()
+        x = X0.copy()
+        Ke = min(K, 40)
+        for _ in range(W):
+            s = ctl.solve_batch(x, XT)
+            x = dyn.step_batch(x, s.u0, DT)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(Ke):
+            s = ctl.solve_batch(x, XT)          # H2D: x, XT ; D2H: u0, X_opt, U_opt, cost, flags
+            x = dyn.step_batch(x, s.u0, DT)     # H2D: x, u0 ; D2H: x_next
+        barrier()
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        h2d = B * (7 + 7 + 7 + 3) * 8
+        d2h = B * ((N_HORIZON + 1) * 7 + N_HORIZON * 3 + 1) * 8 + B * (4 + 1 + 1 + 4 + 4) + B * 7 * 8
+        e2e = {"value": world * B * Ke / float(te.item()), "unit": "solves/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": Ke, "timer": "host wall clock around synchronised steps"}
+
+    if rank == 0:
+        # ---- roofline of the dominant phase -------------------------------------------------------------------
+        share = {k: v[0] / ms for k, v in phases.items()}
+        dom = max(phases, key=lambda k: phases[k][0])
+        Q = B * N_HORIZON
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:  # noqa: BLE001
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        tot, cnt = phases[dom]
+        avg_s = tot / cnt * 1e-3
+        if dom in ("gp_variance",):
+            flops = Q * float(N_TRAIN) ** 2          # n^2 per query (L^-1 k* : n^2/2 FMA), SURVEY 8(d)
+            roof = {"kernel": "gp_variance (blocked DMMA TRSM + fused sum of squares, dgemm_nt_kernel)",
+                    "bound": "tensor", "achieved": flops / avg_s / 1e12, "peak": peak64, "unit": "TFLOP/s",
+                    "peak_source": "cuBLAS DGEMM 8192^3 FP64 measured in this run (FP64 is not in MEASURED_PEAKS.json)",
+                    "traffic": None}
+        else:
+            per_qp = 22e3 if dom == "admm" else 33e3
+            byts = B * per_qp
+            roof = {"kernel": dom, "bound": "hbm", "achieved": byts / avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                    "note": "compulsory bytes only; the ADMM kernel is dependency-chain bound, not HBM bound "
+                            "(DESIGN.md)", "traffic": None}
+        roof["frac"] = roof["achieved"] / roof["peak"] if roof["peak"] else None
+        roof["avg_launch_ms"] = avg_s * 1e3
+        line = {
+            "metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config_dict(args, world), "e2e": e2e, "gpu_launches": launches,
+            "roofline": roof, "cpu_baseline": cpu_base, "clocks": clk,
+            "phases_share_of_step": share, "phase_ms_per_step": {k: v[0] / K for k, v in phases.items()},
+            "mean_admm_iters_per_solve": qp_it / (B * K), "p50_step_latency_ms": ms / K,
+            "fp64_peak_tflops_measured": peak64,
+            "outcomes": {n: int(stats[i].item()) for i, n in enumerate(
+                ("", "success", "crash", "fuel_exhausted", "constraint_violation", "timeout", "divergence")) if n},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference_arm(a)
+    else:
+        run_b200_arm(a)

@@ -4,8 +4,7 @@ shiivashaakeri/gp-mpc-rocket-landing, batched over Monte Carlo descent scenarios
 Sub-packages mirror the reference's module layout for the hot path:
   gp   <- src/gp   (kernels, exact / sparse / fast GP, features, Simple3DoFGP / StructuredRocketGP)
   mpc  <- src/mpc  (OSQPRTIMPC, GPMPC, NominalMPC3DoF, uncertainty propagation, configs) + solve_batch / step_batch
-All numerics run in libgpmpc_b200.so (include/gpmpc_b200.h); there is no CPU fallback.
+All numerics run in libgpmpc_b200.so (include/gpmpc_b200.h); there is no CPU fallback: importing `gp` or `mpc`
+fails loudly when the library has not been built (`python -m gp_mpc_rocket_landing_b200.build`).
 """
-from . import _lib  # noqa: F401  (fails loudly when the CUDA library is missing)
-
 __version__ = "0.1.0"

@@ -581,7 +581,8 @@ __global__ void __launch_bounds__(ADMM_THREADS) admm_kernel(int N, int nbatch, c
   for (int j = tid; j < n; j += ADMM_THREADS) ob[0] += (0.5 * P.Pb[j] * P.x[j] + P.qb[j]) * P.x[j];
   block_reduce<1, false>(ob, P.red);
   for (int j = tid; j < n; j += ADMM_THREADS) xg[(size_t)b * n + j] = P.D[j] * P.x[j];
-  for (int r = tid; r < m; r += ADMM_THREADS) yg[(size_t)b * m + r] = P.E[r] * P.y[r] / P.c;
+  if (!S.commit_y_solved_only || status == GPMPC_QP_SOLVED)
+    for (int r = tid; r < m; r += ADMM_THREADS) yg[(size_t)b * m + r] = P.E[r] * P.y[r] / P.c;
   if (tid == 0) {
     status_g[b] = status;
     iters_g[b] = it;

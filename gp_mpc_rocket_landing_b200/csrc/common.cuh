@@ -72,10 +72,11 @@ __device__ __forceinline__ double numpy_pairwise_sum_small(const double* a, int 
 }
 
 // Covariance function value from the scaled squared distance (reference kernels.py:238-262 SE-ARD, :532-545 Matern32,
-// :625-638 Matern52), same operation order as the numpy expressions.  kind: 0 SE, 1 Matern-3/2, 2 Matern-5/2.
+// :625-638 Matern52), same operation order as the numpy expressions.  kind: 0 SE, 1 Matern-3/2, 2 Matern-5/2, 3 = the distance.
 __device__ __forceinline__ double kernel_value(int kind, double d2, double sv) {
   d2 = fmax(d2, 0.0);
   if (kind == 0) return sv * exp(-0.5 * d2);
+  if (kind == 3) return d2;  // clamped scaled squared distance itself (isotropic SE, kernels.py:417-421)
   const double r = sqrt(d2);
   if (kind == 1) {
     const double s = 1.7320508075688772 * r;  // np.sqrt(3)

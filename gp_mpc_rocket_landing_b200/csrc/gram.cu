@@ -118,7 +118,7 @@ static int launch_gram(int mode, int kind, const double* Xs1, const double* sq1,
                        cudaStream_t stream) {
   GPMPC_REQUIRE(n1_pad % 128 == 0 && n2_pad % 128 == 0, "gpmpc_gram: padded sizes must be multiples of 128");
   GPMPC_REQUIRE(DP % 4 == 0 && DP >= 4 && DP <= 64 && (ldk & 1) == 0, "gpmpc_gram: DP%4==0, 4<=DP<=64, even ldk");
-  GPMPC_REQUIRE(kind >= 0 && kind <= 2, "gpmpc_gram: unknown kernel kind");
+  GPMPC_REQUIRE(kind >= 0 && kind <= 3, "gpmpc_gram: unknown kernel kind");
   if (n1_pad == 0 || n2_pad == 0) return GPMPC_OK;
   const int pitch = ((DP + 15) / 16) * 16 + 4;
   size_t smem = sizeof(double) * 2 * 128 * pitch;

@@ -76,7 +76,67 @@ __device__ __forceinline__ void jac3_fd(const double* x, const double* u, const 
 constexpr int ROLL_WARPS = 8;
 constexpr int MAXP = 6, MAXDP = 64;
 
+// GP posterior means of one (x,u) query evaluated by one warp: features (features.py:403-444), scaling and row norm
+// (kernels.py:223-229), cross-covariance row against the n training points (each lane n/32 of them, written as one
+// coalesced row of Ks when requested) and the P means accumulated on the fly (exact_gp.py:237-245).
 template <int DP_T>  // DP_T > 0: compile-time padded feature dimension (registers); 0: runtime (shared memory)
+__device__ __forceinline__ void gp_query_warp(const GpmpcExactModel& M, const double* x, const double* u, double* zs,
+                                              int lane, double* __restrict__ ks_row, double* dm) {
+  const int DP = DP_T > 0 ? DP_T : M.DP;
+  double z[11], sqv[11];
+  features_3dof_dev(x, u, z);
+#pragma unroll
+  for (int d = 0; d < 11; ++d) {
+    z[d] = z[d] / M.lengthscales[d];
+    sqv[d] = z[d] * z[d];
+  }
+  const double sqz = numpy_pairwise_sum_small(sqv, 11);
+  __syncwarp();
+  if (lane == 0) {
+#pragma unroll
+    for (int d = 0; d < 11; ++d) zs[d] = z[d];
+    for (int d = 11; d < DP; ++d) zs[d] = 0.0;
+  }
+  __syncwarp();
+  double zr[DP_T > 0 ? DP_T : 1];
+  if (DP_T > 0) {
+#pragma unroll
+    for (int d = 0; d < DP_T; ++d) zr[d] = zs[d];
+  }
+  double acc[MAXP];
+#pragma unroll
+  for (int p = 0; p < MAXP; ++p) acc[p] = 0.0;
+  for (int j = lane; j < M.n_pad; j += 32) {
+    double kv = 0.0;
+    if (j < M.n) {
+      const double* xr = M.Xs + (long)j * DP;
+      double dot = 0.0;
+      if (DP_T > 0) {
+#pragma unroll
+        for (int d = 0; d < DP_T; d += 4) {
+          const double4 t = *reinterpret_cast<const double4*>(xr + d);
+          dot = fma(zr[d], t.x, dot);
+          dot = fma(zr[d + 1], t.y, dot);
+          dot = fma(zr[d + 2], t.z, dot);
+          dot = fma(zr[d + 3], t.w, dot);
+        }
+      } else {
+        for (int d = 0; d < DP; ++d) dot = fma(zs[d], __ldg(xr + d), dot);
+      }
+      const double d2 = (sqz + __ldg(M.sq + j)) - 2.0 * dot;
+      kv = kernel_value(M.kind, d2, M.signal_var);
+#pragma unroll
+      for (int p = 0; p < MAXP; ++p)
+        if (p < M.P) acc[p] = fma(kv, __ldg(M.alpha + (long)p * M.n_pad + j), acc[p]);
+    }
+    if (ks_row) ks_row[j] = kv;
+  }
+#pragma unroll
+  for (int p = 0; p < MAXP; ++p)
+    if (p < M.P) dm[p] = warp_sum(acc[p]) * M.ystd[p] + M.ymean[p];  // exact_gp.py:240-245
+}
+
+template <int DP_T>
 __global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactModel M, int has_model, GpmpcDyn3 dyn,
                                                                    int nbatch, int N, const double* __restrict__ x0,
                                                                    const double* __restrict__ U,
@@ -88,7 +148,6 @@ __global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactMod
   const int b = blockIdx.x * ROLL_WARPS + warp;
   if (b >= nbatch) return;
   const bool act = (active == nullptr) || active[b] != 0;
-  const int DP = DP_T > 0 ? DP_T : M.DP;
   double* zs = zs_sm[warp];
   double x[NX], xn[NX], u[NU];
 #pragma unroll
@@ -106,60 +165,7 @@ __global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactMod
     double dm[MAXP];
 #pragma unroll
     for (int p = 0; p < MAXP; ++p) dm[p] = 0.0;
-    if (has_model) {
-      // features (features.py:403-444), scaling and row norm (kernels.py:223-229)
-      double z[11], sqv[11];
-      features_3dof_dev(x, u, z);
-#pragma unroll
-      for (int d = 0; d < 11; ++d) {
-        z[d] = z[d] / M.lengthscales[d];
-        sqv[d] = z[d] * z[d];
-      }
-      const double sqz = numpy_pairwise_sum_small(sqv, 11);
-      __syncwarp();
-      if (lane == 0) {
-#pragma unroll
-        for (int d = 0; d < 11; ++d) zs[d] = z[d];
-        for (int d = 11; d < DP; ++d) zs[d] = 0.0;
-      }
-      __syncwarp();
-      double zr[DP_T > 0 ? DP_T : 1];
-      if (DP_T > 0) {
-#pragma unroll
-        for (int d = 0; d < DP_T; ++d) zr[d] = zs[d];
-      }
-      double acc[MAXP];
-#pragma unroll
-      for (int p = 0; p < MAXP; ++p) acc[p] = 0.0;
-      for (int j = lane; j < M.n_pad; j += 32) {
-        double kv = 0.0;
-        if (j < M.n) {
-          const double* xr = M.Xs + (long)j * DP;
-          double dot = 0.0;
-          if (DP_T > 0) {
-#pragma unroll
-            for (int d = 0; d < DP_T; d += 4) {
-              const double4 t = *reinterpret_cast<const double4*>(xr + d);
-              dot = fma(zr[d], t.x, dot);
-              dot = fma(zr[d + 1], t.y, dot);
-              dot = fma(zr[d + 2], t.z, dot);
-              dot = fma(zr[d + 3], t.w, dot);
-            }
-          } else {
-            for (int d = 0; d < DP; ++d) dot = fma(zs[d], __ldg(xr + d), dot);
-          }
-          const double d2 = (sqz + __ldg(M.sq + j)) - 2.0 * dot;
-          kv = kernel_value(M.kind, d2, M.signal_var);
-#pragma unroll
-          for (int p = 0; p < MAXP; ++p)
-            if (p < M.P) acc[p] = fma(kv, __ldg(M.alpha + (long)p * M.n_pad + j), acc[p]);
-        }
-        if (Ks) Ks[row * ldk + j] = kv;
-      }
-#pragma unroll
-      for (int p = 0; p < MAXP; ++p)
-        if (p < M.P) dm[p] = warp_sum(acc[p]) * M.ystd[p] + M.ymean[p];  // exact_gp.py:240-245
-    }
+    if (has_model) gp_query_warp<DP_T>(M, x, u, zs, lane, Ks ? Ks + row * ldk : nullptr, dm);
     step3(x, u, dyn, xn);
 #pragma unroll
     for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dm[i] * dyn.dt;  // gp_mpc.py:165-167
@@ -168,6 +174,49 @@ __global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactMod
 #pragma unroll
     for (int d = 0; d < NX; ++d) x[d] = xn[d];
   }
+}
+
+// GP means at given trajectory points (X[b,k], U[b,k]), k < N: the affine terms c_k of one SQP iteration
+// (gp_mpc.py:309-317).  One warp per point.
+template <int DP_T>
+__global__ void __launch_bounds__(ROLL_WARPS * 32) gp_points3_kernel(GpmpcExactModel M, int nbatch, int N,
+                                                                     const double* __restrict__ X,
+                                                                     const double* __restrict__ U,
+                                                                     double* __restrict__ dmean,
+                                                                     double* __restrict__ Ks, long ldk,
+                                                                     const int* __restrict__ active) {
+  __shared__ double zs_sm[ROLL_WARPS][MAXDP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long pt = (long)blockIdx.x * ROLL_WARPS + warp;
+  if (pt >= (long)nbatch * N) return;
+  const int b = (int)(pt / N), k = (int)(pt - (long)b * N);
+  if (active && !active[b]) {
+    if (Ks)
+      for (int j = lane; j < M.n_pad; j += 32) Ks[pt * ldk + j] = 0.0;
+    return;
+  }
+  double x[NX], u[NU], dm[MAXP];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) x[d] = X[((long)b * (N + 1) + k) * NX + d];
+#pragma unroll
+  for (int d = 0; d < NU; ++d) u[d] = U[pt * NU + d];
+#pragma unroll
+  for (int p = 0; p < MAXP; ++p) dm[p] = 0.0;
+  gp_query_warp<DP_T>(M, x, u, zs_sm[warp], lane, Ks ? Ks + pt * ldk : nullptr, dm);
+  if (lane < 3) dmean[pt * 3 + lane] = dm[lane];
+}
+
+// z = [x_0,u_0,...,x_N] from (X, U): osqp_rti.py:601-614 (_solution_to_vector), the primal warm start.
+__global__ void __launch_bounds__(256) pack_traj3_kernel(int nbatch, int N, const double* __restrict__ X,
+                                                         const double* __restrict__ U, double* __restrict__ z,
+                                                         const int* __restrict__ active) {
+  const int n = N * NS + NX;
+  const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long)nbatch * n) return;
+  const int b = (int)(idx / n), j = (int)(idx - (long)b * n);
+  if (active && !active[b]) return;
+  const int k = j / NS, i = j - k * NS;
+  z[idx] = (i < NX) ? X[((long)b * (N + 1) + k) * NX + i] : U[((long)b * N + k) * NU + (i - NX)];
 }
 
 // ------------------------------------------------------------------------------------------------ covariance
@@ -304,6 +353,87 @@ __global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nb
   }
 }
 
+// Discrete Jacobians at a list of points (dynamics.linearize protocol: osqp_rti.py:374-401 / :656-710), unfiltered.
+__global__ void __launch_bounds__(128) linearize3_kernel(GpmpcDyn3 dyn, int npts, int lin_mode,
+                                                         const double* __restrict__ X, const double* __restrict__ U,
+                                                         double* __restrict__ AB) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npts) return;
+  double x[NX], u[NU], A[NX][NX], Bm[NX][NU];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) x[d] = X[(long)i * NX + d];
+#pragma unroll
+  for (int d = 0; d < NU; ++d) u[d] = U[(long)i * NU + d];
+  if (lin_mode == 0) jac3_analytic(x, u, dyn, A, Bm);
+  else jac3_fd(x, u, dyn, A, Bm);
+  double* ab = AB + (long)i * NX * NS;
+#pragma unroll
+  for (int r = 0; r < NX; ++r) {
+#pragma unroll
+    for (int j = 0; j < NX; ++j) ab[r * NS + j] = A[r][j];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) ab[r * NS + NX + j] = Bm[r][j];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ Monte Carlo step
+// One closed-loop simulation step per scenario (experiments/monte_carlo.py:455-549): plant step x <- f(x,u) (+ the
+// drag-like "true" residual of the synthetic workload, cf. experiments/dispersion.py:349-360), then the termination
+// rules the reference applies at the top of its next loop iteration (:460-488) and LandingConstraints.check_landing
+// (:54-104, defaults).  Outcome codes follow LandingOutcome (:24-33): 1 success, 2 crash, 3 fuel, 4 violation,
+// 5 timeout, 6 divergence; 0 = still running.
+__device__ __forceinline__ int classify3(const double* x, double m0) {
+  if (x[1] < 0.0) return 2;
+  if (x[0] <= 1.0 + 0.01) return 3;
+  bool bad = false;
+#pragma unroll
+  for (int d = 0; d < NX; ++d) bad = bad || !(fabs(x[d]) <= 1e6);
+  if (bad) return 6;
+  if (x[1] < 1.0 && fabs(x[4]) < 5.0) {
+    const bool ok = fabs(x[1]) <= 1.0 && fabs(x[2]) <= 5.0 && fabs(x[3]) <= 5.0 && fabs(x[4]) <= 2.0 &&
+                    fabs(x[5]) <= 1.0 && fabs(x[6]) <= 1.0 && !(1.0 - x[0] / m0 > 1.0 - 0.05);
+    return ok ? 1 : 4;
+  }
+  return 0;
+}
+
+__global__ void __launch_bounds__(128) mc_step3_kernel(GpmpcDyn3 dyn, int nbatch, double drag_cda, int max_steps,
+                                                       double* __restrict__ x, const double* __restrict__ u,
+                                                       const double* __restrict__ m0, int* __restrict__ t_step,
+                                                       int* __restrict__ active, int* __restrict__ outcome,
+                                                       double* __restrict__ x_final,
+                                                       unsigned long long* __restrict__ counts) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  if (!active[b]) return;
+  double xl[NX], ul[NU], xn[NX];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) xl[d] = x[(long)b * NX + d];
+#pragma unroll
+  for (int d = 0; d < NU; ++d) ul[d] = u[(long)b * NU + d];
+  step3(xl, ul, dyn, xn);
+  if (drag_cda != 0.0) {
+    const double rho = 1.225 * exp(-xl[1] / 8500.0);
+    const double sp = sqrt(xl[4] * xl[4] + xl[5] * xl[5] + xl[6] * xl[6]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dyn.dt * (-0.5 * rho * drag_cda * sp * xl[4 + i] / xl[0]);
+  }
+  const int t = t_step[b] + 1;
+  int code = classify3(xn, m0[b]);
+  if (code == 0 && t >= max_steps) code = 5;
+#pragma unroll
+  for (int d = 0; d < NX; ++d) x[(long)b * NX + d] = xn[d];
+  t_step[b] = t;
+  if (code != 0) {
+    active[b] = 0;
+    outcome[b] = code;
+    if (x_final)
+#pragma unroll
+      for (int d = 0; d < NX; ++d) x_final[(long)b * NX + d] = xn[d];
+    if (counts) atomicAdd(counts + code, 1ULL);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ post-QP update
 // One warp per scenario.  mode 0 = RTI (osqp_rti.py:532-552), mode 1 = GP-MPC SQP iteration (gp_mpc.py:336-345).
 __global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int mode, const double* __restrict__ z,
@@ -393,6 +523,49 @@ extern "C" int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3*
   else
     rollout3_kernel<0><<<grid, ROLL_WARPS * 32, 0, s>>>(M, has_model, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
   return gpmpc_check_launch("rollout_3dof");
+}
+
+extern "C" int gpmpc_gp_mean_points_3dof(const GpmpcExactModel* model, int B, int N, const double* X, const double* U,
+                                        double* dmean, double* Ks, long ldk, const int* active, void* stream) {
+  GPMPC_REQUIRE(model != nullptr && B >= 0 && N >= 1 && dmean != nullptr, "gpmpc_gp_mean_points_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  GpmpcExactModel M = *model;
+  GPMPC_REQUIRE(M.D == 11 && M.DP >= 12 && M.DP <= MAXDP && M.DP % 4 == 0, "gpmpc_gp_mean_points_3dof: model must have D=11, DP%4==0");
+  GPMPC_REQUIRE(M.P >= 3 && M.P <= MAXP, "gpmpc_gp_mean_points_3dof: model must have 3..6 outputs");
+  GPMPC_REQUIRE(Ks == nullptr || ldk >= M.n_pad, "gpmpc_gp_mean_points_3dof: ldk < n_pad");
+  const long pts = (long)B * N;
+  const int grid = (int)((pts + ROLL_WARPS - 1) / ROLL_WARPS);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (M.DP == 12) gp_points3_kernel<12><<<grid, ROLL_WARPS * 32, 0, s>>>(M, B, N, X, U, dmean, Ks, ldk, active);
+  else gp_points3_kernel<0><<<grid, ROLL_WARPS * 32, 0, s>>>(M, B, N, X, U, dmean, Ks, ldk, active);
+  return gpmpc_check_launch("gp_mean_points_3dof");
+}
+
+extern "C" int gpmpc_linearize_3dof(const GpmpcDyn3* dyn, int npts, int lin_mode, const double* X, const double* U,
+                                    double* AB, void* stream) {
+  GPMPC_REQUIRE(dyn != nullptr && npts >= 0 && (lin_mode == 0 || lin_mode == 1), "gpmpc_linearize_3dof: bad arguments");
+  if (npts == 0) return GPMPC_OK;
+  linearize3_kernel<<<(npts + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, npts, lin_mode, X, U, AB);
+  return gpmpc_check_launch("linearize_3dof");
+}
+
+extern "C" int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_steps, double* x, const double* u,
+                                  const double* m0, int* t_step, int* active, int* outcome, double* x_final,
+                                  unsigned long long* counts, void* stream) {
+  GPMPC_REQUIRE(dyn != nullptr && B >= 0 && x && u && m0 && t_step && active && outcome, "gpmpc_mc_step_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  mc_step3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, B, drag_cda, max_steps, x, u, m0, t_step,
+                                                                      active, outcome, x_final, counts);
+  return gpmpc_check_launch("mc_step_3dof");
+}
+
+extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active,
+                                    void* stream) {
+  GPMPC_REQUIRE(B >= 0 && N >= 1, "gpmpc_pack_traj_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  const long total = (long)B * (N * NS + NX);
+  pack_traj3_kernel<<<(int)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, N, X, U, z, active);
+  return gpmpc_check_launch("pack_traj_3dof");
 }
 
 extern "C" int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U,

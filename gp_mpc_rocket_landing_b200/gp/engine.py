@@ -13,7 +13,7 @@ import numpy as np
 from .. import _lib
 from .._lib import call, ptr, stream
 
-SE, M32, M52 = 0, 1, 2
+SE, M32, M52, DIST2 = 0, 1, 2, 3
 
 
 def torch_():
@@ -115,24 +115,44 @@ def potrf(A, batch=1):
 
 
 class ExactFactor:
-    """K = k(X,X) + (noise+jitter) I = L L^T for one hyper-parameter set (exact_gp.py:157-175)."""
+    """K = k(X,X) + (noise+jitter) I = L L^T for one hyper-parameter set (exact_gp.py:157-175).
 
-    def __init__(self, kind, ls, sv, noise):
-        self.kind, self.sv, self.noise = int(kind), float(sv), float(noise)
+    kind in (SE, M32, M52): the Gram is built by the fused device kernel from (ls, sv).  kind None: `kernel` is any
+    object with the reference Kernel API (Sum / Product / isotropic ...) evaluated on device tensors."""
+
+    JITTERS = (0.0, 1e-6, 1e-5, 1e-4, 1e-3, 1e-2, 1e-1)  # exact_gp.py:163-175 (1e-6 * 10^j while < 1.0)
+
+    def __init__(self, kind, ls, sv, noise, kernel=None):
+        self.kind = None if kind is None else int(kind)
+        self.sv, self.noise = float(sv), float(noise)
         self.ls_host = np.asarray(ls, dtype=np.float64).copy()
+        self.kernel = kernel
         self.jitter = 0.0
 
-    def fit(self, X, jitters=(0.0, 1e-6, 1e-5, 1e-4, 1e-3, 1e-2, 1e-1)):
+    def _gram_noise(self, jit, out):
+        if self.kind is not None:
+            gram_scaled(self.kind, self.Xs, self.sq, self.n, self.Xs, self.sq, self.n, self.sv,
+                        diag_add=self.noise + jit, pad_identity=1, lower_only=1, out=out)
+            return out
+        torch = torch_()
+        out.zero_()
+        out.diagonal().fill_(1.0)
+        out[: self.n, : self.n] = self.kernel._gram_dev(self.X)
+        out.diagonal()[: self.n].add_(self.noise + jit)
+        return out
+
+    def fit(self, X, jitters=None):
         torch = torch_()
         self.X = to_dev(X)
         self.n, self.D = self.X.shape
-        self.ls = to_dev(self.ls_host)
-        self.Xs, self.sq = scale_inputs(self.X, self.ls)
-        self.n_pad, self.DP = self.Xs.shape
+        self.n_pad = pad_to(self.n, 128)
+        if self.kind is not None:
+            self.ls = to_dev(self.ls_host)
+            self.Xs, self.sq = scale_inputs(self.X, self.ls)
+            self.DP = self.Xs.shape[1]
         L = torch.empty((self.n_pad, self.n_pad), dtype=torch.float64, device=self.X.device)
-        for jit in jitters:  # exact_gp.py:163-175: retry chol(K_noise + jitter I), jitter = 1e-6 * 10^j < 1
-            gram_scaled(self.kind, self.Xs, self.sq, self.n, self.Xs, self.sq, self.n, self.sv,
-                        diag_add=self.noise + jit, pad_identity=1, lower_only=1, out=L)
+        for jit in (self.JITTERS if jitters is None else jitters):
+            self._gram_noise(jit, L)
             self.Winv, info = potrf(L)
             if int(info.item()) == 0:
                 self.L, self.jitter = L, jit
@@ -148,8 +168,19 @@ class ExactFactor:
     def cross(self, Xq, out=None):
         """K* rows for queries Xq (Q,D): returns (Ks (q_pad, n_pad), Q)."""
         Q = Xq.shape[0]
-        Xqs, sqq = scale_inputs(Xq, self.ls, DP=self.DP)
-        return gram_scaled(self.kind, Xqs, sqq, Q, self.Xs, self.sq, self.n, self.sv, out=out), Q
+        if self.kind is not None:
+            Xqs, sqq = scale_inputs(Xq, self.ls, DP=self.DP)
+            return gram_scaled(self.kind, Xqs, sqq, Q, self.Xs, self.sq, self.n, self.sv, out=out), Q
+        torch = torch_()
+        Ks = torch.zeros((pad_to(Q, 128), self.n_pad), dtype=torch.float64, device=Xq.device) if out is None else out.zero_()
+        Ks[:Q, : self.n] = self.kernel._gram_dev(Xq, self.X)
+        return Ks, Q
+
+    def prior_diag(self, Xq):
+        """k(x*, x*) per query (kernels.py:264-277): a constant for the ARD kernels."""
+        if self.kind is not None:
+            return None
+        return to_dev(self.kernel.diagonal(Xq))
 
     def sumsq_inplace(self, Ks):
         """v = L^{-1} K*^T in place (row-wise) and sum_i v_i^2 per query (exact_gp.py:260-261)."""
@@ -166,7 +197,8 @@ class ExactModelDev:
     def __init__(self, factor: ExactFactor):
         self.f = factor
 
-    def fit_targets(self, Y, normalize=True):
+    def fit_targets(self, Y, normalize=True, prior_mean=None):
+        """prior_mean: optional (n, P) values m(X) subtracted as m(X)/y_std (exact_gp.py:152-154)."""
         torch = torch_()
         f = self.f
         Y = to_dev(Y)
@@ -179,34 +211,53 @@ class ExactModelDev:
         self.ystd = torch.empty((self.P,), dtype=torch.float64, device=dev)
         call("gpmpc_normalize_targets", ptr(Y), f.n, self.P, Y.stride(0), f.n_pad, int(normalize), ptr(self.Yn),
              ptr(self.ymean), ptr(self.ystd), stream())
+        if prior_mean is not None:
+            pm = to_dev(prior_mean)
+            if pm.dim() == 1:
+                pm = pm[:, None]
+            self.Yn[:, : f.n] -= (pm / self.ystd[None, :]).T
         self.alpha = f.solve(self.Yn.clone())
         self.lml = torch.empty((self.P,), dtype=torch.float64, device=dev)
         call("gpmpc_lml", ptr(f.L), f.n, f.n_pad, f.L.stride(0), 0, ptr(self.Yn), ptr(self.alpha), self.P, 1,
              ptr(self.lml), stream())
         return self
 
-    def predict(self, Xq, want_var=True, chunk=65536):
-        """-> mean (Q,P), var (Q,P) CUDA tensors."""
+    def predict(self, Xq, want_var=True, chunk=65536, col=None, keep_v=False):
+        """-> mean (Q,P), var (Q,P) CUDA tensors (col: a single output -> (Q,1)).  keep_v: also return the solved
+        V = (L^{-1} K*^T)^T rows (Q_pad, n_pad) of the last chunk (full-covariance branch, exact_gp.py:247-254)."""
         torch = torch_()
         f = self.f
         Xq = to_dev(Xq)
         Q = Xq.shape[0]
-        mean = torch.empty((Q, self.P), dtype=torch.float64, device=Xq.device)
-        var = torch.empty((Q, self.P), dtype=torch.float64, device=Xq.device) if want_var else None
+        c0, P = (0, self.P) if col is None else (int(col), 1)
+        alpha, ymean, ystd = self.alpha[c0:c0 + P], self.ymean[c0:c0 + P], self.ystd[c0:c0 + P]
+        mean = torch.empty((Q, P), dtype=torch.float64, device=Xq.device)
+        var = torch.empty((Q, P), dtype=torch.float64, device=Xq.device) if want_var else None
+        V = None
         for s in range(0, Q, chunk):
             e = min(Q, s + chunk)
             Ks, q = f.cross(Xq[s:e])
-            call("gpmpc_predict_mean", ptr(Ks), Ks.stride(0), q, f.n, ptr(self.alpha), f.n_pad, self.P,
-                 ptr(self.ymean), ptr(self.ystd), ptr(mean[s:e]), mean.stride(0), 0, stream())
-            if want_var:
+            call("gpmpc_predict_mean", ptr(Ks), Ks.stride(0), q, f.n, ptr(alpha), f.n_pad, P,
+                 ptr(ymean), ptr(ystd), ptr(mean[s:e]), mean.stride(0), 0, stream())
+            if want_var or keep_v:
                 sumsq = f.sumsq_inplace(Ks)
-                call("gpmpc_predict_var", ptr(sumsq), None, q, self.P, f.sv, 1e-10, ptr(self.ystd), ptr(var[s:e]),
-                     var.stride(0), 0, stream())
+                V = Ks
+            if want_var:
+                prior = f.prior_diag(Xq[s:e])
+                if prior is None:
+                    call("gpmpc_predict_var", ptr(sumsq), None, q, P, f.sv, 1e-10, ptr(ystd), ptr(var[s:e]),
+                         var.stride(0), 0, stream())
+                else:  # generic kernels: per-query prior variance
+                    var[s:e] = torch.clamp(prior - sumsq[:q], min=1e-10)[:, None] * (ystd * ystd)[None, :]
+        if keep_v:
+            return mean, var, V
         return mean, var
 
     def struct(self):
         """GpmpcExactModel for the fused horizon kernels (keeps the tensors alive through self)."""
         f = self.f
+        if f.kind is None:
+            raise _lib.GpmpcError("the fused horizon kernels need an SE-ARD / Matern kernel (one fused Gram launch)")
         return _lib.ExactModel(kind=f.kind, n=f.n, n_pad=f.n_pad, D=f.D, DP=f.DP, P=self.P, signal_var=f.sv,
                                lengthscales=ptr(f.ls), Xs=ptr(f.Xs), sq=ptr(f.sq), alpha=ptr(self.alpha),
                                ymean=ptr(self.ymean), ystd=ptr(self.ystd), L=ptr(f.L), Winv=ptr(f.Winv))

@@ -28,6 +28,50 @@ U_MIN = np.array([0.3, -5.0, -5.0])
 U_MAX = np.array([5.0, 5.0, 5.0])
 
 
+class PhaseTimers:
+    """CUDA-event timers around the phases of a batched solve (events on the launching stream).  Used by bench.py to
+    attribute the step time to kernels live, inside the timed region; disabled (None) in normal operation."""
+
+    def __init__(self):
+        self.pairs = {}
+
+    class _Span:
+        def __init__(self, owner, name):
+            self.o, self.n = owner, name
+
+        def __enter__(self):
+            torch = torch_()
+            self.a = torch.cuda.Event(enable_timing=True)
+            self.b = torch.cuda.Event(enable_timing=True)
+            self.a.record()
+
+        def __exit__(self, *exc):
+            self.b.record()
+            self.o.pairs.setdefault(self.n, []).append((self.a, self.b))
+
+    def span(self, name):
+        return PhaseTimers._Span(self, name)
+
+    def totals(self):
+        """name -> (total ms, number of spans); synchronises."""
+        torch_().cuda.synchronize()
+        return {k: (sum(a.elapsed_time(b) for a, b in v), len(v)) for k, v in self.pairs.items()}
+
+    def reset(self):
+        self.pairs = {}
+
+
+class _NullSpan:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+NULL_SPAN = _NullSpan()
+
+
 def qp_dims(N):
     n = N * NS + NX
     return n, NX * (N + 1) + n
@@ -103,6 +147,25 @@ def rollout(model_struct, dyn, x0, U, X, dmean=None, Ks=None, active=None):
     B, N = U.shape[0], U.shape[1]
     call("gpmpc_rollout_3dof", C.byref(model_struct) if model_struct is not None else None, C.byref(dyn), B, N,
          ptr(x0), ptr(U), ptr(X), ptr(dmean), ptr(Ks), Ks.stride(0) if Ks is not None else 0, ptr(active), stream())
+
+
+def gp_mean_points(model_struct, X, U, dmean, Ks=None, active=None):
+    """GP means at the trajectory points (X[b,k], U[b,k]), k < N (gp_mpc.py:309-317)."""
+    B, N = U.shape[0], U.shape[1]
+    call("gpmpc_gp_mean_points_3dof", C.byref(model_struct), B, N, ptr(X), ptr(U), ptr(dmean), ptr(Ks),
+         Ks.stride(0) if Ks is not None else 0, ptr(active), stream())
+
+
+def pack_traj(X, U, z, active=None):
+    """z = [x_0,u_0,...,x_N] (osqp_rti.py:601-614)."""
+    B, N = U.shape[0], U.shape[1]
+    call("gpmpc_pack_traj_3dof", B, N, ptr(X), ptr(U), ptr(z), ptr(active), stream())
+
+
+def linearize(dyn, X, U, AB, lin_mode=0):
+    """[A_d | B_d] at the flattened points of X (...,7), U (...,3) -> AB (...,7,10)."""
+    npts = X.numel() // NX
+    call("gpmpc_linearize_3dof", C.byref(dyn), npts, lin_mode, ptr(X), ptr(U), ptr(AB), stream())
 
 
 def propagate_cov(dyn, X, U, dvar, covs, sigma0=1e-6, active=None):

@@ -1,0 +1,371 @@
+"""GP-MPC with the reference's API (src/mpc/gp_mpc.py: `GPMPCConfig`, `GPMPC.setup/solve/reset_warm_start`) plus the
+new `solve_batch` entry point: B independent controller instances advanced by one fused sequence of device kernels.
+
+Algorithm = `GPMPC.solve` (gp_mpc.py:229-369) specialised to the 3-DoF 7-state model:
+  1. GP-augmented rollout of the warm-start controls            (:266-281, `_predict_with_gp` :139-175)
+  2. linear covariance propagation with GP variance             (:284-289 -> uncertainty_prop.py:117-177)
+  3. up to `max_sqp_iter` (reference: 10) iterations of  linearise + GP-mean affine term + QP  (:296-353),
+     convergence max|dX|,max|dU| < 1e-4 (:337-345), failure -> keep the nominal trajectory, cost = inf (:478-482)
+  4. warm start = the last iterate, unshifted                   (:355-357)
+The inner IPOPT "QP" of the reference (CasADi, absent, non-convex thrust annulus) is replaced by the OSQP-form QP of
+osqp_rti.py:203-372 (box bounds, diagonal cost) solved by the batched ADMM kernel -- north_star's design; numerical
+parity of u0 with IPOPT is not a target.  Everything numeric runs in libgpmpc_b200.so; there is no CPU path.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from .. import _lib
+from ..gp import engine as ge
+from . import engine as me
+from .constraints import ConstraintParams, TightenedConstraints
+from .cost_functions import CostWeights
+from .nominal_mpc import BatchMPCSolution, MPCConfig, MPCSolution
+
+NX, NU = 7, 3
+
+
+@dataclass
+class GPMPCConfig(MPCConfig):
+    """gp_mpc.py:48-63 fields, then the knobs the reference hard-codes or leaves to OSQP defaults."""
+
+    use_gp_mean: bool = True
+    use_gp_uncertainty: bool = True
+    confidence_level: float = 0.95
+    max_variance_for_constraint: float = 1.0
+    robust_horizon: int = -1
+    # --- additions (reference values as defaults) ---
+    max_sqp_iter: int = 10            # gp_mpc.py:293 `max_iters = 10`
+    sqp_tol: float = 1e-4             # gp_mpc.py:343 (the device kernel implements exactly this constant)
+    repropagate_uncertainty: bool = True  # gp_mpc.py:348-353 (computed and discarded by the reference)
+    qp_max_iter: int = 1000           # config/mpc_params.yaml:48 (osqp_rti.py:53 uses 50, which rarely converges)
+    qp_eps_abs: float = 1e-4          # osqp_rti.py:54
+    qp_eps_rel: float = 1e-4          # osqp_rti.py:55
+    qp_check_every: int = 25          # OSQP default check_termination
+    qp_adaptive_rho_interval: int = 25  # iteration based (OSQP's default is timing based, i.e. not reproducible)
+    qp_scaling: int = 3               # osqp_rti.py:477
+
+
+def _is_dev(a):
+    return hasattr(a, "is_cuda")
+
+
+class _BatchState:
+    """Device-resident state of B controller instances (buffers are allocated once and reused every step)."""
+
+    def __init__(self, B: int, N: int, model, device="cuda"):
+        torch = ge.torch_()
+        f64 = dict(dtype=torch.float64, device=device)
+        i32 = dict(dtype=torch.int32, device=device)
+        n, m = me.qp_dims(N)
+        self.B, self.N = B, N
+        self.X = torch.zeros((B, N + 1, NX), **f64)
+        self.U = torch.zeros((B, N, NU), **f64)
+        self.Xs = torch.zeros((B, N + 1, NX), **f64)       # scratch rollout of the re-propagation
+        self.dmean = torch.zeros((B, N, 3), **f64)
+        self.dmean_s = torch.zeros((B, N, 3), **f64)
+        self.q_pad = ge.pad_to(B * N, 128)
+        self.dvar = torch.zeros((self.q_pad, 3), **f64)
+        self.Ks = torch.zeros((self.q_pad, model.f.n_pad), **f64) if model is not None else None
+        self.covs = torch.zeros((B, N + 1, NX, NX), **f64)
+        self.AB = torch.zeros((B, N, NX, NX + NU), **f64)
+        self.beq = torch.zeros((B, NX * (N + 1)), **f64)
+        self.q = torch.zeros((B, n), **f64)
+        self.cost = torch.zeros((B,), **f64)
+        self.converged = torch.zeros((B,), **i32)
+        self.active = torch.ones((B,), **i32)
+        self.n_iter = torch.zeros((B,), **i32)
+        self.qp_iters = torch.zeros((B,), **i32)
+        self.ws = me.AdmmWorkspace(B, N, device=device)
+        self.U_warm = torch.zeros((B, N, NU), **f64)
+        self.X_warm = torch.zeros((B, N + 1, NX), **f64)
+        self.has_warm = False
+        self._pinned = [{}, {}]   # two alternating sets of pinned staging buffers for the host results
+        self._flip = 0
+
+    def to_host(self, tensors: dict) -> dict:
+        """Device -> pinned host copies of the result tensors (async on the current stream, one synchronise).
+        The returned numpy arrays are views of pinned buffers that stay valid until the next-but-one call."""
+        torch = ge.torch_()
+        self._flip ^= 1
+        bufs = self._pinned[self._flip]
+        out = {}
+        for k, t in tensors.items():
+            b = bufs.get(k)
+            if b is None or b.shape != t.shape or b.dtype != t.dtype:
+                b = torch.empty(t.shape, dtype=t.dtype, device="cpu", pin_memory=True)
+                bufs[k] = b
+            b.copy_(t, non_blocking=True)
+            out[k] = b
+        torch.cuda.current_stream().synchronize()
+        return {k: v.numpy() for k, v in out.items()}
+
+
+class GPMPC:
+    """gp_mpc.py:66-502 (3-DoF specialisation; `gp_model` = `Simple3DoFGP` or None for nominal MPC)."""
+
+    def __init__(self, dynamics, gp_model, config: Optional[GPMPCConfig] = None,
+                 constraint_params: Optional[ConstraintParams] = None, cost_weights: Optional[CostWeights] = None):
+        self.dynamics = dynamics
+        self.gp = gp_model
+        self.config = config or GPMPCConfig()
+        self.constraint_params = constraint_params or ConstraintParams()
+        self.cost_weights = cost_weights or CostWeights()
+        self.n_x, self.n_u = NX, NU
+        self._tightened_constraints = TightenedConstraints(base_params=self.constraint_params,
+                                                           confidence_level=self.config.confidence_level)
+        self._X_warm = None
+        self._U_warm = None
+        self._single: Optional[_BatchState] = None
+        self._batch: Optional[_BatchState] = None
+        self._model = None
+        self._model_struct = None
+        self._qp = None
+        self._dyn = None
+        self._is_setup = False
+        self.last_kernel_launches = 0
+        self.timers: Optional[me.PhaseTimers] = None   # set to me.PhaseTimers() to time the phases (bench.py)
+
+    def _span(self, name):
+        return self.timers.span(name) if self.timers is not None else me.NULL_SPAN
+
+    # ------------------------------------------------------------------------------------------------ setup
+    def setup(self) -> None:
+        """Upload the scenario-independent data: dynamics parameters, cost / bound vectors, the fitted GP factor."""
+        ge.torch_()
+        p = self.dynamics.params
+        g_vec = getattr(p, "g_vec", None)
+        if g_vec is None:
+            g_vec = getattr(p, "g_I")
+        self._dyn = me.make_dyn(p.alpha, np.asarray(g_vec, dtype=np.float64), self.config.dt)
+        Qd, Qfd, Rd = self.cost_weights.diag_3dof()
+        self._qp = me.QPData.reference(self.config.N, Q=Qd, Qf=Qfd, R=Rd)
+        self.refresh_gp()
+        self._is_setup = True
+
+    def refresh_gp(self) -> None:
+        """(Re)read the GP's fitted device state -- call after the GP was refit (e.g. new hyper-parameters)."""
+        self._model = None
+        self._model_struct = None
+        if self.gp is not None and (self.config.use_gp_mean or self.config.use_gp_uncertainty):
+            dm = self.gp.device_model() if hasattr(self.gp, "device_model") else None
+            if dm is None and getattr(self.gp, "n_data", 0) > 0:
+                raise _lib.GpmpcError("GPMPC needs an exact GP whose outputs share one factor "
+                                      "(Simple3DoFGP(use_sparse=False)); sparse models are served by predict_batch")
+            if dm is not None:
+                self._model = dm
+                self._model_struct = dm.struct()
+
+    def reset_warm_start(self) -> None:
+        """gp_mpc.py:494-497."""
+        self._X_warm = None
+        self._U_warm = None
+        for st in (self._single, self._batch):
+            if st is not None:
+                st.has_warm = False
+                st.ws.y.zero_()
+
+    def reset_scenarios(self, mask, X0) -> None:
+        """Per-scenario `reset_warm_start` for the batched state: scenarios with mask != 0 restart from the hover
+        guess at mass X0[b,0] with zero duals (a fresh controller instance for a respawned Monte Carlo run)."""
+        st = self._batch
+        if st is None or not st.has_warm:
+            return
+        torch = ge.torch_()
+        mask = ge.to_dev(mask, torch.bool)
+        hover = torch.zeros_like(st.U_warm)
+        hover[:, :, 0] = (ge.to_dev(X0)[:, 0] * float(self.dynamics.params.g0))[:, None]
+        st.U_warm = torch.where(mask[:, None, None], hover, st.U_warm).contiguous()
+        st.ws.y.masked_fill_(mask[:, None], 0.0)
+
+    def _settings(self):
+        c = self.config
+        return _lib.AdmmSettings.reference_defaults(
+            max_iter=c.qp_max_iter, eps_abs=c.qp_eps_abs, eps_rel=c.qp_eps_rel, check_every=c.qp_check_every,
+            adaptive_rho_interval=c.qp_adaptive_rho_interval, scaling=c.qp_scaling,
+            warm_x=1, warm_y=1, rho_from_input=0, commit_y_solved_only=1)
+
+    # ------------------------------------------------------------------------------------------------ core
+    def _variance_and_cov(self, st: _BatchState, X, U, active):
+        """GP variances of the rows of st.Ks (blocked DMMA TRSM with fused sum of squares) -> covariance chain."""
+        f = self._model.f
+        with self._span("gp_variance"):
+            sumsq = f.sumsq_inplace(st.Ks)
+        with self._span("cov"):
+            ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, st.B * st.N, 3, f.sv, 1e-10, ge.ptr(self._model.ystd),
+                    ge.ptr(st.dvar), 3, 0, ge.stream())
+            me.propagate_cov(self._dyn, X, U, st.dvar, st.covs, sigma0=1e-6, active=active)
+        return 2 * (f.n_pad // 64) + 2  # launches: memset is not a kernel; (n/64 - 1) GEMM + n/64 W-GEMM + var + cov
+
+    def _solve_device(self, st: _BatchState, x0, x_ref, U_ref=None, active_in=None):
+        """One GP-MPC solve for every scenario of `st` (all tensors on the device).  Returns #kernel launches."""
+        c = self.config
+        N = c.N
+        use_model = self._model is not None
+        use_mean = c.use_gp_mean and use_model
+        use_unc = c.use_gp_uncertainty and use_model
+        launches = 0
+        # --- initial controls: warm start | U_ref | hover along the up axis (gp_mpc.py:266-275; the 3-DoF frame of
+        #     nominal_mpc.py:651-657 / osqp_rti.py:427-431 has "up" = axis 0)
+        if st.has_warm and c.warm_start:
+            st.U.copy_(st.U_warm)
+        elif U_ref is not None:
+            st.U.copy_(U_ref[..., :N, :].expand_as(st.U))
+        else:
+            st.U.zero_()
+            st.U[:, :, 0] = (x0[:, 0] * float(self.dynamics.params.g0))[:, None]
+        if active_in is None:
+            st.active.fill_(1)
+        else:
+            st.active.copy_(active_in)
+        st.n_iter.zero_()
+        st.qp_iters.zero_()
+        st.converged.zero_()
+        # --- 1. rollout with the GP mean
+        need_ks = use_unc
+        with self._span("rollout"):
+            me.rollout(self._model_struct if (use_mean or use_unc) else None, self._dyn, x0, st.U, st.X,
+                       st.dmean if use_model else None, st.Ks if need_ks else None, active=st.active)
+        launches += 1
+        if use_model and not use_mean:
+            # uncertainty only: the GP mean must not enter the prediction (use_gp_mean=False)
+            me.rollout(None, self._dyn, x0, st.U, st.X, None, None, active=st.active)
+            launches += 1
+        # --- 2. uncertainty propagation
+        if use_unc:
+            launches += self._variance_and_cov(st, st.X, st.U, st.active)
+        # --- 3. SQP iterations
+        S = self._settings()
+        for it in range(c.max_sqp_iter):
+            if use_mean and it > 0:
+                with self._span("gp_mean"):
+                    me.gp_mean_points(self._model_struct, st.X, st.U, st.dmean, None, active=st.active)
+                launches += 1
+            with self._span("assemble"):
+                me.qp_assemble(self._dyn, self._qp, st.X, st.U, x0, x_ref, st.AB, st.beq, st.q,
+                               c_gp=st.dmean if use_mean else None, lin_mode=0, rhs_mode=1, active=st.active)
+                me.pack_traj(st.X, st.U, st.ws.x, active=st.active)
+            with self._span("admm"):
+                me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active)
+            with self._span("update"):
+                st.qp_iters += st.ws.iters * st.active
+                me.mpc_update(self._qp, 1, st.ws.x, st.ws.status, x_ref, st.X, st.U, None, None, st.cost,
+                              st.converged, active=st.active, n_iter=st.n_iter)
+            launches += 5
+            if it == c.max_sqp_iter - 1:
+                break
+            if int(st.active.sum().item()) == 0:
+                break
+            if use_unc and c.repropagate_uncertainty:  # gp_mpc.py:348-353
+                with self._span("rollout"):
+                    me.rollout(self._model_struct, self._dyn, x0, st.U, st.Xs, st.dmean_s, st.Ks, active=st.active)
+                launches += 1 + self._variance_and_cov(st, st.Xs, st.U, st.active)
+        # --- 4. warm start for the next call (unshifted, gp_mpc.py:355-357)
+        st.U_warm.copy_(st.U)
+        st.X_warm.copy_(st.X)
+        st.has_warm = True
+        return launches
+
+    def _state_for(self, B: int, single: bool) -> _BatchState:
+        attr = "_single" if single else "_batch"
+        st = getattr(self, attr)
+        if st is None or st.B != B or st.N != self.config.N:
+            st = _BatchState(B, self.config.N, self._model)
+            setattr(self, attr, st)
+        return st
+
+    def _x_ref(self, x_target, X_ref, B):
+        torch = ge.torch_()
+        N = self.config.N
+        if X_ref is not None:
+            r = ge.to_dev(X_ref)
+            return r[..., : N + 1, :].contiguous()
+        t = ge.to_dev(x_target)
+        if t.dim() == 1:
+            return t[None, :].expand(N + 1, NX).contiguous()
+        return t[:, None, :].expand(B, N + 1, NX).contiguous()
+
+    # ------------------------------------------------------------------------------------------------ public API
+    def solve_batch(self, X0, x_target, X_ref=None, U_ref=None, active=None) -> BatchMPCSolution:
+        """B independent `solve` calls (each scenario keeps its own warm start between calls).
+
+        X0 (B,7); x_target (7,) or (B,7); optional X_ref (N+1,7)|(B,N+1,7), U_ref (N,3)|(B,N,3); optional `active`
+        (B,) mask -- scenarios with 0 are skipped (their outputs repeat the previous call).  numpy in -> numpy out,
+        CUDA float64 tensors in -> CUDA tensors out."""
+        if not self._is_setup:
+            self.setup()
+        torch = ge.torch_()
+        t0 = time.perf_counter()
+        dev_in = _is_dev(X0)
+        x0 = ge.to_dev(X0)
+        if x0.dim() == 1:
+            x0 = x0[None, :]
+        B = x0.shape[0]
+        st = self._state_for(B, single=False)
+        x_ref = self._x_ref(x_target, X_ref, B)
+        act = None if active is None else ge.to_dev(active, torch.int32)
+        uref = None if U_ref is None else ge.to_dev(U_ref)
+        self.last_kernel_launches = self._solve_device(st, x0, x_ref, uref, act)
+        return self._collect(st, dev_in, t0)
+
+    def _collect(self, st: _BatchState, dev_in: bool, t0: float, with_cov: bool = False) -> BatchMPCSolution:
+        torch = ge.torch_()
+        success = st.converged.to(torch.bool)
+        status = st.converged.to(torch.int8)
+        has_cov = self._model is not None and self.config.use_gp_uncertainty
+        if dev_in:
+            torch.cuda.current_stream().synchronize()
+            sol = BatchMPCSolution(
+                u0=st.U[:, 0].clone(), X_opt=st.X.clone(), U_opt=st.U.clone(), cost=st.cost.clone(),
+                iterations=st.n_iter.clone(), success=success, status=status, solve_time=0.0,
+                qp_status=st.ws.status.clone(), qp_iterations=st.qp_iters.clone(),
+                covariances=st.covs.clone() if has_cov else None)
+        else:
+            t = dict(X=st.X, U=st.U, cost=st.cost, it=st.n_iter, ok=success, status=status, qs=st.ws.status,
+                     qi=st.qp_iters)
+            if has_cov and with_cov:
+                t["cov"] = st.covs
+            h = st.to_host(t)
+            sol = BatchMPCSolution(
+                u0=h["U"][:, 0], X_opt=h["X"], U_opt=h["U"], cost=h["cost"], iterations=h["it"], success=h["ok"],
+                status=h["status"], solve_time=0.0, qp_status=h["qs"], qp_iterations=h["qi"],
+                covariances=h.get("cov"))
+        sol.solve_time = time.perf_counter() - t0
+        return sol
+
+    def last_covariances(self, batch: bool = True):
+        """Propagated state covariances (B,N+1,7,7) of the last `solve_batch` (or `solve`) as a numpy array.  The
+        reference computes them and discards them (gp_mpc.py:486-492 returns None); they are kept on the device and
+        copied to the host only on request (34 MB at B=4096)."""
+        st = self._batch if batch else self._single
+        if st is None or self._model is None or not self.config.use_gp_uncertainty:
+            return None
+        return st.covs.cpu().numpy()
+
+    def solve(self, x0, x_target, X_ref=None, U_ref=None) -> MPCSolution:
+        """gp_mpc.py:229-369 signature; a B = 1 view of the batched path with its own warm start."""
+        if not self._is_setup:
+            self.setup()
+        t0 = time.perf_counter()
+        x0d = ge.to_dev(np.asarray(x0, dtype=np.float64)[None, :])
+        st = self._state_for(1, single=True)
+        x_ref = self._x_ref(np.asarray(x_target, dtype=np.float64), X_ref, 1)
+        uref = None if U_ref is None else ge.to_dev(np.asarray(U_ref, dtype=np.float64))
+        self.last_kernel_launches = self._solve_device(st, x0d, x_ref, uref, None)
+        b = self._collect(st, False, t0, with_cov=True)
+        b.X_opt, b.U_opt, b.u0 = b.X_opt.copy(), b.U_opt.copy(), b.u0.copy()   # detach from the pinned staging
+        if b.covariances is not None:
+            b.covariances = b.covariances.copy()
+        self._X_warm, self._U_warm = b.X_opt[0].copy(), b.U_opt[0].copy()
+        self._last_batch = b
+        return b[0]
+
+    def get_uncertainty_at_horizon(self):
+        """gp_mpc.py:486-492 returns None in the reference; here: the propagated covariances (N+1,7,7) of the last
+        `solve`, when uncertainty propagation is on."""
+        b = getattr(self, "_last_batch", None)
+        return None if b is None or b.covariances is None else b.covariances[0]

@@ -1,0 +1,105 @@
+"""`MPCConfig`, `MPCSolution` and `NominalMPC3DoF` with the reference's API (src/mpc/nominal_mpc.py:42-82, :537-679).
+
+The reference's `NominalMPC3DoF` is a CasADi/IPOPT NLP (third-party, absent).  Here it is the same 3-DoF model and
+cost (nominal_mpc.py:579-631: Euler dynamics, Q = diag(0,10,10,10,1,1,1), R = 0.01 I, terminal 10 Q) solved by the
+batched SQP-on-OSQP-form-QP path of `GPMPC` with no GP -- see gp_mpc.py in this package and DESIGN.md "Deviations".
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Optional
+
+
+@dataclass
+class MPCConfig:
+    """nominal_mpc.py:42-64."""
+
+    N: int = 20
+    dt: float = 0.1
+    integration_method: str = "rk4"
+    max_iter: int = 100
+    tol: float = 1e-6
+    warm_start: bool = True
+    verbose: bool = False
+    soft_constraints: bool = False
+    constraint_slack_weight: float = 1e4
+    use_reference: bool = False
+
+
+@dataclass
+class MPCSolution:
+    """nominal_mpc.py:67-82."""
+
+    success: bool
+    X_opt: Any
+    U_opt: Any
+    cost: float
+    solve_time: float
+    iterations: int
+    status: str
+
+    @property
+    def u0(self):
+        return self.U_opt[0]
+
+
+@dataclass
+class BatchMPCSolution:
+    """Result of `solve_batch` (new entry point): B independent `MPCSolution`s as arrays.
+
+    u0 (B,3), X_opt (B,N+1,7), U_opt (B,N,3), cost (B,), iterations (B,) int, success (B,) bool,
+    status (B,) int8 (1 = "Converged", 0 = "Max iterations"), qp_status (B,) int (OSQP code of the last QP),
+    qp_iterations (B,) int (ADMM iterations summed over the SQP loop), covariances (B,N+1,7,7) or None.
+    numpy arrays when the inputs were numpy, CUDA tensors when they were CUDA tensors."""
+
+    u0: Any
+    X_opt: Any
+    U_opt: Any
+    cost: Any
+    iterations: Any
+    success: Any
+    status: Any
+    solve_time: float
+    qp_status: Any = None
+    qp_iterations: Any = None
+    covariances: Any = None
+
+    def __len__(self):
+        return self.u0.shape[0]
+
+    def __getitem__(self, b: int) -> MPCSolution:
+        ok = bool(self.success[b])
+        return MPCSolution(success=ok, X_opt=self.X_opt[b], U_opt=self.U_opt[b], cost=float(self.cost[b]),
+                           solve_time=self.solve_time, iterations=int(self.iterations[b]),
+                           status="Converged" if ok else "Max iterations")
+
+
+class NominalMPC3DoF:
+    """nominal_mpc.py:537-679 signature: `NominalMPC3DoF(dynamics, config=None)`, `.setup()`, `.solve(x0, x_target)`."""
+
+    def __init__(self, dynamics, config: Optional[MPCConfig] = None):
+        from .gp_mpc import GPMPC, GPMPCConfig
+        self.dynamics = dynamics
+        self.config = config or MPCConfig()
+        c = self.config
+        self._impl = GPMPC(dynamics, None, GPMPCConfig(N=c.N, dt=c.dt, warm_start=c.warm_start, verbose=c.verbose,
+                                                       use_gp_mean=False, use_gp_uncertainty=False))
+        self.n_x, self.n_u = 7, 3
+        self._is_setup = False
+
+    def setup(self) -> None:
+        self._impl.setup()
+        self._is_setup = True
+
+    def solve(self, x0, x_target) -> MPCSolution:
+        if not self._is_setup:
+            self.setup()
+        return self._impl.solve(x0, x_target)
+
+    def solve_batch(self, X0, x_target) -> BatchMPCSolution:
+        if not self._is_setup:
+            self.setup()
+        return self._impl.solve_batch(X0, x_target)
+
+    def reset_warm_start(self) -> None:
+        self._impl.reset_warm_start()

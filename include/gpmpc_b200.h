@@ -20,6 +20,7 @@ extern "C" {
 #define GPMPC_KERNEL_SE 0        /* src/gp/kernels.py:130-379  SquaredExponentialARD */
 #define GPMPC_KERNEL_MATERN32 1  /* src/gp/kernels.py:482-576  Matern32 */
 #define GPMPC_KERNEL_MATERN52 2  /* src/gp/kernels.py:579-668  Matern52 */
+#define GPMPC_KERNEL_DIST2 3     /* max(scaled squared distance, 0): kernels.py:205-236; isotropic SE :417-421 */
 
 #define GPMPC_FEATURES_3DOF 0        /* src/gp/features.py:403-444 (11 features) */
 #define GPMPC_FEATURES_6DOF_TRANS 1  /* src/gp/features.py:194-258 (13 features) */
@@ -114,6 +115,8 @@ typedef struct GpmpcAdmmSettings {
   int adaptive_rho, adaptive_rho_interval;
   int warm_x, warm_y;      /* use x / y buffers as warm start (osqp_rti.py:522-524) */
   int rho_from_input;      /* start from rho[b] when > 0 (OSQP keeps its adapted rho between solves) */
+  int commit_y_solved_only; /* write y back only when status == SOLVED (GP-MPC SQP loop keeps the last good duals) */
+  int reserved_;
 } GpmpcAdmmSettings;
 
 /* 3-DoF Euler model parameters (nominal_mpc.py:579-605, rocket_3dof.py:33-65). */
@@ -154,6 +157,27 @@ int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const doubl
 int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3* dyn, int B, int N, const double* x0,
                        const double* U, double* X, double* dmean, double* Ks, long ldk, const int* active,
                        void* stream);
+
+/* GP posterior means at given trajectory points (X[b,k], U[b,k]), k < N: the affine terms c_k of one SQP iteration
+ * (gp_mpc.py:309-317: gp.predict at every stage of the current iterate).  dmean: B x N x 3; Ks as in rollout. */
+int gpmpc_gp_mean_points_3dof(const GpmpcExactModel* model, int B, int N, const double* X, const double* U,
+                              double* dmean, double* Ks, long ldk, const int* active, void* stream);
+
+/* Discrete Jacobians [A_d | B_d] (npts x 7 x 10) at npts points (X: npts x 7, U: npts x 3): the dynamics.linearize
+ * protocol consumed at osqp_rti.py:295,340, gp_mpc.py:305, uncertainty_prop.py:147.  lin_mode as in qp_assemble. */
+int gpmpc_linearize_3dof(const GpmpcDyn3* dyn, int npts, int lin_mode, const double* X, const double* U, double* AB,
+                         void* stream);
+
+/* One closed-loop Monte Carlo step per scenario (experiments/monte_carlo.py:455-549): x <- step(x,u) (+ optional
+ * drag-like true residual -0.5 rho(alt) drag_cda |v| v / m), t_step += 1, then the termination rules :460-488 and
+ * check_landing :54-104.  Terminated scenarios get active=0, outcome = LandingOutcome code (1 success, 2 crash, 3 fuel,
+ * 4 violation, 5 timeout, 6 divergence), x_final (B x 7, may be NULL) and counts[code] += 1 (8 counters, may be NULL). */
+int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_steps, double* x, const double* u,
+                       const double* m0, int* t_step, int* active, int* outcome, double* x_final,
+                       unsigned long long* counts, void* stream);
+
+/* z = [x_0,u_0,...,x_N] from (X, U): OSQPRTIMPC._solution_to_vector, osqp_rti.py:601-614 (primal warm start). */
+int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active, void* stream);
 
 /* Linear covariance propagation (uncertainty_prop.py:117-177, 7-state): Sigma_{k+1} = A_k Sigma_k A_k' + diag(var)dt^2
  * on the velocity block, A_k = analytic discrete Jacobian at (X[b,k],U[b,k]).  covs: B x (N+1) x 7 x 7. */

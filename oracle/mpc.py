@@ -545,7 +545,9 @@ class GPMPCOracle:
         if self.U_warm is not None:                                   # gp_mpc.py:266-275
             U_init = self.U_warm
         else:
-            U_init = np.tile(np.array([0, 0, x0[0] * p.g0]), (N, 1))
+            # hover thrust along the "up" axis of the 3-DoF frame (axis 0: nominal_mpc.py:651-657,
+            # osqp_rti.py:427-431); gp_mpc.py:273 writes [0,0,m*g0] in the 6-DoF body frame
+            U_init = np.tile(np.array([x0[0] * p.g0, 0, 0]), (N, 1))
         for k in range(N):                                             # gp_mpc.py:278-281
             U[k] = U_init[k]
             xn = step_3dof(X[k], U[k], dt, p)
