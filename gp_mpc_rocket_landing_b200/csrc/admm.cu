@@ -615,6 +615,8 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
   static size_t configured = 0;
   if (smem > configured) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // the default carveout heuristic left one CTA per SM resident; ask for the full 228 KB so 3-4 QPs share an SM
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured = smem;
   }
   kern<<<B, ADMM_THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, x, y, rho, status, iters, obj,

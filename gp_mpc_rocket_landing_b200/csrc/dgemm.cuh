@@ -202,6 +202,7 @@ int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured = true;
   }
   dim3 grid(p.N / BN, p.M / BM, batch);

@@ -411,35 +411,24 @@ class OSQPOracle:
         return UNSOLVED
 
 
-def kkt_active_set_solve(Pd, q, A, l, u, x_guess, y_guess, tol=1e-7, max_rounds=50):
-    """Independent check of a QP solution: primal active-set iteration started from the active set
-    identified by (x_guess, y_guess), each round an equality-constrained KKT solve with numpy.
-    Returns (x, active_lower mask, active_upper mask)."""
-    n, m = A.shape[1], A.shape[0]
-    Ax = A @ x_guess
-    lo = (np.abs(Ax - l) <= 1e-5 * (1 + np.abs(l))) & (y_guess < -1e-9) | ((u - l) < 1e-9)
-    up = (np.abs(Ax - u) <= 1e-5 * (1 + np.abs(u))) & (y_guess > 1e-9) & ~((u - l) < 1e-9)
-    x = x_guess
-    for _ in range(max_rounds):
-        act = lo | up
-        Aa = A[act]
-        b = np.where(lo, l, u)[act]
-        na = Aa.shape[0]
-        K = np.zeros((n + na, n + na))
-        K[:n, :n] = np.diag(Pd) + 1e-12 * np.eye(n)
-        K[:n, n:] = Aa.T; K[n:, :n] = Aa
-        sol = np.linalg.lstsq(K, np.concatenate([-q, b]), rcond=None)[0]
-        x, lam = sol[:n], sol[n:]
-        y = np.zeros(m); y[act] = lam
-        Ax = A @ x
-        viol_lo = Ax < l - tol * (1 + np.abs(l)); viol_up = Ax > u + tol * (1 + np.abs(u))
-        eq = (u - l) < 1e-9
-        drop_lo = lo & ~eq & (y > 1e-9); drop_up = up & (y < -1e-9)
-        if not (viol_lo.any() or viol_up.any() or drop_lo.any() or drop_up.any()):
-            return x, lo, up, y
-        lo = (lo & ~drop_lo) | viol_lo
-        up = (up & ~drop_up) | viol_up
-    return x, lo, up, y
+def kkt_residuals(Pd, q, A, l, u, x, y):
+    """Solver-independent optimality check of a QP solution (x, y): the KKT conditions of
+    min 1/2 x'Px + q'x s.t. l <= Ax <= u, which are sufficient because the QP is convex.
+    Returns (primal infeasibility, stationarity |Px + q + A'y|_inf, complementarity max_i |y_i| * slack_i) with the
+    OSQP sign convention (y_i < 0: lower bound active, y_i > 0: upper bound active)."""
+    Ax = A @ x
+    prim = float(max(np.max(l - Ax), np.max(Ax - u), 0.0))
+    stat = float(np.max(np.abs(Pd * x + q + A.T @ y)))
+    slack_lo = np.where(np.isfinite(l) & (l > -1e29), Ax - l, 0.0)
+    slack_up = np.where(np.isfinite(u) & (u < 1e29), u - Ax, 0.0)
+    comp = float(max(np.max(np.maximum(-y, 0.0) * np.abs(slack_lo)), np.max(np.maximum(y, 0.0) * np.abs(slack_up))))
+    return prim, stat, comp
+
+
+def active_set(y, l, u, ytol):
+    """(lower-active, upper-active) masks of the inequality rows from the multipliers."""
+    ineq = ~((u - l) < 1e-9)
+    return (y < -ytol) & ineq, (y > ytol) & ineq
 
 
 # --------------------------------------------------------------------------- RTI orchestration
