@@ -8,12 +8,17 @@
 // rho_min on loose rows, over-relaxation alpha, termination / infeasibility checks in unscaled units every
 // `check_every` iterations, iteration-count based adaptive rho with refactorisation).
 //
-// B200 mapping: one CTA per scenario, the whole problem resident in shared memory (~62 KB at N=20, 3 CTAs / SM).
-// The reduced KKT system (P + sigma I + A' diag(rho) A) is block tridiagonal in the stage ordering with
-// (nx+nu)-square blocks; it is factorised ONCE per rho (block Cholesky, inverse diagonal blocks kept) and every ADMM
-// iteration is two block substitutions on warp 0 plus embarrassingly parallel vector work on all 128 threads.  The
-// only HBM traffic is the problem in and the solution out (coalesced, ~22 kB per QP) -- the kernel is bound by the
-// substitution dependency chain, not by HBM or FP64 throughput (DESIGN.md states this next to the roofline).
+// B200 mapping: one CTA (4 warps) per scenario, the whole problem resident in shared memory (~75 KB at N=20, so three
+// QPs share an SM).  The reduced KKT matrix M = P + sigma I + A' diag(rho) A is block tridiagonal in the stage
+// ordering with (nx+nu)-square blocks.  It is factorised once per rho by a block Cholesky chain; the factor is kept
+// in the form that makes the per-iteration solve short:
+//     forward   y_k = c_k - G_k y_{k-1},   c_k = Li_k r_k        (c for all stages in parallel, then a 1-matvec chain)
+//     backward  v_k = d_k - H_k v_{k+1},   d_k = Li_k' y_k       (same)
+// with Li_k = L_kk^{-1}, G_k = Li_k Ls_{k-1}, H_k = Li_k' Ls_k'.  The chain is the critical path of an iteration
+// (2N dependent small matvecs on one warp); everything else is embarrassingly parallel vector work on 128 threads.
+// HBM traffic is the problem in and the solution out (~22 kB per QP, coalesced) plus the scaling vectors D, E which
+// live in a global scratch (read only at termination checks): the kernel is bound by the dependency chain of the
+// substitutions, not by HBM or FP64 throughput (DESIGN.md states this next to the roofline).
 #include <math.h>
 
 #include "common.cuh"
@@ -26,6 +31,7 @@ namespace {
 constexpr int ADMM_THREADS = 128;
 constexpr double OSQP_INFTY = 1e30, MIN_SCALING = 1e-4, MAX_SCALING = 1e4;
 constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_TOL = 1e-4, RHO_EQ_OVER_INEQ = 1e3;
+constexpr double INF_T = OSQP_INFTY * MIN_SCALING;
 
 __device__ __forceinline__ double limit_scaling(double v) {
   v = (v < MIN_SCALING) ? 1.0 : v;
@@ -36,47 +42,38 @@ template <int NX, int NU>
 struct Prob {
   static constexpr int NS = NX + NU;
   static constexpr int NP = NS * (NS + 1) / 2;  // packed lower triangle
+  static constexpr int GP = (NS + 1) & ~1;      // row pitch of G_k (even: 16-byte vector loads)
+  static constexpr int HP = (NX + 1) & ~1;      // row pitch of H_k
   int N, n, m, neq;
   // shared-memory arrays
-  double *AB, *Nd, *Ei, *Bd, *D, *E, *Pb, *qb, *beq, *x, *xt, *z, *y, *zt, *Lp, *Ls, *Mw, *Vw, *red;
-  const double *lb, *ub;  // global, shared by all scenarios (n)
+  double *AB, *G, *H, *Li, *Nd, *Ei, *Bd, *Pb, *qb, *x, *xt, *w, *lbs, *ubs, *z, *y, *zt, *red;
+  double *D, *E;          // global scratch (n, m): cumulative Ruiz scalings, needed only at checks / unscaling
   double c, rho, sigma;
 
-  __device__ static size_t smem_doubles_unused(int N) {
-    const int n = N * NS + NX, m = NX * (N + 1) + n;
-    return (size_t)N * NX * NS * 2 + N * NX + NX + 5 * n + m + NX * (N + 1) + 3 * m + (size_t)(N + 1) * NP + NS * NS +
-           2 * NS + 64;
+  static __host__ __device__ size_t smem_doubles(int N) {
+    const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
+    return (size_t)N * NX * NS + (size_t)N * NS * GP + (size_t)N * NS * HP + (size_t)(N + 1) * NP + (size_t)N * NX + 8 +
+           6 * n + 5 * m + 64 + 2 * 17;  // + alignment slack of the 17 arrays
   }
   __device__ void carve(double* s, int N_) {
     N = N_; n = N * NS + NX; neq = NX * (N + 1); m = neq + n;
-    AB = s; s += N * NX * NS;
-    Ls = s; s += N * NX * NS;
-    Nd = s; s += N * NX;
-    Ei = s; s += NX;
-    Bd = s; s += n;
-    D = s; s += n;
-    Pb = s; s += n;
-    qb = s; s += n;
-    x = s; s += n;
-    xt = s; s += n;
-    E = s; s += m;
-    beq = s; s += neq;
-    z = s; s += m;
-    y = s; s += m;
-    zt = s; s += m;
-    Lp = s; s += (N + 1) * NP;
-    Mw = s; s += NS * NS;
-    Vw = s; s += 2 * NS;
-    red = s; s += 64;
+    auto take = [&](size_t cnt) { double* p = s; s += (cnt + 1) & ~(size_t)1; return p; };  // keep 16-byte alignment
+    AB = take(N * NX * NS);
+    G = take(N * NS * GP);
+    H = take(N * NS * HP);
+    Li = take((N + 1) * NP);
+    Nd = take(N * NX);
+    Ei = take(8);
+    Bd = take(n); Pb = take(n); qb = take(n); x = take(n); xt = take(n); w = take(n);
+    lbs = take(m); ubs = take(m); z = take(m); y = take(m); zt = take(m);
+    red = take(64);
   }
 
-  // ---- row classes and bounds (scaled) ----------------------------------------------------------------------
-  __device__ __forceinline__ double lbar(int r) const { return (r < neq) ? beq[r] : E[r] * lb[r - neq]; }
-  __device__ __forceinline__ double ubar(int r) const { return (r < neq) ? beq[r] : E[r] * ub[r - neq]; }
+  // ---- row classes (scaled bounds are precomputed: lbs/ubs; equality rows have lbs == ubs == E*beq) ----------------
   __device__ __forceinline__ double rho_row(int r) const {
     if (r < neq) return RHO_EQ_OVER_INEQ * rho;
-    const double l = E[r] * lb[r - neq], u = E[r] * ub[r - neq];
-    if (l < -OSQP_INFTY * MIN_SCALING && u > OSQP_INFTY * MIN_SCALING) return RHO_MIN;
+    const double l = lbs[r], u = ubs[r];
+    if (l < -INF_T && u > INF_T) return RHO_MIN;
     if (u - l < RHO_TOL) return RHO_EQ_OVER_INEQ * rho;
     return rho;
   }
@@ -99,19 +96,19 @@ struct Prob {
     }
     return Bd[r - neq] * v[r - neq];
   }
-  __device__ __forceinline__ double At_col(int j, const double* w) const {
+  __device__ __forceinline__ double At_col(int j, const double* wv) const {
     const int k = j / NS, i = j - k * NS;
-    double s = Bd[j] * w[neq + j];
-    if (k == 0 && i < NX) s = fma(Ei[i], w[i], s);
+    double s = Bd[j] * wv[neq + j];
+    if (k == 0 && i < NX) s = fma(Ei[i], wv[i], s);
     if (k < N) {
-      const double* wk = w + NX + k * NX;
+      const double* wk = wv + NX + k * NX;
       const double* a = AB + k * NX * NS + i;
       double s1 = 0.0;
 #pragma unroll
       for (int r = 0; r < NX; ++r) s1 = fma(a[r * NS], wk[r], s1);
       s += s1;
     }
-    if (k >= 1 && i < NX) s = fma(Nd[(k - 1) * NX + i], w[NX + (k - 1) * NX + i], s);
+    if (k >= 1 && i < NX) s = fma(Nd[(k - 1) * NX + i], wv[NX + (k - 1) * NX + i], s);
     return s;
   }
 };
@@ -137,12 +134,15 @@ __device__ void block_reduce(double (&v)[K], double* red) {
 }
 
 // ---- factorisation of M = Pb + sigma I + Abar' diag(rho) Abar (block tridiagonal) -------------------------------
+// Phase 1 (all threads): packed lower triangles of the diagonal blocks M_kk into Li.
+// Phase 2 (warp 0): block Cholesky chain.  Per stage k: Ls = C_{k-1} Li_{k-1}' (C = sub-diagonal block), H_{k-1},
+// Schur update of M_kk, dense Cholesky (right-looking, lane = row) and triangular inverse (lane = column) -> Li_k,
+// then G_k.  Scratch (dense 10x10 workspace, previous Li, Ls) is overlaid on zt, which is free here.
 template <int NX, int NU>
 __device__ void factorize(Prob<NX, NU>& P) {
-  constexpr int NS = NX + NU, NP = Prob<NX, NU>::NP;
+  constexpr int NS = NX + NU, NP = Prob<NX, NU>::NP, GP = Prob<NX, NU>::GP, HP = Prob<NX, NU>::HP;
   const int tid = threadIdx.x, N = P.N;
   const double rho_eq = RHO_EQ_OVER_INEQ * P.rho;
-  // phase 1 (all threads): packed lower triangles of the diagonal blocks M_kk
   for (int idx = tid; idx < (N + 1) * NP; idx += ADMM_THREADS) {
     const int k = idx / NP, pidx = idx - k * NP;
     int i = 0;
@@ -150,7 +150,7 @@ __device__ void factorize(Prob<NX, NU>& P) {
     const int j = pidx - i * (i + 1) / 2;
     double v = 0.0;
     if (k == N && i >= NX) {  // last block has only NX variables: keep an identity tail
-      P.Lp[idx] = (i == j) ? 1.0 : 0.0;
+      P.Li[idx] = (i == j) ? 1.0 : 0.0;
       continue;
     }
     if (k < N) {
@@ -168,154 +168,202 @@ __device__ void factorize(Prob<NX, NU>& P) {
       if (k >= 1 && i < NX) d = fma(rho_eq, P.Nd[(k - 1) * NX + i] * P.Nd[(k - 1) * NX + i], d);
       v += d;
     }
-    P.Lp[idx] = v;
+    P.Li[idx] = v;
   }
   __syncthreads();
-  // phase 2 (warp 0): block Cholesky chain; Lp[k] <- packed inverse of L_kk ; Ls[k-1] = M_{k,k-1} L_{k-1,k-1}^{-T}
   if (tid < 32) {
     const int lane = tid;
-    double* Mw = P.Mw;  // dense NS x NS scratch
+    double* Mw = P.zt;                              // NS x NS dense workspace
+    double* Ld = Mw + ((NS * NS + 1) & ~1);         // NS x GP dense Li of the current / previous stage
+    double* Lsv = Ld + NS * GP;                     // NX x GP
+    for (int e = lane; e < NS * GP; e += 32) Ld[e] = 0.0;
+    for (int e = lane; e < NX * GP; e += 32) Lsv[e] = 0.0;
+    __syncwarp();
     for (int k = 0; k <= N; ++k) {
-      double* Lk = P.Lp + k * NP;
+      double* Lk = P.Li + k * NP;
       if (k > 0) {
-        const double* Lip = P.Lp + (k - 1) * NP;  // inverse of previous diagonal factor (packed)
-        const double* a = P.AB + (k - 1) * NX * NS;
-        double* ls = P.Ls + (k - 1) * NX * NS;
-        for (int e = lane; e < NX * NS; e += 32) {
+        const double* a0 = P.AB + (k - 1) * NX * NS;
+        for (int e = lane; e < NX * NS; e += 32) {  // Ls[i][j] = rho_eq Nd_i sum_t AB[i][t] Li_{k-1}[j][t]
           const int i = e / NS, j = e - i * NS;
-          const double sc = rho_eq * P.Nd[(k - 1) * NX + i];
-          double s = 0.0;
-          for (int t = 0; t <= j; ++t) s = fma(sc * a[i * NS + t], Lip[j * (j + 1) / 2 + t], s);
-          ls[e] = s;
+          const double* a = a0 + i * NS;
+          const double* ld = Ld + j * GP;
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int t = 0; t + 1 < NS; t += 2) {
+            s0 = fma(a[t], ld[t], s0);
+            s1 = fma(a[t + 1], ld[t + 1], s1);
+          }
+          if (NS & 1) s0 = fma(a[NS - 1], ld[NS - 1], s0);
+          Lsv[i * GP + j] = (rho_eq * P.Nd[(k - 1) * NX + i]) * (s0 + s1);
         }
         __syncwarp();
-        for (int e = lane; e < NX * (NX + 1) / 2; e += 32) {
+        double* Hk = P.H + (size_t)(k - 1) * NS * HP;
+        for (int e = lane; e < NS * NX; e += 32) {  // H_{k-1}[r][i] = sum_j Li_{k-1}[j][r] Ls[i][j]
+          const int r = e / NX, i = e - r * NX;
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int j = 0; j + 1 < NS; j += 2) {
+            s0 = fma(Ld[j * GP + r], Lsv[i * GP + j], s0);
+            s1 = fma(Ld[(j + 1) * GP + r], Lsv[i * GP + j + 1], s1);
+          }
+          if (NS & 1) s0 = fma(Ld[(NS - 1) * GP + r], Lsv[i * GP + NS - 1], s0);
+          Hk[r * HP + i] = s0 + s1;
+        }
+        for (int e = lane; e < NX * (NX + 1) / 2; e += 32) {  // Schur: M_kk[i][j] -= sum_t Ls[i][t] Ls[j][t]
           int i = 0;
           while ((i + 1) * (i + 2) / 2 <= e) ++i;
           const int j = e - i * (i + 1) / 2;
-          double s = 0.0;
+          double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-          for (int t = 0; t < NS; ++t) s = fma(ls[i * NS + t], ls[j * NS + t], s);
-          Lk[e] -= s;
+          for (int t = 0; t + 1 < NS; t += 2) {
+            s0 = fma(Lsv[i * GP + t], Lsv[j * GP + t], s0);
+            s1 = fma(Lsv[i * GP + t + 1], Lsv[j * GP + t + 1], s1);
+          }
+          if (NS & 1) s0 = fma(Lsv[i * GP + NS - 1], Lsv[j * GP + NS - 1], s0);
+          Lk[e] -= (s0 + s1);
         }
         __syncwarp();
       }
-      // dense copy
-      for (int e = lane; e < NS * NS; e += 32) {
+      for (int e = lane; e < NS * NS; e += 32) {  // dense copy (lower)
         const int i = e / NS, j = e - i * NS;
         Mw[e] = (j <= i) ? Lk[i * (i + 1) / 2 + j] : 0.0;
       }
       __syncwarp();
-      // Cholesky, lane = row
-      for (int j = 0; j < NS; ++j) {
-        double s = 0.0;
-        if (lane >= j && lane < NS) {
-          s = Mw[lane * NS + j];
-          for (int t = 0; t < j; ++t) s = fma(-Mw[lane * NS + t], Mw[j * NS + t], s);
+      double rd_mine = 1.0;  // 1 / L[lane][lane]
+#pragma unroll
+      for (int j = 0; j < NS; ++j) {  // right-looking Cholesky, lane = row
+        const double v = fmax(Mw[j * NS + j], 1e-300);
+        const double rdj = rsqrt(v);
+        double lij = 0.0;
+        const bool below = lane > j && lane < NS;
+        if (lane == j) {
+          Mw[j * NS + j] = v * rdj;
+          rd_mine = rdj;
         }
-        const double djj = sqrt(fmax(__shfl_sync(0xffffffffu, s, j), 1e-300));
-        if (lane == j) Mw[j * NS + j] = djj;
-        else if (lane > j && lane < NS) Mw[lane * NS + j] = s / djj;
+        if (below) {
+          lij = Mw[lane * NS + j] * rdj;
+          Mw[lane * NS + j] = lij;
+        }
+        __syncwarp();
+        if (below) {
+#pragma unroll
+          for (int c = j + 1; c < NS; ++c)
+            if (c <= lane) Mw[lane * NS + c] = fma(-lij, Mw[c * NS + j], Mw[lane * NS + c]);
+        }
         __syncwarp();
       }
-      // inverse, lane = column c ; write packed Li into Lk
-      if (lane < NS) {
-        const int c = lane;
+      double rdv[NS];
+#pragma unroll
+      for (int i = 0; i < NS; ++i) rdv[i] = __shfl_sync(0xffffffffu, rd_mine, i);
+      if (lane < NS) {  // triangular inverse, lane = column c: Li[i][c], i >= c
         double col[NS];
 #pragma unroll
-        for (int i = 0; i < NS; ++i) col[i] = 0.0;
-#pragma unroll
         for (int i = 0; i < NS; ++i) {
-          if (i >= c) {
-            double s = (i == c) ? 1.0 : 0.0;
+          double s = (i == lane) ? 1.0 : 0.0;
 #pragma unroll
-            for (int t = 0; t < NS; ++t)
-              if (t >= c && t < i) s = fma(-Mw[i * NS + t], col[t], s);
-            col[i] = s / Mw[i * NS + i];
-            Lk[i * (i + 1) / 2 + c] = col[i];
-          }
+          for (int t = 0; t < i; ++t) s = fma(-Mw[i * NS + t], col[t], s);
+          col[i] = (i >= lane) ? s * rdv[i] : 0.0;
+          if (i >= lane) Lk[i * (i + 1) / 2 + lane] = col[i];
+          Ld[i * GP + lane] = col[i];
         }
       }
       __syncwarp();
+      if (k > 0) {
+        double* Gk = P.G + (size_t)(k - 1) * NS * GP;
+        for (int e = lane; e < NS * GP; e += 32) {  // G_k[r][c] = sum_{i<NX} Li_k[r][i] Ls[i][c]
+          const int r = e / GP, c = e - r * GP;
+          double s = 0.0;
+#pragma unroll
+          for (int i = 0; i < NX; ++i) s = fma(Ld[r * GP + i], Lsv[i * GP + c], s);
+          Gk[e] = s;
+        }
+        __syncwarp();
+      }
     }
   }
   __syncthreads();
 }
 
-// ---- solve M v = rhs in place (rhs in P.xt), warp 0, lane = row of the stage block ------------------------------------
+// ---- solve M v = rhs in place (rhs in P.xt) -------------------------------------------------------------------------
 template <int NX, int NU>
 __device__ void block_solve(Prob<NX, NU>& P) {
-  constexpr int NS = NX + NU, NP = Prob<NX, NU>::NP;
-  if (threadIdx.x >= 32) return;
-  const int lane = threadIdx.x, N = P.N;
-  double* v = P.xt;
-  double* w = P.Vw;  // NS scratch
-  // forward: y_k = Li_k (r_k - Ls_{k-1} y_{k-1})
-  for (int k = 0; k <= N; ++k) {
-    const int ns = (k < N) ? NS : NX;
-    double t = 0.0;
-    if (lane < ns) {
-      t = v[k * NS + lane];
-      if (k > 0 && lane < NX) {
-        const double* ls = P.Ls + ((k - 1) * NX + lane) * NS;
-        const double* yp = v + (k - 1) * NS;
-        double s0 = 0.0, s1 = 0.0;
+  constexpr int NS = NX + NU, NP = Prob<NX, NU>::NP, GP = Prob<NX, NU>::GP, HP = Prob<NX, NU>::HP;
+  const int tid = threadIdx.x, N = P.N, n = P.n;
+  // c_k = Li_k r_k for every stage (parallel)
+  for (int row = tid; row < n; row += ADMM_THREADS) {
+    const int k = row / NS, i = row - k * NS;
+    const double* li = P.Li + k * NP + i * (i + 1) / 2;
+    const double* r = P.xt + k * NS;
+    double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-        for (int j = 0; j + 1 < NS; j += 2) {
-          s0 = fma(ls[j], yp[j], s0);
-          s1 = fma(ls[j + 1], yp[j + 1], s1);
-        }
-        if (NS & 1) s0 = fma(ls[NS - 1], yp[NS - 1], s0);
-        t -= (s0 + s1);
-      }
-      w[lane] = t;
+    for (int j = 0; j < NS; j += 2) {
+      if (j <= i) s0 = fma(li[j], r[j], s0);
+      if (j + 1 <= i && j + 1 < NS) s1 = fma(li[j + 1], r[j + 1], s1);
     }
-    __syncwarp();
-    if (lane < ns) {
-      const double* li = P.Lp + k * NP + lane * (lane + 1) / 2;
-      double s0 = 0.0, s1 = 0.0;
-      int j = 0;
-      for (; j + 1 <= lane; j += 2) {
-        s0 = fma(li[j], w[j], s0);
-        s1 = fma(li[j + 1], w[j + 1], s1);
-      }
-      if (j <= lane) s0 = fma(li[j], w[j], s0);
-      v[k * NS + lane] = s0 + s1;
-    }
-    __syncwarp();
+    P.w[row] = s0 + s1;
   }
-  // backward: x_k = Li_k^T (y_k - Ls_k^T x_{k+1})
-  for (int k = N; k >= 0; --k) {
-    const int ns = (k < N) ? NS : NX;
-    if (lane < ns) {
-      double t = v[k * NS + lane];
-      if (k < N) {
-        const double* ls = P.Ls + k * NX * NS + lane;
-        const double* xn = v + (k + 1) * NS;
-        double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-        for (int i = 0; i + 1 < NX; i += 2) {
-          s0 = fma(ls[i * NS], xn[i], s0);
-          s1 = fma(ls[(i + 1) * NS], xn[i + 1], s1);
-        }
-        if (NX & 1) s0 = fma(ls[(NX - 1) * NS], xn[NX - 1], s0);
-        t -= (s0 + s1);
-      }
-      w[lane] = t;
-    }
-    __syncwarp();
-    if (lane < ns) {
-      const double* lp = P.Lp + k * NP;
+  __syncthreads();
+  // forward chain y_k = c_k - G_k y_{k-1} (warp 0, lane = row)
+  if (tid < NS) {
+    constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
+    const double* g = P.G + tid * GP;
+    for (int k = 1; k <= N; ++k) {
+      const double* yp = P.w + (k - 1) * NS;
       double s0 = 0.0, s1 = 0.0;
-      int i = lane;
-      for (; i + 1 < ns; i += 2) {
-        s0 = fma(lp[i * (i + 1) / 2 + lane], w[i], s0);
-        s1 = fma(lp[(i + 1) * (i + 2) / 2 + lane], w[i + 1], s1);
+      if (NS % 2 == 0) {
+        const double2* g2 = reinterpret_cast<const double2*>(g);
+        const double2* y2 = reinterpret_cast<const double2*>(yp);
+#pragma unroll
+        for (int c = 0; c < NS / 2; ++c) {
+          const double2 a = g2[c], b = y2[c];
+          s0 = fma(a.x, b.x, s0);
+          s1 = fma(a.y, b.y, s1);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < NS; ++c) {
+          if (c & 1) s1 = fma(g[c], yp[c], s1);
+          else s0 = fma(g[c], yp[c], s0);
+        }
       }
-      if (i < ns) s0 = fma(lp[i * (i + 1) / 2 + lane], w[i], s0);
-      v[k * NS + lane] = s0 + s1;
+      if (k < N || tid < NX) P.w[k * NS + tid] -= (s0 + s1);
+      g += NS * GP;
+      __syncwarp(mask);
     }
-    __syncwarp();
+  }
+  __syncthreads();
+  // d_k = Li_k' y_k for every stage (parallel)
+  for (int row = tid; row < n; row += ADMM_THREADS) {
+    const int k = row / NS, i = row - k * NS;
+    const int ns = (k < N) ? NS : NX;
+    const double* lk = P.Li + k * NP + i;
+    const double* yv = P.w + k * NS;
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+    for (int j = 0; j < NS; j += 2) {
+      if (j >= i && j < ns) s0 = fma(lk[j * (j + 1) / 2], yv[j], s0);
+      if (j + 1 >= i && j + 1 < ns) s1 = fma(lk[(j + 1) * (j + 2) / 2], yv[j + 1], s1);
+    }
+    P.xt[row] = s0 + s1;
+  }
+  __syncthreads();
+  // backward chain v_k = d_k - H_k v_{k+1}[0:NX] (warp 0, lane = row)
+  if (tid < NS) {
+    constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
+    const double* h = P.H + (size_t)(N - 1) * NS * HP + tid * HP;
+    for (int k = N - 1; k >= 0; --k) {
+      const double* vn = P.xt + (k + 1) * NS;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int i = 0; i + 1 < NX; i += 2) {
+        s0 = fma(h[i], vn[i], s0);
+        s1 = fma(h[i + 1], vn[i + 1], s1);
+      }
+      if (NX & 1) s0 = fma(h[NX - 1], vn[NX - 1], s0);
+      P.xt[k * NS + tid] -= (s0 + s1);
+      h -= NS * HP;
+      __syncwarp(mask);
+    }
   }
 }
 
@@ -330,17 +378,15 @@ struct CheckOut {
 template <int NX, int NU>
 __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& S, bool approx) {
   const int tid = threadIdx.x;
-  const double INF_T = OSQP_INFTY * MIN_SCALING;
-  // --- m-indexed quantities
   double a[6] = {0, 0, 0, 0, 0, 0};  // max: pri_u, |Ax|_u, |z|_u, pri_s, |Ax|_s, |z|_s
   double b[2] = {0, 0};              // max: |E dy_proj| ; (dual infeas) bound violation flag as max
   double lhs[1] = {0};
-  double ndx[3] = {0, 0, 0};  // max |D dx|, max |Pb dx / D|, (filled below)
+  double ndx[3] = {0, 0, 0};  // max |D dx|, max |Pb dx / D|
   double qdx[1] = {0};
   for (int j = tid; j < P.n; j += ADMM_THREADS) {
-    const double dx = P.xt[j];
-    ndx[0] = fmax(ndx[0], fabs(P.D[j] * dx));
-    ndx[1] = fmax(ndx[1], fabs(P.Pb[j] * dx / P.D[j]));
+    const double dx = P.xt[j], Dj = P.D[j];
+    ndx[0] = fmax(ndx[0], fabs(Dj * dx));
+    ndx[1] = fmax(ndx[1], fabs(P.Pb[j] * dx / Dj));
     qdx[0] = fma(P.qb[j], dx, qdx[0]);
   }
   block_reduce<3, true>(ndx, P.red);
@@ -349,7 +395,8 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
   const double eps_pinf = f * S.eps_prim_inf, eps_dinf = f * S.eps_dual_inf;
   const double nrm_dx = ndx[0];
   for (int r = tid; r < P.m; r += ADMM_THREADS) {
-    const double Ax = P.A_row(r, P.x), zz = P.z[r], Ei = 1.0 / P.E[r];
+    const double Er = P.E[r];
+    const double Ax = P.A_row(r, P.x), zz = P.z[r], Ei = 1.0 / Er;
     a[0] = fmax(a[0], fabs(Ei * (Ax - zz)));
     a[1] = fmax(a[1], fabs(Ei * Ax));
     a[2] = fmax(a[2], fabs(Ei * zz));
@@ -357,14 +404,14 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
     a[4] = fmax(a[4], fabs(Ax));
     a[5] = fmax(a[5], fabs(zz));
     // primal infeasibility: project dy on the polar of the recession cone of [l,u]
-    const double l = P.lbar(r), u = P.ubar(r);
+    const double l = P.lbs[r], u = P.ubs[r];
     double dy = P.zt[r];
     const bool uinf = u > INF_T, linf = l < -INF_T;
     if (uinf && linf) dy = 0.0;
     else if (uinf) dy = fmin(dy, 0.0);
     else if (linf) dy = fmax(dy, 0.0);
     P.zt[r] = dy;  // projected dy (consumed below by At_col)
-    b[0] = fmax(b[0], fabs(P.E[r] * dy));
+    b[0] = fmax(b[0], fabs(Er * dy));
     lhs[0] += u * fmax(dy, 0.0) + l * fmin(dy, 0.0);
     // dual infeasibility: (A dx)_r must stay inside the recession cone
     const double Adx = P.A_row(r, P.xt) * Ei;
@@ -374,7 +421,6 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
   block_reduce<6, true>(a, P.red);
   block_reduce<2, true>(b, P.red);
   block_reduce<1, false>(lhs, P.red);
-  // --- n-indexed quantities
   double d[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // dua_u, |Px|_u, |Aty|_u, |q|_u, dua_s, |Px|_s, |Aty|_s, |q|_s
   double e[1] = {0};                       // |D^-1 A' dy_proj|
   for (int j = tid; j < P.n; j += ADMM_THREADS) {
@@ -411,41 +457,43 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
 }
 
 template <int NX, int NU>
-__global__ void __launch_bounds__(ADMM_THREADS) admm_kernel(int N, int nbatch, const double* __restrict__ ABg,
-                                                            const double* __restrict__ beqg,
-                                                            const double* __restrict__ qg,
-                                                            const double* __restrict__ Pdiag,
-                                                            const double* __restrict__ lb,
-                                                            const double* __restrict__ ub, GpmpcAdmmSettings S,
-                                                            const int* __restrict__ active, double* __restrict__ xg,
-                                                            double* __restrict__ yg, double* __restrict__ rhog,
-                                                            int* __restrict__ status_g, int* __restrict__ iters_g,
-                                                            double* __restrict__ obj_g, double* __restrict__ pri_g,
-                                                            double* __restrict__ dua_g) {
+__global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch, const double* __restrict__ ABg,
+                                                               const double* __restrict__ beqg,
+                                                               const double* __restrict__ qg,
+                                                               const double* __restrict__ Pdiag,
+                                                               const double* __restrict__ lb,
+                                                               const double* __restrict__ ub, GpmpcAdmmSettings S,
+                                                               const int* __restrict__ active,
+                                                               double* __restrict__ scratch, double* __restrict__ xg,
+                                                               double* __restrict__ yg, double* __restrict__ rhog,
+                                                               int* __restrict__ status_g, int* __restrict__ iters_g,
+                                                               double* __restrict__ obj_g, double* __restrict__ pri_g,
+                                                               double* __restrict__ dua_g) {
   constexpr int NS = NX + NU;
-  extern __shared__ double smem[];
+  extern __shared__ __align__(16) double smem[];
   const int b = blockIdx.x, tid = threadIdx.x;
   if (b >= nbatch) return;
   if (active && !active[b]) return;
   Prob<NX, NU> P;
   P.carve(smem, N);
-  P.lb = lb; P.ub = ub;
   P.sigma = S.sigma;
   P.rho = (S.rho_from_input && rhog[b] > 0.0) ? rhog[b] : S.rho;
   P.c = 1.0;
   const int n = P.n, m = P.m, neq = P.neq;
+  P.D = scratch + (size_t)b * (n + m);
+  P.E = P.D + n;
 
   // ---- load (coalesced) -----------------------------------------------------------------------------------------
   for (int i = tid; i < N * NX * NS; i += ADMM_THREADS) P.AB[i] = ABg[(size_t)b * N * NX * NS + i];
   for (int i = tid; i < N * NX; i += ADMM_THREADS) P.Nd[i] = -1.0;
-  for (int i = tid; i < NX; i += ADMM_THREADS) P.Ei[i] = 1.0;
+  for (int i = tid; i < 8; i += ADMM_THREADS) P.Ei[i] = 1.0;
   for (int i = tid; i < n; i += ADMM_THREADS) {
     P.Bd[i] = 1.0; P.D[i] = 1.0;
     P.Pb[i] = Pdiag[i];
     P.qb[i] = qg[(size_t)b * n + i];
   }
   for (int i = tid; i < m; i += ADMM_THREADS) P.E[i] = 1.0;
-  for (int i = tid; i < neq; i += ADMM_THREADS) P.beq[i] = beqg[(size_t)b * neq + i];
+  for (int i = tid; i < N * NS * Prob<NX, NU>::HP; i += ADMM_THREADS) P.H[i] = 0.0;  // pad columns stay zero
   __syncthreads();
 
   // ---- modified Ruiz equilibration + cost scaling (OSQP scaling.c; oracle/mpc.py OSQPOracle._scale) --------------------
@@ -505,9 +553,18 @@ __global__ void __launch_bounds__(ADMM_THREADS) admm_kernel(int N, int nbatch, c
     P.c *= ct;
     __syncthreads();
   }
-  for (int r = tid; r < neq; r += ADMM_THREADS) P.beq[r] *= P.E[r];
-  __syncthreads();
-
+  // scaled bounds: equality rows l = u = E beq ; box rows E lb, E ub
+  for (int r = tid; r < m; r += ADMM_THREADS) {
+    const double Er = P.E[r];
+    if (r < neq) {
+      const double v = Er * beqg[(size_t)b * neq + r];
+      P.lbs[r] = v;
+      P.ubs[r] = v;
+    } else {
+      P.lbs[r] = Er * lb[r - neq];
+      P.ubs[r] = Er * ub[r - neq];
+    }
+  }
   // ---- iterates (scaled): x = x_in / D ; z = Abar x ; y = c y_in / E -----------------------------------------------------
   for (int j = tid; j < n; j += ADMM_THREADS) P.x[j] = S.warm_x ? xg[(size_t)b * n + j] / P.D[j] : 0.0;
   for (int r = tid; r < m; r += ADMM_THREADS) P.y[r] = S.warm_y ? P.c * yg[(size_t)b * m + r] / P.E[r] : 0.0;
@@ -535,7 +592,7 @@ __global__ void __launch_bounds__(ADMM_THREADS) admm_kernel(int N, int nbatch, c
       const double zt = P.A_row(r, P.xt);
       const double rr = P.rho_row(r), zp = P.z[r], yy = P.y[r];
       const double zr = alpha * zt + (1.0 - alpha) * zp;
-      const double zn = fmin(fmax(zr + yy / rr, P.lbar(r)), P.ubar(r));
+      const double zn = fmin(fmax(zr + yy / rr, P.lbs[r]), P.ubs[r]);
       const double dy = rr * (zr - zn);
       P.z[r] = zn;
       P.y[r] = yy + dy;
@@ -594,19 +651,11 @@ __global__ void __launch_bounds__(ADMM_THREADS) admm_kernel(int N, int nbatch, c
 }
 
 template <int NX, int NU>
-size_t admm_smem_bytes(int N) {
-  constexpr int NS = NX + NU, NP = NS * (NS + 1) / 2;
-  const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
-  size_t d = (size_t)N * NX * NS * 2 + N * NX + NX + 6 * n + m + NX * (N + 1) + 3 * m + (size_t)(N + 1) * NP + NS * NS +
-             2 * NS + 64;
-  return d * sizeof(double);
-}
-
-template <int NX, int NU>
 int launch_admm(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
                 const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x, double* y,
                 double* rho, int* status, int* iters, double* obj, double* pri, double* dua, cudaStream_t stream) {
-  const size_t smem = admm_smem_bytes<NX, NU>(N);
+  constexpr int NS = NX + NU;
+  const size_t smem = Prob<NX, NU>::smem_doubles(N) * sizeof(double);
   if (smem > 227 * 1024) {
     gpmpc_set_error("gpmpc_admm_solve: horizon too long for the shared-memory resident solver");
     return GPMPC_ERR_ARG;
@@ -615,13 +664,33 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
   static size_t configured = 0;
   if (smem > configured) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    // the default carveout heuristic left one CTA per SM resident; ask for the full 228 KB so 3-4 QPs share an SM
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured = smem;
   }
-  kern<<<B, ADMM_THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, x, y, rho, status, iters, obj,
-                                          pri, dua);
-  return gpmpc_check_launch("admm");
+  // stream-ordered scratch for the cumulative scaling vectors D (n) and E (m) of every scenario
+  const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
+  static bool pool_configured = false;
+  if (!pool_configured) {  // keep freed blocks in the pool: without this every call re-allocates from the driver
+    int dev = 0;
+    cudaMemPool_t pool;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      unsigned long long thr = ~0ULL;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+    pool_configured = true;
+  }
+  double* scratch = nullptr;
+  if (cudaMallocAsync(&scratch, sizeof(double) * (n + m) * (size_t)B, stream) != cudaSuccess) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_admm_solve: could not allocate the scaling scratch");
+    return GPMPC_ERR_CUDA;
+  }
+  kern<<<B, ADMM_THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters,
+                                          obj, pri, dua);
+  int rc = gpmpc_check_launch("admm");
+  cudaFreeAsync(scratch, stream);
+  return rc;
 }
 
 }  // namespace
