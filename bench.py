@@ -259,7 +259,7 @@ def run_b200_arm(args):
     peak64 = fp64_peak_tflops(torch) if rank == 0 else None
     ctl.timers = me.PhaseTimers()
     clocks = ClockSampler(local)
-    qp_it, launches = 0.0, 0
+    qp_it, launches = torch.zeros((), dtype=torch.float64, device="cuda"), 0
     barrier()
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -267,7 +267,7 @@ def run_b200_arm(args):
     for _ in range(K):
         sol = mc.step()
         launches += ctl.last_kernel_launches + 1
-        qp_it += float(sol.qp_iterations.sum().item())
+        qp_it += sol.qp_iterations.sum()     # stays on the device: no host synchronisation inside the timed region
     e1.record()
     barrier()
     clk = clocks.stop()
@@ -342,7 +342,7 @@ def run_b200_arm(args):
             "data": "synthetic", "config": config_dict(args, world), "e2e": e2e, "gpu_launches": launches,
             "roofline": roof, "cpu_baseline": cpu_base, "clocks": clk,
             "phases_share_of_step": share, "phase_ms_per_step": {k: v[0] / K for k, v in phases.items()},
-            "mean_admm_iters_per_solve": qp_it / (B * K), "p50_step_latency_ms": ms / K,
+            "mean_admm_iters_per_solve": float(qp_it.item()) / (B * K), "p50_step_latency_ms": ms / K,
             "fp64_peak_tflops_measured": peak64,
             "outcomes": {n: int(stats[i].item()) for i, n in enumerate(
                 ("", "success", "crash", "fuel_exhausted", "constraint_violation", "timeout", "divergence")) if n},

@@ -194,21 +194,11 @@ __device__ void factorize(Prob<NX, NU>& P) {
             s1 = fma(a[t + 1], ld[t + 1], s1);
           }
           if (NS & 1) s0 = fma(a[NS - 1], ld[NS - 1], s0);
-          Lsv[i * GP + j] = (rho_eq * P.Nd[(k - 1) * NX + i]) * (s0 + s1);
+          const double v = (rho_eq * P.Nd[(k - 1) * NX + i]) * (s0 + s1);
+          Lsv[i * GP + j] = v;
+          P.H[(size_t)(k - 1) * NS * HP + e] = v;   // kept (row-major NX x NS) for the parallel G / H phase below
         }
         __syncwarp();
-        double* Hk = P.H + (size_t)(k - 1) * NS * HP;
-        for (int e = lane; e < NS * NX; e += 32) {  // H_{k-1}[r][i] = sum_j Li_{k-1}[j][r] Ls[i][j]
-          const int r = e / NX, i = e - r * NX;
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int j = 0; j + 1 < NS; j += 2) {
-            s0 = fma(Ld[j * GP + r], Lsv[i * GP + j], s0);
-            s1 = fma(Ld[(j + 1) * GP + r], Lsv[i * GP + j + 1], s1);
-          }
-          if (NS & 1) s0 = fma(Ld[(NS - 1) * GP + r], Lsv[i * GP + NS - 1], s0);
-          Hk[r * HP + i] = s0 + s1;
-        }
         for (int e = lane; e < NX * (NX + 1) / 2; e += 32) {  // Schur: M_kk[i][j] -= sum_t Ls[i][t] Ls[j][t]
           int i = 0;
           while ((i + 1) * (i + 2) / 2 <= e) ++i;
@@ -268,39 +258,90 @@ __device__ void factorize(Prob<NX, NU>& P) {
         }
       }
       __syncwarp();
-      if (k > 0) {
-        double* Gk = P.G + (size_t)(k - 1) * NS * GP;
-        for (int e = lane; e < NS * GP; e += 32) {  // G_k[r][c] = sum_{i<NX} Li_k[r][i] Ls[i][c]
-          const int r = e / GP, c = e - r * GP;
-          double s = 0.0;
+    }
+  }
+  __syncthreads();
+  // Phase 3 (all threads): G_k = Li_k[:, :NX] Ls_{k-1} for k = 1..N  (Ls_{k-1} sits in the H region, Li packed)
+  for (int e = tid; e < N * NS * GP; e += ADMM_THREADS) {
+    const int k1 = e / (NS * GP), rem = e - k1 * NS * GP, r = rem / GP, c = rem - r * GP;  // k1 = k - 1
+    const double* li = P.Li + (size_t)(k1 + 1) * NP + r * (r + 1) / 2;
+    const double* ls = P.H + (size_t)k1 * NS * HP + c;
+    double sacc = 0.0;
+    if (c < NS) {
 #pragma unroll
-          for (int i = 0; i < NX; ++i) s = fma(Ld[r * GP + i], Lsv[i * GP + c], s);
-          Gk[e] = s;
+      for (int i = 0; i < NX; ++i)
+        if (i <= r) sacc = fma(li[i], ls[i * NS], sacc);
+    }
+    P.G[e] = sacc;
+  }
+  __syncthreads();
+  // Phase 4 (one warp per stage, in place): H_k[r][i] = sum_{j>=r} Li_k[j][r] Ls_k[i][j]
+  {
+    const int warp = tid >> 5, lane = tid & 31;
+    constexpr int PER = (NS * NX + 31) / 32;
+    for (int k = warp; k < N; k += ADMM_THREADS / 32) {
+      double* Hk = P.H + (size_t)k * NS * HP;
+      const double* lk = P.Li + (size_t)k * NP;
+      double out[PER];
+#pragma unroll
+      for (int t = 0; t < PER; ++t) {
+        const int e = lane + 32 * t;
+        double sacc = 0.0;
+        if (e < NS * NX) {
+          const int r = e / NX, i = e - r * NX;
+#pragma unroll
+          for (int j = 0; j < NS; ++j)
+            if (j >= r) sacc = fma(lk[j * (j + 1) / 2 + r], Hk[i * NS + j], sacc);
         }
-        __syncwarp();
+        out[t] = sacc;
       }
+      __syncwarp();
+#pragma unroll
+      for (int t = 0; t < PER; ++t) {
+        const int e = lane + 32 * t;
+        if (e < NS * NX) {
+          const int r = e / NX, i = e - r * NX;
+          Hk[r * HP + i] = out[t];
+        }
+      }
+      __syncwarp();
+      for (int e = lane; e < NS; e += 32)
+        for (int i = NX; i < HP; ++i) Hk[e * HP + i] = 0.0;   // pad columns
     }
   }
   __syncthreads();
 }
 
-// ---- solve M v = rhs in place (rhs in P.xt) -------------------------------------------------------------------------
+// ---- one KKT solve per ADMM iteration: x_tilde = M^{-1} (sigma x - q + Abar' (rho z - y)) into P.xt ---------------------
+// Phase A fuses the right-hand side with c_k = Li_k r_k: the columns of a stage are owned by consecutive lanes of ONE
+// warp (SPW stages per warp and round), so only a __syncwarp separates the two.
 template <int NX, int NU>
 __device__ void block_solve(Prob<NX, NU>& P) {
   constexpr int NS = NX + NU, NP = Prob<NX, NU>::NP, GP = Prob<NX, NU>::GP, HP = Prob<NX, NU>::HP;
+  constexpr int SPW = 32 / NS;                       // stages per warp per round
+  constexpr int SPR = SPW * (ADMM_THREADS / 32);     // stages per round
   const int tid = threadIdx.x, N = P.N, n = P.n;
-  // c_k = Li_k r_k for every stage (parallel)
-  for (int row = tid; row < n; row += ADMM_THREADS) {
-    const int k = row / NS, i = row - k * NS;
-    const double* li = P.Li + k * NP + i * (i + 1) / 2;
-    const double* r = P.xt + k * NS;
-    double s0 = 0.0, s1 = 0.0;
+  {
+    const int warp = tid >> 5, lane = tid & 31;
+    const int slot = lane / NS, i = lane - slot * NS;
+    for (int k0 = 0; k0 <= N; k0 += SPR) {
+      const int k = k0 + warp * SPW + slot;
+      const bool on = slot < SPW && k <= N && (k < N || i < NX);
+      const int row = k * NS + i;
+      if (on) P.xt[row] = fma(P.sigma, P.x[row], -P.qb[row]) + P.At_col(row, P.zt);
+      __syncwarp();
+      if (on) {
+        const double* li = P.Li + k * NP + i * (i + 1) / 2;
+        const double* r = P.xt + k * NS;
+        double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-    for (int j = 0; j < NS; j += 2) {
-      if (j <= i) s0 = fma(li[j], r[j], s0);
-      if (j + 1 <= i && j + 1 < NS) s1 = fma(li[j + 1], r[j + 1], s1);
+        for (int j = 0; j < NS; j += 2) {
+          if (j <= i) s0 = fma(li[j], r[j], s0);
+          if (j + 1 <= i && j + 1 < NS) s1 = fma(li[j + 1], r[j + 1], s1);
+        }
+        P.w[row] = s0 + s1;
+      }
     }
-    P.w[row] = s0 + s1;
   }
   __syncthreads();
   // forward chain y_k = c_k - G_k y_{k-1} (warp 0, lane = row)
@@ -374,7 +415,7 @@ struct CheckOut {
 
 // Residuals, termination, infeasibility certificates and the rho estimate (oracle/mpc.py _residuals/_check/_rho_estimate;
 // OSQP auxil.c compute_pri_res/compute_dua_res/is_primal_infeasible/is_dual_infeasible/compute_rho_estimate).
-// dx is in P.xt, dy in P.zt.  All threads participate.
+// dx is in P.w, dy in P.zt.  All threads participate.
 template <int NX, int NU>
 __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& S, bool approx) {
   const int tid = threadIdx.x;
@@ -384,7 +425,7 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
   double ndx[3] = {0, 0, 0};  // max |D dx|, max |Pb dx / D|
   double qdx[1] = {0};
   for (int j = tid; j < P.n; j += ADMM_THREADS) {
-    const double dx = P.xt[j], Dj = P.D[j];
+    const double dx = P.w[j], Dj = P.D[j];
     ndx[0] = fmax(ndx[0], fabs(Dj * dx));
     ndx[1] = fmax(ndx[1], fabs(P.Pb[j] * dx / Dj));
     qdx[0] = fma(P.qb[j], dx, qdx[0]);
@@ -414,7 +455,7 @@ __device__ CheckOut check_termination(Prob<NX, NU>& P, const GpmpcAdmmSettings& 
     b[0] = fmax(b[0], fabs(Er * dy));
     lhs[0] += u * fmax(dy, 0.0) + l * fmin(dy, 0.0);
     // dual infeasibility: (A dx)_r must stay inside the recession cone
-    const double Adx = P.A_row(r, P.xt) * Ei;
+    const double Adx = P.A_row(r, P.w) * Ei;
     const bool bad = (!uinf && Adx > eps_dinf * nrm_dx) || (!linf && Adx < -eps_dinf * nrm_dx);
     b[1] = fmax(b[1], bad ? 1.0 : 0.0);
   }
@@ -578,46 +619,57 @@ __global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch
   CheckOut co;
   co.pri = co.dua = 0.0;
   const double alpha = S.alpha;
+  // w = rho*z - y (into zt) for the first iteration
+  for (int r = tid; r < m; r += ADMM_THREADS) P.zt[r] = (S.max_iter > 0) ? fma(P.rho_row(r), P.z[r], -P.y[r]) : 0.0;
+  for (int j = tid; j < n; j += ADMM_THREADS) P.w[j] = 0.0;
+  __syncthreads();
   for (it = 1; it <= S.max_iter; ++it) {
-    // w = rho*z - y  (into zt)
-    for (int r = tid; r < m; r += ADMM_THREADS) P.zt[r] = fma(P.rho_row(r), P.z[r], -P.y[r]);
+    const bool can_check = S.check_every > 0 && (it % S.check_every) == 0;
+    const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval > 0 && (it % S.adaptive_rho_interval) == 0;
+    const bool checking = can_check || can_adapt || it == S.max_iter;
+    block_solve(P);  // xt <- x_tilde  (reads zt = rho z - y)
     __syncthreads();
-    // rhs = sigma x - q + Abar' w (into xt)
-    for (int j = tid; j < n; j += ADMM_THREADS) P.xt[j] = fma(P.sigma, P.x[j], -P.qb[j]) + P.At_col(j, P.zt);
-    __syncthreads();
-    block_solve(P);  // xt <- x_tilde
-    __syncthreads();
-    // z_tilde = Abar x_tilde ; z, y updates ; dy into zt
+    // z_tilde = Abar x_tilde ; z, y, x updates.  Normal iterations leave the next w = rho z - y in zt; iterations that
+    // run the termination check leave dy in zt and dx in w instead (consumed by check_termination).
+    const double rho_eq = RHO_EQ_OVER_INEQ * P.rho;
+    const double inv_eq = 1.0 / rho_eq, inv_rho = 1.0 / P.rho, inv_min = 1.0 / RHO_MIN;
     for (int r = tid; r < m; r += ADMM_THREADS) {
       const double zt = P.A_row(r, P.xt);
       const double rr = P.rho_row(r), zp = P.z[r], yy = P.y[r];
+      const double ri = (rr == rho_eq) ? inv_eq : ((rr == RHO_MIN) ? inv_min : inv_rho);
       const double zr = alpha * zt + (1.0 - alpha) * zp;
-      const double zn = fmin(fmax(zr + yy / rr, P.lbs[r]), P.ubs[r]);
+      const double zn = fmin(fmax(fma(yy, ri, zr), P.lbs[r]), P.ubs[r]);
       const double dy = rr * (zr - zn);
+      const double yn = yy + dy;
       P.z[r] = zn;
-      P.y[r] = yy + dy;
-      P.zt[r] = dy;
+      P.y[r] = yn;
+      P.zt[r] = checking ? dy : fma(rr, zn, -yn);
     }
-    __syncthreads();  // all reads of xt (x_tilde) by A_row are done before it is overwritten with dx
     for (int j = tid; j < n; j += ADMM_THREADS) {
       const double xp = P.x[j];
       const double xn = alpha * P.xt[j] + (1.0 - alpha) * xp;
       P.x[j] = xn;
-      P.xt[j] = xn - xp;
+      if (checking) P.w[j] = xn - xp;
     }
     __syncthreads();
-    const bool can_check = S.check_every > 0 && (it % S.check_every) == 0;
-    const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval > 0 && (it % S.adaptive_rho_interval) == 0;
-    if (can_check || can_adapt) {
-      co = check_termination(P, S, false);
-      if (can_check && co.status != GPMPC_QP_UNSOLVED) {
-        status = co.status;
-        break;
+    if (checking) {
+      if (can_check || can_adapt) {
+        co = check_termination(P, S, false);
+        if (can_check && co.status != GPMPC_QP_UNSOLVED) {
+          status = co.status;
+          break;
+        }
+        if (can_adapt &&
+            (co.rho_est > P.rho * S.adaptive_rho_tolerance || co.rho_est < P.rho / S.adaptive_rho_tolerance)) {
+          P.rho = co.rho_est;
+          __syncthreads();
+          factorize(P);
+        }
       }
-      if (can_adapt && (co.rho_est > P.rho * S.adaptive_rho_tolerance || co.rho_est < P.rho / S.adaptive_rho_tolerance)) {
-        P.rho = co.rho_est;
+      if (it < S.max_iter) {  // restore zt = rho z - y for the next iteration
         __syncthreads();
-        factorize(P);
+        for (int r = tid; r < m; r += ADMM_THREADS) P.zt[r] = fma(P.rho_row(r), P.z[r], -P.y[r]);
+        __syncthreads();
       }
     }
   }

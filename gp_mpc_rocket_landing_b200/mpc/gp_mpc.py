@@ -48,6 +48,7 @@ class GPMPCConfig(MPCConfig):
     qp_check_every: int = 25          # OSQP default check_termination
     qp_adaptive_rho_interval: int = 25  # iteration based (OSQP's default is timing based, i.e. not reproducible)
     qp_scaling: int = 3               # osqp_rti.py:477
+    qp_keep_rho: bool = True          # the adapted rho persists across solves, as inside one OSQP solver object
 
 
 def _is_dev(a):
@@ -168,6 +169,7 @@ class GPMPC:
             if st is not None:
                 st.has_warm = False
                 st.ws.y.zero_()
+                st.ws.rho.zero_()
 
     def reset_scenarios(self, mask, X0) -> None:
         """Per-scenario `reset_warm_start` for the batched state: scenarios with mask != 0 restart from the hover
@@ -181,13 +183,14 @@ class GPMPC:
         hover[:, :, 0] = (ge.to_dev(X0)[:, 0] * float(self.dynamics.params.g0))[:, None]
         st.U_warm = torch.where(mask[:, None, None], hover, st.U_warm).contiguous()
         st.ws.y.masked_fill_(mask[:, None], 0.0)
+        st.ws.rho.masked_fill_(mask, 0.0)
 
     def _settings(self):
         c = self.config
         return _lib.AdmmSettings.reference_defaults(
             max_iter=c.qp_max_iter, eps_abs=c.qp_eps_abs, eps_rel=c.qp_eps_rel, check_every=c.qp_check_every,
             adaptive_rho_interval=c.qp_adaptive_rho_interval, scaling=c.qp_scaling,
-            warm_x=1, warm_y=1, rho_from_input=0, commit_y_solved_only=1)
+            warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1)
 
     # ------------------------------------------------------------------------------------------------ core
     def _variance_and_cov(self, st: _BatchState, X, U, active):
@@ -317,8 +320,7 @@ class GPMPC:
         success = st.converged.to(torch.bool)
         status = st.converged.to(torch.int8)
         has_cov = self._model is not None and self.config.use_gp_uncertainty
-        if dev_in:
-            torch.cuda.current_stream().synchronize()
+        if dev_in:  # stream-ordered results, no host synchronisation (solve_time is then the launch time only)
             sol = BatchMPCSolution(
                 u0=st.U[:, 0].clone(), X_opt=st.X.clone(), U_opt=st.U.clone(), cost=st.cost.clone(),
                 iterations=st.n_iter.clone(), success=success, status=status, solve_time=0.0,

@@ -193,8 +193,6 @@ class OSQPRTIMPC:
         sol = BatchRTISolution(u0=out(U_opt[:, 0]), X_opt=out(X_opt), U_opt=out(U_opt), cost=out(cost),
                                osqp_iterations=out(self._ws.iters), success=out(ok), status=out(self._ws.status),
                                prep_time_ms=0.0, feedback_time_ms=0.0, total_time_ms=0.0)
-        if dev_in:
-            torch.cuda.current_stream().synchronize()
         sol.total_time_ms = sol.feedback_time_ms = (time.perf_counter() - t0) * 1000
         return sol
 

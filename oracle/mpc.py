@@ -518,7 +518,8 @@ class GPMPCOracle:
     """gp_mpc.py:229-369 specialised to 7 states, with the inner IPOPT 'QP' replaced by the OSQP-form QP
     of osqp_rti.py: box bounds only; GP mean as affine term c_k=[0,0,0,0,d_v*dt]."""
 
-    def __init__(self, gp_predict, params=None, N=20, dt=0.1, settings=None, max_sqp_iter=10, use_gp_mean=True):
+    def __init__(self, gp_predict, params=None, N=20, dt=0.1, settings=None, max_sqp_iter=10, use_gp_mean=True,
+                 keep_rho=True):
         self.gp_predict = gp_predict
         self.p = params or Rocket3DoFParams()
         self.N, self.dt = N, dt
@@ -526,6 +527,10 @@ class GPMPCOracle:
         self.max_sqp_iter, self.use_gp_mean = max_sqp_iter, use_gp_mean
         self.U_warm = None
         self.y_warm = None
+        # one OSQP solver object per controller lives across solves (as osqp_rti.py:464-478/517 does): its adapted
+        # rho persists; the primal iterate is re-seeded from (X, U) and the duals from the last *solved* QP
+        self.keep_rho = keep_rho
+        self.rho_warm = None
 
     def solve(self, x0, x_target):
         N, dt, p = self.N, self.dt, self.p
@@ -555,8 +560,13 @@ class GPMPCOracle:
                     d, _ = self.gp_predict(X[k], U[k]); c_gp[k, 4:7] = d * dt
             A, l, u = build_constraints(N, X, U, x0, dt, p, "analytic", c_gp, mode="gpmpc")
             qp = OSQPOracle(Pd, q, A, l, u, self.settings)
+            if self.keep_rho and self.rho_warm is not None:
+                qp.rho = self.rho_warm
+                qp._set_rho_vec()
+                qp._factor()
             qp.warm_start(x=traj_to_vec(X, U), y=y)
             res = qp.solve()
+            self.rho_warm = res.rho
             stats.append(res.status); its.append(res.iters)
             if res.status == SOLVED:
                 Xn, Un = vec_to_traj(res.x, N); y = res.y
