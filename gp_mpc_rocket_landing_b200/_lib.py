@@ -73,6 +73,11 @@ _PROTOS = {
     "gpmpc_dgemm_nt": (c_int, [c_dp, c_long, c_dp, c_long, c_dp, c_long, c_int, c_int, c_int, c_double, c_double,
                                c_int, c_dp]),
     "gpmpc_features": (c_int, [c_int, c_dp, c_long, c_dp, c_long, c_int, c_dp, c_long, c_dp]),
+    "gpmpc_add_diag": (c_int, [c_dp, c_int, c_long, c_double, c_dp]),
+    "gpmpc_fitc_scale": (c_int, [c_dp, c_long, c_int, c_int, c_int, c_dp, c_double, c_double, c_double, c_dp, c_int,
+                                 c_dp, c_dp, c_long, c_dp, c_dp]),
+    "gpmpc_sparse_lml": (c_int, [c_int, c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                 c_dp, c_double, c_double, c_int, c_dp, c_dp]),
     "gpmpc_admm_solve": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
                                  C.POINTER(AdmmSettings), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_rollout_3dof": (c_int, [C.POINTER(ExactModel), C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_dp,

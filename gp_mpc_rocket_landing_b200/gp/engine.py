@@ -222,7 +222,7 @@ class ExactModelDev:
              ptr(self.lml), stream())
         return self
 
-    def predict(self, Xq, want_var=True, chunk=65536, col=None, keep_v=False):
+    def predict(self, Xq, want_var=True, chunk=65536, col=None, keep_v=False, var_floor=1e-10):
         """-> mean (Q,P), var (Q,P) CUDA tensors (col: a single output -> (Q,1)).  keep_v: also return the solved
         V = (L^{-1} K*^T)^T rows (Q_pad, n_pad) of the last chunk (full-covariance branch, exact_gp.py:247-254)."""
         torch = torch_()
@@ -245,10 +245,10 @@ class ExactModelDev:
             if want_var:
                 prior = f.prior_diag(Xq[s:e])
                 if prior is None:
-                    call("gpmpc_predict_var", ptr(sumsq), None, q, P, f.sv, 1e-10, ptr(ystd), ptr(var[s:e]),
+                    call("gpmpc_predict_var", ptr(sumsq), None, q, P, f.sv, var_floor, ptr(ystd), ptr(var[s:e]),
                          var.stride(0), 0, stream())
                 else:  # generic kernels: per-query prior variance
-                    var[s:e] = torch.clamp(prior - sumsq[:q], min=1e-10)[:, None] * (ystd * ystd)[None, :]
+                    var[s:e] = torch.clamp(prior - sumsq[:q], min=var_floor)[:, None] * (ystd * ystd)[None, :]
         if keep_v:
             return mean, var, V
         return mean, var
@@ -261,3 +261,144 @@ class ExactModelDev:
         return _lib.ExactModel(kind=f.kind, n=f.n, n_pad=f.n_pad, D=f.D, DP=f.DP, P=self.P, signal_var=f.sv,
                                lengthscales=ptr(f.ls), Xs=ptr(f.Xs), sq=ptr(f.sq), alpha=ptr(self.alpha),
                                ymean=ptr(self.ymean), ystd=ptr(self.ystd), L=ptr(f.L), Winv=ptr(f.Winv))
+
+
+# ====================================================================================================== sparse GP
+class SparseFactor:
+    """Inducing-point factor shared by every output with the same kernel, noise and Z (sparse_gp.py:150-232).
+
+    FITC and VFE both need (L_uu, L_B); neither depends on the targets, so P outputs cost one factorisation (the
+    reference refits them per output, sparse_gp.py:448-454).  All matrices are M_pad x M_pad with a unit diagonal in the
+    padding (M_pad = 128 for M <= 128), so the blocked DMMA TRSM of the exact GP serves the predict path unchanged."""
+
+    def __init__(self, kind, ls, sv, noise, method="fitc", jitter=1e-6):
+        self.kind = int(kind)
+        self.ls_host = np.asarray(ls, dtype=np.float64).copy()
+        self.sv, self.noise, self.jitter = float(sv), float(noise), float(jitter)
+        assert method in ("fitc", "vfe")
+        self.method = method
+
+    def fit(self, X, Z):
+        torch = torch_()
+        self.X, self.Z = to_dev(X), to_dev(Z)
+        self.n, self.D = self.X.shape
+        self.M = self.Z.shape[0]
+        if self.M > 144:
+            raise _lib.GpmpcError("SparseFactor: at most 144 inducing points (gpmpc_trsm_small keeps L_uu in shared memory)")
+        self.n_pad, self.M_pad = pad_to(self.n, 128), pad_to(self.M, 128)
+        dev = self.X.device
+        self.ls = to_dev(self.ls_host)
+        self.Xs, self.sq = scale_inputs(self.X, self.ls)
+        self.DP = self.Xs.shape[1]
+        self.Zs, self.sqz = scale_inputs(self.Z, self.ls, DP=self.DP)
+        M, n, Mp, npad = self.M, self.n, self.M_pad, self.n_pad
+        # K_uu (kept without jitter for VFE's B and the bound), L_uu = chol(K_uu + jitter I)
+        self.Kuu = gram_scaled(self.kind, self.Zs, self.sqz, M, self.Zs, self.sqz, M, self.sv, pad_identity=1)
+        self.L_uu = self.Kuu.clone()
+        call("gpmpc_add_diag", ptr(self.L_uu), M, Mp, self.jitter, stream())
+        self.W_uu, info = potrf(self.L_uu)
+        if int(info.item()) != 0:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")   # np.linalg.cholesky at sparse_gp.py:187
+        # K_uf (M_pad x n_pad) and A = L_uu^{-1} K_uf with q_ff = column sums of A^2 (sparse_gp.py:190,196)
+        self.Kuf = gram_scaled(self.kind, self.Zs, self.sqz, M, self.Xs, self.sq, n, self.sv)
+        self.A = self.Kuf.clone()
+        self.qff = torch.zeros((npad,), dtype=torch.float64, device=dev)
+        call("gpmpc_trsm_small", ptr(self.L_uu), M, Mp, ptr(self.A), npad, n, 0, ptr(self.qff), 1.0, stream())
+        return self
+
+    def factor_B(self, Yn):
+        """(L_B, c) for the normalised targets Yn (P, n_pad): sparse_gp.py:198-210 (FITC) / :225-232 (VFE)."""
+        torch = torch_()
+        M, n, Mp, npad = self.M, self.n, self.M_pad, self.n_pad
+        P = Yn.shape[0]
+        dev = Yn.device
+        self.Lam = None
+        if self.method == "fitc":
+            self.Lam = torch.empty((npad,), dtype=torch.float64, device=dev)
+            As = torch.empty_like(self.A)
+            Ylam = torch.empty_like(Yn)
+            call("gpmpc_fitc_scale", ptr(self.A), npad, Mp, n, npad, ptr(self.qff), self.sv, self.noise, 1e-10, ptr(Yn), P,
+                 ptr(self.Lam), ptr(As), npad, ptr(Ylam), stream())
+            Bm = torch.eye(Mp, dtype=torch.float64, device=dev)
+            call("gpmpc_dgemm_nt", ptr(As), npad, ptr(As), npad, ptr(Bm), Mp, Mp, Mp, npad, 1.0, 1.0, 0, stream())
+            rows, rhs, scale = self.A, Ylam, None
+        else:
+            Bm = self.Kuu.clone()
+            call("gpmpc_dgemm_nt", ptr(self.Kuf), npad, ptr(self.Kuf), npad, ptr(Bm), Mp, Mp, Mp, npad, 1.0 / self.noise,
+                 1.0, 0, stream())
+            call("gpmpc_add_diag", ptr(Bm), M, Mp, self.jitter, stream())
+            rows, rhs, scale = self.Kuf, Yn, self.noise
+        self.W_B, info = potrf(Bm)
+        if int(info.item()) != 0:
+            raise np.linalg.LinAlgError("Matrix is not positive definite")
+        self.L_B = Bm
+        # c[p, m] = sum_i rows[m, i] rhs[p, i]  (A @ (y / Lambda) or K_uf @ y / s2)
+        cT = torch.zeros((Mp, P), dtype=torch.float64, device=dev)
+        zeros, ones = torch.zeros((P,), dtype=torch.float64, device=dev), torch.ones((P,), dtype=torch.float64, device=dev)
+        call("gpmpc_predict_mean", ptr(rows), npad, M, n, ptr(rhs), npad, P, ptr(zeros), ptr(ones), ptr(cT), P, 0, stream())
+        c = cT.T.contiguous()
+        if scale is not None:
+            c = c / scale
+        return c
+
+    def solve_B(self, c):
+        out = c.clone()
+        call("gpmpc_potrs", ptr(self.L_B), self.M_pad, self.M_pad, 0, ptr(self.W_B), ptr(out), out.shape[0], 1, stream())
+        return out
+
+
+class SparseModelDev:
+    """P outputs on one SparseFactor: alpha, normalisation, LML / ELBO, predict (sparse_gp.py:150-305)."""
+
+    def __init__(self, factor: SparseFactor):
+        self.f = factor
+
+    def fit_targets(self, Y):
+        torch = torch_()
+        f = self.f
+        Y = to_dev(Y)
+        if Y.dim() == 1:
+            Y = Y[:, None].contiguous()
+        self.P = Y.shape[1]
+        dev = Y.device
+        self.Yn = torch.empty((self.P, f.n_pad), dtype=torch.float64, device=dev)
+        self.ymean = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        self.ystd = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        call("gpmpc_normalize_targets", ptr(Y), f.n, self.P, Y.stride(0), f.n_pad, 1, ptr(self.Yn), ptr(self.ymean),
+             ptr(self.ystd), stream())
+        self.c = f.factor_B(self.Yn)
+        self.alpha = f.solve_B(self.c)
+        self.lml = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        call("gpmpc_sparse_lml", 0 if f.method == "fitc" else 1, f.M, f.n, f.n_pad, f.M_pad, ptr(f.Kuf), ptr(f.Kuu),
+             ptr(f.L_B), ptr(f.L_uu), ptr(self.Yn), ptr(self.alpha), ptr(self.c), ptr(f.Lam) if f.Lam is not None else None,
+             ptr(f.qff), f.sv, f.noise, self.P, ptr(self.lml), stream())
+        return self
+
+    def predict(self, Xq, want_var=True, chunk=262144, col=None):
+        """mean = K*u alpha (no L_uu^-T: reference quirk, sparse_gp.py:281), var = max(sv - |v|^2 + |w|^2, 1e-10) ystd^2
+        with v = L_uu^{-1} K_u*, w = L_B^{-1} v (:293-300).  -> (Q,P), (Q,P) CUDA tensors."""
+        torch = torch_()
+        f = self.f
+        Xq = to_dev(Xq)
+        Q = Xq.shape[0]
+        c0, P = (0, self.P) if col is None else (int(col), 1)
+        alpha, ymean, ystd = self.alpha[c0:c0 + P], self.ymean[c0:c0 + P], self.ystd[c0:c0 + P]
+        mean = torch.empty((Q, P), dtype=torch.float64, device=Xq.device)
+        var = torch.empty((Q, P), dtype=torch.float64, device=Xq.device) if want_var else None
+        for s in range(0, Q, chunk):
+            e = min(Q, s + chunk)
+            q = e - s
+            Xqs, sqq = scale_inputs(Xq[s:e], f.ls, DP=f.DP)
+            Ks = gram_scaled(f.kind, Xqs, sqq, q, f.Zs, f.sqz, f.M, f.sv)        # (q_pad, M_pad)
+            call("gpmpc_predict_mean", ptr(Ks), Ks.stride(0), q, f.M, ptr(alpha), f.M_pad, P, ptr(ymean), ptr(ystd),
+                 ptr(mean[s:e]), mean.stride(0), 0, stream())
+            if want_var:
+                ssv = torch.empty((Ks.shape[0],), dtype=torch.float64, device=Xq.device)
+                ssw = torch.empty_like(ssv)
+                call("gpmpc_trsm_sumsq", ptr(f.L_uu), f.M_pad, f.M_pad, ptr(f.W_uu), ptr(Ks), Ks.shape[0], Ks.stride(0),
+                     ptr(ssv), stream())
+                call("gpmpc_trsm_sumsq", ptr(f.L_B), f.M_pad, f.M_pad, ptr(f.W_B), ptr(Ks), Ks.shape[0], Ks.stride(0),
+                     ptr(ssw), stream())
+                call("gpmpc_predict_var", ptr(ssv), ptr(ssw), q, P, f.sv, 1e-10, ptr(ystd), ptr(var[s:e]), var.stride(0),
+                     0, stream())
+        return mean, var

@@ -93,6 +93,24 @@ int gpmpc_features(int which, const double* X, long ldx, const double* U, long l
                    void* stream);
 
 
+/* ---- sparse (inducing-point) GP glue: sparse_gp.py:150-253 ------------------------------------------------------- */
+
+/* A[i,i] += value for i < n (K_uu + jitter I at sparse_gp.py:186, B + jitter I at :227). */
+int gpmpc_add_diag(double* A, int n, long lda, double value, void* stream);
+
+/* FITC diagonal (sparse_gp.py:194-208): Lam[i] = max(prior - qff[i] + noise, floor); As[m,i] = A[m,i] / sqrt(Lam[i]);
+ * Ylam[p,i] = Yn[p,i] / Lam[i].  A, As: M x n_pad row-major; Yn, Ylam: P x n_pad; padding columns get 1 / 0 / 0. */
+int gpmpc_fitc_scale(const double* A, long lda, int M, int n, int n_pad, const double* qff, double prior, double noise,
+                     double floor_, const double* Yn, int P, double* Lam, double* As, long ldas, double* Ylam,
+                     void* stream);
+
+/* FITC log marginal likelihood (method 0, sparse_gp.py:212-218) / VFE bound (method 1, :234-251), one value per output.
+ * Kuf: M_pad x n_pad; Kuu, LB, Luu: M_pad x M_pad; Yn: P x n_pad; alpha, c: P x M_pad; Lam, qff: n_pad. */
+int gpmpc_sparse_lml(int method, int M, int n, int n_pad, int M_pad, const double* Kuf, const double* Kuu,
+                     const double* LB, const double* Luu, const double* Yn, const double* alpha, const double* c,
+                     const double* Lam, const double* qff, double sv, double noise, int P, double* lml, void* stream);
+
+
 /* ---- MPC: dynamics, horizon rollout / propagation, QP assembly, ADMM ---------------------------------------------- */
 
 /* OSQP status codes (osqp constants; the reference tests result.info.status, osqp_rti.py:532). */
