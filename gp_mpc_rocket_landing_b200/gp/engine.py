@@ -402,3 +402,72 @@ class SparseModelDev:
                 call("gpmpc_predict_var", ptr(ssv), ptr(ssw), q, P, f.sv, 1e-10, ptr(ystd), ptr(var[s:e]), var.stride(0),
                      0, stream())
         return mean, var
+
+
+# ====================================================================================================== refit sweep
+class ExactSweep:
+    """Batched exact-GP refit over a hyper-parameter grid (BASELINE config 3; the loop `optimize_hyperparameters`
+    (exact_gp.py:357-421) / `HyperparameterTuner._compute_nll` (learning/hyperparameter_tuner.py:361-395) runs one
+    `ExactGP.fit` at a time).  G candidates theta_g = (lengthscales (D,), signal_var, noise) share the inputs X and the
+    P target columns; the G Gram matrices are built into one (G, n_pad, n_pad) buffer and factorised by ONE batched
+    blocked Cholesky (every panel / trailing-update launch covers all candidates), then cho_solve and LML for all
+    (g, p).  Jitter escalation (exact_gp.py:163-175) is per candidate: failed ones are rebuilt with the next jitter."""
+
+    def __init__(self, kind, X, Y, normalize=True):
+        torch = torch_()
+        self.kind = int(kind)
+        self.X = to_dev(X)
+        self.n, self.D = self.X.shape
+        self.n_pad = pad_to(self.n, 128)
+        Y = to_dev(Y)
+        if Y.dim() == 1:
+            Y = Y[:, None].contiguous()
+        self.P = Y.shape[1]
+        dev = self.X.device
+        self.Yn = torch.empty((self.P, self.n_pad), dtype=torch.float64, device=dev)
+        self.ymean = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        self.ystd = torch.empty((self.P,), dtype=torch.float64, device=dev)
+        call("gpmpc_normalize_targets", ptr(Y), self.n, self.P, Y.stride(0), self.n_pad, int(normalize), ptr(self.Yn),
+             ptr(self.ymean), ptr(self.ystd), stream())
+
+    def _build(self, L, g, ls, sv, diag):
+        Xs, sq = scale_inputs(self.X, to_dev(np.asarray(ls, dtype=np.float64)))
+        gram_scaled(self.kind, Xs, sq, self.n, Xs, sq, self.n, sv, diag_add=diag, pad_identity=1, lower_only=1, out=L[g])
+
+    def fit(self, lengthscales, signal_vars, noises, keep_factors=False):
+        """lengthscales (G,D), signal_vars (G,), noises (G,) -> dict(lml (G,P), alpha (G,P,n), jitter (G,), info (G,))
+        (+ L (G,n_pad,n_pad) when keep_factors)."""
+        torch = torch_()
+        ls = np.atleast_2d(np.asarray(lengthscales, dtype=np.float64))
+        G = ls.shape[0]
+        sv = np.broadcast_to(np.asarray(signal_vars, dtype=np.float64), (G,))
+        nz = np.broadcast_to(np.asarray(noises, dtype=np.float64), (G,))
+        dev = self.X.device
+        npad = self.n_pad
+        L = torch.empty((G, npad, npad), dtype=torch.float64, device=dev)
+        for g in range(G):
+            self._build(L, g, ls[g], sv[g], nz[g])
+        Winv = torch.empty((G, npad // 64, 64, 64), dtype=torch.float64, device=dev)
+        info = torch.empty((G,), dtype=torch.int32, device=dev)
+        call("gpmpc_potrf", ptr(L), npad, npad, npad * npad, G, ptr(Winv), ptr(info), stream())
+        jitter = np.zeros(G)
+        bad = np.nonzero(info.cpu().numpy())[0]
+        for g in bad:                                   # exact_gp.py:163-175, candidate by candidate
+            ok = False
+            for jit in ExactFactor.JITTERS[1:]:
+                self._build(L, g, ls[g], sv[g], nz[g] + jit)
+                call("gpmpc_potrf", ptr(L[g]), npad, npad, 0, 1, ptr(Winv[g]), ptr(info[g:g + 1]), stream())
+                if int(info[g].item()) == 0:
+                    jitter[g], ok = jit, True
+                    break
+            if not ok:
+                jitter[g] = np.nan
+        Yg = self.Yn[None].expand(G, self.P, npad).contiguous()
+        alpha = Yg.clone()
+        call("gpmpc_potrs", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(alpha), self.P, G, stream())
+        lml = torch.empty((G, self.P), dtype=torch.float64, device=dev)
+        call("gpmpc_lml", ptr(L), self.n, npad, npad, npad * npad, ptr(Yg), ptr(alpha), self.P, G, ptr(lml), stream())
+        out = {"lml": lml, "alpha": alpha[:, :, : self.n], "jitter": jitter, "info": info}
+        if keep_factors:
+            out["L"], out["Winv"] = L, Winv
+        return out

@@ -133,3 +133,30 @@ def test_predict_batch_equals_singles_and_variance_floor(eng):
         assert np.array_equal(m1.cpu().numpy()[0], mean[i]) and np.array_equal(v1.cpu().numpy()[0], var[i])
     ystd = m.ystd.cpu().numpy()
     assert np.all(var >= 1e-10 * ystd**2 * (1 - 1e-15))
+
+
+def test_refit_sweep_matches_sequential_fits(eng):
+    """BASELINE config 3 (reduced): a batched hyper-parameter grid equals the loop of single fits (exact_gp.py:118-204),
+    including per-candidate jitter escalation."""
+    from gp_mpc_rocket_landing_b200.gp import refit
+    from oracle import gp as ogp
+    rng = np.random.default_rng(3)
+    n, D, P = 300, 11, 3
+    X = rng.normal(0, 0.5, (n, D))
+    Y = np.stack([np.sin(X[:, 0] * 2) + 0.1 * rng.normal(size=n), X[:, 1] ** 2, X[:, 2] - X[:, 3]], axis=1)
+    for kind in (0, 2):
+        ls, sv, nz = refit.default_grid(D, n_lengthscales=3, noises=(1e-3, 1e-1))
+        r = refit.refit_sweep(X, Y, ls, sv, nz, kind=kind)
+        assert r["lml"].shape == (6, P)
+        for g in range(6):
+            for p in range(P):
+                f = ogp.exact_fit(kind, X, Y[:, p], ls[g], sv[g], nz[g])
+                assert relerr(r["lml"][g, p], f.lml) < 1e-9, (kind, g, p)
+        assert r["best_shared"] == int(np.argmax(r["lml"].sum(1)))
+    # duplicated rows + tiny noise: the first Cholesky fails, the candidate alone escalates its jitter
+    g = load_golden("exact_gp.npz")
+    fo = ogp.exact_fit(ogp.SE, g["jit_X"], g["jit_y"], g["jit_ls"], float(g["sv"]), float(g["jit_noise"]))
+    sweep = eng.ExactSweep(0, g["jit_X"], g["jit_y"])
+    out = sweep.fit(np.stack([g["jit_ls"], g["jit_ls"]]), float(g["sv"]), [float(g["jit_noise"]), 1e-2])
+    assert out["jitter"][0] == fo.jitter > 0.0 and out["jitter"][1] == 0.0
+    assert relerr(out["lml"].cpu().numpy()[0, 0], g["jit_lml"]) < 1e-6
