@@ -27,6 +27,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
+# dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` captures (profiles/), B = 4096
+NCU_TRAFFIC = {"admm": 82.6e6, "rollout": 653.3e6, "gp_variance": None}
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 
 
@@ -309,9 +311,8 @@ def run_b200_arm(args):
                "d2h_bytes_per_step": d2h, "steps": Ke, "timer": "host wall clock around synchronised steps"}
 
     if rank == 0:
-        # ---- roofline of the dominant phase -------------------------------------------------------------------
+        # ---- rooflines: algorithmic work per launch / measured launch time ------------------------
         share = {k: v[0] / ms for k, v in phases.items()}
-        dom = max(phases, key=lambda k: phases[k][0])
         Q = B * N_HORIZON
         peaks = {}
         try:
@@ -319,28 +320,46 @@ def run_b200_arm(args):
         except Exception:  # noqa: BLE001
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        tot, cnt = phases[dom]
-        avg_s = tot / cnt * 1e-3
-        if dom in ("gp_variance",):
-            flops = Q * float(N_TRAIN) ** 2          # n^2 per query (L^-1 k* : n^2/2 FMA), SURVEY 8(d)
-            roof = {"kernel": "gp_variance (blocked DMMA TRSM + fused sum of squares, dgemm_nt_kernel)",
-                    "bound": "tensor", "achieved": flops / avg_s / 1e12, "peak": peak64, "unit": "TFLOP/s",
-                    "peak_source": "cuBLAS DGEMM 8192^3 FP64 measured in this run (FP64 is not in MEASURED_PEAKS.json)",
-                    "traffic": None}
-        else:
-            per_qp = 22e3 if dom == "admm" else 33e3
-            byts = B * per_qp
-            roof = {"kernel": dom, "bound": "hbm", "achieved": byts / avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
-                    "note": "compulsory bytes only; the ADMM kernel is dependency-chain bound, not HBM bound "
-                            "(DESIGN.md)", "traffic": None}
-        roof["frac"] = roof["achieved"] / roof["peak"] if roof["peak"] else None
-        roof["avg_launch_ms"] = avg_s * 1e3
+        hbm_src = "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+        n_pad = ((N_TRAIN + 127) // 128) * 128
+        work = {  # phase -> (bound, algorithmic units per step: flops or bytes, kernel description)
+            "gp_variance": ("tensor", Q * float(n_pad) ** 2,
+                            "dgemm_nt_kernel x31: blocked DMMA TRSM V = L^-1 K*^T with fused sum of squares (n_pad^2 flop "
+                            "per query, SURVEY 8d)"),
+            "admm": ("hbm", B * 22e3, "admm_kernel<7,3>: 22 kB compulsory per QP (SURVEY 8d); dependency-chain bound, "
+                                      "neither HBM nor FLOP limited (DESIGN.md section 4)"),
+            "rollout": ("hbm", Q * 8.0 * n_pad + B * 8.0 * (7 + 60 + 147 + 60),
+                        "rollout3_kernel: K* rows written once (8 n_pad bytes per query) + trajectories"),
+            "cov": ("hbm", B * 8.0 * (21 * 49 + 60 + 60 + 147 + 60), "predict_var + propagate_cov3_kernel"),
+            "assemble": ("hbm", B * 8.0 * (1400 + 147 + 207 + 207 + 147 + 60 + 60), "qp_assemble3 + pack_traj3 kernels"),
+            "update": ("hbm", B * 8.0 * (207 + 2 * 207 + 2), "mpc_update3_kernel"),
+        }
+        by_kernel = {}
+        for name, (tot, cnt) in phases.items():
+            if name not in work or cnt == 0:
+                continue
+            bound, units, desc = work[name]
+            avg_s = tot / cnt * 1e-3
+            if bound == "tensor":
+                r = {"kernel": desc, "bound": "tensor", "achieved": units / avg_s / 1e12, "peak": peak64,
+                     "unit": "TFLOP/s", "peak_source": "cuBLAS DGEMM 8192^3 FP64 measured in this run (MEASURED_PEAKS.json "
+                                                       "has no FP64 entry; FP64 has no tcgen05 kind: DMMA is the tensor path)"}
+            else:
+                r = {"kernel": desc, "bound": "hbm", "achieved": units / avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "peak_source": hbm_src}
+            r["frac"] = r["achieved"] / r["peak"] if r["peak"] else None
+            r["avg_ms_per_step"] = avg_s * 1e3
+            r["share_of_step"] = share[name]
+            r["traffic"] = NCU_TRAFFIC.get(name)
+            by_kernel[name] = r
+        dom = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"])
+        roof = dict(by_kernel[dom])
+        roof["phase"] = dom
         line = {
             "metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config_dict(args, world), "e2e": e2e, "gpu_launches": launches,
-            "roofline": roof, "cpu_baseline": cpu_base, "clocks": clk,
+            "roofline": roof, "roofline_by_kernel": by_kernel, "cpu_baseline": cpu_base, "clocks": clk,
             "phases_share_of_step": share, "phase_ms_per_step": {k: v[0] / K for k, v in phases.items()},
             "mean_admm_iters_per_solve": float(qp_it.item()) / (B * K), "p50_step_latency_ms": ms / K,
             "fp64_peak_tflops_measured": peak64,
