@@ -176,6 +176,138 @@ __global__ void __launch_bounds__(ROLL_WARPS * 32) rollout3_kernel(GpmpcExactMod
   }
 }
 
+// Shared-memory variant (the one the 1000-point model takes): the whole model -- scaled training inputs (feature-major, so
+// lane j reads a conflict-free column), row norms and the P alpha vectors, 16 n_pad (DP+1+P) bytes = 131 kB at n_pad = 1024
+// -- is staged once per CTA, and every warp rolls out TWO scenarios at once, so each training point read from shared
+// memory serves two queries and the two dot-product chains overlap.  The grid is sized so that all scenario pairs run in
+// ONE wave (one CTA per SM, W warps each, W * #SM >= B/2).  Same per-element arithmetic as gp_query_warp.
+constexpr int ROLLS_MAX_WARPS = 16;
+
+template <int DP_T, int P_T>
+__global__ void __launch_bounds__(ROLLS_MAX_WARPS * 32, 1)
+    rollout3_smem_kernel(GpmpcExactModel M, GpmpcDyn3 dyn, int nbatch, int N, const double* __restrict__ x0,
+                         const double* __restrict__ U, double* __restrict__ X, double* __restrict__ dmean,
+                         double* __restrict__ Ks, long ldk, const int* __restrict__ active) {
+  extern __shared__ __align__(16) double rsm[];
+  const int n_pad = M.n_pad, n = M.n;
+  double* XsT = rsm;                          // DP_T x n_pad
+  double* sqs = XsT + (size_t)DP_T * n_pad;   // n_pad
+  double* als = sqs + n_pad;                  // P_T x n_pad
+  for (int e = threadIdx.x; e < n_pad * DP_T; e += blockDim.x) {
+    const int j = e / DP_T, d = e - j * DP_T;
+    XsT[(size_t)d * n_pad + j] = M.Xs[e];
+  }
+  for (int e = threadIdx.x; e < n_pad; e += blockDim.x) sqs[e] = M.sq[e];
+  for (int e = threadIdx.x; e < n_pad * P_T; e += blockDim.x) als[e] = M.alpha[e];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, W = blockDim.x >> 5;
+  const int ntask = (nbatch + 1) / 2;
+  double ls[11];
+#pragma unroll
+  for (int d = 0; d < 11; ++d) ls[d] = M.lengthscales[d];
+  for (int task = blockIdx.x * W + warp; task < ntask; task += gridDim.x * W) {
+    const int b0 = 2 * task, b1 = min(b0 + 1, nbatch - 1);
+    const bool has1 = b0 + 1 < nbatch;
+    const bool act0 = (active == nullptr) || active[b0] != 0;
+    const bool act1 = has1 && ((active == nullptr) || active[b1] != 0);
+    double xa[NX], xb[NX], xn[NX], ua[NU], ub[NU];
+#pragma unroll
+    for (int d = 0; d < NX; ++d) {
+      xa[d] = x0[(long)b0 * NX + d];
+      xb[d] = x0[(long)b1 * NX + d];
+    }
+    if (lane < NX) {
+      if (act0) X[(long)b0 * (N + 1) * NX + lane] = xa[lane];
+      if (act1) X[(long)b1 * (N + 1) * NX + lane] = xb[lane];
+    }
+    for (int k = 0; k < N; ++k) {
+      const long r0 = (long)b0 * N + k, r1 = (long)b1 * N + k;
+      double* k0 = Ks ? Ks + r0 * ldk : nullptr;
+      double* k1 = (Ks && has1) ? Ks + r1 * ldk : nullptr;
+      if (!act0 && !act1) {  // keep the rows of skipped scenarios finite for the variance TRSM that follows
+        for (int j = lane; j < n_pad; j += 32) {
+          if (k0) k0[j] = 0.0;
+          if (k1) k1[j] = 0.0;
+        }
+        continue;
+      }
+#pragma unroll
+      for (int d = 0; d < NU; ++d) {
+        ua[d] = U[r0 * NU + d];
+        ub[d] = U[r1 * NU + d];
+      }
+      double za[DP_T], zb[DP_T], sqv[11];
+      features_3dof_dev(xa, ua, za);
+#pragma unroll
+      for (int d = 0; d < 11; ++d) {
+        za[d] = za[d] / ls[d];
+        sqv[d] = za[d] * za[d];
+      }
+      const double sqa = numpy_pairwise_sum_small(sqv, 11);
+      features_3dof_dev(xb, ub, zb);
+#pragma unroll
+      for (int d = 0; d < 11; ++d) {
+        zb[d] = zb[d] / ls[d];
+        sqv[d] = zb[d] * zb[d];
+      }
+      const double sqb = numpy_pairwise_sum_small(sqv, 11);
+#pragma unroll
+      for (int d = 11; d < DP_T; ++d) za[d] = zb[d] = 0.0;
+      double acca[P_T], accb[P_T];
+#pragma unroll
+      for (int p = 0; p < P_T; ++p) acca[p] = accb[p] = 0.0;
+#pragma unroll 2
+      for (int j = lane; j < n_pad; j += 32) {
+        double kva = 0.0, kvb = 0.0;
+        if (j < n) {
+          double da = 0.0, db = 0.0;
+#pragma unroll
+          for (int d = 0; d < DP_T; ++d) {
+            const double t = XsT[(size_t)d * n_pad + j];
+            da = fma(za[d], t, da);
+            db = fma(zb[d], t, db);
+          }
+          const double sj = sqs[j];
+          kva = kernel_value(M.kind, (sqa + sj) - 2.0 * da, M.signal_var);
+          kvb = kernel_value(M.kind, (sqb + sj) - 2.0 * db, M.signal_var);
+#pragma unroll
+          for (int p = 0; p < P_T; ++p) {
+            const double a = als[(size_t)p * n_pad + j];
+            acca[p] = fma(kva, a, acca[p]);
+            accb[p] = fma(kvb, a, accb[p]);
+          }
+        }
+        if (k0) k0[j] = act0 ? kva : 0.0;
+        if (k1) k1[j] = act1 ? kvb : 0.0;
+      }
+      double dma[3], dmb[3];
+#pragma unroll
+      for (int p = 0; p < 3; ++p) {
+        dma[p] = warp_sum(acca[p]) * M.ystd[p] + M.ymean[p];  // exact_gp.py:240-245
+        dmb[p] = warp_sum(accb[p]) * M.ystd[p] + M.ymean[p];
+      }
+      if (act0) {
+        step3(xa, ua, dyn, xn);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dma[i] * dyn.dt;  // gp_mpc.py:165-167
+        if (lane < NX) X[((long)b0 * (N + 1) + k + 1) * NX + lane] = xn[lane];
+        if (dmean && lane < 3) dmean[r0 * 3 + lane] = dma[lane];
+#pragma unroll
+        for (int d = 0; d < NX; ++d) xa[d] = xn[d];
+      }
+      if (act1) {
+        step3(xb, ub, dyn, xn);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dmb[i] * dyn.dt;
+        if (lane < NX) X[((long)b1 * (N + 1) + k + 1) * NX + lane] = xn[lane];
+        if (dmean && lane < 3) dmean[r1 * 3 + lane] = dmb[lane];
+#pragma unroll
+        for (int d = 0; d < NX; ++d) xb[d] = xn[d];
+      }
+    }
+  }
+}
+
 // GP means at given trajectory points (X[b,k], U[b,k]), k < N: the affine terms c_k of one SQP iteration
 // (gp_mpc.py:309-317).  One warp per point.
 template <int DP_T>
@@ -518,7 +650,23 @@ extern "C" int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3*
   }
   const int grid = (B + ROLL_WARPS - 1) / ROLL_WARPS;
   cudaStream_t s = (cudaStream_t)stream;
-  if (has_model && M.DP == 12)
+  const size_t smem = sizeof(double) * (size_t)M.n_pad * (12 + 1 + 3);
+  if (has_model && M.DP == 12 && M.P == 3 && smem <= 200 * 1024) {
+    // one wave: one CTA per SM, W warps each, two scenarios per warp
+    static int n_sm = 0;
+    if (n_sm == 0) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+      cudaFuncSetAttribute(rollout3_smem_kernel<12, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    }
+    const int ntask = (B + 1) / 2;
+    const int passes = (ntask + n_sm * ROLLS_MAX_WARPS - 1) / (n_sm * ROLLS_MAX_WARPS);
+    int W = (ntask + n_sm * passes - 1) / (n_sm * passes);
+    W = W < 1 ? 1 : (W > ROLLS_MAX_WARPS ? ROLLS_MAX_WARPS : W);
+    const int ctas = (ntask + W - 1) / W < n_sm ? (ntask + W - 1) / W : n_sm;
+    rollout3_smem_kernel<12, 3><<<ctas, W * 32, smem, s>>>(M, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
+  } else if (has_model && M.DP == 12)
     rollout3_kernel<12><<<grid, ROLL_WARPS * 32, 0, s>>>(M, has_model, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
   else
     rollout3_kernel<0><<<grid, ROLL_WARPS * 32, 0, s>>>(M, has_model, *dyn, B, N, x0, U, X, dmean, Ks, ldk, active);
