@@ -49,6 +49,11 @@ class GPMPCConfig(MPCConfig):
     qp_adaptive_rho_interval: int = 25  # iteration based (OSQP's default is timing based, i.e. not reproducible)
     qp_scaling: int = 3               # osqp_rti.py:477
     qp_keep_rho: bool = True          # the adapted rho persists across solves, as inside one OSQP solver object
+    overlap_uncertainty: bool = False  # GP variance + covariance chain on a side stream, concurrent with the QP (the QP
+                                       # does not read them: gp_mpc.py:414 evaluates the tightening at k = 0 only).
+                                       # Measured on B200: step 11.13 -> 10.58 ms only -- both kernels fill the SMs'
+                                       # shared memory, so they time-slice rather than overlap; off by default so
+                                       # that per-kernel timings stay clean.
 
 
 def _is_dev(a):
@@ -67,6 +72,10 @@ class _BatchState:
         self.X = torch.zeros((B, N + 1, NX), **f64)
         self.U = torch.zeros((B, N, NU), **f64)
         self.Xs = torch.zeros((B, N + 1, NX), **f64)       # scratch rollout of the re-propagation
+        self.X_unc = torch.zeros((B, N + 1, NX), **f64)    # snapshot read by the side-stream covariance chain
+        self.U_unc = torch.zeros((B, N, NU), **f64)
+        self.active_unc = torch.ones((B,), **i32)
+        self.unc_event = None
         self.dmean = torch.zeros((B, N, 3), **f64)
         self.dmean_s = torch.zeros((B, N, 3), **f64)
         self.q_pad = ge.pad_to(B * N, 128)
@@ -128,6 +137,7 @@ class GPMPC:
         self._qp = None
         self._dyn = None
         self._is_setup = False
+        self._side = None
         self.last_kernel_launches = 0
         self.timers: Optional[me.PhaseTimers] = None   # set to me.PhaseTimers() to time the phases (bench.py)
 
@@ -204,6 +214,31 @@ class GPMPC:
             me.propagate_cov(self._dyn, X, U, st.dvar, st.covs, sigma0=1e-6, active=active)
         return 2 * (f.n_pad // 64) + 2  # launches: memset is not a kernel; (n/64 - 1) GEMM + n/64 W-GEMM + var + cov
 
+    def _fork_uncertainty(self, st: _BatchState, X, U, active):
+        """`_variance_and_cov` on the side stream: the blocked DMMA TRSM (tensor pipe) runs concurrently with the
+        latency-bound ADMM kernel of the main stream.  Inputs that the main stream later overwrites are snapshotted."""
+        torch = ge.torch_()
+        if not self.config.overlap_uncertainty:
+            return self._variance_and_cov(st, X, U, active)
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        self._join_uncertainty(st)
+        st.X_unc.copy_(X)
+        st.U_unc.copy_(U)
+        st.active_unc.copy_(active)
+        main = torch.cuda.current_stream()
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            n = self._variance_and_cov(st, st.X_unc, st.U_unc, st.active_unc)
+            st.unc_event = torch.cuda.Event()
+            st.unc_event.record(self._side)
+        return n + 3
+
+    def _join_uncertainty(self, st: _BatchState):
+        if st.unc_event is not None:
+            ge.torch_().cuda.current_stream().wait_event(st.unc_event)
+            st.unc_event = None
+
     def _solve_device(self, st: _BatchState, x0, x_ref, U_ref=None, active_in=None):
         """One GP-MPC solve for every scenario of `st` (all tensors on the device).  Returns #kernel launches."""
         c = self.config
@@ -240,7 +275,7 @@ class GPMPC:
             launches += 1
         # --- 2. uncertainty propagation
         if use_unc:
-            launches += self._variance_and_cov(st, st.X, st.U, st.active)
+            launches += self._fork_uncertainty(st, st.X, st.U, st.active)
         # --- 3. SQP iterations
         S = self._settings()
         for it in range(c.max_sqp_iter):
@@ -264,9 +299,11 @@ class GPMPC:
             if int(st.active.sum().item()) == 0:
                 break
             if use_unc and c.repropagate_uncertainty:  # gp_mpc.py:348-353
+                self._join_uncertainty(st)   # the rollout below overwrites Ks
                 with self._span("rollout"):
                     me.rollout(self._model_struct, self._dyn, x0, st.U, st.Xs, st.dmean_s, st.Ks, active=st.active)
-                launches += 1 + self._variance_and_cov(st, st.Xs, st.U, st.active)
+                launches += 1 + self._fork_uncertainty(st, st.Xs, st.U, st.active)
+        self._join_uncertainty(st)
         # --- 4. warm start for the next call (unshifted, gp_mpc.py:355-357)
         st.U_warm.copy_(st.U)
         st.X_warm.copy_(st.X)
