@@ -46,32 +46,39 @@ __global__ void __launch_bounds__(256) potrf_diag64_kernel(double* __restrict__ 
     Wi[i][k] = 0.0;
   }
   __syncthreads();
-  for (int j = 0; j < 64; ++j) {
-    double d = S[j][j];
-    if (!(d > 0.0)) {  // uniform: every thread reads the same value
-      if (tid == 0 && info[b] == 0) info[b] = k0 + j + 1;  // LAPACK: order of the first non-PD leading minor
-      d = 1.0;  // keep going on finite numbers; the host checks info and retries with jitter
-    }
-    d = sqrt(d);
-    const double rd = 1.0 / d;
-    __syncthreads();
-    if (tid == 0) S[j][j] = d;
-    for (int i = j + 1 + tid; i < 64; i += 256) S[i][j] *= rd;
-    __syncthreads();
-    for (int idx = tid; idx < 4096; idx += 256) {
-      int i = idx >> 6, k = idx & 63;
-      if (k > j && k <= i) S[i][k] -= S[i][j] * S[k][j];
+  // Right-looking Cholesky, four threads per row (columns k = q, q+4, ...), ONE barrier per column: the scaling of
+  // column j is folded into the update, (a_ij rd)(a_kj rd), and stored by the thread that owns (i, j).
+  {
+    const int i = tid >> 2, q = tid & 3;
+    for (int j = 0; j < 64; ++j) {
+      double d = S[j][j];
+      if (!(d > 0.0)) {  // uniform: every thread reads the same value
+        if (tid == 0 && info[b] == 0) info[b] = k0 + j + 1;  // LAPACK: order of the first non-PD leading minor
+        d = 1.0;  // keep going on finite numbers; the host checks info and retries with jitter
+      }
+      d = sqrt(d);
+      const double rd = 1.0 / d;
+      double lij = 0.0;
+      if (i > j) {
+        lij = S[i][j] * rd;
+        for (int k = j + 1 + ((q - (j + 1)) & 3); k <= i; k += 4) S[i][k] -= lij * (S[k][j] * rd);
+      }
+      __syncthreads();   // every read of the unscaled column j is done; column j+1 and S[j+1][j+1] are final
+      if (i > j && q == (j & 3)) S[i][j] = lij;   // nobody reads column j again before the barrier after the loop
+      if (tid == 0) S[j][j] = d;
     }
     __syncthreads();
   }
-  // inverse of the lower-triangular block, one column per thread
-  if (tid < 64) {
-    const int j = tid;
-    Wi[j][j] = 1.0 / S[j][j];
-    for (int i = j + 1; i < 64; ++i) {
-      double s = 0.0;
-      for (int k = j; k < i; ++k) s += S[i][k] * Wi[k][j];
-      Wi[i][j] = -s / S[i][i];
+  // W = L^{-1}: four threads per column j split every dot product (k = q, q+4, ...) and combine it by two shuffles
+  {
+    const int j = tid >> 2, q = tid & 3;
+    for (int i = 0; i < 64; ++i) {   // uniform trip count: the shuffles below need the whole warp
+      double sacc = 0.0;
+      for (int k = j + ((q - j) & 3); k < i; k += 4) sacc = fma(S[i][k], Wi[k][j], sacc);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+      if (q == 0 && i >= j) Wi[i][j] = (i == j) ? 1.0 / S[j][j] : -sacc / S[i][i];
+      __syncwarp();
     }
   }
   __syncthreads();
@@ -102,28 +109,45 @@ extern "C" int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int bat
     cudaFuncSetAttribute(potrf_diag64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
     configured = true;
   }
-  for (int k0 = 0; k0 < n_pad; k0 += 64) {
-    double* W = Winv + (long)(k0 / 64) * 4096;
-    potrf_diag64_kernel<<<batch, 256, diag_smem, stream>>>(A, lda, strideA, W, strideW, info, k0);
-    int rc = gpmpc_check_launch("potrf_diag64");
-    if (rc) return rc;
-    if (k0 + 64 >= n_pad) break;
-    const int o = ((k0 + 64) / 128) * 128;  // 128-aligned tile origin; rows/cols below k0+64 are masked
-    GemmParams p{};
-    p.A = A + (long)o * lda + k0; p.lda = lda; p.strideA = strideA;
-    p.B = W; p.ldb = 64; p.strideB = strideW;
-    p.C = A + (long)o * lda + k0; p.ldc = lda; p.strideC = strideA;
-    p.M = n_pad - o; p.N = 64; p.K = 64; p.alpha = 1.0; p.beta = 0.0; p.epi = EPI_STORE;
-    p.row_min = k0 + 64 - o;
-    rc = launch_dgemm_nt<128, 64, 4, 2>(p, batch, stream);  // L21 = A21 * W^T  (in place)
-    if (rc) return rc;
-    GemmParams s{};
-    s.A = A + (long)o * lda + k0; s.lda = lda; s.strideA = strideA;
-    s.B = s.A; s.ldb = lda; s.strideB = strideA;
-    s.C = A + (long)o * lda + o; s.ldc = lda; s.strideC = strideA;
-    s.M = n_pad - o; s.N = n_pad - o; s.K = 64; s.alpha = -1.0; s.beta = 1.0; s.epi = EPI_STORE;
-    s.lower_only = 1; s.row_min = k0 + 64 - o; s.col_min = k0 + 64 - o;
-    rc = launch_dgemm_nt<128, 128, 2, 4>(s, batch, stream);  // A22 -= L21 * L21^T (lower tiles)
+  // Two-level blocking: 64-wide right-looking steps INSIDE a 256-wide outer panel (their rank-64 updates touch the panel
+  // columns only), then ONE rank-256 update of the trailing matrix per outer panel.  The trailing matrix is streamed
+  // through HBM n/256 times instead of n/64 times and its GEMM runs a 16-step k-loop instead of 4.
+  constexpr int NB = 512;
+  for (int K0 = 0; K0 < n_pad; K0 += NB) {
+    const int Kend = (K0 + NB < n_pad) ? K0 + NB : n_pad;
+    for (int k0 = K0; k0 < Kend; k0 += 64) {
+      double* W = Winv + (long)(k0 / 64) * 4096;
+      potrf_diag64_kernel<<<batch, 256, diag_smem, stream>>>(A, lda, strideA, W, strideW, info, k0);
+      int rc = gpmpc_check_launch("potrf_diag64");
+      if (rc) return rc;
+      if (k0 + 64 >= n_pad) break;
+      const int o = ((k0 + 64) / 128) * 128;  // 128-aligned tile origin; rows/cols below k0+64 are masked
+      GemmParams p{};
+      p.A = A + (long)o * lda + k0; p.lda = lda; p.strideA = strideA;
+      p.B = W; p.ldb = 64; p.strideB = strideW;
+      p.C = A + (long)o * lda + k0; p.ldc = lda; p.strideC = strideA;
+      p.M = n_pad - o; p.N = 64; p.K = 64; p.alpha = 1.0; p.beta = 0.0; p.epi = EPI_STORE;
+      p.row_min = k0 + 64 - o;
+      rc = launch_dgemm_nt<128, 64, 4, 2>(p, batch, stream);  // L21 = A21 * W^T  (in place, all rows below)
+      if (rc) return rc;
+      if (k0 + 64 >= Kend) break;
+      GemmParams s{};                                          // panel columns [k0+64, Kend): rank-64 update
+      s.A = A + (long)o * lda + k0; s.lda = lda; s.strideA = strideA;
+      s.B = s.A; s.ldb = lda; s.strideB = strideA;
+      s.C = A + (long)o * lda + o; s.ldc = lda; s.strideC = strideA;
+      s.M = n_pad - o; s.N = Kend - o; s.K = 64; s.alpha = -1.0; s.beta = 1.0; s.epi = EPI_STORE;
+      s.lower_only = 1; s.row_min = k0 + 64 - o; s.col_min = k0 + 64 - o;
+      rc = launch_dgemm_nt<128, 128, 2, 4>(s, batch, stream);
+      if (rc) return rc;
+    }
+    if (Kend >= n_pad) break;
+    GemmParams t{};                                            // trailing matrix: A22 -= L21 * L21^T, K = 256
+    t.A = A + (long)Kend * lda + K0; t.lda = lda; t.strideA = strideA;
+    t.B = t.A; t.ldb = lda; t.strideB = strideA;
+    t.C = A + (long)Kend * lda + Kend; t.ldc = lda; t.strideC = strideA;
+    t.M = n_pad - Kend; t.N = n_pad - Kend; t.K = Kend - K0; t.alpha = -1.0; t.beta = 1.0; t.epi = EPI_STORE;
+    t.lower_only = 1;
+    int rc = launch_dgemm_nt<128, 128, 2, 4>(t, batch, stream);
     if (rc) return rc;
   }
   dim3 grid((n_pad + 255) / 256, n_pad, batch);
@@ -285,32 +309,40 @@ extern "C" int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strid
 // row by block row (64 wide):   R_i = Ks_i - L[i, :i] V[:i]   (DMMA GEMM, K = 64 i)
 //                               V_i = W_i R_i                (DMMA GEMM, K = 64) + sumsq[q] += sum_rows V_i^2
 // Same arithmetic as a blocked dtrsm; the fused column sum of squares is exact_gp.py:261.
-extern "C" int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad,
-                                long ldk, double* sumsq, void* stream_) {
+extern "C" int gpmpc_trsm_sumsq_batched(const double* L, int n_pad, long lda, long strideL, const double* Winv,
+                                        double* Ks, int q_pad, long ldk, long strideK, double* sumsq, int batch,
+                                        void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0, "gpmpc_trsm_sumsq: n_pad and q_pad must be multiples of 128");
-  cudaMemsetAsync(sumsq, 0, sizeof(double) * q_pad, stream);
+  GPMPC_REQUIRE(batch >= 1, "gpmpc_trsm_sumsq: batch < 1");
+  const long strideW = (long)(n_pad / 64) * 4096;
+  cudaMemsetAsync(sumsq, 0, sizeof(double) * (size_t)q_pad * batch, stream);
   for (int ib = 0; ib < n_pad / 64; ++ib) {
     const int i0 = ib * 64;
     if (ib > 0) {
       GemmParams p{};
-      p.A = L + (long)i0 * lda; p.lda = lda;
-      p.B = Ks; p.ldb = ldk;
-      p.C = Ks + i0; p.ldc = ldk; p.c_trans = 1;
+      p.A = L + (long)i0 * lda; p.lda = lda; p.strideA = strideL;
+      p.B = Ks; p.ldb = ldk; p.strideB = strideK;
+      p.C = Ks + i0; p.ldc = ldk; p.strideC = strideK; p.c_trans = 1;
       p.M = 64; p.N = q_pad; p.K = i0; p.alpha = -1.0; p.beta = 1.0; p.epi = EPI_STORE;
-      int rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
+      int rc = launch_dgemm_nt<64, 128, 2, 4>(p, batch, stream);
       if (rc) return rc;
     }
     GemmParams s{};
-    s.A = Winv + (long)ib * 4096; s.lda = 64;
-    s.B = Ks + i0; s.ldb = ldk;
-    s.C = Ks + i0; s.ldc = ldk; s.c_trans = 1;
+    s.A = Winv + (long)ib * 4096; s.lda = 64; s.strideA = strideW;
+    s.B = Ks + i0; s.ldb = ldk; s.strideB = strideK;
+    s.C = Ks + i0; s.ldc = ldk; s.strideC = strideK; s.c_trans = 1;
     s.M = 64; s.N = q_pad; s.K = 64; s.alpha = 1.0; s.beta = 0.0; s.epi = EPI_STORE_SUMSQ;
-    s.sumsq = sumsq;
-    int rc = launch_dgemm_nt<64, 128, 2, 4>(s, 1, stream);
+    s.sumsq = sumsq; s.strideS = q_pad;
+    int rc = launch_dgemm_nt<64, 128, 2, 4>(s, batch, stream);
     if (rc) return rc;
   }
   return GPMPC_OK;
+}
+
+extern "C" int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad,
+                                long ldk, double* sumsq, void* stream_) {
+  return gpmpc_trsm_sumsq_batched(L, n_pad, lda, 0, Winv, Ks, q_pad, ldk, 0, sumsq, 1, stream_);
 }
 
 // ------------------------------------------------------------------------------------------------ small-M TRSM

@@ -434,8 +434,8 @@ class ExactSweep:
         Xs, sq = scale_inputs(self.X, to_dev(np.asarray(ls, dtype=np.float64)))
         gram_scaled(self.kind, Xs, sq, self.n, Xs, sq, self.n, sv, diag_add=diag, pad_identity=1, lower_only=1, out=L[g])
 
-    def fit(self, lengthscales, signal_vars, noises, keep_factors=False):
-        """lengthscales (G,D), signal_vars (G,), noises (G,) -> dict(lml (G,P), alpha (G,P,n), jitter (G,), info (G,))
+    def fit(self, lengthscales, signal_vars, noises, keep_factors=False, want_alpha=False):
+        """lengthscales (G,D), signal_vars (G,), noises (G,) -> dict(lml (G,P), jitter (G,), info (G,)[, alpha (G,P,n)])
         (+ L (G,n_pad,n_pad) when keep_factors)."""
         torch = torch_()
         ls = np.atleast_2d(np.asarray(lengthscales, dtype=np.float64))
@@ -462,12 +462,20 @@ class ExactSweep:
                     break
             if not ok:
                 jitter[g] = np.nan
-        Yg = self.Yn[None].expand(G, self.P, npad).contiguous()
-        alpha = Yg.clone()
-        call("gpmpc_potrs", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(alpha), self.P, G, stream())
+        # y' K^-1 y = |L^-1 y|^2: forward solve only, all candidates in one batched DMMA TRSM with the P targets as rows
+        V = torch.zeros((G, 128, npad), dtype=torch.float64, device=dev)
+        V[:, : self.P] = self.Yn[None]
+        ss = torch.empty((G, 128), dtype=torch.float64, device=dev)
+        call("gpmpc_trsm_sumsq_batched", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(V), 128, npad, 128 * npad, ptr(ss),
+             G, stream())
+        Vp = V[:, : self.P].contiguous()
         lml = torch.empty((G, self.P), dtype=torch.float64, device=dev)
-        call("gpmpc_lml", ptr(L), self.n, npad, npad, npad * npad, ptr(Yg), ptr(alpha), self.P, G, ptr(lml), stream())
-        out = {"lml": lml, "alpha": alpha[:, :, : self.n], "jitter": jitter, "info": info}
+        call("gpmpc_lml", ptr(L), self.n, npad, npad, npad * npad, ptr(Vp), ptr(Vp), self.P, G, ptr(lml), stream())
+        out = {"lml": lml, "jitter": jitter, "info": info}
+        if want_alpha:                                  # alpha = K^-1 y (exact_gp.py:179) for every candidate
+            alpha = self.Yn[None].expand(G, self.P, npad).contiguous()
+            call("gpmpc_potrs", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(alpha), self.P, G, stream())
+            out["alpha"] = alpha[:, :, : self.n]
         if keep_factors:
             out["L"], out["Winv"] = L, Winv
         return out

@@ -71,6 +71,11 @@ int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strideL, const d
 int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad, long ldk,
                      double* sumsq, void* stream);
 
+/* The same solve for `batch` factors at once (L + f*strideL, Winv + f*(n_pad/64)*4096, Ks + f*strideK, sumsq + f*q_pad):
+ * every GEMM launch covers all factors.  The hyper-parameter sweep uses it for y' K^-1 y = |L^-1 y|^2 (exact_gp.py:199). */
+int gpmpc_trsm_sumsq_batched(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* Ks,
+                             int q_pad, long ldk, long strideK, double* sumsq, int batch, void* stream);
+
 /* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
  * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
 int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, long ldb, int ncols, int b_colmajor, double* sumsq,
