@@ -747,6 +747,13 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
 
 }  // namespace
 
+// second-generation kernel (csrc/admm_stage.cu); returns GPMPC_ERR_ARG without launching when the problem does not fit
+template <int NX, int NU>
+int launch_admm_stage(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
+                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x,
+                      double* y, double* rho, int* status, int* iters, double* obj, double* pri, double* dua,
+                      cudaStream_t stream);
+
 extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const double* beq, const double* q,
                                 const double* Pdiag, const double* lb, const double* ub,
                                 const GpmpcAdmmSettings* settings, const int* active, double* x, double* y, double* rho,
@@ -754,6 +761,11 @@ extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, 
   GPMPC_REQUIRE(settings != nullptr, "gpmpc_admm_solve: settings is NULL");
   GPMPC_REQUIRE(N >= 1 && B >= 0, "gpmpc_admm_solve: bad N or B");
   if (B == 0) return GPMPC_OK;
+  if (nx == 7 && nu == 3 && settings->kernel_variant == 0) {
+    const int rc = launch_admm_stage<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, x, y, rho, status, iters,
+                                           obj, pri_res, dua_res, (cudaStream_t)stream);
+    if (rc != GPMPC_ERR_ARG) return rc;  // GPMPC_ERR_ARG: horizon too long for the stage-parallel kernel
+  }
   if (nx == 7 && nu == 3)
     return launch_admm<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, x, y, rho, status, iters, obj, pri_res,
                              dua_res, (cudaStream_t)stream);

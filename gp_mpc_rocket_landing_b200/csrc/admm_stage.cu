@@ -1,0 +1,778 @@
+// Stage-parallel OSQP-style ADMM for the stage-structured MPC QP (same problem, same algorithm and the same C entry
+// point as csrc/admm.cu -- see the header there for the reference call sites osqp_rti.py:464-478,496,517,524,527 and
+// for what is restated from Stellato et al. 2020).  This file is the second generation of the kernel:
+//
+//  * one thread per (stage k, variable i): thread (k,i) owns x_{k,i}, the box row on that variable and -- for the state
+//    part i < NX -- the equality row that *defines* x_{k,i} (the initial-state row for k = 0, the dynamics row
+//    A_{k-1} x_{k-1} + B_{k-1} u_{k-1} - x_k = b_{k-1} otherwise).  All per-row / per-variable iterates
+//    (x, z, y, bounds, scalings, rho class) live in REGISTERS; shared memory holds only the stage blocks, the factor
+//    and four exchange vectors, so a QP needs ~50 KB instead of 75 KB.
+//  * the reduced KKT matrix M = P + sigma I + A' diag(rho) A (block tridiagonal, NS x NS blocks) is factorised by a
+//    TWISTED block elimination ("burn at both ends"): stages 0..p-1 are eliminated top-down by warp 0 while stages
+//    N..p+1 are eliminated bottom-up by warp 1; the middle stage p receives both Schur updates.  The factor is stored
+//    as explicit inverses S_k^{-1} and coupling products F_k = C_{k-1} S_{k-1}^{-1} (top), Fb_k = C_k' S_{k+1}^{-1}
+//    (bottom), so that one KKT solve is
+//        forward   yt_k = r_k - F_k yt_{k-1}   (k = 1..p)      ||   yt_k = r_k - Fb_k yt_{k+1}   (k = N-1..p)
+//        parallel  d_k  = S_k^{-1} yt_k        (all stages at once)
+//        backward  v_k  = d_k - F_{k+1}' v_{k+1} (k = p-1..0)   ||   v_k = d_k - Fb_{k-1}' v_{k-1} (k = p+1..N)
+//    i.e. two dependent chains of N/2 one-matvec steps each (the first generation had 2N steps on one warp).
+//  * termination checks use ONE block reduction (20 maxima + 2 sums) instead of eight.
+#include <math.h>
+
+#include "common.cuh"
+#include "gpmpc_b200.h"
+
+using namespace gpmpc;
+
+namespace {
+
+constexpr double OSQP_INFTY = 1e30, MIN_SCALING = 1e-4, MAX_SCALING = 1e4;
+constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_TOL = 1e-4, RHO_EQ_OVER_INEQ = 1e3;
+constexpr double INF_T = OSQP_INFTY * MIN_SCALING;
+constexpr int MAX_WARPS = 8;
+#ifndef ADMM_STAGE_MIN_CTAS
+#define ADMM_STAGE_MIN_CTAS 2  // resident QPs per SM the register allocation is sized for (measured: 2 beats 3, which spills)
+#endif
+constexpr int NRED_MAX = 20, NRED_SUM = 2, NRED = NRED_MAX + NRED_SUM;
+
+__device__ __forceinline__ double limit_scaling(double v) {
+  v = (v < MIN_SCALING) ? 1.0 : v;
+  return (v > MAX_SCALING) ? MAX_SCALING : v;
+}
+
+template <int NX, int NU>
+struct Stage {
+  static constexpr int NS = NX + NU;
+  static constexpr int SPW = 32 / NS;  // stages per warp
+  static __host__ __device__ int warps(int N) { return (N + 1 + SPW - 1) / SPW; }
+  static __host__ __device__ int mid(int N) { return N / 2; }
+  static __host__ __device__ size_t smem_doubles(int N) {
+    const int p = mid(N);
+    size_t s = 0;
+    auto add = [&](size_t c) { s += (c + 1) & ~(size_t)1; };
+    add((size_t)N * NX * NS);            // AB
+    add((size_t)(N + 1) * NS * NS);      // Sinv
+    add((size_t)(p > 0 ? p : 1) * NS * NX);  // Ft
+    add((size_t)(N - p > 0 ? N - p : 1) * NS * NS);  // Fbt
+    add((size_t)(N + 1) * NS);           // yt
+    add((size_t)(N + 1) * NS);           // xt
+    add((size_t)(N + 2) * NX);           // weq
+    add((size_t)(N + 2) * NX);           // tmp
+    add((size_t)(N + 2) * NX);           // ec
+    add((size_t)(N + 2) * NX);           // sbe
+    add((size_t)(N + 2) * NX);           // sEe
+    for (int t = 0; t < 8; ++t) add((size_t)(N + 1) * NS);  // sq sBd slb sub sPb sD sEb sdy
+    add((size_t)NS);                     // mrg
+    add((size_t)MAX_WARPS * NRED);       // red
+    return s;
+  }
+};
+
+// In-place inverse of a symmetric positive definite NS x NS matrix held one row per lane (lanes >= NS hold zeros):
+// Gauss-Jordan without pivoting (the pivots are the positive Schur complements of an SPD matrix).
+template <int NS>
+__device__ __forceinline__ void gj_inverse(double (&a)[NS], int lane) {
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    double rowj[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) rowj[c] = __shfl_sync(0xffffffffu, a[c], j);
+    const double rp = 1.0 / rowj[j];
+    const double f = a[j];
+    if (lane == j) {
+#pragma unroll
+      for (int c = 0; c < NS; ++c) a[c] = rowj[c] * rp;
+      a[j] = rp;
+    } else {
+      const double g = f * rp;
+#pragma unroll
+      for (int c = 0; c < NS; ++c) a[c] = fma(-g, rowj[c], a[c]);
+      a[j] = -g;
+    }
+  }
+}
+
+// block reduction: v[0..NM) maxima, v[NRED_MAX..NRED_MAX+NSUM) sums; result broadcast to every thread
+template <int NM, int NSUM>
+__device__ __forceinline__ void block_reduce_mixed(double (&v)[NRED], double* red, int warp, int lane, int nwarps) {
+#pragma unroll
+  for (int e = 0; e < NM; ++e) v[e] = warp_max(v[e]);
+#pragma unroll
+  for (int e = 0; e < NSUM; ++e) v[NRED_MAX + e] = warp_sum(v[NRED_MAX + e]);
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int e = 0; e < NM; ++e) red[warp * NRED + e] = v[e];
+#pragma unroll
+    for (int e = 0; e < NSUM; ++e) red[warp * NRED + NRED_MAX + e] = v[NRED_MAX + e];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int e = 0; e < NM; ++e) {
+    double r = red[e];
+    for (int w = 1; w < nwarps; ++w) r = fmax(r, red[w * NRED + e]);
+    v[e] = r;
+  }
+#pragma unroll
+  for (int e = 0; e < NSUM; ++e) {
+    double r = red[NRED_MAX + e];
+    for (int w = 1; w < nwarps; ++w) r += red[w * NRED + NRED_MAX + e];
+    v[NRED_MAX + e] = r;
+  }
+}
+
+template <int I>
+struct IC { static constexpr int value = I; };
+
+template <int NX, int NU, int NT>  // NT > 0: horizon known at compile time (all shared-memory offsets fold); 0: run time
+__global__ void __launch_bounds__(224, ADMM_STAGE_MIN_CTAS)
+admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const double* __restrict__ beqg,
+                  const double* __restrict__ qg, const double* __restrict__ Pdiag, const double* __restrict__ lb,
+                  const double* __restrict__ ub, GpmpcAdmmSettings S, const int* __restrict__ active,
+                  double* __restrict__ xg, double* __restrict__ yg, double* __restrict__ rhog,
+                  int* __restrict__ status_g, int* __restrict__ iters_g, double* __restrict__ obj_g,
+                  double* __restrict__ pri_g, double* __restrict__ dua_g) {
+  using L = Stage<NX, NU>;
+  constexpr int NS = L::NS, SPW = L::SPW;
+  extern __shared__ __align__(16) double smem[];
+  const int N = (NT > 0) ? NT : Nrt;
+  const int b = blockIdx.x, tid = threadIdx.x, nthreads = (NT > 0) ? 32 * L::warps(NT) : blockDim.x;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+  const int p = L::mid(N);
+  const int n = N * NS + NX, neq = NX * (N + 1), m = neq + n;
+  const int npad = (N + 1) * NS, epad = (N + 2) * NX;
+
+  // ---- shared memory carve (must match Stage::smem_doubles) ---------------------------------------------------------
+  double* sp = smem;
+  auto take = [&](size_t cnt) { double* q_ = sp; sp += (cnt + 1) & ~(size_t)1; return q_; };
+  double* AB = take((size_t)N * NX * NS);
+  double* Sinv = take((size_t)(N + 1) * NS * NS);
+  double* Ft = take((size_t)(p > 0 ? p : 1) * NS * NX);           // Ft[k-1][j][i] = F_k[i][j],   k = 1..p
+  double* Fbt = take((size_t)(N - p > 0 ? N - p : 1) * NS * NS);  // Fbt[k-p][c][j] = Fb_k[j][c], k = p..N-1
+  double* yt = take(npad);
+  double* xt = take(npad);
+  double* weq = take(epad);   // equality-row exchange vector, indexed by owner (k,i): k*NX+i ; stage N+1 stays zero
+  double* tmp = take(epad);
+  double* ec = take(epad);    // own-variable coefficient of every equality row (scaled Ei / Nd)
+  double* sbe = take(epad);   // scaled equality right-hand sides
+  double* sEe = take(epad);   // cumulative row scaling of the equality rows
+  double* sq = take(npad);    // per-variable constants of the scaled problem (read-only during the iterations)
+  double* sBd = take(npad);
+  double* slb = take(npad);
+  double* sub = take(npad);
+  double* sPb = take(npad);
+  double* sD = take(npad);
+  double* sEb = take(npad);
+  double* sdy = take(npad);   // dy of the box rows at termination checks
+  double* mrg = take((size_t)NS);  // bottom chain's contribution to the middle stage
+  double* red = take((size_t)MAX_WARPS * NRED);
+
+  // ---- thread <-> (stage, variable) ------------------------------------------------------------------------------
+  const int slot = lane / NS, i = lane - slot * NS;
+  const int k = warp * SPW + slot;
+  const bool on = slot < SPW && k <= N;                 // has a slot in the padded (N+1) x NS layout
+  const bool live = on && (k < N || i < NX);            // a real variable
+  const bool eqo = live && i < NX;                      // owns an equality row
+  const bool hasAB = on && k < N;                       // stage has a dynamics block (columns of AB_k)
+  const bool hasPrev = eqo && k >= 1;                   // own equality row is a dynamics row (rows of AB_{k-1})
+  const int j = on ? k * NS + i : 0;                    // index into the padded per-variable arrays and the global x
+  const int er = eqo ? k * NX + i : 0;                  // index into the equality-row arrays and the global rows
+  const double* ABk = AB + (size_t)(hasAB ? k : 0) * NX * NS + i;           // column i of AB_k, stride NS
+  const double* ABp = AB + (size_t)(hasPrev ? (k - 1) * NX + i : 0) * NS;   // row i of AB_{k-1}
+  const double* wnext = weq + (size_t)((on ? k : 0) + 1) * NX;               // equality-row values owned by stage k+1
+
+  auto reduce = [&](double (&v)[NRED], auto nmax_c, auto nsum_c) {
+    block_reduce_mixed<decltype(nmax_c)::value, decltype(nsum_c)::value>(v, red, warp, lane, nwarps);
+  };
+
+  // ---- load ------------------------------------------------------------------------------------------------------
+  for (int e = tid; e < N * NX * NS; e += nthreads) AB[e] = ABg[(size_t)b * N * NX * NS + e];
+  for (int e = tid; e < epad; e += nthreads) { weq[e] = 0.0; tmp[e] = 0.0; ec[e] = 0.0; sbe[e] = 0.0; sEe[e] = 1.0; }
+  const double sigma = S.sigma;
+  double rho = (S.rho_from_input && rhog[b] > 0.0) ? rhog[b] : S.rho, cscale = 1.0;
+  double x = 0.0, zb = 0.0, yb = 0.0, ze = 0.0, ye = 0.0;
+  int cls = 2;  // box row class: 0 loose (rho_min), 1 equality-like (rho_eq), 2 inequality (rho)
+  __syncthreads();
+  {
+    // ---- modified Ruiz equilibration + cost scaling (OSQP scaling.c; oracle/mpc.py OSQPOracle._scale) ---------------
+    double q = 0.0, Pb = 0.0, Bd = 0.0, e_ = 0.0, Dj = 1.0, Eb = 1.0, Ee = 1.0;
+    if (live) {
+      Pb = Pdiag[j];
+      q = qg[(size_t)b * n + j];
+      Bd = 1.0;
+      if (i < NX) e_ = (k == 0) ? 1.0 : -1.0;
+    }
+    for (int it = 0; it < S.scaling; ++it) {
+      double v = fmax(fabs(Pb), fabs(Bd));
+      v = fmax(v, fabs(e_));
+      if (hasAB)
+#pragma unroll
+        for (int r = 0; r < NX; ++r) v = fmax(v, fabs(ABk[r * NS]));
+      const double Dt = 1.0 / sqrt(limit_scaling(v));
+      const double Etb = 1.0 / sqrt(limit_scaling(fabs(Bd)));
+      double ve = fabs(e_);
+      if (hasPrev)
+#pragma unroll
+        for (int c = 0; c < NS; ++c) ve = fmax(ve, fabs(ABp[c]));
+      const double Ete = 1.0 / sqrt(limit_scaling(ve));
+      if (on) yt[j] = Dt;
+      if (eqo) weq[er] = Ete;
+      __syncthreads();
+      if (hasAB) {
+#pragma unroll
+        for (int r = 0; r < NX; ++r) {
+          double* a = AB + ((size_t)k * NX + r) * NS + i;
+          *a = (wnext[r] * *a) * Dt;
+        }
+      }
+      e_ = (Ete * e_) * Dt;
+      Bd = (Etb * Bd) * Dt;
+      Pb = (Dt * Pb) * Dt;
+      q = Dt * q;
+      Dj *= Dt; Eb *= Etb; Ee *= Ete;
+      double rv[NRED];
+      rv[0] = live ? fabs(q) : 0.0;
+      rv[NRED_MAX] = live ? fabs(Pb) : 0.0;
+      reduce(rv, IC<1>{}, IC<1>{});
+      double ct = limit_scaling(fmax(rv[NRED_MAX] / n, limit_scaling(rv[0])));
+      ct = 1.0 / ct;
+      Pb *= ct;
+      q *= ct;
+      cscale *= ct;
+      __syncthreads();
+    }
+    // scaled bounds, row classes, warm start (x = x_in / D ; y = c y_in / E)
+    double lbs = 0.0, ubs = 0.0;
+    if (live) {
+      lbs = Eb * lb[j];
+      ubs = Eb * ub[j];
+      if (lbs < -INF_T && ubs > INF_T) cls = 0;
+      else if (ubs - lbs < RHO_TOL) cls = 1;
+      if (S.warm_x) x = xg[(size_t)b * n + j] / Dj;
+      if (S.warm_y) yb = cscale * yg[(size_t)b * m + neq + j] / Eb;
+    }
+    if (on) {
+      sq[j] = q; sBd[j] = Bd; slb[j] = lbs; sub[j] = ubs; sPb[j] = Pb; sD[j] = Dj; sEb[j] = Eb;
+      sdy[j] = 0.0; yt[j] = 0.0; xt[j] = x;
+    }
+    if (eqo) {
+      ec[er] = e_;
+      sEe[er] = Ee;
+      sbe[er] = Ee * beqg[(size_t)b * neq + er];
+      if (S.warm_y) ye = cscale * yg[(size_t)b * m + er] / Ee;
+      weq[er] = 0.0;
+    }
+  }
+  __syncthreads();
+
+  // (A v)_own-equality-row given v in shared memory (padded stage layout) and the own value vj  [only for eqo threads]
+  auto eq_row = [&](const double* v, double vj) -> double {
+    double s0 = 0.0, s1 = 0.0;
+    if (hasPrev) {
+      const double* vp = v + (size_t)(k - 1) * NS;
+#pragma unroll
+      for (int c = 0; c + 1 < NS; c += 2) {
+        s0 = fma(ABp[c], vp[c], s0);
+        s1 = fma(ABp[c + 1], vp[c + 1], s1);
+      }
+      if (NS & 1) s0 = fma(ABp[NS - 1], vp[NS - 1], s0);
+    }
+    return fma(ec[er], vj, s0 + s1);
+  };
+  // (A' w)_own-column given the own box value wb, the own equality value we and the shared equality vector
+  auto at_col = [&](double wb, double we, const double* wn) -> double {
+    double s = sBd[j] * wb;
+    if (eqo) s = fma(ec[er], we, s);
+    if (hasAB) {
+      double s1 = 0.0;
+#pragma unroll
+      for (int r = 0; r < NX; ++r) s1 = fma(ABk[r * NS], wn[r], s1);
+      s += s1;
+    }
+    return s;
+  };
+
+  // z = A x for the warm start
+  if (S.warm_x) {
+    zb = sBd[j] * x;
+    if (eqo) ze = eq_row(xt, x);
+  }
+  __syncthreads();
+
+  // ---- twisted block factorisation ----------------------------------------------------------------------------------
+  auto factorize = [&]() {
+    const double rho_eq = RHO_EQ_OVER_INEQ * rho;
+    // phase 1: row i of M_k into Sinv[k][i][:]
+    if (on) {
+      double col[NX];
+#pragma unroll
+      for (int r = 0; r < NX; ++r) col[r] = hasAB ? ABk[r * NS] : 0.0;
+      double* out = Sinv + (size_t)k * NS * NS + i * NS;
+      const double rb = (cls == 0) ? RHO_MIN : ((cls == 1) ? rho_eq : rho);
+      const double Bd = sBd[j], e_ = eqo ? ec[er] : 0.0;
+      double d = sPb[j] + sigma;
+      d = fma(rb, Bd * Bd, d);
+      d = fma(rho_eq, e_ * e_, d);
+#pragma unroll
+      for (int c = 0; c < NS; ++c) {
+        double s = 0.0;
+        if (hasAB) {
+          const double* a = AB + (size_t)k * NX * NS + c;
+#pragma unroll
+          for (int r = 0; r < NX; ++r) s = fma(col[r], a[r * NS], s);
+        }
+        double v = rho_eq * s;
+        if (c == i) v = live ? v + d : 1.0;
+        out[c] = v;
+      }
+    }
+    __syncthreads();
+    const bool row = lane < NS;
+    // Schur update of the row held in a[] with the top coupling F_kk (stored at Ft[kk-1]) of stage kk
+    auto schur_top = [&](double (&a)[NS], int kk) {
+      if (lane < NX) {
+        const double* f = Ft + (size_t)(kk - 1) * NS * NX + lane;        // F_kk[lane][jj] at f[jj*NX]
+        const double* ab = AB + (size_t)(kk - 1) * NX * NS;              // AB_{kk-1}
+        double fr[NS];
+#pragma unroll
+        for (int jj = 0; jj < NS; ++jj) fr[jj] = f[jj * NX];
+#pragma unroll
+        for (int i2 = 0; i2 < NX; ++i2) {
+          double s = 0.0;
+#pragma unroll
+          for (int jj = 0; jj < NS; ++jj) s = fma(fr[jj], ab[i2 * NS + jj], s);
+          a[i2] = fma(-(rho_eq * ec[kk * NX + i2]), s, a[i2]);
+        }
+      }
+    };
+    // Schur update with the bottom coupling Fb_kk (stored at Fbt[kk-p]) of stage kk
+    auto schur_bot = [&](double (&a)[NS], int kk) {
+      if (row) {
+        const double* fb = Fbt + (size_t)(kk - p) * NS * NS + lane;      // Fb_kk[lane][i2] at fb[i2*NS]
+        const double* ab = AB + (size_t)kk * NX * NS;                    // AB_kk
+#pragma unroll
+        for (int i2 = 0; i2 < NX; ++i2) {
+          const double g = fb[i2 * NS] * (rho_eq * ec[(kk + 1) * NX + i2]);
+#pragma unroll
+          for (int c = 0; c < NS; ++c) a[c] = fma(-g, ab[i2 * NS + c], a[c]);
+        }
+      }
+    };
+    auto load_row = [&](double (&a)[NS], int kk) {
+#pragma unroll
+      for (int c = 0; c < NS; ++c) a[c] = row ? Sinv[(size_t)kk * NS * NS + lane * NS + c] : 0.0;
+    };
+    auto store_row = [&](const double (&a)[NS], int kk) {
+      if (row)
+#pragma unroll
+        for (int c = 0; c < NS; ++c) Sinv[(size_t)kk * NS * NS + lane * NS + c] = a[c];
+    };
+    if (warp == 0) {  // top chain
+      for (int kk = 0; kk < p; ++kk) {
+        double a[NS];
+        load_row(a, kk);
+        if (kk > 0) schur_top(a, kk);
+        gj_inverse<NS>(a, lane);
+        store_row(a, kk);
+        // F_{kk+1}[i2][lane] = rho_eq ec[(kk+1),i2] sum_c AB_kk[i2][c] Sinv_kk[c][lane]   (a[] = column `lane` by symmetry)
+        if (row) {
+          const double* ab = AB + (size_t)kk * NX * NS;
+          double* f = Ft + (size_t)kk * NS * NX + lane * NX;
+#pragma unroll
+          for (int i2 = 0; i2 < NX; ++i2) {
+            double s = 0.0;
+#pragma unroll
+            for (int c = 0; c < NS; ++c) s = fma(ab[i2 * NS + c], a[c], s);
+            f[i2] = (rho_eq * ec[(kk + 1) * NX + i2]) * s;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    if (warp == (nwarps > 1 ? 1 : 0)) {  // bottom chain
+      for (int kk = N; kk > p; --kk) {
+        double a[NS];
+        load_row(a, kk);
+        if (kk < N) schur_bot(a, kk);
+        gj_inverse<NS>(a, lane);
+        store_row(a, kk);
+        // Fb_{kk-1}[jj][lane] = sum_{i2<NX} rho_eq ec[kk,i2] AB_{kk-1}[i2][jj] Sinv_kk[i2][lane]
+        if (row) {
+          const double* ab = AB + (size_t)(kk - 1) * NX * NS;
+          double* f = Fbt + (size_t)(kk - 1 - p) * NS * NS + lane * NS;
+          double g[NX];
+#pragma unroll
+          for (int i2 = 0; i2 < NX; ++i2) g[i2] = (rho_eq * ec[kk * NX + i2]) * a[i2];
+#pragma unroll
+          for (int jj = 0; jj < NS; ++jj) {
+            double s = 0.0;
+#pragma unroll
+            for (int i2 = 0; i2 < NX; ++i2) s = fma(ab[i2 * NS + jj], g[i2], s);
+            f[jj] = s;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    if (warp == 0) {
+      double a[NS];
+      load_row(a, p);
+      if (p > 0) schur_top(a, p);
+      if (p < N) schur_bot(a, p);
+      gj_inverse<NS>(a, lane);
+      store_row(a, p);
+    }
+    __syncthreads();
+  };
+  factorize();
+
+  // ---- one KKT solve: xt <- M^{-1} r with r already in yt -------------------------------------------------------------
+  auto kkt_solve = [&]() {
+    // forward chains
+    if (warp == 0) {
+      if (lane < NX && p >= 1) {
+        double fr[NS];
+#pragma unroll
+        for (int c = 0; c < NS; ++c) fr[c] = Ft[c * NX + lane];
+        for (int kk = 1; kk <= p; ++kk) {
+          const double* yp = yt + (size_t)(kk - 1) * NS;
+          const double own = yt[kk * NS + lane];
+          double yv[NS];
+#pragma unroll
+          for (int c = 0; c < NS; ++c) yv[c] = yp[c];
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int c = 0; c + 1 < NS; c += 2) {
+            s0 = fma(fr[c], yv[c], s0);
+            s1 = fma(fr[c + 1], yv[c + 1], s1);
+          }
+          if (NS & 1) s0 = fma(fr[NS - 1], yv[NS - 1], s0);
+          yt[kk * NS + lane] = own - (s0 + s1);
+          if (kk < p) {
+            const double* f = Ft + (size_t)kk * NS * NX + lane;
+#pragma unroll
+            for (int c = 0; c < NS; ++c) fr[c] = f[c * NX];
+          }
+          __syncwarp((1u << NX) - 1u);
+        }
+      }
+    }
+    if (warp == (nwarps > 1 ? 1 : 0)) {
+      if (lane < NS && N - 1 >= p) {
+        constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
+        double fr[NS];
+#pragma unroll
+        for (int c = 0; c < NS; ++c) fr[c] = Fbt[(size_t)(N - 1 - p) * NS * NS + c * NS + lane];
+        for (int kk = N - 1; kk >= p; --kk) {
+          const double* yn = yt + (size_t)(kk + 1) * NS;
+          const double own = yt[kk * NS + lane];
+          double yv[NS];
+#pragma unroll
+          for (int c = 0; c < NS; ++c) yv[c] = yn[c];
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int c = 0; c + 1 < NS; c += 2) {
+            s0 = fma(fr[c], yv[c], s0);
+            s1 = fma(fr[c + 1], yv[c + 1], s1);
+          }
+          if (NS & 1) s0 = fma(fr[NS - 1], yv[NS - 1], s0);
+          if (kk > p) yt[kk * NS + lane] = own - (s0 + s1);
+          else mrg[lane] = s0 + s1;       // merged into the middle stage by the parallel phase below
+          if (kk > p) {
+            const double* f = Fbt + (size_t)(kk - 1 - p) * NS * NS + lane;
+#pragma unroll
+            for (int c = 0; c < NS; ++c) fr[c] = f[c * NS];
+          }
+          __syncwarp(mask);
+        }
+      }
+    }
+    __syncthreads();
+    // d_k = S_k^{-1} yt_k for every stage
+    if (on) {
+      const double* si = Sinv + (size_t)k * NS * NS + i;
+      const double* yk = yt + (size_t)k * NS;
+      double sv[NS], yv[NS];
+#pragma unroll
+      for (int c = 0; c < NS; ++c) { sv[c] = si[c * NS]; yv[c] = yk[c]; }
+      if (k == p && p < N) {
+#pragma unroll
+        for (int c = 0; c < NS; ++c) yv[c] -= mrg[c];
+      }
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int c = 0; c + 1 < NS; c += 2) {
+        s0 = fma(sv[c], yv[c], s0);
+        s1 = fma(sv[c + 1], yv[c + 1], s1);
+      }
+      if (NS & 1) s0 = fma(sv[NS - 1], yv[NS - 1], s0);
+      xt[j] = s0 + s1;
+    }
+    __syncthreads();
+    // backward chains (outwards from the middle stage)
+    if (warp == 0) {
+      if (lane < NS && p >= 1) {
+        constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
+        double fr[NX];
+#pragma unroll
+        for (int i2 = 0; i2 < NX; ++i2) fr[i2] = Ft[(size_t)(p - 1) * NS * NX + lane * NX + i2];
+        for (int kk = p - 1; kk >= 0; --kk) {
+          const double* vn = xt + (size_t)(kk + 1) * NS;
+          const double own = xt[kk * NS + lane];
+          double vv[NX];
+#pragma unroll
+          for (int i2 = 0; i2 < NX; ++i2) vv[i2] = vn[i2];
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int i2 = 0; i2 + 1 < NX; i2 += 2) {
+            s0 = fma(fr[i2], vv[i2], s0);
+            s1 = fma(fr[i2 + 1], vv[i2 + 1], s1);
+          }
+          if (NX & 1) s0 = fma(fr[NX - 1], vv[NX - 1], s0);
+          xt[kk * NS + lane] = own - (s0 + s1);
+          if (kk > 0) {
+            const double* f = Ft + (size_t)(kk - 1) * NS * NX + lane * NX;   // F_kk[i2][lane]
+#pragma unroll
+            for (int i2 = 0; i2 < NX; ++i2) fr[i2] = f[i2];
+          }
+          __syncwarp(mask);
+        }
+      }
+    }
+    if (warp == (nwarps > 1 ? 1 : 0)) {
+      if (lane < NS && p + 1 <= N) {
+        constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
+        double fr[NS];
+#pragma unroll
+        for (int c = 0; c < NS; ++c) fr[c] = Fbt[lane * NS + c];          // Fb_p[jj][lane]
+        for (int kk = p + 1; kk <= N; ++kk) {
+          const double* vp = xt + (size_t)(kk - 1) * NS;
+          const double own = xt[kk * NS + lane];
+          double vv[NS];
+#pragma unroll
+          for (int c = 0; c < NS; ++c) vv[c] = vp[c];
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int c = 0; c + 1 < NS; c += 2) {
+            s0 = fma(fr[c], vv[c], s0);
+            s1 = fma(fr[c + 1], vv[c + 1], s1);
+          }
+          if (NS & 1) s0 = fma(fr[NS - 1], vv[NS - 1], s0);
+          xt[kk * NS + lane] = own - (s0 + s1);
+          if (kk < N) {
+            const double* f = Fbt + (size_t)(kk - p) * NS * NS + lane * NS;  // Fb_kk[jj][lane]
+#pragma unroll
+            for (int c = 0; c < NS; ++c) fr[c] = f[c];
+          }
+          __syncwarp(mask);
+        }
+      }
+    }
+    __syncthreads();
+  };
+
+  // ---- residuals / termination / infeasibility / rho estimate (oracle/mpc.py _residuals, _check, _rho_estimate) --------
+  // Reads the exchange vectors written at a checking iteration: x in xt, dx in yt, y_eq in tmp, dy_eq in weq, dy_box in sdy.
+  struct CheckOut { double pri, dua, rho_est; int status; };
+  auto check = [&](bool approx) -> CheckOut {
+    const double f = approx ? 10.0 : 1.0;
+    const double eps_pinf = f * S.eps_prim_inf, eps_dinf = f * S.eps_dual_inf;
+    double v[NRED];
+#pragma unroll
+    for (int e = 0; e < NRED; ++e) v[e] = 0.0;
+    if (live) {
+      const double lbs = slb[j], ubs = sub[j], Bd = sBd[j], Pb = sPb[j], Dj = sD[j], Eb = sEb[j], q = sq[j];
+      const double dx = yt[j], dyb = sdy[j];
+      const bool uinf = ubs > INF_T, linf = lbs < -INF_T;
+      // box row: projection of dy on the polar of the recession cone
+      double dyp = dyb;
+      if (uinf && linf) dyp = 0.0;
+      else if (uinf) dyp = fmin(dyp, 0.0);
+      else if (linf) dyp = fmax(dyp, 0.0);
+      v[0] = fabs(Dj * dx);
+      v[1] = fabs(Pb * dx / Dj);
+      v[NRED_MAX + 0] = q * dx;
+      {
+        const double Ax = Bd * x, Ei = 1.0 / Eb;
+        v[2] = fabs(Ei * (Ax - zb)); v[3] = fabs(Ei * Ax); v[4] = fabs(Ei * zb);
+        v[5] = fabs(Ax - zb); v[6] = fabs(Ax); v[7] = fabs(zb);
+        v[8] = fabs(Eb * dyp);
+        v[NRED_MAX + 1] = ubs * fmax(dyp, 0.0) + lbs * fmin(dyp, 0.0);
+        const double Adx = (Bd * dx) * Ei;
+        if (!uinf) v[9] = fmax(v[9], Adx);
+        if (!linf) v[10] = fmax(v[10], -Adx);
+      }
+      double dye = 0.0;
+      if (eqo) {
+        const double Ee = sEe[er], bes = sbe[er];
+        dye = weq[er];
+        const double Ax = eq_row(xt, x), Ei = 1.0 / Ee;
+        v[2] = fmax(v[2], fabs(Ei * (Ax - ze))); v[3] = fmax(v[3], fabs(Ei * Ax)); v[4] = fmax(v[4], fabs(Ei * ze));
+        v[5] = fmax(v[5], fabs(Ax - ze)); v[6] = fmax(v[6], fabs(Ax)); v[7] = fmax(v[7], fabs(ze));
+        v[8] = fmax(v[8], fabs(Ee * dye));
+        v[NRED_MAX + 1] += bes * fmax(dye, 0.0) + bes * fmin(dye, 0.0);
+        const double Adx = eq_row(yt, dx) * Ei;
+        v[9] = fmax(v[9], Adx);
+        v[10] = fmax(v[10], -Adx);
+      }
+      {
+        const double Px = Pb * x, Aty = at_col(yb, ye, tmp + (size_t)(k + 1) * NX), Di = 1.0 / Dj;
+        v[11] = fabs(Di * (Px + q + Aty)); v[12] = fabs(Di * Px); v[13] = fabs(Di * Aty); v[14] = fabs(Di * q);
+        v[15] = fabs(Px + q + Aty); v[16] = fabs(Px); v[17] = fabs(Aty); v[18] = fabs(q);
+        v[19] = fabs(at_col(dyp, dye, wnext) * Di);
+      }
+    }
+    reduce(v, IC<NRED_MAX>{}, IC<NRED_SUM>{});
+    CheckOut o;
+    o.pri = v[2];
+    o.dua = v[11] / cscale;
+    const double eps_pri = f * S.eps_abs + f * S.eps_rel * fmax(v[3], v[4]);
+    const double eps_dua = f * S.eps_abs + f * S.eps_rel * fmax(fmax(v[12], v[13]), v[14]) / cscale;
+    const double pr = v[5] / (fmax(v[7], v[6]) + 1e-10);
+    const double du = v[15] / (fmax(fmax(v[18], v[17]), v[16]) + 1e-10);
+    o.rho_est = fmin(fmax(rho * sqrt(pr / (du + 1e-10)), RHO_MIN), RHO_MAX);
+    o.status = GPMPC_QP_UNSOLVED;
+    const double nrm_dx = v[0], nrm_dy = v[8], lhs = v[NRED_MAX + 1], qdx = v[NRED_MAX + 0];
+    bool pinf = false, dinf = false;
+    if (nrm_dy > eps_pinf && lhs < -eps_pinf * nrm_dy) pinf = v[19] < eps_pinf * nrm_dy;
+    if (nrm_dx > eps_dinf && qdx < -cscale * eps_dinf * nrm_dx && v[1] < cscale * eps_dinf * nrm_dx)
+      dinf = !(v[9] > eps_dinf * nrm_dx || v[10] > eps_dinf * nrm_dx);
+    if (pinf) o.status = approx ? GPMPC_QP_PRIMAL_INFEASIBLE_INACCURATE : GPMPC_QP_PRIMAL_INFEASIBLE;
+    else if (dinf) o.status = approx ? GPMPC_QP_DUAL_INFEASIBLE_INACCURATE : GPMPC_QP_DUAL_INFEASIBLE;
+    else if (o.pri <= eps_pri && o.dua <= eps_dua) o.status = approx ? GPMPC_QP_SOLVED_INACCURATE : GPMPC_QP_SOLVED;
+    return o;
+  };
+
+  // ---- ADMM iterations -----------------------------------------------------------------------------------------------------
+  int status = GPMPC_QP_UNSOLVED, it = 0;
+  CheckOut co;
+  co.pri = co.dua = 0.0; co.rho_est = rho; co.status = GPMPC_QP_UNSOLVED;
+  const double alpha = S.alpha;
+  if (S.max_iter > 0) {
+    if (eqo) weq[er] = fma(RHO_EQ_OVER_INEQ * rho, ze, -ye);
+  } else if (eqo) {
+    tmp[er] = ye;  // check buffers for a solve without iterations: dx = dy = 0 (yt, sdy, weq are zero), x in xt
+  }
+  __syncthreads();
+  for (it = 1; it <= S.max_iter; ++it) {
+    const bool can_check = S.check_every > 0 && (it % S.check_every) == 0;
+    const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval > 0 && (it % S.adaptive_rho_interval) == 0;
+    const bool checking = can_check || can_adapt || it == S.max_iter;
+    const double rho_eq = RHO_EQ_OVER_INEQ * rho, rei = 1.0 / rho_eq;
+    const double rb = (cls == 0) ? RHO_MIN : ((cls == 1) ? rho_eq : rho);
+    const double rbi = (cls == 0) ? (1.0 / RHO_MIN) : ((cls == 1) ? rei : 1.0 / rho);
+    // right-hand side sigma x - q + A'(rho z - y)
+    if (on) yt[j] = fma(sigma, x, -sq[j]) + at_col(fma(rb, zb, -yb), eqo ? weq[er] : 0.0, wnext);
+    __syncthreads();
+    kkt_solve();
+    // z_tilde = A x_tilde ; z, y, x updates
+    const double xtj = on ? xt[j] : 0.0;
+    double dx, dyb, dye = 0.0;
+    {
+      const double ztb = sBd[j] * xtj;
+      const double zr = alpha * ztb + (1.0 - alpha) * zb;
+      const double zn = fmin(fmax(fma(yb, rbi, zr), slb[j]), sub[j]);
+      dyb = rb * (zr - zn);
+      yb += dyb;
+      zb = zn;
+    }
+    if (eqo) {
+      const double zte = eq_row(xt, xtj), bes = sbe[er];
+      const double zr = alpha * zte + (1.0 - alpha) * ze;
+      const double zn = fmin(fmax(fma(ye, rei, zr), bes), bes);
+      dye = rho_eq * (zr - zn);
+      ye += dye;
+      ze = zn;
+    }
+    {
+      const double xn = alpha * xtj + (1.0 - alpha) * x;
+      dx = xn - x;
+      x = xn;
+    }
+    if (!checking) {  // (every read of weq of this iteration happened before the barriers inside kkt_solve)
+      if (eqo) weq[er] = fma(rho_eq, ze, -ye);
+      __syncthreads();
+      continue;
+    }
+    __syncthreads();  // every read of xt (eq_row above) is done
+    if (on) { xt[j] = x; yt[j] = dx; sdy[j] = dyb; }
+    if (eqo) { tmp[er] = ye; weq[er] = dye; }
+    __syncthreads();
+    if (can_check || can_adapt) {
+      co = check(false);
+      if (can_check && co.status != GPMPC_QP_UNSOLVED) {
+        status = co.status;
+        break;
+      }
+      if (can_adapt && (co.rho_est > rho * S.adaptive_rho_tolerance || co.rho_est < rho / S.adaptive_rho_tolerance)) {
+        rho = co.rho_est;
+        factorize();
+      }
+      if (it < S.max_iter) {  // (the block reduction inside check() separates its reads of weq from this write)
+        if (eqo) weq[er] = fma(RHO_EQ_OVER_INEQ * rho, ze, -ye);
+        __syncthreads();
+      }
+    }
+  }
+  if (it > S.max_iter) it = S.max_iter;
+  if (status == GPMPC_QP_UNSOLVED) {
+    if (!(S.check_every > 0 && (it % S.check_every) == 0)) {
+      co = check(false);
+      status = co.status;
+    }
+    if (status == GPMPC_QP_UNSOLVED) {
+      CheckOut ca = check(true);
+      status = ca.status;
+    }
+    if (status == GPMPC_QP_UNSOLVED) status = GPMPC_QP_MAX_ITER;
+  }
+  // ---- objective and solution out (unscaled) ---------------------------------------------------------------------------
+  double ob[NRED];
+  ob[NRED_MAX] = live ? (0.5 * sPb[j] * x + sq[j]) * x : 0.0;
+  reduce(ob, IC<0>{}, IC<1>{});
+  if (live) xg[(size_t)b * n + j] = sD[j] * x;
+  if (!S.commit_y_solved_only || status == GPMPC_QP_SOLVED) {
+    if (live) yg[(size_t)b * m + neq + j] = sEb[j] * yb / cscale;
+    if (eqo) yg[(size_t)b * m + er] = sEe[er] * ye / cscale;
+  }
+  if (tid == 0) {
+    status_g[b] = status;
+    iters_g[b] = it;
+    obj_g[b] = ob[NRED_MAX] / cscale;
+    pri_g[b] = co.pri;
+    dua_g[b] = co.dua;
+    rhog[b] = rho;
+  }
+}
+
+}  // namespace
+
+// Launcher used by gpmpc_admm_solve (csrc/admm.cu).  Returns GPMPC_ERR_ARG when the problem does not fit this kernel
+// (the caller then falls back to the first-generation kernel).
+template <int NX, int NU>
+int launch_admm_stage(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
+                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x,
+                      double* y, double* rho, int* status, int* iters, double* obj, double* pri, double* dua,
+                      cudaStream_t stream) {
+  using L = Stage<NX, NU>;
+  const size_t smem = L::smem_doubles(N) * sizeof(double);
+  const int warps = L::warps(N);
+  if (smem > 227 * 1024 || warps > 7) return GPMPC_ERR_ARG;
+  auto kern = (N == 20) ? admm_stage_kernel<NX, NU, 20> : admm_stage_kernel<NX, NU, 0>;
+  static size_t configured[2] = {0, 0};
+  if (smem > configured[N == 20]) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    configured[N == 20] = smem;
+  }
+  kern<<<B, warps * 32, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, x, y, rho, status, iters, obj, pri,
+                                        dua);
+  return gpmpc_check_launch("admm_stage");
+}
+
+template int launch_admm_stage<7, 3>(int, int, const double*, const double*, const double*, const double*,
+                                     const double*, const double*, const GpmpcAdmmSettings&, const int*, double*,
+                                     double*, double*, int*, int*, double*, double*, double*, cudaStream_t);

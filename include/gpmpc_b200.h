@@ -139,7 +139,8 @@ typedef struct GpmpcAdmmSettings {
   int warm_x, warm_y;      /* use x / y buffers as warm start (osqp_rti.py:522-524) */
   int rho_from_input;      /* start from rho[b] when > 0 (OSQP keeps its adapted rho between solves) */
   int commit_y_solved_only; /* write y back only when status == SOLVED (GP-MPC SQP loop keeps the last good duals) */
-  int reserved_;
+  int kernel_variant;     /* 0: stage-parallel kernel (csrc/admm_stage.cu) when the problem fits it; 1: force the
+                             first-generation one-chain kernel (csrc/admm.cu) */
 } GpmpcAdmmSettings;
 
 /* 3-DoF Euler model parameters (nominal_mpc.py:579-605, rocket_3dof.py:33-65). */

@@ -71,8 +71,9 @@ def _oracle_qp(N, x0, xt, seed=0, perturb=0.0):
     return Pd, q, A, l, u, X_lin, U_lin
 
 
+@pytest.mark.parametrize("variant", [0, 1])  # 0: stage-parallel kernel (admm_stage.cu), 1: first-generation kernel
 @pytest.mark.parametrize("max_iter", [50, 4000])
-def test_admm_matches_osqp_restatement(E, max_iter):
+def test_admm_matches_osqp_restatement(E, max_iter, variant):
     """Same algorithm, different linear algebra (block-tridiagonal reduced KKT vs dense LU): statuses, iteration
     counts and rho histories must agree, iterates to ~1e-7 relative."""
     import torch
@@ -92,7 +93,7 @@ def test_admm_matches_osqp_restatement(E, max_iter):
     x_ref = np.stack([np.tile(xts[b], (N + 1, 1)) for b in range(B)])
     qp, AB, beq, q = _assemble(ge, me, N, Xl, Ul, x0s, x_ref)
     ws = me.AdmmWorkspace(B, N)
-    S = me.AdmmSettings.reference_defaults(max_iter=max_iter)
+    S = me.AdmmSettings.reference_defaults(max_iter=max_iter, kernel_variant=variant)
     me.admm_solve(qp, AB, beq, q, S, ws)
     torch.cuda.synchronize()
     st, it = ws.status.cpu().numpy(), ws.iters.cpu().numpy()
@@ -112,7 +113,7 @@ def test_admm_matches_osqp_restatement(E, max_iter):
         # QP in plain numpy (sufficient for optimality: the QP is convex).  Then u0 at the reference tolerance
         # (eps_abs = eps_rel = 1e-4) must be within that tolerance of the optimum, with the same (strongly) active set.
         ws2 = me.AdmmWorkspace(B, N)
-        S2 = me.AdmmSettings.reference_defaults(max_iter=20000, eps_abs=1e-9, eps_rel=1e-9)
+        S2 = me.AdmmSettings.reference_defaults(max_iter=20000, eps_abs=1e-9, eps_rel=1e-9, kernel_variant=variant)
         me.admm_solve(qp, AB, beq, q, S2, ws2)
         torch.cuda.synchronize()
         x2, y2, st2 = ws2.x.cpu().numpy(), ws2.y.cpu().numpy(), ws2.status.cpu().numpy()
@@ -133,7 +134,8 @@ def test_admm_matches_osqp_restatement(E, max_iter):
             assert np.array_equal(lo, lo2) and np.array_equal(up, up2) and lo2.sum() + up2.sum() > 0
 
 
-def test_admm_warm_start_and_inactive(E):
+@pytest.mark.parametrize("variant", [0, 1])
+def test_admm_warm_start_and_inactive(E, variant):
     """x/y/rho persist across solves like the OSQP object does (osqp_rti.py:522-527); inactive scenarios are
     untouched."""
     import torch
@@ -149,10 +151,10 @@ def test_admm_warm_start_and_inactive(E):
     r2 = o.solve()
     qp, AB, beq, qd = _assemble(ge, me, N, np.stack([Xl, Xl]), np.stack([Ul, Ul]), np.stack([x0, x0]), np.tile(xt, (N + 1, 1)))
     ws = me.AdmmWorkspace(2, N)
-    S = me.AdmmSettings.reference_defaults(max_iter=200)
+    S = me.AdmmSettings.reference_defaults(max_iter=200, kernel_variant=variant)
     me.admm_solve(qp, AB, beq, qd, S, ws)
     assert ws.iters.cpu().tolist() == [r1.iters, r1.iters]
-    S2 = me.AdmmSettings.reference_defaults(max_iter=200, warm_x=1, warm_y=1, rho_from_input=1)
+    S2 = me.AdmmSettings.reference_defaults(max_iter=200, warm_x=1, warm_y=1, rho_from_input=1, kernel_variant=variant)
     active = torch.tensor([1, 0], dtype=torch.int32, device="cuda")
     x_before = ws.x.clone()
     me.admm_solve(qp, AB, beq, qd, S2, ws, active=active)
