@@ -702,6 +702,28 @@ __global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch
   }
 }
 
+// stream-ordered scratch for the cumulative scaling vectors D (n) and E (m) of every scenario
+double* alloc_scaling_scratch(size_t doubles, cudaStream_t stream) {
+  static bool pool_configured = false;
+  if (!pool_configured) {  // keep freed blocks in the pool: without this every call re-allocates from the driver
+    int dev = 0;
+    cudaMemPool_t pool;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+      unsigned long long thr = ~0ULL;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+    pool_configured = true;
+  }
+  double* scratch = nullptr;
+  if (cudaMallocAsync(&scratch, sizeof(double) * doubles, stream) != cudaSuccess) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_admm_solve: could not allocate the scaling scratch");
+    return nullptr;
+  }
+  return scratch;
+}
+
 template <int NX, int NU>
 int launch_admm(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
                 const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x, double* y,
@@ -719,25 +741,9 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured = smem;
   }
-  // stream-ordered scratch for the cumulative scaling vectors D (n) and E (m) of every scenario
   const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
-  static bool pool_configured = false;
-  if (!pool_configured) {  // keep freed blocks in the pool: without this every call re-allocates from the driver
-    int dev = 0;
-    cudaMemPool_t pool;
-    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-      unsigned long long thr = ~0ULL;
-      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
-    }
-    cudaGetLastError();
-    pool_configured = true;
-  }
-  double* scratch = nullptr;
-  if (cudaMallocAsync(&scratch, sizeof(double) * (n + m) * (size_t)B, stream) != cudaSuccess) {
-    cudaGetLastError();
-    gpmpc_set_error("gpmpc_admm_solve: could not allocate the scaling scratch");
-    return GPMPC_ERR_CUDA;
-  }
+  double* scratch = alloc_scaling_scratch((n + m) * (size_t)B, stream);
+  if (!scratch) return GPMPC_ERR_CUDA;
   kern<<<B, ADMM_THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters,
                                           obj, pri, dua);
   int rc = gpmpc_check_launch("admm");
@@ -750,9 +756,9 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
 // second-generation kernel (csrc/admm_stage.cu); returns GPMPC_ERR_ARG without launching when the problem does not fit
 template <int NX, int NU>
 int launch_admm_stage(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
-                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x,
-                      double* y, double* rho, int* status, int* iters, double* obj, double* pri, double* dua,
-                      cudaStream_t stream);
+                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active,
+                      double* scratch, double* x, double* y, double* rho, int* status, int* iters, double* obj,
+                      double* pri, double* dua, cudaStream_t stream);
 
 extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const double* beq, const double* q,
                                 const double* Pdiag, const double* lb, const double* ub,
@@ -762,8 +768,12 @@ extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, 
   GPMPC_REQUIRE(N >= 1 && B >= 0, "gpmpc_admm_solve: bad N or B");
   if (B == 0) return GPMPC_OK;
   if (nx == 7 && nu == 3 && settings->kernel_variant == 0) {
-    const int rc = launch_admm_stage<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, x, y, rho, status, iters,
-                                           obj, pri_res, dua_res, (cudaStream_t)stream);
+    const size_t nm = 2 * ((size_t)N * 10 + 7) + 7 * ((size_t)N + 1);  // n + m
+    double* scratch = alloc_scaling_scratch(nm * (size_t)B, (cudaStream_t)stream);
+    if (!scratch) return GPMPC_ERR_CUDA;
+    const int rc = launch_admm_stage<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y, rho, status,
+                                           iters, obj, pri_res, dua_res, (cudaStream_t)stream);
+    cudaFreeAsync(scratch, (cudaStream_t)stream);
     if (rc != GPMPC_ERR_ARG) return rc;  // GPMPC_ERR_ARG: horizon too long for the stage-parallel kernel
   }
   if (nx == 7 && nu == 3)

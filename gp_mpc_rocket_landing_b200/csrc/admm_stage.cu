@@ -31,7 +31,8 @@ constexpr double RHO_MIN = 1e-6, RHO_MAX = 1e6, RHO_TOL = 1e-4, RHO_EQ_OVER_INEQ
 constexpr double INF_T = OSQP_INFTY * MIN_SCALING;
 constexpr int MAX_WARPS = 8;
 #ifndef ADMM_STAGE_MIN_CTAS
-#define ADMM_STAGE_MIN_CTAS 2  // resident QPs per SM the register allocation is sized for (measured: 2 beats 3, which spills)
+#define ADMM_STAGE_MIN_CTAS 3  // resident QPs per SM the register allocation is sized for (128 threads x 3 -> 168 registers;
+                               // measured on B200: 4 QPs per SM at 128 registers spills and is 4-10 % slower)
 #endif
 constexpr int NRED_MAX = 20, NRED_SUM = 2, NRED = NRED_MAX + NRED_SUM;
 
@@ -43,8 +44,7 @@ __device__ __forceinline__ double limit_scaling(double v) {
 template <int NX, int NU>
 struct Stage {
   static constexpr int NS = NX + NU;
-  static constexpr int SPW = 32 / NS;  // stages per warp
-  static __host__ __device__ int warps(int N) { return (N + 1 + SPW - 1) / SPW; }
+  static constexpr int THREADS = 128;
   static __host__ __device__ int mid(int N) { return N / 2; }
   static __host__ __device__ size_t smem_doubles(int N) {
     const int p = mid(N);
@@ -54,14 +54,8 @@ struct Stage {
     add((size_t)(N + 1) * NS * NS);      // Sinv
     add((size_t)(p > 0 ? p : 1) * NS * NX);  // Ft
     add((size_t)(N - p > 0 ? N - p : 1) * NS * NS);  // Fbt
-    add((size_t)(N + 1) * NS);           // yt
-    add((size_t)(N + 1) * NS);           // xt
-    add((size_t)(N + 2) * NX);           // weq
-    add((size_t)(N + 2) * NX);           // tmp
-    add((size_t)(N + 2) * NX);           // ec
-    add((size_t)(N + 2) * NX);           // sbe
-    add((size_t)(N + 2) * NX);           // sEe
-    for (int t = 0; t < 8; ++t) add((size_t)(N + 1) * NS);  // sq sBd slb sub sPb sD sEb sdy
+    for (int t = 0; t < 4; ++t) add((size_t)(N + 1) * NS);  // yt xt sPb sdy
+    for (int t = 0; t < 4; ++t) add((size_t)(N + 2) * NX);  // weq tmp ec sbe
     add((size_t)NS);                     // mrg
     add((size_t)MAX_WARPS * NRED);       // red
     return s;
@@ -124,22 +118,24 @@ __device__ __forceinline__ void block_reduce_mixed(double (&v)[NRED], double* re
 template <int I>
 struct IC { static constexpr int value = I; };
 
-template <int NX, int NU, int NT>  // NT > 0: horizon known at compile time (all shared-memory offsets fold); 0: run time
-__global__ void __launch_bounds__(224, ADMM_STAGE_MIN_CTAS)
+// NT > 0: horizon known at compile time (all shared-memory offsets fold); 0: run time.  NSLOT: (stage, variable) slots
+// per thread -- 128 threads cover (N+1)*NS <= 128*NSLOT slots; slot s of thread t is index t + 128 s.
+template <int NX, int NU, int NT, int NSLOT>
+__global__ void __launch_bounds__(128, ADMM_STAGE_MIN_CTAS)
 admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const double* __restrict__ beqg,
                   const double* __restrict__ qg, const double* __restrict__ Pdiag, const double* __restrict__ lb,
                   const double* __restrict__ ub, GpmpcAdmmSettings S, const int* __restrict__ active,
-                  double* __restrict__ xg, double* __restrict__ yg, double* __restrict__ rhog,
-                  int* __restrict__ status_g, int* __restrict__ iters_g, double* __restrict__ obj_g,
-                  double* __restrict__ pri_g, double* __restrict__ dua_g) {
+                  double* __restrict__ scratch, double* __restrict__ xg, double* __restrict__ yg,
+                  double* __restrict__ rhog, int* __restrict__ status_g, int* __restrict__ iters_g,
+                  double* __restrict__ obj_g, double* __restrict__ pri_g, double* __restrict__ dua_g) {
   using L = Stage<NX, NU>;
-  constexpr int NS = L::NS, SPW = L::SPW;
+  constexpr int NS = L::NS, NTHR = L::THREADS, NWARPS = NTHR / 32;
   extern __shared__ __align__(16) double smem[];
   const int N = (NT > 0) ? NT : Nrt;
-  const int b = blockIdx.x, tid = threadIdx.x, nthreads = (NT > 0) ? 32 * L::warps(NT) : blockDim.x;
+  const int b = blockIdx.x, tid = threadIdx.x;
   if (b >= nbatch) return;
   if (active && !active[b]) return;
-  const int warp = tid >> 5, lane = tid & 31, nwarps = nthreads >> 5;
+  const int warp = tid >> 5, lane = tid & 31;
   const int p = L::mid(N);
   const int n = N * NS + NX, neq = NX * (N + 1), m = neq + n;
   const int npad = (N + 1) * NS, epad = (N + 2) * NX;
@@ -153,151 +149,190 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   double* Fbt = take((size_t)(N - p > 0 ? N - p : 1) * NS * NS);  // Fbt[k-p][c][j] = Fb_k[j][c], k = p..N-1
   double* yt = take(npad);
   double* xt = take(npad);
+  double* sPb = take(npad);   // scaled cost diagonal
+  double* sdy = take(npad);   // dy of the box rows at termination checks
   double* weq = take(epad);   // equality-row exchange vector, indexed by owner (k,i): k*NX+i ; stage N+1 stays zero
   double* tmp = take(epad);
   double* ec = take(epad);    // own-variable coefficient of every equality row (scaled Ei / Nd)
   double* sbe = take(epad);   // scaled equality right-hand sides
-  double* sEe = take(epad);   // cumulative row scaling of the equality rows
-  double* sq = take(npad);    // per-variable constants of the scaled problem (read-only during the iterations)
-  double* sBd = take(npad);
-  double* slb = take(npad);
-  double* sub = take(npad);
-  double* sPb = take(npad);
-  double* sD = take(npad);
-  double* sEb = take(npad);
-  double* sdy = take(npad);   // dy of the box rows at termination checks
   double* mrg = take((size_t)NS);  // bottom chain's contribution to the middle stage
   double* red = take((size_t)MAX_WARPS * NRED);
+  // cumulative Ruiz scalings (needed only at termination checks and for unscaling): global scratch, D (n) then E (m)
+  double* gD = scratch + (size_t)b * (n + m);
+  double* gE = gD + n;
 
-  // ---- thread <-> (stage, variable) ------------------------------------------------------------------------------
-  const int slot = lane / NS, i = lane - slot * NS;
-  const int k = warp * SPW + slot;
-  const bool on = slot < SPW && k <= N;                 // has a slot in the padded (N+1) x NS layout
-  const bool live = on && (k < N || i < NX);            // a real variable
-  const bool eqo = live && i < NX;                      // owns an equality row
-  const bool hasAB = on && k < N;                       // stage has a dynamics block (columns of AB_k)
-  const bool hasPrev = eqo && k >= 1;                   // own equality row is a dynamics row (rows of AB_{k-1})
-  const int j = on ? k * NS + i : 0;                    // index into the padded per-variable arrays and the global x
-  const int er = eqo ? k * NX + i : 0;                  // index into the equality-row arrays and the global rows
-  const double* ABk = AB + (size_t)(hasAB ? k : 0) * NX * NS + i;           // column i of AB_k, stride NS
-  const double* ABp = AB + (size_t)(hasPrev ? (k - 1) * NX + i : 0) * NS;   // row i of AB_{k-1}
-  const double* wnext = weq + (size_t)((on ? k : 0) + 1) * NX;               // equality-row values owned by stage k+1
+  // ---- thread <-> (stage, variable) slots ------------------------------------------------------------------------
+  int j[NSLOT], er[NSLOT], oABk[NSLOT], oABp[NSLOT], oWn[NSLOT], oVp[NSLOT];
+  bool on[NSLOT], live[NSLOT], eqo[NSLOT], hasAB[NSLOT], hasPrev[NSLOT];
+#pragma unroll
+  for (int s = 0; s < NSLOT; ++s) {
+    const int idx = tid + s * NTHR;
+    const int k = idx / NS, i = idx - k * NS;
+    on[s] = idx < npad;                              // has a slot in the padded (N+1) x NS layout
+    live[s] = on[s] && (k < N || i < NX);            // a real variable
+    eqo[s] = live[s] && i < NX;                      // owns an equality row
+    hasAB[s] = on[s] && k < N;                       // stage has a dynamics block (columns of AB_k)
+    hasPrev[s] = eqo[s] && k >= 1;                   // own equality row is a dynamics row (rows of AB_{k-1})
+    j[s] = on[s] ? idx : 0;                          // index into the padded per-variable arrays and the global x
+    er[s] = eqo[s] ? k * NX + i : 0;                 // index into the equality-row arrays and the global rows
+    oABk[s] = (hasAB[s] ? k : 0) * NX * NS + i;                // column i of AB_k, stride NS
+    oABp[s] = (hasPrev[s] ? (k - 1) * NX + i : 0) * NS;        // row i of AB_{k-1}
+    oWn[s] = ((on[s] ? k : 0) + 1) * NX;                        // equality-row values owned by stage k+1
+    oVp[s] = (hasPrev[s] ? k - 1 : 0) * NS;                     // variables of stage k-1
+  }
 
   auto reduce = [&](double (&v)[NRED], auto nmax_c, auto nsum_c) {
-    block_reduce_mixed<decltype(nmax_c)::value, decltype(nsum_c)::value>(v, red, warp, lane, nwarps);
+    block_reduce_mixed<decltype(nmax_c)::value, decltype(nsum_c)::value>(v, red, warp, lane, NWARPS);
   };
 
   // ---- load ------------------------------------------------------------------------------------------------------
-  for (int e = tid; e < N * NX * NS; e += nthreads) AB[e] = ABg[(size_t)b * N * NX * NS + e];
-  for (int e = tid; e < epad; e += nthreads) { weq[e] = 0.0; tmp[e] = 0.0; ec[e] = 0.0; sbe[e] = 0.0; sEe[e] = 1.0; }
+  for (int e = tid; e < N * NX * NS; e += NTHR) AB[e] = ABg[(size_t)b * N * NX * NS + e];
+  for (int e = tid; e < epad; e += NTHR) { weq[e] = 0.0; tmp[e] = 0.0; ec[e] = 0.0; sbe[e] = 0.0; }
   const double sigma = S.sigma;
   double rho = (S.rho_from_input && rhog[b] > 0.0) ? rhog[b] : S.rho, cscale = 1.0;
-  double x = 0.0, zb = 0.0, yb = 0.0, ze = 0.0, ye = 0.0;
-  int cls = 2;  // box row class: 0 loose (rho_min), 1 equality-like (rho_eq), 2 inequality (rho)
+  // per-slot iterates (registers) and per-slot constants of the scaled problem
+  double x[NSLOT], zb[NSLOT], yb[NSLOT], ze[NSLOT], ye[NSLOT], q[NSLOT], Bd[NSLOT], lbs[NSLOT], ubs[NSLOT];
+  int cls[NSLOT];  // box row class: 0 loose (rho_min), 1 equality-like (rho_eq), 2 inequality (rho)
   __syncthreads();
   {
     // ---- modified Ruiz equilibration + cost scaling (OSQP scaling.c; oracle/mpc.py OSQPOracle._scale) ---------------
-    double q = 0.0, Pb = 0.0, Bd = 0.0, e_ = 0.0, Dj = 1.0, Eb = 1.0, Ee = 1.0;
-    if (live) {
-      Pb = Pdiag[j];
-      q = qg[(size_t)b * n + j];
-      Bd = 1.0;
-      if (i < NX) e_ = (k == 0) ? 1.0 : -1.0;
+    double Pb[NSLOT], e_[NSLOT], Dj[NSLOT], Eb[NSLOT], Ee[NSLOT];
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      x[s] = zb[s] = yb[s] = ze[s] = ye[s] = 0.0;
+      q[s] = Pb[s] = Bd[s] = e_[s] = 0.0;
+      Dj[s] = Eb[s] = Ee[s] = 1.0;
+      cls[s] = 2;
+      if (live[s]) {
+        Pb[s] = Pdiag[j[s]];
+        q[s] = qg[(size_t)b * n + j[s]];
+        Bd[s] = 1.0;
+        if (eqo[s]) e_[s] = (er[s] < NX) ? 1.0 : -1.0;
+      }
     }
     for (int it = 0; it < S.scaling; ++it) {
-      double v = fmax(fabs(Pb), fabs(Bd));
-      v = fmax(v, fabs(e_));
-      if (hasAB)
+      double Dt[NSLOT], Etb[NSLOT], Ete[NSLOT];
 #pragma unroll
-        for (int r = 0; r < NX; ++r) v = fmax(v, fabs(ABk[r * NS]));
-      const double Dt = 1.0 / sqrt(limit_scaling(v));
-      const double Etb = 1.0 / sqrt(limit_scaling(fabs(Bd)));
-      double ve = fabs(e_);
-      if (hasPrev)
+      for (int s = 0; s < NSLOT; ++s) {
+        double v = fmax(fabs(Pb[s]), fabs(Bd[s]));
+        v = fmax(v, fabs(e_[s]));
+        if (hasAB[s])
 #pragma unroll
-        for (int c = 0; c < NS; ++c) ve = fmax(ve, fabs(ABp[c]));
-      const double Ete = 1.0 / sqrt(limit_scaling(ve));
-      if (on) yt[j] = Dt;
-      if (eqo) weq[er] = Ete;
+          for (int r = 0; r < NX; ++r) v = fmax(v, fabs(AB[oABk[s] + r * NS]));
+        Dt[s] = 1.0 / sqrt(limit_scaling(v));
+        Etb[s] = 1.0 / sqrt(limit_scaling(fabs(Bd[s])));
+        double ve = fabs(e_[s]);
+        if (hasPrev[s])
+#pragma unroll
+          for (int c = 0; c < NS; ++c) ve = fmax(ve, fabs(AB[oABp[s] + c]));
+        Ete[s] = 1.0 / sqrt(limit_scaling(ve));
+        if (on[s]) yt[j[s]] = Dt[s];
+        if (eqo[s]) weq[er[s]] = Ete[s];
+      }
       __syncthreads();
-      if (hasAB) {
+      double rv[NRED];
+      rv[0] = 0.0;
+      rv[NRED_MAX] = 0.0;
 #pragma unroll
-        for (int r = 0; r < NX; ++r) {
-          double* a = AB + ((size_t)k * NX + r) * NS + i;
-          *a = (wnext[r] * *a) * Dt;
+      for (int s = 0; s < NSLOT; ++s) {
+        if (hasAB[s]) {
+#pragma unroll
+          for (int r = 0; r < NX; ++r) {
+            double* a = AB + oABk[s] + r * NS;
+            *a = (weq[oWn[s] + r] * *a) * Dt[s];
+          }
+        }
+        e_[s] = (Ete[s] * e_[s]) * Dt[s];
+        Bd[s] = (Etb[s] * Bd[s]) * Dt[s];
+        Pb[s] = (Dt[s] * Pb[s]) * Dt[s];
+        q[s] = Dt[s] * q[s];
+        Dj[s] *= Dt[s]; Eb[s] *= Etb[s]; Ee[s] *= Ete[s];
+        if (live[s]) {
+          rv[0] = fmax(rv[0], fabs(q[s]));
+          rv[NRED_MAX] += fabs(Pb[s]);
         }
       }
-      e_ = (Ete * e_) * Dt;
-      Bd = (Etb * Bd) * Dt;
-      Pb = (Dt * Pb) * Dt;
-      q = Dt * q;
-      Dj *= Dt; Eb *= Etb; Ee *= Ete;
-      double rv[NRED];
-      rv[0] = live ? fabs(q) : 0.0;
-      rv[NRED_MAX] = live ? fabs(Pb) : 0.0;
       reduce(rv, IC<1>{}, IC<1>{});
       double ct = limit_scaling(fmax(rv[NRED_MAX] / n, limit_scaling(rv[0])));
       ct = 1.0 / ct;
-      Pb *= ct;
-      q *= ct;
+#pragma unroll
+      for (int s = 0; s < NSLOT; ++s) {
+        Pb[s] *= ct;
+        q[s] *= ct;
+      }
       cscale *= ct;
       __syncthreads();
     }
     // scaled bounds, row classes, warm start (x = x_in / D ; y = c y_in / E)
-    double lbs = 0.0, ubs = 0.0;
-    if (live) {
-      lbs = Eb * lb[j];
-      ubs = Eb * ub[j];
-      if (lbs < -INF_T && ubs > INF_T) cls = 0;
-      else if (ubs - lbs < RHO_TOL) cls = 1;
-      if (S.warm_x) x = xg[(size_t)b * n + j] / Dj;
-      if (S.warm_y) yb = cscale * yg[(size_t)b * m + neq + j] / Eb;
-    }
-    if (on) {
-      sq[j] = q; sBd[j] = Bd; slb[j] = lbs; sub[j] = ubs; sPb[j] = Pb; sD[j] = Dj; sEb[j] = Eb;
-      sdy[j] = 0.0; yt[j] = 0.0; xt[j] = x;
-    }
-    if (eqo) {
-      ec[er] = e_;
-      sEe[er] = Ee;
-      sbe[er] = Ee * beqg[(size_t)b * neq + er];
-      if (S.warm_y) ye = cscale * yg[(size_t)b * m + er] / Ee;
-      weq[er] = 0.0;
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      lbs[s] = ubs[s] = 0.0;
+      if (live[s]) {
+        lbs[s] = Eb[s] * lb[j[s]];
+        ubs[s] = Eb[s] * ub[j[s]];
+        if (lbs[s] < -INF_T && ubs[s] > INF_T) cls[s] = 0;
+        else if (ubs[s] - lbs[s] < RHO_TOL) cls[s] = 1;
+        if (S.warm_x) x[s] = xg[(size_t)b * n + j[s]] / Dj[s];
+        if (S.warm_y) yb[s] = cscale * yg[(size_t)b * m + neq + j[s]] / Eb[s];
+        gD[j[s]] = Dj[s];
+        gE[neq + j[s]] = Eb[s];
+      }
+      if (on[s]) {
+        sPb[j[s]] = Pb[s];
+        sdy[j[s]] = 0.0; yt[j[s]] = 0.0; xt[j[s]] = x[s];
+      }
+      if (eqo[s]) {
+        ec[er[s]] = e_[s];
+        gE[er[s]] = Ee[s];
+        sbe[er[s]] = Ee[s] * beqg[(size_t)b * neq + er[s]];
+        if (S.warm_y) ye[s] = cscale * yg[(size_t)b * m + er[s]] / Ee[s];
+        weq[er[s]] = 0.0;
+      }
     }
   }
   __syncthreads();
 
-  // (A v)_own-equality-row given v in shared memory (padded stage layout) and the own value vj  [only for eqo threads]
-  auto eq_row = [&](const double* v, double vj) -> double {
+  // (A v)_own-equality-row given v in shared memory (padded stage layout) and the own value vj  [only for eqo slots]
+  auto eq_row = [&](int s, const double* v, double vj) -> double {
     double s0 = 0.0, s1 = 0.0;
-    if (hasPrev) {
-      const double* vp = v + (size_t)(k - 1) * NS;
+    if (hasPrev[s]) {
+      const double* a = AB + oABp[s];
+      const double* vp = v + oVp[s];
 #pragma unroll
       for (int c = 0; c + 1 < NS; c += 2) {
-        s0 = fma(ABp[c], vp[c], s0);
-        s1 = fma(ABp[c + 1], vp[c + 1], s1);
+        s0 = fma(a[c], vp[c], s0);
+        s1 = fma(a[c + 1], vp[c + 1], s1);
       }
-      if (NS & 1) s0 = fma(ABp[NS - 1], vp[NS - 1], s0);
+      if (NS & 1) s0 = fma(a[NS - 1], vp[NS - 1], s0);
     }
-    return fma(ec[er], vj, s0 + s1);
+    return fma(ec[er[s]], vj, s0 + s1);
   };
   // (A' w)_own-column given the own box value wb, the own equality value we and the shared equality vector
-  auto at_col = [&](double wb, double we, const double* wn) -> double {
-    double s = sBd[j] * wb;
-    if (eqo) s = fma(ec[er], we, s);
-    if (hasAB) {
-      double s1 = 0.0;
+  auto at_col = [&](int s, double wb, double we, const double* wv) -> double {
+    double r0 = Bd[s] * wb;
+    if (eqo[s]) r0 = fma(ec[er[s]], we, r0);
+    if (hasAB[s]) {
+      const double* a = AB + oABk[s];
+      const double* wn = wv + oWn[s];
+      double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-      for (int r = 0; r < NX; ++r) s1 = fma(ABk[r * NS], wn[r], s1);
-      s += s1;
+      for (int r = 0; r + 1 < NX; r += 2) {
+        s0 = fma(a[r * NS], wn[r], s0);
+        s1 = fma(a[(r + 1) * NS], wn[r + 1], s1);
+      }
+      if (NX & 1) s0 = fma(a[(NX - 1) * NS], wn[NX - 1], s0);
+      r0 += s0 + s1;
     }
-    return s;
+    return r0;
   };
 
   // z = A x for the warm start
   if (S.warm_x) {
-    zb = sBd[j] * x;
-    if (eqo) ze = eq_row(xt, x);
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      zb[s] = Bd[s] * x[s];
+      if (eqo[s]) ze[s] = eq_row(s, xt, x[s]);
+    }
   }
   __syncthreads();
 
@@ -305,27 +340,31 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   auto factorize = [&]() {
     const double rho_eq = RHO_EQ_OVER_INEQ * rho;
     // phase 1: row i of M_k into Sinv[k][i][:]
-    if (on) {
-      double col[NX];
 #pragma unroll
-      for (int r = 0; r < NX; ++r) col[r] = hasAB ? ABk[r * NS] : 0.0;
-      double* out = Sinv + (size_t)k * NS * NS + i * NS;
-      const double rb = (cls == 0) ? RHO_MIN : ((cls == 1) ? rho_eq : rho);
-      const double Bd = sBd[j], e_ = eqo ? ec[er] : 0.0;
-      double d = sPb[j] + sigma;
-      d = fma(rb, Bd * Bd, d);
-      d = fma(rho_eq, e_ * e_, d);
+    for (int s = 0; s < NSLOT; ++s) {
+      if (on[s]) {
+        const int k = j[s] / NS, i = j[s] - k * NS;
+        double col[NX];
 #pragma unroll
-      for (int c = 0; c < NS; ++c) {
-        double s = 0.0;
-        if (hasAB) {
-          const double* a = AB + (size_t)k * NX * NS + c;
+        for (int r = 0; r < NX; ++r) col[r] = hasAB[s] ? AB[oABk[s] + r * NS] : 0.0;
+        double* out = Sinv + (size_t)j[s] * NS;
+        const double rb = (cls[s] == 0) ? RHO_MIN : ((cls[s] == 1) ? rho_eq : rho);
+        const double e_ = eqo[s] ? ec[er[s]] : 0.0;
+        double d = sPb[j[s]] + sigma;
+        d = fma(rb, Bd[s] * Bd[s], d);
+        d = fma(rho_eq, e_ * e_, d);
 #pragma unroll
-          for (int r = 0; r < NX; ++r) s = fma(col[r], a[r * NS], s);
+        for (int c = 0; c < NS; ++c) {
+          double acc = 0.0;
+          if (hasAB[s]) {
+            const double* a = AB + (size_t)k * NX * NS + c;
+#pragma unroll
+            for (int r = 0; r < NX; ++r) acc = fma(col[r], a[r * NS], acc);
+          }
+          double v = rho_eq * acc;
+          if (c == i) v = live[s] ? v + d : 1.0;
+          out[c] = v;
         }
-        double v = rho_eq * s;
-        if (c == i) v = live ? v + d : 1.0;
-        out[c] = v;
       }
     }
     __syncthreads();
@@ -340,10 +379,10 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
         for (int jj = 0; jj < NS; ++jj) fr[jj] = f[jj * NX];
 #pragma unroll
         for (int i2 = 0; i2 < NX; ++i2) {
-          double s = 0.0;
+          double acc = 0.0;
 #pragma unroll
-          for (int jj = 0; jj < NS; ++jj) s = fma(fr[jj], ab[i2 * NS + jj], s);
-          a[i2] = fma(-(rho_eq * ec[kk * NX + i2]), s, a[i2]);
+          for (int jj = 0; jj < NS; ++jj) acc = fma(fr[jj], ab[i2 * NS + jj], acc);
+          a[i2] = fma(-(rho_eq * ec[kk * NX + i2]), acc, a[i2]);
         }
       }
     };
@@ -382,16 +421,16 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
           double* f = Ft + (size_t)kk * NS * NX + lane * NX;
 #pragma unroll
           for (int i2 = 0; i2 < NX; ++i2) {
-            double s = 0.0;
+            double acc = 0.0;
 #pragma unroll
-            for (int c = 0; c < NS; ++c) s = fma(ab[i2 * NS + c], a[c], s);
-            f[i2] = (rho_eq * ec[(kk + 1) * NX + i2]) * s;
+            for (int c = 0; c < NS; ++c) acc = fma(ab[i2 * NS + c], a[c], acc);
+            f[i2] = (rho_eq * ec[(kk + 1) * NX + i2]) * acc;
           }
         }
         __syncwarp();
       }
     }
-    if (warp == (nwarps > 1 ? 1 : 0)) {  // bottom chain
+    if (warp == 1) {  // bottom chain
       for (int kk = N; kk > p; --kk) {
         double a[NS];
         load_row(a, kk);
@@ -407,10 +446,10 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
           for (int i2 = 0; i2 < NX; ++i2) g[i2] = (rho_eq * ec[kk * NX + i2]) * a[i2];
 #pragma unroll
           for (int jj = 0; jj < NS; ++jj) {
-            double s = 0.0;
+            double acc = 0.0;
 #pragma unroll
-            for (int i2 = 0; i2 < NX; ++i2) s = fma(ab[i2 * NS + jj], g[i2], s);
-            f[jj] = s;
+            for (int i2 = 0; i2 < NX; ++i2) acc = fma(ab[i2 * NS + jj], g[i2], acc);
+            f[jj] = acc;
           }
         }
         __syncwarp();
@@ -429,6 +468,19 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   };
   factorize();
 
+  // own - sum_c f[c] v[c] with a short dependency chain (4 partial sums, `own` folded into the first)
+  auto chain_dot = [&](const double* f, const double* v, int len, double own) -> double {
+    double a0 = own, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+    for (int c = 0; c < NS; c += 4) {
+      if (c < len) a0 = fma(-f[c], v[c], a0);
+      if (c + 1 < len) a1 = fma(f[c + 1], v[c + 1], a1);
+      if (c + 2 < len) a2 = fma(f[c + 2], v[c + 2], a2);
+      if (c + 3 < len) a3 = fma(f[c + 3], v[c + 3], a3);
+    }
+    return (a0 - a1) - (a2 + a3);
+  };
+
   // ---- one KKT solve: xt <- M^{-1} r with r already in yt -------------------------------------------------------------
   auto kkt_solve = [&]() {
     // forward chains
@@ -437,54 +489,43 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
         double fr[NS];
 #pragma unroll
         for (int c = 0; c < NS; ++c) fr[c] = Ft[c * NX + lane];
+        double own = yt[NS + lane];
         for (int kk = 1; kk <= p; ++kk) {
           const double* yp = yt + (size_t)(kk - 1) * NS;
-          const double own = yt[kk * NS + lane];
           double yv[NS];
 #pragma unroll
           for (int c = 0; c < NS; ++c) yv[c] = yp[c];
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int c = 0; c + 1 < NS; c += 2) {
-            s0 = fma(fr[c], yv[c], s0);
-            s1 = fma(fr[c + 1], yv[c + 1], s1);
-          }
-          if (NS & 1) s0 = fma(fr[NS - 1], yv[NS - 1], s0);
-          yt[kk * NS + lane] = own - (s0 + s1);
+          yt[kk * NS + lane] = chain_dot(fr, yv, NS, own);
           if (kk < p) {
             const double* f = Ft + (size_t)kk * NS * NX + lane;
 #pragma unroll
             for (int c = 0; c < NS; ++c) fr[c] = f[c * NX];
+            own = yt[(kk + 1) * NS + lane];
           }
           __syncwarp((1u << NX) - 1u);
         }
       }
     }
-    if (warp == (nwarps > 1 ? 1 : 0)) {
+    if (warp == 1) {
       if (lane < NS && N - 1 >= p) {
         constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
         double fr[NS];
 #pragma unroll
         for (int c = 0; c < NS; ++c) fr[c] = Fbt[(size_t)(N - 1 - p) * NS * NS + c * NS + lane];
+        double own = (N - 1 > p) ? yt[(N - 1) * NS + lane] : 0.0;
         for (int kk = N - 1; kk >= p; --kk) {
           const double* yn = yt + (size_t)(kk + 1) * NS;
-          const double own = yt[kk * NS + lane];
           double yv[NS];
 #pragma unroll
           for (int c = 0; c < NS; ++c) yv[c] = yn[c];
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int c = 0; c + 1 < NS; c += 2) {
-            s0 = fma(fr[c], yv[c], s0);
-            s1 = fma(fr[c + 1], yv[c + 1], s1);
-          }
-          if (NS & 1) s0 = fma(fr[NS - 1], yv[NS - 1], s0);
-          if (kk > p) yt[kk * NS + lane] = own - (s0 + s1);
-          else mrg[lane] = s0 + s1;       // merged into the middle stage by the parallel phase below
+          const double r = chain_dot(fr, yv, NS, own);
+          if (kk > p) yt[kk * NS + lane] = r;
+          else mrg[lane] = -r;            // merged into the middle stage by the parallel phase below
           if (kk > p) {
             const double* f = Fbt + (size_t)(kk - 1 - p) * NS * NS + lane;
 #pragma unroll
             for (int c = 0; c < NS; ++c) fr[c] = f[c * NS];
+            own = (kk - 1 > p) ? yt[(kk - 1) * NS + lane] : 0.0;
           }
           __syncwarp(mask);
         }
@@ -492,80 +533,72 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
     }
     __syncthreads();
     // d_k = S_k^{-1} yt_k for every stage
-    if (on) {
-      const double* si = Sinv + (size_t)k * NS * NS + i;
-      const double* yk = yt + (size_t)k * NS;
-      double sv[NS], yv[NS];
 #pragma unroll
-      for (int c = 0; c < NS; ++c) { sv[c] = si[c * NS]; yv[c] = yk[c]; }
-      if (k == p && p < N) {
+    for (int s = 0; s < NSLOT; ++s) {
+      if (on[s]) {
+        const int k = j[s] / NS, i = j[s] - k * NS;
+        const double* si = Sinv + (size_t)k * NS * NS + i;
+        const double* yk = yt + (size_t)k * NS;
+        double sv[NS], yv[NS];
 #pragma unroll
-        for (int c = 0; c < NS; ++c) yv[c] -= mrg[c];
+        for (int c = 0; c < NS; ++c) { sv[c] = si[c * NS]; yv[c] = yk[c]; }
+        if (k == p && p < N) {
+#pragma unroll
+          for (int c = 0; c < NS; ++c) yv[c] -= mrg[c];
+        }
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int c = 0; c + 1 < NS; c += 2) {
+          s0 = fma(sv[c], yv[c], s0);
+          s1 = fma(sv[c + 1], yv[c + 1], s1);
+        }
+        if (NS & 1) s0 = fma(sv[NS - 1], yv[NS - 1], s0);
+        xt[j[s]] = s0 + s1;
       }
-      double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-      for (int c = 0; c + 1 < NS; c += 2) {
-        s0 = fma(sv[c], yv[c], s0);
-        s1 = fma(sv[c + 1], yv[c + 1], s1);
-      }
-      if (NS & 1) s0 = fma(sv[NS - 1], yv[NS - 1], s0);
-      xt[j] = s0 + s1;
     }
     __syncthreads();
     // backward chains (outwards from the middle stage)
     if (warp == 0) {
       if (lane < NS && p >= 1) {
         constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
-        double fr[NX];
+        double fr[NS];
 #pragma unroll
         for (int i2 = 0; i2 < NX; ++i2) fr[i2] = Ft[(size_t)(p - 1) * NS * NX + lane * NX + i2];
+        double own = xt[(p - 1) * NS + lane];
         for (int kk = p - 1; kk >= 0; --kk) {
           const double* vn = xt + (size_t)(kk + 1) * NS;
-          const double own = xt[kk * NS + lane];
-          double vv[NX];
+          double vv[NS];
 #pragma unroll
           for (int i2 = 0; i2 < NX; ++i2) vv[i2] = vn[i2];
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int i2 = 0; i2 + 1 < NX; i2 += 2) {
-            s0 = fma(fr[i2], vv[i2], s0);
-            s1 = fma(fr[i2 + 1], vv[i2 + 1], s1);
-          }
-          if (NX & 1) s0 = fma(fr[NX - 1], vv[NX - 1], s0);
-          xt[kk * NS + lane] = own - (s0 + s1);
+          xt[kk * NS + lane] = chain_dot(fr, vv, NX, own);
           if (kk > 0) {
             const double* f = Ft + (size_t)(kk - 1) * NS * NX + lane * NX;   // F_kk[i2][lane]
 #pragma unroll
             for (int i2 = 0; i2 < NX; ++i2) fr[i2] = f[i2];
+            own = xt[(kk - 1) * NS + lane];
           }
           __syncwarp(mask);
         }
       }
     }
-    if (warp == (nwarps > 1 ? 1 : 0)) {
+    if (warp == 1) {
       if (lane < NS && p + 1 <= N) {
         constexpr unsigned mask = (NS >= 32) ? 0xffffffffu : ((1u << NS) - 1u);
         double fr[NS];
 #pragma unroll
         for (int c = 0; c < NS; ++c) fr[c] = Fbt[lane * NS + c];          // Fb_p[jj][lane]
+        double own = xt[(p + 1) * NS + lane];
         for (int kk = p + 1; kk <= N; ++kk) {
           const double* vp = xt + (size_t)(kk - 1) * NS;
-          const double own = xt[kk * NS + lane];
           double vv[NS];
 #pragma unroll
           for (int c = 0; c < NS; ++c) vv[c] = vp[c];
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int c = 0; c + 1 < NS; c += 2) {
-            s0 = fma(fr[c], vv[c], s0);
-            s1 = fma(fr[c + 1], vv[c + 1], s1);
-          }
-          if (NS & 1) s0 = fma(fr[NS - 1], vv[NS - 1], s0);
-          xt[kk * NS + lane] = own - (s0 + s1);
+          xt[kk * NS + lane] = chain_dot(fr, vv, NS, own);
           if (kk < N) {
             const double* f = Fbt + (size_t)(kk - p) * NS * NS + lane * NS;  // Fb_kk[jj][lane]
 #pragma unroll
             for (int c = 0; c < NS; ++c) fr[c] = f[c];
+            own = xt[(kk + 1) * NS + lane];
           }
           __syncwarp(mask);
         }
@@ -583,46 +616,51 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
     double v[NRED];
 #pragma unroll
     for (int e = 0; e < NRED; ++e) v[e] = 0.0;
-    if (live) {
-      const double lbs = slb[j], ubs = sub[j], Bd = sBd[j], Pb = sPb[j], Dj = sD[j], Eb = sEb[j], q = sq[j];
-      const double dx = yt[j], dyb = sdy[j];
-      const bool uinf = ubs > INF_T, linf = lbs < -INF_T;
-      // box row: projection of dy on the polar of the recession cone
-      double dyp = dyb;
-      if (uinf && linf) dyp = 0.0;
-      else if (uinf) dyp = fmin(dyp, 0.0);
-      else if (linf) dyp = fmax(dyp, 0.0);
-      v[0] = fabs(Dj * dx);
-      v[1] = fabs(Pb * dx / Dj);
-      v[NRED_MAX + 0] = q * dx;
-      {
-        const double Ax = Bd * x, Ei = 1.0 / Eb;
-        v[2] = fabs(Ei * (Ax - zb)); v[3] = fabs(Ei * Ax); v[4] = fabs(Ei * zb);
-        v[5] = fabs(Ax - zb); v[6] = fabs(Ax); v[7] = fabs(zb);
-        v[8] = fabs(Eb * dyp);
-        v[NRED_MAX + 1] = ubs * fmax(dyp, 0.0) + lbs * fmin(dyp, 0.0);
-        const double Adx = (Bd * dx) * Ei;
-        if (!uinf) v[9] = fmax(v[9], Adx);
-        if (!linf) v[10] = fmax(v[10], -Adx);
-      }
-      double dye = 0.0;
-      if (eqo) {
-        const double Ee = sEe[er], bes = sbe[er];
-        dye = weq[er];
-        const double Ax = eq_row(xt, x), Ei = 1.0 / Ee;
-        v[2] = fmax(v[2], fabs(Ei * (Ax - ze))); v[3] = fmax(v[3], fabs(Ei * Ax)); v[4] = fmax(v[4], fabs(Ei * ze));
-        v[5] = fmax(v[5], fabs(Ax - ze)); v[6] = fmax(v[6], fabs(Ax)); v[7] = fmax(v[7], fabs(ze));
-        v[8] = fmax(v[8], fabs(Ee * dye));
-        v[NRED_MAX + 1] += bes * fmax(dye, 0.0) + bes * fmin(dye, 0.0);
-        const double Adx = eq_row(yt, dx) * Ei;
-        v[9] = fmax(v[9], Adx);
-        v[10] = fmax(v[10], -Adx);
-      }
-      {
-        const double Px = Pb * x, Aty = at_col(yb, ye, tmp + (size_t)(k + 1) * NX), Di = 1.0 / Dj;
-        v[11] = fabs(Di * (Px + q + Aty)); v[12] = fabs(Di * Px); v[13] = fabs(Di * Aty); v[14] = fabs(Di * q);
-        v[15] = fabs(Px + q + Aty); v[16] = fabs(Px); v[17] = fabs(Aty); v[18] = fabs(q);
-        v[19] = fabs(at_col(dyp, dye, wnext) * Di);
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      if (live[s]) {
+        const double Pb = sPb[j[s]], Dj = gD[j[s]], Eb = gE[neq + j[s]];
+        const double dx = yt[j[s]], dyb = sdy[j[s]];
+        const bool uinf = ubs[s] > INF_T, linf = lbs[s] < -INF_T;
+        // box row: projection of dy on the polar of the recession cone
+        double dyp = dyb;
+        if (uinf && linf) dyp = 0.0;
+        else if (uinf) dyp = fmin(dyp, 0.0);
+        else if (linf) dyp = fmax(dyp, 0.0);
+        v[0] = fmax(v[0], fabs(Dj * dx));
+        v[1] = fmax(v[1], fabs(Pb * dx / Dj));
+        v[NRED_MAX + 0] += q[s] * dx;
+        {
+          const double Ax = Bd[s] * x[s], Ei = 1.0 / Eb;
+          v[2] = fmax(v[2], fabs(Ei * (Ax - zb[s]))); v[3] = fmax(v[3], fabs(Ei * Ax)); v[4] = fmax(v[4], fabs(Ei * zb[s]));
+          v[5] = fmax(v[5], fabs(Ax - zb[s])); v[6] = fmax(v[6], fabs(Ax)); v[7] = fmax(v[7], fabs(zb[s]));
+          v[8] = fmax(v[8], fabs(Eb * dyp));
+          v[NRED_MAX + 1] += ubs[s] * fmax(dyp, 0.0) + lbs[s] * fmin(dyp, 0.0);
+          const double Adx = (Bd[s] * dx) * Ei;
+          if (!uinf) v[9] = fmax(v[9], Adx);
+          if (!linf) v[10] = fmax(v[10], -Adx);
+        }
+        double dye = 0.0;
+        if (eqo[s]) {
+          const double Ee = gE[er[s]], bes = sbe[er[s]];
+          dye = weq[er[s]];
+          const double Ax = eq_row(s, xt, x[s]), Ei = 1.0 / Ee;
+          v[2] = fmax(v[2], fabs(Ei * (Ax - ze[s]))); v[3] = fmax(v[3], fabs(Ei * Ax)); v[4] = fmax(v[4], fabs(Ei * ze[s]));
+          v[5] = fmax(v[5], fabs(Ax - ze[s])); v[6] = fmax(v[6], fabs(Ax)); v[7] = fmax(v[7], fabs(ze[s]));
+          v[8] = fmax(v[8], fabs(Ee * dye));
+          v[NRED_MAX + 1] += bes * fmax(dye, 0.0) + bes * fmin(dye, 0.0);
+          const double Adx = eq_row(s, yt, dx) * Ei;
+          v[9] = fmax(v[9], Adx);
+          v[10] = fmax(v[10], -Adx);
+        }
+        {
+          const double Px = Pb * x[s], Aty = at_col(s, yb[s], ye[s], tmp), Di = 1.0 / Dj;
+          v[11] = fmax(v[11], fabs(Di * (Px + q[s] + Aty))); v[12] = fmax(v[12], fabs(Di * Px));
+          v[13] = fmax(v[13], fabs(Di * Aty)); v[14] = fmax(v[14], fabs(Di * q[s]));
+          v[15] = fmax(v[15], fabs(Px + q[s] + Aty)); v[16] = fmax(v[16], fabs(Px));
+          v[17] = fmax(v[17], fabs(Aty)); v[18] = fmax(v[18], fabs(q[s]));
+          v[19] = fmax(v[19], fabs(at_col(s, dyp, dye, weq) * Di));
+        }
       }
     }
     reduce(v, IC<NRED_MAX>{}, IC<NRED_SUM>{});
@@ -651,55 +689,71 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   CheckOut co;
   co.pri = co.dua = 0.0; co.rho_est = rho; co.status = GPMPC_QP_UNSOLVED;
   const double alpha = S.alpha;
-  if (S.max_iter > 0) {
-    if (eqo) weq[er] = fma(RHO_EQ_OVER_INEQ * rho, ze, -ye);
-  } else if (eqo) {
-    tmp[er] = ye;  // check buffers for a solve without iterations: dx = dy = 0 (yt, sdy, weq are zero), x in xt
+  double rho_eq = RHO_EQ_OVER_INEQ * rho, rei = 1.0 / rho_eq, rhoi = 1.0 / rho;  // (divisions only when rho changes)
+#pragma unroll
+  for (int s = 0; s < NSLOT; ++s) {
+    if (eqo[s]) {
+      if (S.max_iter > 0) weq[er[s]] = fma(RHO_EQ_OVER_INEQ * rho, ze[s], -ye[s]);
+      else tmp[er[s]] = ye[s];  // check buffers for a solve without iterations: dx = dy = 0, x in xt
+    }
   }
   __syncthreads();
   for (it = 1; it <= S.max_iter; ++it) {
     const bool can_check = S.check_every > 0 && (it % S.check_every) == 0;
     const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval > 0 && (it % S.adaptive_rho_interval) == 0;
     const bool checking = can_check || can_adapt || it == S.max_iter;
-    const double rho_eq = RHO_EQ_OVER_INEQ * rho, rei = 1.0 / rho_eq;
-    const double rb = (cls == 0) ? RHO_MIN : ((cls == 1) ? rho_eq : rho);
-    const double rbi = (cls == 0) ? (1.0 / RHO_MIN) : ((cls == 1) ? rei : 1.0 / rho);
     // right-hand side sigma x - q + A'(rho z - y)
-    if (on) yt[j] = fma(sigma, x, -sq[j]) + at_col(fma(rb, zb, -yb), eqo ? weq[er] : 0.0, wnext);
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      const double rb = (cls[s] == 0) ? RHO_MIN : ((cls[s] == 1) ? rho_eq : rho);
+      if (on[s])
+        yt[j[s]] = fma(sigma, x[s], -q[s]) + at_col(s, fma(rb, zb[s], -yb[s]), eqo[s] ? weq[er[s]] : 0.0, weq);
+    }
     __syncthreads();
     kkt_solve();
     // z_tilde = A x_tilde ; z, y, x updates
-    const double xtj = on ? xt[j] : 0.0;
-    double dx, dyb, dye = 0.0;
-    {
-      const double ztb = sBd[j] * xtj;
-      const double zr = alpha * ztb + (1.0 - alpha) * zb;
-      const double zn = fmin(fmax(fma(yb, rbi, zr), slb[j]), sub[j]);
-      dyb = rb * (zr - zn);
-      yb += dyb;
-      zb = zn;
-    }
-    if (eqo) {
-      const double zte = eq_row(xt, xtj), bes = sbe[er];
-      const double zr = alpha * zte + (1.0 - alpha) * ze;
-      const double zn = fmin(fmax(fma(ye, rei, zr), bes), bes);
-      dye = rho_eq * (zr - zn);
-      ye += dye;
-      ze = zn;
-    }
-    {
-      const double xn = alpha * xtj + (1.0 - alpha) * x;
-      dx = xn - x;
-      x = xn;
+    double dx[NSLOT], dyb[NSLOT], dye[NSLOT];
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      const double rb = (cls[s] == 0) ? RHO_MIN : ((cls[s] == 1) ? rho_eq : rho);
+      const double rbi = (cls[s] == 0) ? (1.0 / RHO_MIN) : ((cls[s] == 1) ? rei : rhoi);
+      const double xtj = on[s] ? xt[j[s]] : 0.0;
+      {
+        const double ztb = Bd[s] * xtj;
+        const double zr = alpha * ztb + (1.0 - alpha) * zb[s];
+        const double zn = fmin(fmax(fma(yb[s], rbi, zr), lbs[s]), ubs[s]);
+        dyb[s] = rb * (zr - zn);
+        yb[s] += dyb[s];
+        zb[s] = zn;
+      }
+      dye[s] = 0.0;
+      if (eqo[s]) {
+        const double zte = eq_row(s, xt, xtj), bes = sbe[er[s]];
+        const double zr = alpha * zte + (1.0 - alpha) * ze[s];
+        const double zn = bes;  // projection of zr + y / rho on the degenerate interval [b, b]
+        dye[s] = rho_eq * (zr - zn);
+        ye[s] += dye[s];
+        ze[s] = zn;
+      }
+      {
+        const double xn = alpha * xtj + (1.0 - alpha) * x[s];
+        dx[s] = xn - x[s];
+        x[s] = xn;
+      }
     }
     if (!checking) {  // (every read of weq of this iteration happened before the barriers inside kkt_solve)
-      if (eqo) weq[er] = fma(rho_eq, ze, -ye);
+#pragma unroll
+      for (int s = 0; s < NSLOT; ++s)
+        if (eqo[s]) weq[er[s]] = fma(rho_eq, ze[s], -ye[s]);
       __syncthreads();
       continue;
     }
     __syncthreads();  // every read of xt (eq_row above) is done
-    if (on) { xt[j] = x; yt[j] = dx; sdy[j] = dyb; }
-    if (eqo) { tmp[er] = ye; weq[er] = dye; }
+#pragma unroll
+    for (int s = 0; s < NSLOT; ++s) {
+      if (on[s]) { xt[j[s]] = x[s]; yt[j[s]] = dx[s]; sdy[j[s]] = dyb[s]; }
+      if (eqo[s]) { tmp[er[s]] = ye[s]; weq[er[s]] = dye[s]; }
+    }
     __syncthreads();
     if (can_check || can_adapt) {
       co = check(false);
@@ -709,10 +763,13 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
       }
       if (can_adapt && (co.rho_est > rho * S.adaptive_rho_tolerance || co.rho_est < rho / S.adaptive_rho_tolerance)) {
         rho = co.rho_est;
+        rho_eq = RHO_EQ_OVER_INEQ * rho; rei = 1.0 / rho_eq; rhoi = 1.0 / rho;
         factorize();
       }
       if (it < S.max_iter) {  // (the block reduction inside check() separates its reads of weq from this write)
-        if (eqo) weq[er] = fma(RHO_EQ_OVER_INEQ * rho, ze, -ye);
+#pragma unroll
+        for (int s = 0; s < NSLOT; ++s)
+          if (eqo[s]) weq[er[s]] = fma(RHO_EQ_OVER_INEQ * rho, ze[s], -ye[s]);
         __syncthreads();
       }
     }
@@ -731,12 +788,19 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   }
   // ---- objective and solution out (unscaled) ---------------------------------------------------------------------------
   double ob[NRED];
-  ob[NRED_MAX] = live ? (0.5 * sPb[j] * x + sq[j]) * x : 0.0;
+  ob[NRED_MAX] = 0.0;
+#pragma unroll
+  for (int s = 0; s < NSLOT; ++s)
+    if (live[s]) ob[NRED_MAX] += (0.5 * sPb[j[s]] * x[s] + q[s]) * x[s];
   reduce(ob, IC<0>{}, IC<1>{});
-  if (live) xg[(size_t)b * n + j] = sD[j] * x;
-  if (!S.commit_y_solved_only || status == GPMPC_QP_SOLVED) {
-    if (live) yg[(size_t)b * m + neq + j] = sEb[j] * yb / cscale;
-    if (eqo) yg[(size_t)b * m + er] = sEe[er] * ye / cscale;
+  const bool commit_y = !S.commit_y_solved_only || status == GPMPC_QP_SOLVED;
+#pragma unroll
+  for (int s = 0; s < NSLOT; ++s) {
+    if (live[s]) {
+      xg[(size_t)b * n + j[s]] = gD[j[s]] * x[s];
+      if (commit_y) yg[(size_t)b * m + neq + j[s]] = gE[neq + j[s]] * yb[s] / cscale;
+    }
+    if (eqo[s] && commit_y) yg[(size_t)b * m + er[s]] = gE[er[s]] * ye[s] / cscale;
   }
   if (tid == 0) {
     status_g[b] = status;
@@ -750,29 +814,29 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
 
 }  // namespace
 
-// Launcher used by gpmpc_admm_solve (csrc/admm.cu).  Returns GPMPC_ERR_ARG when the problem does not fit this kernel
-// (the caller then falls back to the first-generation kernel).
+// Launcher used by gpmpc_admm_solve (csrc/admm.cu).  Returns GPMPC_ERR_ARG without launching when the problem does not
+// fit this kernel (the caller then falls back to the first-generation kernel).  `scratch`: B x (n + m) doubles.
 template <int NX, int NU>
 int launch_admm_stage(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
-                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active, double* x,
-                      double* y, double* rho, int* status, int* iters, double* obj, double* pri, double* dua,
-                      cudaStream_t stream) {
+                      const double* lb, const double* ub, const GpmpcAdmmSettings& S, const int* active,
+                      double* scratch, double* x, double* y, double* rho, int* status, int* iters, double* obj,
+                      double* pri, double* dua, cudaStream_t stream) {
   using L = Stage<NX, NU>;
+  constexpr int NSLOT = 2;
   const size_t smem = L::smem_doubles(N) * sizeof(double);
-  const int warps = L::warps(N);
-  if (smem > 227 * 1024 || warps > 7) return GPMPC_ERR_ARG;
-  auto kern = (N == 20) ? admm_stage_kernel<NX, NU, 20> : admm_stage_kernel<NX, NU, 0>;
+  if (smem > 227 * 1024 || (N + 1) * L::NS > NSLOT * L::THREADS) return GPMPC_ERR_ARG;
+  auto kern = (N == 20) ? admm_stage_kernel<NX, NU, 20, NSLOT> : admm_stage_kernel<NX, NU, 0, NSLOT>;
   static size_t configured[2] = {0, 0};
   if (smem > configured[N == 20]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     configured[N == 20] = smem;
   }
-  kern<<<B, warps * 32, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, x, y, rho, status, iters, obj, pri,
-                                        dua);
+  kern<<<B, L::THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters,
+                                        obj, pri, dua);
   return gpmpc_check_launch("admm_stage");
 }
 
 template int launch_admm_stage<7, 3>(int, int, const double*, const double*, const double*, const double*,
                                      const double*, const double*, const GpmpcAdmmSettings&, const int*, double*,
-                                     double*, double*, int*, int*, double*, double*, double*, cudaStream_t);
+                                     double*, double*, double*, int*, int*, double*, double*, double*, cudaStream_t);
