@@ -324,9 +324,12 @@ def run_b200_arm(args):
         n_pad = ((N_TRAIN + 127) // 128) * 128
         work = {  # phase -> (bound, algorithmic units per step: flops or bytes, kernel description)
             "gp_variance": ("tensor", Q * float(n_pad) ** 2,
-                            "dgemm_nt_kernel x31: blocked DMMA TRSM V = L^-1 K*^T with fused sum of squares (n_pad^2 flop "
-                            "per query, SURVEY 8d)"),
-            "admm": ("hbm", B * 22e3, "admm_kernel<7,3>: 22 kB compulsory per QP (SURVEY 8d); dependency-chain bound, "
+                            ("dgemm_nt_kernel x1: triangular DMMA GEMM |L^-1 K*^T|^2 against the explicit inverse factor, "
+                             "sum of squares fused, V never stored (n_pad^2 flop per query, SURVEY 8d)")
+                            if ctl.config.variance_via_inverse else
+                            ("dgemm_nt_kernel x31: blocked DMMA TRSM V = L^-1 K*^T with fused sum of squares (n_pad^2 flop "
+                             "per query, SURVEY 8d)")),
+            "admm": ("hbm", B * 22e3, "admm_stage_kernel<7,3,20,2>: 22 kB compulsory per QP (SURVEY 8d); dependency-chain bound, "
                                       "neither HBM nor FLOP limited (DESIGN.md section 4)"),
             "rollout": ("hbm", Q * 8.0 * n_pad + B * 8.0 * (7 + 60 + 147 + 60),
                         "rollout3_kernel: K* rows written once (8 n_pad bytes per query) + trajectories"),

@@ -21,6 +21,7 @@ constexpr int GEMM_THREADS = 256;
 enum GemmEpilogue : int {
   EPI_STORE = 0,         // C = alpha*acc + beta*C
   EPI_STORE_SUMSQ = 1,   // C = alpha*acc (+beta*C) and sumsq[n] += sum_m (alpha*acc)^2   (one M tile only)
+  EPI_SUMSQ_PART = 2,    // no C store: sumsq[(m0/BM)*part_stride + n] = sum_{m in tile} (alpha*acc)^2   (any number of M tiles)
 };
 
 struct GemmParams {
@@ -36,6 +37,8 @@ struct GemmParams {
   int lower_only;   // skip tiles strictly above the block diagonal (n0 >= m0 + BM)
   int row_min;      // rows  m < row_min are computed but not stored
   int col_min;      // cols  n < col_min are computed but not stored
+  long part_stride; // EPI_SUMSQ_PART: distance between the partial-sum rows of consecutive M tiles
+  int m_fast;       // grid = (M tiles, N tiles) with the M tiles of one N tile adjacent and the longest k loops first
 };
 
 template <int BM, int BN>
@@ -53,7 +56,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) d
   extern __shared__ __align__(16) unsigned char smem_raw[];
   GemmSmem<BM, BN>& sm = *reinterpret_cast<GemmSmem<BM, BN>*>(smem_raw);
 
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int m0 = (p.m_fast ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.y) * BM;
+  const int n0 = (p.m_fast ? (int)blockIdx.y : (int)blockIdx.x) * BN;
   if (p.lower_only && n0 >= m0 + BM) return;
   const int bz = blockIdx.z;
   const double* __restrict__ A = p.A + bz * p.strideA + (long)m0 * p.lda;
@@ -135,7 +139,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) d
       const int n = n0 + wn * WN + j * 8 + 2 * t;
       double v0 = alpha * acc[i][j][0], v1 = alpha * acc[i][j][1];
       const bool row_ok = (m >= p.row_min);
-      if (!p.c_trans) {
+      if (p.epi == EPI_SUMSQ_PART) {
+      } else if (!p.c_trans) {
         double* cp = C + (long)m * p.ldc + n;
         if (beta != 0.0) {
           double2 old = *reinterpret_cast<const double2*>(cp);
@@ -166,7 +171,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) d
     }
   }
 
-  if (p.epi == EPI_STORE_SUMSQ) {
+  if (p.epi == EPI_STORE_SUMSQ || p.epi == EPI_SUMSQ_PART) {
     // reduce over the 8 row-groups of the warp (lanes with equal t), then across the WARPS_M warps via shared memory
     __shared__ double red[WARPS_M][BN];
 #pragma unroll
@@ -185,7 +190,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) d
       double v = 0.0;
 #pragma unroll
       for (int w = 0; w < WARPS_M; ++w) v += red[w][c];
-      ss[n0 + c] += v;
+      if (p.epi == EPI_SUMSQ_PART) ss[(long)(m0 / BM) * p.part_stride + n0 + c] = v;
+      else ss[n0 + c] += v;
     }
   }
 }
@@ -206,6 +212,7 @@ int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream) {
     configured = true;
   }
   dim3 grid(p.N / BN, p.M / BM, batch);
+  if (p.m_fast) grid = dim3(p.M / BM, p.N / BN, batch);
   kern<<<grid, GEMM_THREADS, smem, stream>>>(p);
   return gpmpc_check_launch("dgemm_nt");
 }

@@ -345,6 +345,75 @@ extern "C" int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const doub
   return gpmpc_trsm_sumsq_batched(L, n_pad, lda, 0, Winv, Ks, q_pad, ldk, 0, sumsq, 1, stream_);
 }
 
+// ------------------------------------------------------------------------------- explicit inverse factor, many RHS
+// The horizon pipeline evaluates the predictive variance (exact_gp.py:259-264) for B*N queries against ONE factor per
+// control step.  With W = L^{-1} formed once per fit, sum_i v_i^2 = |W k*|^2 is a single triangular DMMA GEMM launch
+// (same n^2 flops per query as the blocked solve above, no 2(n/64)-1 dependent launches, V never written back).
+__global__ void set_identity_kernel(double* __restrict__ A, int n, long lda) {
+  const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long)n * n) return;
+  const int r = (int)(idx / n), c = (int)(idx % n);
+  A[(long)r * lda + c] = (r == c) ? 1.0 : 0.0;
+}
+__global__ void __launch_bounds__(256) transpose_inplace_kernel(double* __restrict__ A, int n, long lda) {
+  __shared__ double t0[32][33], t1[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;
+  if (bj > bi) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    t0[r][tx] = A[(long)(bi * 32 + r) * lda + bj * 32 + tx];
+    t1[r][tx] = A[(long)(bj * 32 + r) * lda + bi * 32 + tx];
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    A[(long)(bi * 32 + r) * lda + bj * 32 + tx] = t1[tx][r];
+    if (bi != bj) A[(long)(bj * 32 + r) * lda + bi * 32 + tx] = t0[tx][r];
+  }
+}
+
+extern "C" int gpmpc_tri_inverse(const double* L, int n_pad, long lda, const double* Winv, double* Linv, long ldi,
+                                 void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad % 128 == 0, "gpmpc_tri_inverse: n_pad must be a multiple of 128");
+  const long tot = (long)n_pad * n_pad;
+  set_identity_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(Linv, n_pad, ldi);
+  double* ss = nullptr;
+  if (cudaMallocAsync(&ss, sizeof(double) * n_pad, stream) != cudaSuccess) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_tri_inverse: scratch allocation failed");
+    return GPMPC_ERR_CUDA;
+  }
+  // rows of the identity solved in place: row q <- (L^{-1} e_q)' = column q of L^{-1}, i.e. the result is W'
+  int rc = gpmpc_trsm_sumsq_batched(L, n_pad, lda, 0, Winv, Linv, n_pad, ldi, 0, ss, 1, stream_);
+  cudaFreeAsync(ss, stream);
+  if (rc) return rc;
+  transpose_inplace_kernel<<<dim3(n_pad / 32, n_pad / 32), 256, 0, stream>>>(Linv, n_pad, ldi);
+  return gpmpc_check_launch("tri_inverse");
+}
+
+__global__ void sum_parts_kernel(const double* __restrict__ part, int nparts, long stride, int q, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= q) return;
+  double s = 0.0;
+  for (int t = 0; t < nparts; ++t) s += part[(long)t * stride + i];  // fixed order: bit-reproducible
+  out[i] = s;
+}
+
+extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk,
+                                double* work, double* sumsq, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0, "gpmpc_linv_sumsq: n_pad and q_pad must be multiples of 128");
+  GemmParams p{};
+  p.A = Linv; p.lda = ldi;
+  p.B = Ks; p.ldb = ldk;
+  p.M = n_pad; p.N = q_pad; p.K = n_pad; p.alpha = 1.0; p.beta = 0.0;
+  p.k_tri = 1; p.m_fast = 1; p.epi = EPI_SUMSQ_PART; p.sumsq = work; p.part_stride = q_pad;
+  int rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
+  if (rc) return rc;
+  sum_parts_kernel<<<(q_pad + 255) / 256, 256, 0, stream>>>(work, n_pad / 64, q_pad, q_pad, sumsq);
+  return gpmpc_check_launch("linv_sumsq");
+}
+
 // ------------------------------------------------------------------------------------------------ small-M TRSM
 // X = L^{-1} B for a small lower-triangular L (M <= 128, e.g. the sparse GP's L_uu / L_B, sparse_gp.py:190,293,296)
 // and many columns: L in shared memory, one column per thread (broadcast reads), optional column sum of squares.

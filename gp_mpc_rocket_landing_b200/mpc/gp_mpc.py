@@ -49,6 +49,9 @@ class GPMPCConfig(MPCConfig):
     qp_adaptive_rho_interval: int = 25  # iteration based (OSQP's default is timing based, i.e. not reproducible)
     qp_scaling: int = 3               # osqp_rti.py:477
     qp_keep_rho: bool = True          # the adapted rho persists across solves, as inside one OSQP solver object
+    variance_via_inverse: bool = True  # horizon variances |L^-1 k*|^2 as one triangular DMMA GEMM against the explicit
+                                       # inverse factor (formed once per fit) instead of the blocked in-place solve
+                                       # (31 dependent launches); same quantity, rounding differs by O(cond(L) eps)
     overlap_uncertainty: bool = False  # GP variance + covariance chain on a side stream, concurrent with the QP (the QP
                                        # does not read them: gp_mpc.py:414 evaluates the tightening at k = 0 only).
                                        # Measured on B200: step 11.13 -> 10.58 ms only -- both kernels fill the SMs'
@@ -81,6 +84,7 @@ class _BatchState:
         self.q_pad = ge.pad_to(B * N, 128)
         self.dvar = torch.zeros((self.q_pad, 3), **f64)
         self.Ks = torch.zeros((self.q_pad, model.f.n_pad), **f64) if model is not None else None
+        self.var_work = None  # scratch of the explicit-inverse variance path (allocated on first use)
         self.covs = torch.zeros((B, N + 1, NX, NX), **f64)
         self.AB = torch.zeros((B, N, NX, NX + NU), **f64)
         self.beq = torch.zeros((B, NX * (N + 1)), **f64)
@@ -207,11 +211,19 @@ class GPMPC:
         """GP variances of the rows of st.Ks (blocked DMMA TRSM with fused sum of squares) -> covariance chain."""
         f = self._model.f
         with self._span("gp_variance"):
-            sumsq = f.sumsq_inplace(st.Ks)
+            if self.config.variance_via_inverse:
+                if st.var_work is None:
+                    st.var_work = ge.torch_().empty(((f.n_pad // 64) * st.Ks.shape[0],), dtype=st.Ks.dtype,
+                                                    device=st.Ks.device)
+                sumsq = f.sumsq_linv(st.Ks, st.var_work)
+            else:
+                sumsq = f.sumsq_inplace(st.Ks)
         with self._span("cov"):
             ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, st.B * st.N, 3, f.sv, 1e-10, ge.ptr(self._model.ystd),
                     ge.ptr(st.dvar), 3, 0, ge.stream())
             me.propagate_cov(self._dyn, X, U, st.dvar, st.covs, sigma0=1e-6, active=active)
+        if self.config.variance_via_inverse:
+            return 4  # triangular GEMM + partial-sum reduction + var + cov
         return 2 * (f.n_pad // 64) + 2  # launches: memset is not a kernel; (n/64 - 1) GEMM + n/64 W-GEMM + var + cov
 
     def _fork_uncertainty(self, st: _BatchState, X, U, active):

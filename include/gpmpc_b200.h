@@ -76,6 +76,16 @@ int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, d
 int gpmpc_trsm_sumsq_batched(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* Ks,
                              int q_pad, long ldk, long strideK, double* sumsq, int batch, void* stream);
 
+/* Linv <- L^{-1} (n_pad x n_pad, lower triangular, row-major) from the factor and the inverted diagonal blocks that
+ * gpmpc_potrf returns.  Formed once per fit; lets the horizon pipeline evaluate the predictive variances of
+ * exact_gp.py:259-264 (v = solve_triangular(L, K*^T); sum v^2) as one triangular GEMM launch, see gpmpc_linv_sumsq. */
+int gpmpc_tri_inverse(const double* L, int n_pad, long lda, const double* Winv, double* Linv, long ldi, void* stream);
+
+/* sumsq[q] = | Linv Ks[q,:]^T |^2 for the q_pad rows of Ks (q_pad x n_pad row-major, NOT modified).
+ * work: (n_pad/64) x q_pad doubles of scratch (per-tile partial sums, reduced in a fixed order). */
+int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk, double* work,
+                     double* sumsq, void* stream);
+
 /* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
  * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
 int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, long ldb, int ncols, int b_colmajor, double* sumsq,

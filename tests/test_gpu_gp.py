@@ -119,6 +119,30 @@ def test_simple3dof_exact_1000pt(eng, tag, noise, tol):
     np.testing.assert_allclose(f.L.cpu().numpy()[999, :1000], g[f"{tag}_Lrow999"], rtol=1e-7, atol=1e-12)
 
 
+@pytest.mark.parametrize("tag,noise,tol", [("n1e-2", 1e-2, 1e-9), ("n1e-4", 1e-4, 1e-8)])
+def test_explicit_inverse_variance_path(eng, tag, noise, tol):
+    """The horizon pipeline's one-launch variance (|L^-1 k*|^2 against the explicit inverse factor) against the
+    reference's own predictive variance (golden) and against the blocked in-place solve; Ks must stay untouched."""
+    import torch
+    g = load_golden("simple3dof_exact.npz")
+    f = eng.ExactFactor(0, np.ones(11), 1.0, noise).fit(eng.to_dev(g["Z_train"]))
+    m = eng.ExactModelDev(f).fit_targets(g["D"])
+    W = f.ensure_linv()
+    Lh, Wh = f.L.cpu().numpy()[:1000, :1000], W.cpu().numpy()
+    assert np.max(np.abs(np.triu(Wh, 1))) == 0.0                      # exactly lower triangular
+    assert np.max(np.abs(Wh[:1000, :1000] @ Lh - np.eye(1000))) < 1e-9
+    Ks, Q = f.cross(eng.to_dev(g["Z_query"]))
+    Ks0 = Ks.clone()
+    ss_inv = f.sumsq_linv(Ks)
+    assert torch.equal(Ks, Ks0)
+    ss_trsm = f.sumsq_inplace(Ks)
+    ystd = m.ystd.cpu().numpy()
+    var_inv = np.maximum(1.0 - ss_inv.cpu().numpy()[:Q], 1e-10)[:, None] * ystd[None, :] ** 2
+    var_trsm = np.maximum(1.0 - ss_trsm.cpu().numpy()[:Q], 1e-10)[:, None] * ystd[None, :] ** 2
+    assert relerr(var_inv, g[f"{tag}_var"]) < tol
+    assert relerr(var_inv, var_trsm) < tol
+
+
 def test_predict_batch_equals_singles_and_variance_floor(eng):
     """batch = loop of singles (bitwise: every query row is solved independently), floor 1e-10 * y_std^2."""
     rng = np.random.default_rng(5)
