@@ -52,8 +52,13 @@ struct Prob {
 
   static __host__ __device__ size_t smem_doubles(int N) {
     const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
-    return (size_t)N * NX * NS + (size_t)N * NS * GP + (size_t)N * NS * HP + (size_t)(N + 1) * NP + (size_t)N * NX + 8 +
-           6 * n + 5 * m + 64 + 2 * 17;  // + alignment slack of the 17 arrays
+    return (size_t)N * NX * NS + (size_t)N * NS * GP + (size_t)N * NS * HP + (size_t)(N + 1) * NP + (size_t)N * NX + NX + 2 +
+           6 * n + 4 * m + zt_doubles(m) + 64 + 2 * 17;  // + alignment slack of the 17 arrays
+  }
+  // zt doubles as the factorisation workspace (dense NS x NS block, NS x GP inverse, NX x GP coupling)
+  static __host__ __device__ size_t zt_doubles(size_t m) {
+    const size_t need = ((NS * NS + 1) & ~1) + (size_t)NS * GP + (size_t)NX * GP;
+    return m > need ? m : need;
   }
   __device__ void carve(double* s, int N_) {
     N = N_; n = N * NS + NX; neq = NX * (N + 1); m = neq + n;
@@ -63,9 +68,9 @@ struct Prob {
     H = take(N * NS * HP);
     Li = take((N + 1) * NP);
     Nd = take(N * NX);
-    Ei = take(8);
+    Ei = take(NX + 2);
     Bd = take(n); Pb = take(n); qb = take(n); x = take(n); xt = take(n); w = take(n);
-    lbs = take(m); ubs = take(m); z = take(m); y = take(m); zt = take(m);
+    lbs = take(m); ubs = take(m); z = take(m); y = take(m); zt = take(zt_doubles(m));
     red = take(64);
   }
 
@@ -527,7 +532,7 @@ __global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch
   // ---- load (coalesced) -----------------------------------------------------------------------------------------
   for (int i = tid; i < N * NX * NS; i += ADMM_THREADS) P.AB[i] = ABg[(size_t)b * N * NX * NS + i];
   for (int i = tid; i < N * NX; i += ADMM_THREADS) P.Nd[i] = -1.0;
-  for (int i = tid; i < 8; i += ADMM_THREADS) P.Ei[i] = 1.0;
+  for (int i = tid; i < NX; i += ADMM_THREADS) P.Ei[i] = 1.0;
   for (int i = tid; i < n; i += ADMM_THREADS) {
     P.Bd[i] = 1.0; P.D[i] = 1.0;
     P.Pb[i] = Pdiag[i];
@@ -767,12 +772,14 @@ extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, 
   GPMPC_REQUIRE(settings != nullptr, "gpmpc_admm_solve: settings is NULL");
   GPMPC_REQUIRE(N >= 1 && B >= 0, "gpmpc_admm_solve: bad N or B");
   if (B == 0) return GPMPC_OK;
-  if (nx == 7 && nu == 3 && settings->kernel_variant == 0) {
-    const size_t nm = 2 * ((size_t)N * 10 + 7) + 7 * ((size_t)N + 1);  // n + m
+  if ((nx == 7 || nx == 14) && nu == 3 && settings->kernel_variant == 0) {
+    const size_t nv = (size_t)N * (nx + nu) + nx, nm = 2 * nv + (size_t)nx * (N + 1);  // n + m
     double* scratch = alloc_scaling_scratch(nm * (size_t)B, (cudaStream_t)stream);
     if (!scratch) return GPMPC_ERR_CUDA;
-    const int rc = launch_admm_stage<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y, rho, status,
-                                           iters, obj, pri_res, dua_res, (cudaStream_t)stream);
+    const int rc = (nx == 7) ? launch_admm_stage<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y,
+                                                       rho, status, iters, obj, pri_res, dua_res, (cudaStream_t)stream)
+                             : launch_admm_stage<14, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y,
+                                                        rho, status, iters, obj, pri_res, dua_res, (cudaStream_t)stream);
     cudaFreeAsync(scratch, (cudaStream_t)stream);
     if (rc != GPMPC_ERR_ARG) return rc;  // GPMPC_ERR_ARG: horizon too long for the stage-parallel kernel
   }

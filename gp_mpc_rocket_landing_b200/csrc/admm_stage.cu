@@ -44,7 +44,6 @@ __device__ __forceinline__ double limit_scaling(double v) {
 template <int NX, int NU>
 struct Stage {
   static constexpr int NS = NX + NU;
-  static constexpr int THREADS = 128;
   static __host__ __device__ int mid(int N) { return N / 2; }
   static __host__ __device__ size_t smem_doubles(int N) {
     const int p = mid(N);
@@ -119,9 +118,10 @@ template <int I>
 struct IC { static constexpr int value = I; };
 
 // NT > 0: horizon known at compile time (all shared-memory offsets fold); 0: run time.  NSLOT: (stage, variable) slots
-// per thread -- 128 threads cover (N+1)*NS <= 128*NSLOT slots; slot s of thread t is index t + 128 s.
-template <int NX, int NU, int NT, int NSLOT>
-__global__ void __launch_bounds__(128, ADMM_STAGE_MIN_CTAS)
+// per thread -- NTHR threads cover (N+1)*NS <= NTHR*NSLOT slots; slot s of thread t is index t + NTHR s.  MINB: resident
+// QPs per SM the register allocation is sized for.
+template <int NX, int NU, int NT, int NSLOT, int NTHR, int MINB>
+__global__ void __launch_bounds__(NTHR, MINB)
 admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const double* __restrict__ beqg,
                   const double* __restrict__ qg, const double* __restrict__ Pdiag, const double* __restrict__ lb,
                   const double* __restrict__ ub, GpmpcAdmmSettings S, const int* __restrict__ active,
@@ -129,7 +129,7 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
                   double* __restrict__ rhog, int* __restrict__ status_g, int* __restrict__ iters_g,
                   double* __restrict__ obj_g, double* __restrict__ pri_g, double* __restrict__ dua_g) {
   using L = Stage<NX, NU>;
-  constexpr int NS = L::NS, NTHR = L::THREADS, NWARPS = NTHR / 32;
+  constexpr int NS = L::NS, NWARPS = NTHR / 32;
   extern __shared__ __align__(16) double smem[];
   const int N = (NT > 0) ? NT : Nrt;
   const int b = blockIdx.x, tid = threadIdx.x;
@@ -814,6 +814,11 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
 
 }  // namespace
 
+// Launch shapes: 3-DoF (nx 7): 128 threads x 2 slots, 3 QPs per SM, horizon 20 compiled in;  6-DoF (nx 14, N = 30 needs
+// 220 KB of shared memory): 256 threads x 3 slots, one QP per SM, horizon 30 compiled in.
+template <int NX> struct StageShape { static constexpr int NSLOT = 2, NTHR = 128, MINB = ADMM_STAGE_MIN_CTAS, NFIX = 20; };
+template <> struct StageShape<14> { static constexpr int NSLOT = 3, NTHR = 256, MINB = 1, NFIX = 30; };
+
 // Launcher used by gpmpc_admm_solve (csrc/admm.cu).  Returns GPMPC_ERR_ARG without launching when the problem does not
 // fit this kernel (the caller then falls back to the first-generation kernel).  `scratch`: B x (n + m) doubles.
 template <int NX, int NU>
@@ -822,21 +827,26 @@ int launch_admm_stage(int N, int B, const double* AB, const double* beq, const d
                       double* scratch, double* x, double* y, double* rho, int* status, int* iters, double* obj,
                       double* pri, double* dua, cudaStream_t stream) {
   using L = Stage<NX, NU>;
-  constexpr int NSLOT = 2;
+  using H = StageShape<NX>;
   const size_t smem = L::smem_doubles(N) * sizeof(double);
-  if (smem > 227 * 1024 || (N + 1) * L::NS > NSLOT * L::THREADS) return GPMPC_ERR_ARG;
-  auto kern = (N == 20) ? admm_stage_kernel<NX, NU, 20, NSLOT> : admm_stage_kernel<NX, NU, 0, NSLOT>;
+  if (smem > 227 * 1024 || (N + 1) * L::NS > H::NSLOT * H::NTHR) return GPMPC_ERR_ARG;
+  const bool fixed = (N == H::NFIX);
+  auto kern = fixed ? admm_stage_kernel<NX, NU, H::NFIX, H::NSLOT, H::NTHR, H::MINB>
+                    : admm_stage_kernel<NX, NU, 0, H::NSLOT, H::NTHR, H::MINB>;
   static size_t configured[2] = {0, 0};
-  if (smem > configured[N == 20]) {
+  if (smem > configured[fixed]) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured[N == 20] = smem;
+    configured[fixed] = smem;
   }
-  kern<<<B, L::THREADS, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters,
-                                        obj, pri, dua);
+  kern<<<B, H::NTHR, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj,
+                                     pri, dua);
   return gpmpc_check_launch("admm_stage");
 }
 
 template int launch_admm_stage<7, 3>(int, int, const double*, const double*, const double*, const double*,
                                      const double*, const double*, const GpmpcAdmmSettings&, const int*, double*,
                                      double*, double*, double*, int*, int*, double*, double*, double*, cudaStream_t);
+template int launch_admm_stage<14, 3>(int, int, const double*, const double*, const double*, const double*,
+                                      const double*, const double*, const GpmpcAdmmSettings&, const int*, double*,
+                                      double*, double*, double*, int*, int*, double*, double*, double*, cudaStream_t);

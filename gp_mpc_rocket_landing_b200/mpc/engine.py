@@ -72,9 +72,9 @@ class _NullSpan:
 NULL_SPAN = _NullSpan()
 
 
-def qp_dims(N):
-    n = N * NS + NX
-    return n, NX * (N + 1) + n
+def qp_dims(N, nx=NX, nu=NU):
+    n = N * (nx + nu) + nx
+    return n, nx * (N + 1) + n
 
 
 def make_dyn(alpha, g_vec, dt):
@@ -121,11 +121,11 @@ class QPData:
 class AdmmWorkspace:
     """Per-scenario solver state that OSQP keeps between solves (x, y, rho) + per-solve outputs."""
 
-    def __init__(self, B, N, device=None):
+    def __init__(self, B, N, device=None, nx=NX, nu=NU):
         torch = torch_()
-        n, m = qp_dims(N)
+        n, m = qp_dims(N, nx, nu)
         kw = dict(dtype=torch.float64, device=device or "cuda")
-        self.B, self.N, self.n, self.m = B, N, n, m
+        self.B, self.N, self.n, self.m, self.nx, self.nu = B, N, n, m, nx, nu
         self.x = torch.zeros((B, n), **kw)
         self.y = torch.zeros((B, m), **kw)
         self.rho = torch.zeros((B,), **kw)
@@ -137,7 +137,7 @@ class AdmmWorkspace:
 
 
 def admm_solve(qp: QPData, AB, beq, q, settings: AdmmSettings, ws: AdmmWorkspace, active=None):
-    call("gpmpc_admm_solve", NX, NU, qp.N, ws.B, ptr(AB), ptr(beq), ptr(q), ptr(qp.Pdiag), ptr(qp.lb), ptr(qp.ub),
+    call("gpmpc_admm_solve", ws.nx, ws.nu, qp.N, ws.B, ptr(AB), ptr(beq), ptr(q), ptr(qp.Pdiag), ptr(qp.lb), ptr(qp.ub),
          C.byref(settings), ptr(active), ptr(ws.x), ptr(ws.y), ptr(ws.rho), ptr(ws.status), ptr(ws.iters),
          ptr(ws.obj), ptr(ws.pri), ptr(ws.dua), stream())
     return ws

@@ -134,6 +134,63 @@ def test_admm_matches_osqp_restatement(E, max_iter, variant):
             assert np.array_equal(lo, lo2) and np.array_equal(up, up2) and lo2.sum() + up2.sum() > 0
 
 
+def _random_stage_qp(nx, nu, N, rng):
+    """A feasible stage-structured QP in the reference's row order (osqp_rti.py:260-372) for any state dimension."""
+    ns = nx + nu
+    n, neq = N * ns + nx, nx * (N + 1)
+    AB = np.zeros((N, nx, ns))
+    for k in range(N):
+        AB[k, :, :nx] = np.eye(nx) + 0.1 * rng.normal(size=(nx, nx)) * (rng.random((nx, nx)) < 0.3)
+        AB[k, :, nx:] = 0.1 * rng.normal(size=(nx, nu))
+    x0 = rng.normal(size=nx)
+    beq = np.concatenate([x0, 0.01 * rng.normal(size=nx * N)])
+    Pd = np.concatenate([np.tile(np.concatenate([rng.uniform(0.5, 10.0, nx), np.full(nu, 0.01)]), N),
+                         rng.uniform(5.0, 100.0, nx)])
+    q = rng.normal(size=n)
+    lb, ub = np.full(n, -1e30), np.full(n, 1e30)
+    for k in range(N):
+        lb[k * ns + nx:(k + 1) * ns], ub[k * ns + nx:(k + 1) * ns] = -0.5, 0.5           # input box (active)
+        lb[k * ns + 1:k * ns + 4], ub[k * ns + 1:k * ns + 4] = -3.0, 3.0                  # a few state bounds
+    A = np.zeros((neq + n, n))
+    A[:nx, :nx] = np.eye(nx)
+    for k in range(N):
+        r = nx + k * nx
+        A[r:r + nx, k * ns:(k + 1) * ns] = AB[k]
+        A[r:r + nx, (k + 1) * ns:(k + 1) * ns + nx] = -np.eye(nx)
+    A[neq:, :] = np.eye(n)
+    l = np.concatenate([beq, lb]); u = np.concatenate([beq, ub])
+    return AB, beq, Pd, q, lb, ub, A, l, u
+
+
+@pytest.mark.parametrize("nx,N,variant", [(14, 30, 0), (14, 8, 0), (14, 8, 1), (7, 11, 0)])
+def test_admm_generic_stage_qp(E, nx, N, variant):
+    """The solver on random stage-structured QPs of the 6-DoF size (nx = 14, N = 30: BASELINE configs[3]) and on a
+    run-time horizon, against the dense CPU restatement: same status / iterations / rho, iterates to 1e-6."""
+    import torch
+    from oracle import mpc as ompc
+    ge, me = E
+    rng = np.random.default_rng(100 * nx + N)
+    B = 3
+    probs = [_random_stage_qp(nx, 3, N, rng) for _ in range(B)]
+    for b in range(1, B):  # Pdiag and the box are shared by all scenarios in the C-ABI
+        probs[b] = probs[b][:2] + probs[0][2:3] + probs[b][3:4] + probs[0][4:6] + probs[b][6:7] + (
+            np.concatenate([probs[b][1], probs[0][4]]), np.concatenate([probs[b][1], probs[0][5]]))
+    AB = ge.to_dev(np.stack([p[0] for p in probs])); beq = ge.to_dev(np.stack([p[1] for p in probs]))
+    q = ge.to_dev(np.stack([p[3] for p in probs]))
+    qp = me.QPData(N, ge.to_dev(probs[0][2]), ge.to_dev(probs[0][4]), ge.to_dev(probs[0][5]), None, None, None)
+    ws = me.AdmmWorkspace(B, N, nx=nx, nu=3)
+    S = me.AdmmSettings.reference_defaults(max_iter=2000, kernel_variant=variant)
+    me.admm_solve(qp, AB, beq, q, S, ws)
+    torch.cuda.synchronize()
+    for b in range(B):
+        _, _, Pd, qv, _, _, A, l, u = probs[b]
+        r = ompc.OSQPOracle(Pd, qv, A, l, u, ompc.OSQPSettings(max_iter=2000)).solve()
+        assert ws.status[b].item() == r.status == 1 and ws.iters[b].item() == r.iters, (b, ws.iters[b].item(), r.iters)
+        assert ws.rho[b].item() == pytest.approx(r.rho, rel=1e-6)
+        assert np.max(np.abs(ws.x[b].cpu().numpy() - r.x)) < 1e-6 * max(1.0, np.max(np.abs(r.x)))
+        assert np.max(np.abs(ws.y[b].cpu().numpy() - r.y)) < 1e-6 * max(1.0, np.max(np.abs(r.y)))
+
+
 @pytest.mark.parametrize("variant", [0, 1])
 def test_admm_warm_start_and_inactive(E, variant):
     """x/y/rho persist across solves like the OSQP object does (osqp_rti.py:522-527); inactive scenarios are
