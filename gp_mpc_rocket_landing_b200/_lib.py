@@ -43,6 +43,12 @@ class Dyn3(C.Structure):
     _fields_ = [("alpha", c_double), ("g", c_double * 3), ("dt", c_double)]
 
 
+class Dyn6(C.Structure):
+    """GpmpcDyn6: 6-DoF quaternion model parameters (nominal_mpc.py:163-203, rocket_6dof.py:35-89)."""
+    _fields_ = [("alpha", c_double), ("g", c_double * 3), ("J", c_double * 9), ("Jinv", c_double * 9),
+                ("rT", c_double * 3), ("dt", c_double), ("substeps", c_int), ("normalize_quat", c_int)]
+
+
 class ExactModel(C.Structure):
     """GpmpcExactModel: P outputs sharing one kernel / Cholesky factor (exact_gp.py:464-474)."""
     _fields_ = [
@@ -66,6 +72,15 @@ _PROTOS = {
     "gpmpc_normalize_targets": (c_int, [c_dp, c_int, c_int, c_long, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_lml": (c_int, [c_dp, c_int, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp, c_dp]),
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_step_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_linearize_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_rollout_6dof": (c_int, [C.POINTER(ExactModel), C.POINTER(ExactModel), C.POINTER(Dyn6), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_qp_assemble_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp,
+                                       c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_mpc_update": (c_int, [c_int, c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                 c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_pack_traj": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_unpack_traj": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_tri_inverse": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_long, c_dp]),
     "gpmpc_linv_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp, c_dp]),
     "gpmpc_trsm_sumsq_batched": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_long, c_long, c_dp, c_int,

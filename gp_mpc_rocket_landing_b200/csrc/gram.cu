@@ -212,13 +212,6 @@ extern "C" int gpmpc_predict_var(const double* sumsq, const double* plus, int Q,
 }
 
 // ------------------------------------------------------------------------------------------------ features
-__device__ __forceinline__ void quat_to_dcm(const double* q, double C[3][3]) {  // features.py:260-270
-  const double w = q[0], x = q[1], y = q[2], z = q[3];
-  C[0][0] = 1 - 2 * (y * y + z * z); C[0][1] = 2 * (x * y + w * z);     C[0][2] = 2 * (x * z - w * y);
-  C[1][0] = 2 * (x * y - w * z);     C[1][1] = 1 - 2 * (x * x + z * z); C[1][2] = 2 * (y * z + w * x);
-  C[2][0] = 2 * (x * z + w * y);     C[2][1] = 2 * (y * z - w * x);     C[2][2] = 1 - 2 * (x * x + y * y);
-}
-
 __global__ void features_kernel(int which, const double* __restrict__ X, long ldx, const double* __restrict__ U,
                                 long ldu, int B, double* __restrict__ Z, long ldz) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -234,33 +227,12 @@ __global__ void features_kernel(int which, const double* __restrict__ X, long ld
     for (int d = 0; d < 11; ++d) z[d] = zl[d];
     return;
   }
-  const double alt = x[1];
-  const double speed = norm3(x[4], x[5], x[6]);
-  const double rho = 1.225 * exp(-alt / 8500.0);
-  const double q_dyn = 0.5 * rho * (speed * speed);
-  double C[3][3];
-  double q[4] = {x[7], x[8], x[9], x[10]};
-  quat_to_dcm(q, C);
-  double vB[3];
-  for (int r = 0; r < 3; ++r) vB[r] = __dadd_rn(__dadd_rn(__dmul_rn(C[r][0], x[4]), __dmul_rn(C[r][1], x[5])), __dmul_rn(C[r][2], x[6]));
-  if (which == GPMPC_FEATURES_6DOF_TRANS) {  // features.py:194-258
-    double alpha = 0.0, beta = 0.0;
-    if (speed > 1e-3) {
-      alpha = atan2(-vB[2], vB[0]);
-      beta = asin(fmin(fmax(vB[1] / speed, -1.0), 1.0));
-    }
-    const double T = norm3(u[0], u[1], u[2]);
-    z[0] = x[4] / 10.0; z[1] = x[5] / 10.0; z[2] = x[6] / 10.0; z[3] = speed / 10.0;
-    z[4] = q_dyn / (0.5 * 1.225 * 100.0); z[5] = alpha; z[6] = beta;
-    z[7] = u[0] / 10.0; z[8] = u[1] / 10.0; z[9] = u[2] / 10.0; z[10] = T / 10.0;
-    z[11] = alt / 100.0; z[12] = rho / 1.225;
-  } else {  // features.py:305-354
-    const double om = norm3(x[11], x[12], x[13]);
-    z[0] = x[11] / 1.0; z[1] = x[12] / 1.0; z[2] = x[13] / 1.0; z[3] = om / 1.0;
-    z[4] = u[0] / 10.0; z[5] = u[1] / 10.0; z[6] = u[2] / 10.0;
-    z[7] = vB[0] / 10.0; z[8] = vB[1] / 10.0; z[9] = vB[2] / 10.0; z[10] = speed / 10.0;
-    z[11] = q_dyn / (0.5 * 1.225 * 100.0);
-  }
+  double xl[14], ul[3], zl[13];
+  for (int d = 0; d < 14; ++d) xl[d] = x[d];
+  for (int d = 0; d < 3; ++d) ul[d] = u[d];
+  const int trans = (which == GPMPC_FEATURES_6DOF_TRANS);
+  features_6dof_dev(trans, xl, ul, zl);
+  for (int d = 0; d < (trans ? 13 : 12); ++d) z[d] = zl[d];
 }
 
 extern "C" int gpmpc_features(int which, const double* X, long ldx, const double* U, long ldu, int B, double* Z,

@@ -400,6 +400,14 @@ class SparseModelDev:
              ptr(f.qff), f.sv, f.noise, self.P, ptr(self.lml), stream())
         return self
 
+    def mean_struct(self):
+        """GpmpcExactModel view of the posterior MEAN of this sparse model for the fused horizon kernels: the mean is
+        K*u alpha (sparse_gp.py:281), i.e. an "exact" model whose training inputs are the M scaled inducing points."""
+        f = self.f
+        return _lib.ExactModel(kind=f.kind, n=f.M, n_pad=f.M_pad, D=f.D, DP=f.DP, P=self.P, signal_var=f.sv,
+                               lengthscales=ptr(f.ls), Xs=ptr(f.Zs), sq=ptr(f.sqz), alpha=ptr(self.alpha),
+                               ymean=ptr(self.ymean), ystd=ptr(self.ystd), L=None, Winv=None)
+
     def predict(self, Xq, want_var=True, chunk=262144, col=None):
         """mean = K*u alpha (no L_uu^-T: reference quirk, sparse_gp.py:281), var = max(sv - |v|^2 + |w|^2, 1e-10) ystd^2
         with v = L_uu^{-1} K_u*, w = L_B^{-1} v (:293-300).  -> (Q,P), (Q,P) CUDA tensors."""

@@ -125,6 +125,25 @@ class StructuredRocketGP:
         d_omega_mean, d_omega_var = self.gp_omega.predict(Z_omega)
         return d_v_mean, d_omega_mean, d_v_var, d_omega_var
 
+    def device_mean_models(self):
+        """(gp_v, gp_omega) posterior-mean model structs for `gpmpc_rollout_6dof` (None, None before any data).  The
+        returned objects keep the device tensors alive; both GPs must have outputs sharing one factor (the default)."""
+        if not self._is_fitted:
+            if self.n_data == 0:
+                return None, None
+            self.fit()
+        out = []
+        for gp in (self.gp_v, self.gp_omega):
+            shared = getattr(gp, "_shared", None)
+            if shared is not None:
+                out.append(shared.mean_struct())
+            else:
+                model = gp.device_model()
+                if model is None:
+                    raise RuntimeError("StructuredRocketGP: the fused horizon kernels need outputs sharing one factor")
+                out.append(model.struct())
+        return tuple(out)
+
     def get_full_residual(self, x, u):
         d_v_mean, d_omega_mean, d_v_var, d_omega_var = self.predict(x, u)
         d_mean, d_var = np.zeros(14), np.zeros(14)

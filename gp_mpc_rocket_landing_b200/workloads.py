@@ -61,3 +61,39 @@ def sample_initial_conditions(first: int, count: int, seed: int = 42, cfg: Simul
     XT = np.zeros_like(X0)
     XT[:, 0] = X0[:, 0]
     return X0, XT
+
+
+def residual_dataset_6dof(n: int = 1000, seed: int = 0):
+    """Config 4 GP data: n synthetic residual points on the 14-state model (X (n,14), U (n,3), D_v (n,3), D_omega (n,3)):
+    the translational residual is the drag-like term of `residual_dataset`, the rotational one a damping-like term
+    -0.05 |w| w + 0.02 (v_B x e_x) (cf. experiments/dispersion.py:349-360), both + N(0, 0.01^2)."""
+    rng = np.random.default_rng(seed)
+    m = rng.uniform(1.2, 2, n); alt = rng.uniform(0, 40, n)
+    y = rng.normal(0, 3, n); z = rng.normal(0, 3, n)
+    v = np.stack([rng.normal(-3, 1, n), rng.normal(0, .5, n), rng.normal(0, .5, n)], 1)
+    q = np.concatenate([np.ones((n, 1)), rng.normal(0, 0.05, (n, 3))], 1)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w = rng.normal(0, 0.1, (n, 3))
+    X = np.concatenate([m[:, None], alt[:, None], y[:, None], z[:, None], v, q, w], 1)
+    U = np.stack([rng.uniform(1.5, 5, n), rng.uniform(-.5, .5, n), rng.uniform(-.5, .5, n)], 1)
+    rho = 1.225 * np.exp(-alt / 8500)
+    sp = np.linalg.norm(v, axis=1)
+    Dv = -0.5 * rho[:, None] * 0.5 * 0.5 * sp[:, None] * v / m[:, None] + rng.normal(0, 0.01, (n, 3))
+    wn = np.linalg.norm(w, axis=1)
+    Dw = -0.05 * wn[:, None] * w + 0.02 * np.cross(v, np.array([1.0, 0.0, 0.0])) + rng.normal(0, 0.01, (n, 3))
+    return X, U, Dv, Dw
+
+
+def sample_initial_conditions_6dof(first: int, count: int, seed: int = 42, cfg: SimulationConfig | None = None):
+    """The 3-DoF scenario draw embedded in the 14-state model: identity attitude perturbed by a small seeded rotation,
+    zero body rates.  Targets: [m0, 0, 0, 0, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0]."""
+    X7, _ = sample_initial_conditions(first, count, seed, cfg)
+    X0 = np.zeros((count, 14)); XT = np.zeros((count, 14))
+    X0[:, :7] = X7
+    for i in range(count):
+        r = np.random.default_rng(seed + first + i)
+        q = np.concatenate([[1.0], r.normal(0, 0.02, 3)])
+        X0[i, 7:11] = q / np.linalg.norm(q)
+    XT[:, 0] = X0[:, 0]
+    XT[:, 7] = 1.0
+    return X0, XT

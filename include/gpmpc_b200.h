@@ -234,6 +234,53 @@ int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp
                           double* U, double* X_prev, double* U_prev, double* cost, int* converged, int* active,
                           int* n_iter, void* stream);
 
+/* ---- 6-DoF quaternion model (BASELINE configs[3]): 14 states [m, r_I(3), v_I(3), q_BI(4), w_B(3)], 3 controls ----------- */
+
+/* Parameters of the continuous model stated at nominal_mpc.py:163-203 (defaults rocket_6dof.py:35-89). */
+typedef struct GpmpcDyn6 {
+  double alpha;      /* 1 / (I_sp g0) */
+  double g[3];       /* g_I */
+  double J[9];       /* J_B row-major */
+  double Jinv[9];    /* J_B^{-1} row-major */
+  double rT[3];      /* r_T_B */
+  double dt;
+  int substeps;      /* 1: Euler; 4: the reference's "rk4" (= 4 Euler sub-steps, nominal_mpc.py:205-236) */
+  int normalize_quat; /* renormalise q after the step (rocket_6dof.py:370-387) */
+} GpmpcDyn6;
+
+/* Xn[i] = step(X[i], U[i]) for npts points (dynamics.step protocol, rocket_6dof.py:370-376). */
+int gpmpc_step_6dof(const GpmpcDyn6* dyn, int npts, const double* X, const double* U, double* Xn, void* stream);
+
+/* Forward-difference discrete Jacobians [A | B] (npts x 14 x 17), eps = 1e-6: osqp_rti.py:374-401. */
+int gpmpc_linearize_6dof(const GpmpcDyn6* dyn, int npts, const double* X, const double* U, double* AB, void* stream);
+
+/* GP-augmented horizon rollout, 14-state _predict_with_gp (gp_mpc.py:139-175,277-281):
+ * X[b,k+1] = step(X[b,k],U[b,k]) + dt [0..,d_v,0..,d_w].  gp_v / gp_w: posterior-mean models of the translational
+ * (13 features, features.py:194-258) and rotational (12 features, :305-354) residual GPs -- for a sparse GP the
+ * "training inputs" of the struct are the scaled inducing points and alpha its M-vector (sparse_gp.py:281), L unused.
+ * Either may be NULL (nominal).  dmean: B x N x 6 or NULL. */
+int gpmpc_rollout_6dof(const GpmpcExactModel* gp_v, const GpmpcExactModel* gp_w, const GpmpcDyn6* dyn, int B, int N,
+                       const double* x0, const double* U, double* X, double* dmean, const int* active, void* stream);
+
+/* QP assembly in the OSQP-RTI layout for n_x = 14 (osqp_rti.py:203-372; cost fallback branch :172-175): stage blocks
+ * AB (B x N x 14 x 17, FD Jacobians with |a| <= 1e-10 dropped), beq (B x 14(N+1)) = [x_init ; -(X_lin[k+1] - A x - B u +
+ * dt c_gp)] (gp_mpc.py:402-411), q (B x n) = -Q x_ref.  x_ref: (N+1) x 14 shared (ldxref = 0) or per scenario. */
+int gpmpc_qp_assemble_6dof(const GpmpcDyn6* dyn, int B, int N, const double* X_lin, const double* U_lin,
+                           const double* x_init, const double* x_ref, long ldxref, const double* c_gp, const double* Qd,
+                           const double* Qfd, double* AB, double* beq, double* q, const int* active, void* stream);
+
+/* z = [x_0,u_0,...,x_N] <-> (X, U) for any state dimension (osqp_rti.py:601-631). */
+int gpmpc_pack_traj(int nx, int nu, int B, int N, const double* X, const double* U, double* z, void* stream);
+int gpmpc_unpack_traj(int nx, int nu, int B, int N, const double* z, double* X, double* U, void* stream);
+
+/* Post-QP bookkeeping for any state dimension: unpack z into (X, U), SQP step-size test max|dz| < 1e-4 (gp_mpc.py:336-345,
+ * mode 1; converged scenarios are cleared in `active`) or RTI acceptance (osqp_rti.py:532-552, mode 0), stage cost,
+ * optional shifted warm start (X_prev, U_prev).  Unsolved QPs leave (X, U) untouched and report cost = inf. */
+int gpmpc_mpc_update(int nx, int nu, int B, int N, int mode, const double* z, const int* qp_status, const double* x_ref,
+                     long ldxref, const double* Qd, const double* Qfd, const double* Rd, double* X, double* U,
+                     double* X_prev, double* U_prev, double* cost, int* converged, int* active, int* n_iter,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif
