@@ -28,7 +28,7 @@ sys.path.insert(0, ROOT)
 
 N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
 # dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` captures (profiles/), B = 4096
-NCU_TRAFFIC = {"admm": 82.6e6, "rollout": 653.3e6, "gp_variance": None}
+NCU_TRAFFIC = {"admm": 82.6e6, "rollout": 740.5e6, "gp_variance": 689.2e6}  # profiles/r1_step_kernels_v2_full.md
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 
 

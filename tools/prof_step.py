@@ -10,4 +10,9 @@ dyn, gp, ctl, mc = bench.build_problem(a, 0)
 for k in range(int(os.environ.get("STEPS", 4))):
     mc.step()
 torch.cuda.synchronize()
+if os.environ.get("PROFILE_API"):  # ncu --profile-from-start off: capture exactly one more closed-loop step
+    torch.cuda.profiler.start()
+    mc.step()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
 print("done")

@@ -24,7 +24,7 @@ def launches(src, out):
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     ci = {h: i for i, h in enumerate(rows[hi])}
     data = rows[hi + 1:]
-    adm = [i for i, r in enumerate(data) if "admm_kernel" in r[ci["Kernel Name"]]]
+    adm = [i for i, r in enumerate(data) if "admm" in r[ci["Kernel Name"]]]
     start = adm[-2] + 1 if len(adm) > 1 else 0
     agg, tot = collections.OrderedDict(), 0.0
     for r in data[start:]:
