@@ -35,8 +35,8 @@ METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)   # 200 steps after 20 warm-up
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=4096, help="scenarios per GPU (weak scaling)")
     ap.add_argument("--sqp-iters", type=int, default=1, help="SQP iterations per solve (1 = RTI; reference loop: 10)")
@@ -162,6 +162,13 @@ class ClockSampler:
         except Exception:  # noqa: BLE001
             self.proc = None
 
+    def mark(self):
+        """Start of the timed region: samples written from here on are the ones reported."""
+        try:
+            self.offset = os.path.getsize(self.path)
+        except Exception:  # noqa: BLE001
+            self.offset = 0
+
     def stop(self):
         if self.proc is None:
             return None
@@ -172,7 +179,12 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in open(self.path).read().splitlines():
+        text = open(self.path).read()
+        timed = text[getattr(self, "offset", 0):]
+        window = "timed region"
+        if len([ln for ln in timed.splitlines() if ln.count(",") >= 8]) == 0:
+            timed, window = text, "warm-up + timed region (the timed region was shorter than one 100 ms sample)"
+        for ln in timed.splitlines():
             f = [t.strip() for t in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -187,7 +199,7 @@ class ClockSampler:
         if not sm:
             return None
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "window": window}
 
 
 # ====================================================================================================== GPU arm
@@ -256,14 +268,15 @@ def run_b200_arm(args):
         torch.cuda.synchronize()
 
     # ---- device-resident loop ---------------------------------------------------------------------------------
+    peak64 = fp64_peak_tflops(torch) if rank == 0 else None
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(W):
         mc.step()
-    peak64 = fp64_peak_tflops(torch) if rank == 0 else None
     ctl.timers = me.PhaseTimers()
-    clocks = ClockSampler(local)
     qp_it, launches = torch.zeros((), dtype=torch.float64, device="cuda"), 0
     barrier()
-    clocks.start()
+    clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(K):
@@ -301,6 +314,13 @@ def run_b200_arm(args):
         for _ in range(Ke):
             s = ctl.solve_batch(x, XT)          # H2D: x, XT ; D2H: u0, X_opt, U_opt, cost, flags
             x = dyn.step_batch(x, s.u0, DT)     # H2D: x, u0 ; D2H: x_next
+            # the termination rules of the Monte Carlo loop (experiments/monte_carlo.py:460-488), on the host copy:
+            # finished scenarios restart from their initial condition, exactly as the device-resident loop respawns them
+            done = (x[:, 1] < 0.0) | (x[:, 0] <= 1.01) | ((x[:, 1] < 1.0) & (np.abs(x[:, 4]) < 5.0)) | \
+                   ~np.all(np.abs(x) <= 1e6, axis=1)
+            if done.any():
+                x[done] = X0[done]
+                ctl.reset_scenarios(done, X0)
         barrier()
         te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:

@@ -61,6 +61,7 @@ def _structured_gp(env, n=400, M=40):
     X, U, Dv, Dw = workloads.residual_dataset_6dof(n, seed=1)
     sg = gp.StructuredRocketGP(gp.StructuredGPConfig(n_inducing=M, use_sparse=True, noise_variance=1e-3))
     sg.add_data(X, U, Dv, Dw)
+    np.random.seed(7)   # the reference draws the inducing points from the global numpy RNG (sparse_gp.py:122-148)
     sg.fit()
     Zv = ogp.features_batch(ogp.features_6dof_trans, X, U)
     Zw = ogp.features_batch(ogp.features_6dof_rot, X, U)
