@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--cpu-scenarios", type=int, default=0, help="reference arm: scenarios per step (default: #cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--overlap", type=int, default=0,
+                    help="1: GP variance / covariance chain on a high-priority side stream, concurrent with the QP")
     return ap.parse_args()
 
 
@@ -230,7 +232,8 @@ def build_problem(args, rank):
     gp.add_data(X, U, D)
     gp.fit()
     dyn = Rocket3DoFDynamics()
-    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter)
+    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter,
+                      overlap_uncertainty=bool(getattr(args, "overlap", False)))
     ctl = GPMPC(dyn, gp, cfg)
     ctl.setup()
     mc = BatchedMonteCarlo(dyn, ctl, drag_cda=0.25, respawn=True)

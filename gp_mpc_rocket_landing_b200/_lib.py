@@ -82,7 +82,7 @@ _PROTOS = {
     "gpmpc_pack_traj": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_unpack_traj": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_tri_inverse": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_long, c_dp]),
-    "gpmpc_linv_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp, c_dp]),
+    "gpmpc_linv_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp, c_int, c_dp]),
     "gpmpc_trsm_sumsq_batched": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_long, c_long, c_dp, c_int,
                                          c_dp]),
     "gpmpc_trsm_small": (c_int, [c_dp, c_int, c_long, c_dp, c_long, c_int, c_int, c_dp, c_double, c_dp]),

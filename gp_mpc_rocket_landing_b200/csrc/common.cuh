@@ -20,6 +20,18 @@ int gpmpc_check_launch(const char* what);
     }                                     \
   } while (0)
 
+// Kernels that may run while a shared-memory heavy kernel (ADMM, DMMA GEMM: carve-out = max shared) is resident on another
+// stream ask for the same L1 / shared-memory split: an SM cannot host CTAs that want different carve-outs, so a
+// default-carve-out kernel would wait for the SM to drain.
+#define GPMPC_PREFER_SHARED(kern)                                                                              \
+  do {                                                                                                         \
+    static bool done_ = false;                                                                                 \
+    if (!done_) {                                                                                              \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
+      done_ = true;                                                                                            \
+    }                                                                                                          \
+  } while (0)
+
 namespace gpmpc {
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {

@@ -47,19 +47,14 @@ struct GemmSmem {
   double b[GEMM_STAGES][BN * GEMM_PITCH];
 };
 
+// One BM x BN output tile at (m0, n0) of batch entry bz, computed by the whole CTA.
 template <int BM, int BN, int WARPS_M, int WARPS_N>
-__global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) dgemm_nt_kernel(GemmParams p) {
+__device__ __forceinline__ void dgemm_nt_tile(const GemmParams& p, int m0, int n0, int bz, GemmSmem<BM, BN>& sm) {
   static_assert(WARPS_M * WARPS_N * 32 == GEMM_THREADS, "8 warps");
   constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
   constexpr int MT = WM / 8, NT = WN / 8;
   static_assert(WM % 8 == 0 && WN % 8 == 0, "warp tile multiple of 8");
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  GemmSmem<BM, BN>& sm = *reinterpret_cast<GemmSmem<BM, BN>*>(smem_raw);
-
-  const int m0 = (p.m_fast ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.y) * BM;
-  const int n0 = (p.m_fast ? (int)blockIdx.y : (int)blockIdx.x) * BN;
   if (p.lower_only && n0 >= m0 + BM) return;
-  const int bz = blockIdx.z;
   const double* __restrict__ A = p.A + bz * p.strideA + (long)m0 * p.lda;
   const double* __restrict__ B = p.B + bz * p.strideB + (long)n0 * p.ldb;
 
@@ -197,19 +192,65 @@ __global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) d
 }
 
 template <int BM, int BN, int WARPS_M, int WARPS_N>
-int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream) {
+__global__ void __launch_bounds__(GEMM_THREADS, (BM * BN <= 64 * 128) ? 2 : 1) dgemm_nt_kernel(GemmParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  GemmSmem<BM, BN>& sm = *reinterpret_cast<GemmSmem<BM, BN>*>(smem_raw);
+  const int m0 = (p.m_fast ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.y) * BM;
+  const int n0 = (p.m_fast ? (int)blockIdx.y : (int)blockIdx.x) * BN;
+  dgemm_nt_tile<BM, BN, WARPS_M, WARPS_N>(p, m0, n0, blockIdx.z, sm);
+}
+
+// Persistent variant: gridDim.x CTAs (one per SM) stride over the tiles in the m_fast order (the M tiles of one N tile
+// adjacent, longest k loops first).  Every CTA of the grid is resident from the start, so the blocks of a kernel launched
+// on ANOTHER stream are dispatched into the SMs' remaining resources at once -- the work distributor only starts on a
+// later kernel after all blocks of an earlier one have been dispatched.
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) dgemm_nt_persistent_kernel(GemmParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  GemmSmem<BM, BN>& sm = *reinterpret_cast<GemmSmem<BM, BN>*>(smem_raw);
+  const int mt = p.M / BM, nt = p.N / BN;
+  for (int tile = blockIdx.x; tile < mt * nt; tile += gridDim.x) {
+    const int ni = tile / mt, mi = mt - 1 - (tile - ni * mt);
+    dgemm_nt_tile<BM, BN, WARPS_M, WARPS_N>(p, mi * BM, ni * BN, 0, sm);
+    __syncthreads();  // the tile buffers and the epilogue's reduction scratch are reused by the next tile
+  }
+}
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+int launch_dgemm_nt_persistent(const GemmParams& p, int ctas, int smem_request, cudaStream_t stream) {
+  if (p.M % BM || p.N % BN || p.K % GEMM_BK || (p.lda & 1) || (p.ldb & 1)) {
+    gpmpc_set_error("dgemm_nt: dimensions must be padded (M%BM, N%BN, K%16, even ld)");
+    return GPMPC_ERR_ARG;
+  }
+  if (p.M == 0 || p.N == 0) return GPMPC_OK;
+  auto kern = dgemm_nt_persistent_kernel<BM, BN, WARPS_M, WARPS_N>;
+  const int smem = smem_request > (int)sizeof(GemmSmem<BM, BN>) ? smem_request : (int)sizeof(GemmSmem<BM, BN>);
+  static int configured = 0;
+  if (smem > configured) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    configured = smem;
+  }
+  kern<<<ctas, GEMM_THREADS, smem, stream>>>(p);
+  return gpmpc_check_launch("dgemm_nt_persistent");
+}
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream, int smem_request = 0) {
   if (p.M % BM || p.N % BN || p.K % GEMM_BK || (p.lda & 1) || (p.ldb & 1)) {
     gpmpc_set_error("dgemm_nt: dimensions must be padded (M%BM, N%BN, K%16, even ld)");
     return GPMPC_ERR_ARG;
   }
   if (p.M == 0 || p.N == 0) return GPMPC_OK;
   auto kern = dgemm_nt_kernel<BM, BN, WARPS_M, WARPS_N>;
-  const int smem = (int)sizeof(GemmSmem<BM, BN>);
-  static bool configured = false;
-  if (!configured) {
+  // smem_request > sizeof(GemmSmem): ask for more shared memory than the tiles need, to cap the resident CTAs per SM
+  // (used to leave room for a co-resident kernel on another stream)
+  const int smem = smem_request > (int)sizeof(GemmSmem<BM, BN>) ? smem_request : (int)sizeof(GemmSmem<BM, BN>);
+  static int configured = 0;
+  if (smem > configured) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = true;
+    configured = smem;
   }
   dim3 grid(p.N / BN, p.M / BM, batch);
   if (p.m_fast) grid = dim3(p.M / BM, p.N / BN, batch);

@@ -207,6 +207,7 @@ __global__ void predict_var_kernel(const double* __restrict__ sumsq, const doubl
 extern "C" int gpmpc_predict_var(const double* sumsq, const double* plus, int Q, int P, double prior, double floor_,
                                  const double* ystd, double* var, long ldv, int col0, void* stream) {
   if (Q == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(predict_var_kernel);
   predict_var_kernel<<<(Q + 255) / 256, 256, 0, (cudaStream_t)stream>>>(sumsq, plus, Q, P, prior, floor_, ystd, var, ldv, col0);
   return gpmpc_check_launch("predict_var");
 }

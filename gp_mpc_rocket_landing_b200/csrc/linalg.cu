@@ -400,7 +400,7 @@ __global__ void sum_parts_kernel(const double* __restrict__ part, int nparts, lo
 }
 
 extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk,
-                                double* work, double* sumsq, void* stream_) {
+                                double* work, double* sumsq, int one_cta_per_sm, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0, "gpmpc_linv_sumsq: n_pad and q_pad must be multiples of 128");
   GemmParams p{};
@@ -408,8 +408,23 @@ extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const d
   p.B = Ks; p.ldb = ldk;
   p.M = n_pad; p.N = q_pad; p.K = n_pad; p.alpha = 1.0; p.beta = 0.0;
   p.k_tri = 1; p.m_fast = 1; p.epi = EPI_SUMSQ_PART; p.sumsq = work; p.part_stride = q_pad;
-  int rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
+  // one_cta_per_sm: a persistent grid of one CTA per SM that asks for 114.5 KB of shared memory, so that exactly one CTA is
+  // resident per SM and 112 KB stay free -- room for two QPs of the ADMM kernel running concurrently on another stream
+  // (DMMA runs on the tensor pipe, the ADMM chains on the FP64 FMA pipe: separate units).
+  int rc;
+  if (one_cta_per_sm) {
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    rc = launch_dgemm_nt_persistent<64, 128, 2, 4>(p, sms, 117248, stream);
+  } else {
+    rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
+  }
   if (rc) return rc;
+  GPMPC_PREFER_SHARED(sum_parts_kernel);
   sum_parts_kernel<<<(q_pad + 255) / 256, 256, 0, stream>>>(work, n_pad / 64, q_pad, q_pad, sumsq);
   return gpmpc_check_launch("linv_sumsq");
 }

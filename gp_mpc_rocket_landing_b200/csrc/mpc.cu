@@ -712,6 +712,7 @@ extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double*
   GPMPC_REQUIRE(B >= 0 && N >= 1, "gpmpc_pack_traj_3dof: bad arguments");
   if (B == 0) return GPMPC_OK;
   const long total = (long)B * (N * NS + NX);
+  GPMPC_PREFER_SHARED(pack_traj3_kernel);
   pack_traj3_kernel<<<(int)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, N, X, U, z, active);
   return gpmpc_check_launch("pack_traj_3dof");
 }
@@ -721,6 +722,7 @@ extern "C" int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, cons
                                         void* stream) {
   GPMPC_REQUIRE(dyn != nullptr && B >= 0 && N >= 1, "gpmpc_propagate_cov_3dof: bad arguments");
   if (B == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(propagate_cov3_kernel);
   propagate_cov3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, B, N, X, U, dvar, sigma0, covs, active);
   return gpmpc_check_launch("propagate_cov_3dof");
 }
@@ -734,6 +736,7 @@ extern "C" int gpmpc_qp_assemble_3dof(const GpmpcDyn3* dyn, int B, int N, int li
   GPMPC_REQUIRE(lin_mode >= 0 && lin_mode <= 1 && rhs_mode >= 0 && rhs_mode <= 1, "gpmpc_qp_assemble_3dof: bad mode");
   if (B == 0) return GPMPC_OK;
   const int total = B * (N + 1);
+  GPMPC_PREFER_SHARED(qp_assemble3_kernel);
   qp_assemble3_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
       *dyn, B, N, lin_mode, rhs_mode, X_lin, U_lin, x_init, x_ref, ldxref, c_gp, Qdiag, Qfdiag, AB, beq, q, active);
   return gpmpc_check_launch("qp_assemble_3dof");
@@ -745,6 +748,7 @@ extern "C" int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, co
                                      double* cost, int* converged, int* active, int* n_iter, void* stream) {
   GPMPC_REQUIRE(B >= 0 && N >= 1 && (mode == 0 || mode == 1), "gpmpc_mpc_update_3dof: bad arguments");
   if (B == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(mpc_update3_kernel);
   mpc_update3_kernel<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream>>>(B, N, mode, z, qp_status, x_ref, ldxref, Qdiag,
                                                                      Qfdiag, Rdiag, X, U, X_prev, U_prev, cost,
                                                                      converged, active, n_iter);

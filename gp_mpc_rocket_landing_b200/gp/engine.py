@@ -201,7 +201,7 @@ class ExactFactor:
                  self.Linv.stride(0), stream())
         return self.Linv
 
-    def sumsq_linv(self, Ks, work=None):
+    def sumsq_linv(self, Ks, work=None, one_cta_per_sm=False):
         """sum_i v_i^2 with v = L^{-1} K*^T evaluated as ONE triangular GEMM against the explicit inverse factor (Ks is
         left untouched).  Same quantity as `sumsq_inplace` (exact_gp.py:260-261); the rounding differs by
         O(cond(L) eps) -- measured 1e-11 / 7e-10 relative on the two 1000-point fixtures -- so the reference-faithful
@@ -213,7 +213,7 @@ class ExactFactor:
             work = torch.empty(((self.n_pad // 64) * q_pad,), dtype=torch.float64, device=Ks.device)
         sumsq = torch.empty((q_pad,), dtype=torch.float64, device=Ks.device)
         call("gpmpc_linv_sumsq", ptr(W), self.n_pad, W.stride(0), ptr(Ks), q_pad, Ks.stride(0), ptr(work), ptr(sumsq),
-             stream())
+             1 if one_cta_per_sm else 0, stream())
         return sumsq
 
 

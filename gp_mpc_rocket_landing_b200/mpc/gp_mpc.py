@@ -53,10 +53,11 @@ class GPMPCConfig(MPCConfig):
                                        # inverse factor (formed once per fit) instead of the blocked in-place solve
                                        # (31 dependent launches); same quantity, rounding differs by O(cond(L) eps)
     overlap_uncertainty: bool = False  # GP variance + covariance chain on a side stream, concurrent with the QP (the QP
-                                       # does not read them: gp_mpc.py:414 evaluates the tightening at k = 0 only).
-                                       # Measured on B200: step 11.13 -> 10.58 ms only -- both kernels fill the SMs'
-                                       # shared memory, so they time-slice rather than overlap; off by default so
-                                       # that per-kernel timings stay clean.
+                                       # does not read them: gp_mpc.py:414 evaluates the tightening at k = 0 only).  The
+                                       # variance GEMM then runs as a persistent one-CTA-per-SM grid so that two ADMM QPs
+                                       # fit next to it on every SM.  Measured on B200: the kernels do
+                                       # co-reside, but the step stays at 8.83 ms (8.89 ms serial) -- they contend for the
+                                       # same shared-memory / issue bandwidth.  Off by default: clean per-kernel timings.
 
 
 def _is_dev(a):
@@ -215,7 +216,7 @@ class GPMPC:
                 if st.var_work is None:
                     st.var_work = ge.torch_().empty(((f.n_pad // 64) * st.Ks.shape[0],), dtype=st.Ks.dtype,
                                                     device=st.Ks.device)
-                sumsq = f.sumsq_linv(st.Ks, st.var_work)
+                sumsq = f.sumsq_linv(st.Ks, st.var_work, one_cta_per_sm=self.config.overlap_uncertainty)
             else:
                 sumsq = f.sumsq_inplace(st.Ks)
         with self._span("cov"):
@@ -233,7 +234,7 @@ class GPMPC:
         if not self.config.overlap_uncertainty:
             return self._variance_and_cov(st, X, U, active)
         if self._side is None:
-            self._side = torch.cuda.Stream()
+            self._side = torch.cuda.Stream(priority=-1)
         self._join_uncertainty(st)
         st.X_unc.copy_(X)
         st.U_unc.copy_(U)

@@ -82,9 +82,11 @@ int gpmpc_trsm_sumsq_batched(const double* L, int n_pad, long lda, long strideL,
 int gpmpc_tri_inverse(const double* L, int n_pad, long lda, const double* Winv, double* Linv, long ldi, void* stream);
 
 /* sumsq[q] = | Linv Ks[q,:]^T |^2 for the q_pad rows of Ks (q_pad x n_pad row-major, NOT modified).
- * work: (n_pad/64) x q_pad doubles of scratch (per-tile partial sums, reduced in a fixed order). */
+ * work: (n_pad/64) x q_pad doubles of scratch (per-tile partial sums, reduced in a fixed order).
+ * one_cta_per_sm != 0: keep one CTA resident per SM (same result) so that a kernel on another stream -- the ADMM
+ * solve, which does not read the variances -- can share the SMs. */
 int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk, double* work,
-                     double* sumsq, void* stream);
+                     double* sumsq, int one_cta_per_sm, void* stream);
 
 /* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
  * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
