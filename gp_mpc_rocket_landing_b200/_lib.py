@@ -71,6 +71,9 @@ _PROTOS = {
     "gpmpc_potrs": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp]),
     "gpmpc_normalize_targets": (c_int, [c_dp, c_int, c_int, c_long, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_lml": (c_int, [c_dp, c_int, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp, c_dp]),
+    "gpmpc_lml_grad_se_work_doubles": (C.c_size_t, [c_int, c_int, c_int]),
+    "gpmpc_lml_grad_se": (c_int, [c_dp, c_int, c_int, c_int, c_int, c_double, c_double, c_dp, c_long, c_dp, c_long, c_int,
+                                  c_dp, c_dp, c_dp]),
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_step_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linearize_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),

@@ -248,6 +248,27 @@ class ExactModelDev:
              ptr(self.lml), stream())
         return self
 
+    def lml_gradient(self):
+        """d LML_p / d[log s2, log l_1..l_D, log noise] -> (P, D + 2) CUDA tensor, for the SE-ARD kernel.
+        K^{-1} comes from cho_solve of the identity on the cached factor; the D + 2 contractions with
+        W = alpha alpha' - K^{-1} run as one fused pass (gpmpc_lml_grad_se).  The LML is the one of the normalised
+        targets (exact_gp.py:186-204), so this is the gradient of `self.lml`."""
+        torch = torch_()
+        f = self.f
+        if f.kind != SE:
+            raise ValueError("lml_gradient: analytic gradients are implemented for the SE-ARD kernel")
+        if f.DP > 32:
+            raise ValueError("lml_gradient: input dimension > 32")
+        dev = f.L.device
+        Kinv = torch.eye(f.n_pad, dtype=torch.float64, device=dev)
+        f.solve(Kinv)
+        nwork = int(_lib.lib.gpmpc_lml_grad_se_work_doubles(f.n_pad, f.DP, self.P))
+        work = torch.empty((nwork,), dtype=torch.float64, device=dev)
+        grad = torch.empty((self.P, f.D + 2), dtype=torch.float64, device=dev)
+        call("gpmpc_lml_grad_se", ptr(f.Xs), f.n, f.n_pad, f.DP, f.D, f.sv, f.noise, ptr(Kinv), Kinv.stride(0),
+             ptr(self.alpha), self.alpha.stride(0), self.P, ptr(work), ptr(grad), stream())
+        return grad
+
     def predict(self, Xq, want_var=True, chunk=65536, col=None, keep_v=False, var_floor=1e-10):
         """-> mean (Q,P), var (Q,P) CUDA tensors (col: a single output -> (Q,1)).  keep_v: also return the solved
         V = (L^{-1} K*^T)^T rows (Q_pad, n_pad) of the last chunk (full-covariance branch, exact_gp.py:247-254)."""

@@ -200,11 +200,32 @@ class ExactGP:
         return samples.T
 
     # ---- hyper-parameters -------------------------------------------------------------------------------------------------
-    def optimize_hyperparameters(self, n_restarts: int = 5, verbose: bool = False) -> dict:
-        """exact_gp.py:357-421: L-BFGS-B on the negative LML; every objective evaluation is a device refit."""
+    def _analytic_gradient_available(self) -> bool:
+        k = self.kernel
+        return (getattr(k, "kind", None) == E.SE and getattr(k, "learn_signal_variance", True)
+                and getattr(k, "learn_lengthscales", True) and k.input_dim <= 32)
+
+    def log_marginal_likelihood_gradient(self) -> np.ndarray:
+        """d LML / d[kernel log-parameters..., log noise_variance] at the fitted hyper-parameters (SE-ARD), the
+        parameter order of `optimize_hyperparameters` (exact_gp.py:380-384).  Device pass: gpmpc_lml_grad_se."""
+        if self._model is None:
+            raise RuntimeError("Must call fit() before log_marginal_likelihood_gradient()")
+        if not self._analytic_gradient_available():
+            raise ValueError("analytic LML gradients need an SE-ARD kernel with all parameters learnable")
+        return _host(self._model.lml_gradient()[self._col])
+
+    def optimize_hyperparameters(self, n_restarts: int = 5, verbose: bool = False,
+                                 analytic_gradients: Optional[bool] = None) -> dict:
+        """exact_gp.py:357-421: L-BFGS-B on the negative LML; every objective evaluation is a device refit.
+
+        analytic_gradients (extension; None = when available): pass the device-computed gradient to L-BFGS-B instead of
+        letting scipy difference the objective (the reference's behaviour, n_params + 1 refits per gradient)."""
         from scipy.optimize import minimize
         if self.X_train is None:
             raise RuntimeError("Must call fit() before optimize_hyperparameters()")
+        use_grad = self._analytic_gradient_available() if analytic_gradients is None else bool(analytic_gradients)
+        if use_grad and not self._analytic_gradient_available():
+            raise ValueError("analytic LML gradients need an SE-ARD kernel with all parameters learnable")
 
         def objective(params):
             n_kernel = self.kernel.n_params
@@ -212,16 +233,19 @@ class ExactGP:
             self._noise_variance = np.exp(params[n_kernel])
             try:
                 self.fit(self.X_train, self.y_train * self._y_std + self._y_mean)
+                if use_grad:
+                    return -self._log_marginal_likelihood, -self.log_marginal_likelihood_gradient()
                 return -self._log_marginal_likelihood
             except (np.linalg.LinAlgError, ValueError):
-                return np.inf
+                return (np.inf, np.zeros(len(params))) if use_grad else np.inf
 
         initial_params = np.concatenate([self.kernel.get_params(), [np.log(self._noise_variance)]])
         best_result, best_nll = None, np.inf
         for restart in range(n_restarts):
             params0 = initial_params if restart == 0 else initial_params + 0.5 * np.random.randn(len(initial_params))
             try:
-                result = minimize(objective, params0, method="L-BFGS-B", options={"maxiter": 100, "disp": verbose})
+                result = minimize(objective, params0, method="L-BFGS-B", jac=True if use_grad else None,
+                                  options={"maxiter": 100, "disp": True} if verbose else {"maxiter": 100})
                 if result.fun < best_nll:
                     best_nll, best_result = result.fun, result
             except Exception as e:  # noqa: BLE001 (reference behaviour)

@@ -66,6 +66,18 @@ int gpmpc_normalize_targets(const double* Y, int n, int P, long ldy, int n_pad, 
 int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strideL, const double* Yn, const double* alpha,
               int nrhs, int batch, double* lml, void* stream);
 
+/* Gradient of the log marginal likelihood w.r.t. the SE-ARD log hyper-parameters, all D + 2 components in one pass:
+ * grad[p*(D+2) + c], c = 0: log signal variance, 1..D: log lengthscales, D+1: log noise variance, for P outputs that
+ * share one factor.  dLML/dtheta = 1/2 sum_ij (alpha_i alpha_j - K^{-1}_ij) (dK/dtheta)_ij with the kernel derivatives of
+ * kernels.py:279-318 and d(noise I)/dlog noise = noise I.  Xs: inputs scaled by 1/l (gpmpc_scale_inputs), Kinv: the
+ * symmetric n_pad x n_pad inverse (gpmpc_potrs on the identity), alpha: P x lda.  work: gpmpc_lml_grad_se_work_doubles.
+ * Replaces the finite-difference gradient of scipy's L-BFGS-B in ExactGP.optimize_hyperparameters (exact_gp.py:357-421:
+ * D + 3 refits per gradient) with one refit + one pass. */
+size_t gpmpc_lml_grad_se_work_doubles(int n_pad, int DP, int P);
+int gpmpc_lml_grad_se(const double* Xs, int n, int n_pad, int DP, int D, double signal_var, double noise_var,
+                      const double* Kinv, long ldk, const double* alpha, long lda, int P, double* work, double* grad,
+                      void* stream);
+
 /* Ks (q_pad x n_pad) <- (L^{-1} Ks^T)^T in place and sumsq[q] = sum_i v_iq^2: solve_triangular + np.sum(v**2, axis=0)
  * at exact_gp.py:260-261 / fast_gp.py:194-199, as a blocked DMMA TRSM. */
 int gpmpc_trsm_sumsq(const double* L, int n_pad, long lda, const double* Winv, double* Ks, int q_pad, long ldk,

@@ -130,6 +130,22 @@ def multi_exact_predict(fits, Xq):
     return m, v
 
 
+def exact_lml_gradient(f):
+    """Gradient of exact_fit's LML (exact_gp.py:186-204) w.r.t. [log sv, log l_0.., log noise], the parameter vector of
+    optimize_hyperparameters (exact_gp.py:380-384), from the kernel derivatives of kernels.py:279-318:
+    dLML/dtheta = 1/2 tr((alpha alpha' - K^{-1}) dK/dtheta).  The reference itself differences the LML numerically
+    (scipy L-BFGS-B without jac); tests/ check this closed form against central differences of exact_fit."""
+    n = f.X.shape[0]
+    Kinv = np.linalg.solve(f.L.T, np.linalg.solve(f.L, np.eye(n)))
+    W = np.outer(f.alpha, f.alpha) - Kinv
+    G = se_ard_gradients(f.X, None, f.ls, f.sv)
+    g = [0.5 * np.sum(W * G["log_signal_variance"])]
+    for i in range(f.X.shape[1]):
+        g.append(0.5 * np.sum(W * G[f"log_lengthscale_{i}"]))
+    g.append(0.5 * f.noise * np.trace(W))
+    return np.array(g)
+
+
 # --------------------------------------------------------------------------- sparse GP
 class SparseFit:
     __slots__ = ("kind", "ls", "sv", "noise", "method", "jitter", "Z", "X", "y_n", "y_mean", "y_std",

@@ -184,3 +184,46 @@ def test_refit_sweep_matches_sequential_fits(eng):
     out = sweep.fit(np.stack([g["jit_ls"], g["jit_ls"]]), float(g["sv"]), [float(g["jit_noise"]), 1e-2])
     assert out["jitter"][0] == fo.jitter > 0.0 and out["jitter"][1] == 0.0
     assert relerr(out["lml"].cpu().numpy()[0, 0], g["jit_lml"]) < 1e-6
+
+
+@pytest.mark.parametrize("n,D,noise,tol", [(300, 5, 1e-2, 1e-9), (1000, 11, 1e-2, 1e-8), (130, 17, 1e-3, 1e-8)])
+def test_lml_gradient_matches_closed_form(eng, n, D, noise, tol):
+    """gpmpc_lml_grad_se (all D + 2 components, P outputs on one factor) against the oracle's closed form, which
+    tests/test_oracle_golden.py pins to central differences of the reference LML restatement.  tol: FP64, relative to the
+    largest component; K^{-1} enters, so it scales with cond(K) like the variance checks above."""
+    from oracle import gp as og
+    rng = np.random.default_rng(n + D)
+    X = rng.normal(size=(n, D))
+    Y = np.stack([np.sin(X[:, 0]) + 0.3 * X[:, 1], np.cos(X[:, 2]) * X[:, 0], 0.1 * rng.normal(size=n)], axis=1)
+    ls = np.exp(rng.normal(scale=0.3, size=D)) * np.sqrt(D)
+    sv = 1.7
+    f = eng.ExactFactor(0, ls, sv, noise).fit(X)
+    m = eng.ExactModelDev(f).fit_targets(Y)
+    assert f.jitter == 0.0
+    g = m.lml_gradient().cpu().numpy()
+    assert g.shape == (3, D + 2)
+    for p in range(3):
+        ref = og.exact_lml_gradient(og.exact_fit(0, X, Y[:, p], ls, sv, noise))
+        assert np.abs(g[p] - ref).max() / np.abs(ref).max() < tol, (p, g[p], ref)
+
+
+def test_optimize_hyperparameters_with_device_gradients(eng):
+    """ExactGP.optimize_hyperparameters: L-BFGS-B fed the device gradient reaches the optimum the reference's
+    finite-difference path reaches (exact_gp.py:357-421), with far fewer refits."""
+    from gp_mpc_rocket_landing_b200.gp import ExactGP, SquaredExponentialARD
+    rng = np.random.default_rng(5)
+    X = rng.uniform(-2, 2, size=(200, 3))
+    y = np.sin(2 * X[:, 0]) + 0.5 * X[:, 1] + 0.05 * rng.normal(size=200)
+    res = {}
+    for mode in (True, False):
+        gp = ExactGP(SquaredExponentialARD(3), noise_variance=1e-2).fit(X, y)
+        lml0 = gp.log_marginal_likelihood
+        g = gp.log_marginal_likelihood_gradient()
+        assert g.shape == (5,)
+        out = gp.optimize_hyperparameters(n_restarts=1, analytic_gradients=mode)
+        assert out["log_marginal_likelihood"] > lml0
+        res[mode] = (out["log_marginal_likelihood"], gp.kernel.get_params().copy(), gp.noise_variance)
+    assert abs(res[True][0] - res[False][0]) < 1e-3 * abs(res[False][0])
+    # the finite-difference run stops on its noisier gradient a little earlier: same optimum to a few per cent
+    np.testing.assert_allclose(res[True][1][:3], res[False][1][:3], rtol=0.1)
+    assert res[True][0] >= res[False][0] - 1e-6 * abs(res[False][0])

@@ -66,6 +66,23 @@ def test_exact_gp_jitter_escalation():
     assert relerr(f.lml, g["jit_lml"]) < 1e-9
 
 
+def test_exact_lml_gradient_closed_form_vs_central_differences():
+    """The closed-form LML gradient (kernel derivatives pinned by test_kernels_match_reference) against central
+    differences of the reference LML restatement -- what scipy's L-BFGS-B differences in exact_gp.py:357-421."""
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(60, 4))
+    y = np.sin(X[:, 0]) + 0.1 * rng.normal(size=60)
+    th = np.log(np.array([1.3, 0.8, 1.1, 2.0, 0.6, 3e-2]))
+
+    def fit(t):
+        return ogp.exact_fit(0, X, y, np.exp(t[1:5]), np.exp(t[0]), np.exp(t[5]))
+
+    g = ogp.exact_lml_gradient(fit(th))
+    h = 1e-5
+    fd = np.array([(fit(th + h * e).lml - fit(th - h * e).lml) / (2 * h) for e in np.eye(6)])
+    np.testing.assert_allclose(g, fd, rtol=1e-7, atol=1e-7)
+
+
 def test_sparse_gp():
     g = load_golden("sparse_gp.npz")
     for method in ("fitc", "vfe"):
