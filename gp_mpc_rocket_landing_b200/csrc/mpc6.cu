@@ -404,6 +404,55 @@ extern "C" int gpmpc_qp_assemble_6dof(const GpmpcDyn6* dyn, int B, int N, const 
   return gpmpc_check_launch("qp_assemble6");
 }
 
+// ------------------------------------------------------------------------------------------------ covariance chain
+// Sigma_{k+1} = A_k Sigma_k A_k' + diag(q_k) (uncertainty_prop.py:117-177), any nx <= 16.  One CTA of 16 x 16 threads per
+// scenario: thread (i, j) owns entry (i, j); Sigma and T = A Sigma live in shared memory, A_k is staged per stage.
+__global__ void __launch_bounds__(256) propagate_cov_kernel(int nx, int N, const double* __restrict__ A, long ld_row,
+                                                            long stage_stride, const double* __restrict__ qdiag,
+                                                            double sigma0, double* __restrict__ covs,
+                                                            const int* __restrict__ active) {
+  __shared__ double Sg[16][17], T[16][17], Ak[16][17];
+  const int b = blockIdx.x;
+  if (active && !active[b]) return;
+  const int i = threadIdx.x >> 4, j = threadIdx.x & 15;
+  const bool in = i < nx && j < nx;
+  double* out = covs + (long)b * (N + 1) * nx * nx;
+  double sij = (i == j) ? sigma0 : 0.0;
+  if (in) {
+    Sg[i][j] = sij;
+    out[i * nx + j] = sij;
+  }
+  for (int k = 0; k < N; ++k) {
+    const double* Ag = A + ((long)b * N + k) * stage_stride;
+    if (in) Ak[i][j] = Ag[i * ld_row + j];
+    __syncthreads();
+    if (in) {
+      double t = 0.0;
+      for (int l = 0; l < nx; ++l) t += Ak[i][l] * Sg[l][j];
+      T[i][j] = t;
+    }
+    __syncthreads();
+    if (in) {
+      double v = 0.0;
+      for (int l = 0; l < nx; ++l) v += T[i][l] * Ak[j][l];
+      if (i == j) v += qdiag[((long)b * N + k) * nx + i];
+      sij = v;
+      out[(long)(k + 1) * nx * nx + i * nx + j] = v;
+    }
+    __syncthreads();
+    if (in) Sg[i][j] = sij;
+  }
+}
+
+extern "C" int gpmpc_propagate_cov(int nx, int B, int N, const double* A, long ld_row, long stage_stride,
+                                   const double* qdiag, double sigma0, double* covs, const int* active, void* stream) {
+  GPMPC_REQUIRE(nx >= 1 && nx <= 16 && B >= 0 && N >= 1, "gpmpc_propagate_cov: need 1 <= nx <= 16, N >= 1");
+  GPMPC_REQUIRE(A && qdiag && covs && ld_row >= nx, "gpmpc_propagate_cov: null argument or ld_row < nx");
+  if (B == 0) return GPMPC_OK;
+  propagate_cov_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(nx, N, A, ld_row, stage_stride, qdiag, sigma0, covs, active);
+  return gpmpc_check_launch("propagate_cov");
+}
+
 extern "C" int gpmpc_pack_traj(int nx, int nu, int B, int N, const double* X, const double* U, double* z, void* stream) {
   const long tot = (long)B * (N * (nx + nu) + nx);
   if (tot == 0) return GPMPC_OK;

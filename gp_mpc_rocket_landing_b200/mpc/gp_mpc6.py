@@ -46,6 +46,8 @@ class GPMPC6DoFConfig:
     N: int = 30
     dt: float = 0.1
     use_gp_mean: bool = True
+    use_gp_uncertainty: bool = True   # gp_mpc.py:54: propagate the GP variance through the horizon (linear method)
+    repropagate_uncertainty: bool = True  # gp_mpc.py:347-353 (computed and discarded by the reference)
     warm_start: bool = True
     max_sqp_iter: int = 10            # gp_mpc.py:296
     qp_max_iter: int = 1000
@@ -87,6 +89,13 @@ class _State6:
         self.n_iter = torch.zeros((B,), **i32)
         self.qp_iters = torch.zeros((B,), **i32)
         self.has_warm = False
+        # uncertainty propagation (uncertainty_prop.py:117-177): its own rollout, Jacobians, process noise and chain
+        self.Xr = torch.zeros((B, N + 1, NX6), **f64)
+        self.dmean_r = torch.zeros((B, N, 6), **f64)
+        self.ABr = torch.zeros((B, N, NX6, NS6), **f64)
+        self.qdiag = torch.zeros((B, N, NX6), **f64)
+        self.covs = torch.zeros((B, N + 1, NX6, NX6), **f64)
+        self.has_cov = False
 
 
 class GPMPC6DoF:
@@ -133,10 +142,27 @@ class GPMPC6DoF:
                 C.byref(self._dyn), st.B, st.N, ge.ptr(x0), ge.ptr(U), ge.ptr(X), ge.ptr(dmean), ge.ptr(st.active),
                 ge.stream())
 
+    def _propagate(self, st: _State6, Xr):
+        """Sigma_{k+1} = A_k Sigma_k A_k' + Q_k along the GP-mean rollout Xr of the current controls
+        (uncertainty_prop.py:117-177, Sigma_0 = 1e-6 I as at gp_mpc.py:285-289): Jacobians of `dynamics.step` at
+        (Xr[k], U[k]), Q_k = dt^2 diag(var_v) / diag(var_omega) in the velocity / body-rate rows."""
+        B, N = st.B, st.N
+        dt = float(self.config.dt)
+        Xp = Xr[:, :N].reshape(B * N, NX6).contiguous()
+        Up = st.U.reshape(B * N, NU6).contiguous()
+        _, _, vv, vw = self.gp.predict_batch(Xp, Up)
+        st.qdiag[:, :, 4:7] = vv.reshape(B, N, 3) * (dt * dt)
+        st.qdiag[:, :, 11:14] = vw.reshape(B, N, 3) * (dt * dt)
+        ge.call("gpmpc_linearize_6dof", C.byref(self._dyn), B * N, ge.ptr(Xp), ge.ptr(Up), ge.ptr(st.ABr), ge.stream())
+        ge.call("gpmpc_propagate_cov", NX6, B, N, ge.ptr(st.ABr), NS6, NX6 * NS6, ge.ptr(st.qdiag), 1e-6,
+                ge.ptr(st.covs), ge.ptr(st.active), ge.stream())
+        st.has_cov = True
+
     def _solve_device(self, st: _State6, x0, x_ref):
         c = self.config
         N = c.N
-        use_mean = self._models[0] is not None or self._models[1] is not None
+        use_mean = c.use_gp_mean and (self._models[0] is not None or self._models[1] is not None)
+        use_unc = c.use_gp_uncertainty and self.gp is not None and self.gp.n_data > 0
         if st.has_warm and c.warm_start:
             st.U.copy_(st.U_warm)
         else:  # hover along the body axis (gp_mpc.py:266-275)
@@ -147,6 +173,9 @@ class GPMPC6DoF:
         st.qp_iters.zero_()
         st.converged.zero_()
         self._rollout(st, x0, st.U, st.X, st.dmean if use_mean else None)
+        st.has_cov = False
+        if use_unc:
+            self._propagate(st, st.X)
         S = self._settings()
         ldx = 0 if x_ref.dim() == 2 else x_ref.stride(0)
         for it in range(c.max_sqp_iter):
@@ -163,6 +192,9 @@ class GPMPC6DoF:
                     ge.ptr(st.cost), ge.ptr(st.converged), ge.ptr(st.active), ge.ptr(st.n_iter), ge.stream())
             if it == c.max_sqp_iter - 1 or int(st.active.sum().item()) == 0:
                 break
+            if use_unc and c.repropagate_uncertainty:  # gp_mpc.py:347-353: chain along the rollout of the new controls
+                self._rollout(st, x0, st.U, st.Xr, st.dmean_r if use_mean else None)
+                self._propagate(st, st.Xr)
         st.U_warm.copy_(st.U)
         st.has_warm = True
 
@@ -174,6 +206,14 @@ class GPMPC6DoF:
         dv, dw, _, _ = self.gp.predict_batch(Xp, Up)
         st.dmean[:, :, :3] = dv.reshape(B, N, 3)
         st.dmean[:, :, 3:] = dw.reshape(B, N, 3)
+
+    def last_covariances(self, batch: bool = True):
+        """Propagated state covariances (B, N+1, 14, 14) of the last `solve_batch` (or `solve`), numpy; None when the
+        controller has no GP or `use_gp_uncertainty` is off (cf. get_uncertainty_at_horizon, gp_mpc.py:486-492)."""
+        st = self._batch if batch else self._single
+        if st is None or not st.has_cov:
+            return None
+        return st.covs.cpu().numpy()
 
     def _state_for(self, B, single):
         attr = "_single" if single else "_batch"

@@ -283,6 +283,13 @@ int gpmpc_qp_assemble_6dof(const GpmpcDyn6* dyn, int B, int N, const double* X_l
                            const double* x_init, const double* x_ref, long ldxref, const double* c_gp, const double* Qd,
                            const double* Qfd, double* AB, double* beq, double* q, const int* active, void* stream);
 
+/* Linear covariance chain Sigma_0 = sigma0 I, Sigma_{k+1} = A_k Sigma_k A_k' + diag(qdiag[b,k]) for any nx <= 16:
+ * uncertainty_prop.py:117-177 (the 14-state propagator GPMPC.solve calls at gp_mpc.py:283-289,347-351).  A: entry (i,j) of
+ * the stage-(b,k) Jacobian at A[(b*N+k)*stage_stride + i*ld_row + j] (e.g. the [A|B] blocks of gpmpc_linearize_6dof with
+ * ld_row 17, stage_stride 14*17); qdiag: (B,N,nx) = GP variances * dt^2 in the velocity / rate rows; covs: (B,N+1,nx,nx). */
+int gpmpc_propagate_cov(int nx, int B, int N, const double* A, long ld_row, long stage_stride, const double* qdiag,
+                        double sigma0, double* covs, const int* active, void* stream);
+
 /* z = [x_0,u_0,...,x_N] <-> (X, U) for any state dimension (osqp_rti.py:601-631). */
 int gpmpc_pack_traj(int nx, int nu, int B, int N, const double* X, const double* U, double* z, void* stream);
 int gpmpc_unpack_traj(int nx, int nu, int B, int N, const double* z, double* X, double* U, void* stream);

@@ -170,6 +170,31 @@ def rollout_gp(x0, U, dt, p, predict, **kw):
     return X, D
 
 
+def propagate_linear6(x0, U, dt, p, predict_full, sigma0=1e-6, **kw):
+    """uncertainty_prop.py:117-177 (`_propagate_linear`, the method GPMPC.solve uses: gp_mpc.py:124-127,283-289):
+    Sigma_{k+1} = A_k Sigma_k A_k' + Q_k, Q_k = dt^2 diag(var_v) / diag(var_omega) in rows 4:7 / 11:14, along the GP-mean
+    chain from x0.  A_k: forward differences of the step (the reference calls dynamics.linearize of the absent simdyn
+    backend; the in-repo Jacobian statement is osqp_rti.py:374-401).  predict_full(x, u) -> d_v, d_w, var_v, var_w."""
+    N = U.shape[0]
+    means = np.zeros((N + 1, NX)); covs = np.zeros((N + 1, NX, NX))
+    means[0] = x0
+    covs[0] = np.eye(NX) * sigma0
+    x = np.array(x0, float); S = covs[0].copy()
+    for k in range(N):
+        A, _ = linearize_fd6(x, U[k], dt, p, **kw)
+        dv, dw, vv, vw = predict_full(x, U[k])
+        Q = np.zeros((NX, NX))
+        Q[4:7, 4:7] = np.diag(vv) * dt**2
+        Q[11:14, 11:14] = np.diag(vw) * dt**2
+        xn = step6(x, U[k], dt, p, **kw)
+        xn[4:7] += dv * dt
+        xn[11:14] += dw * dt
+        S = A @ S @ A.T + Q
+        means[k + 1] = xn; covs[k + 1] = S
+        x = xn
+    return means, covs
+
+
 def hover_guess(x0, N, p):
     """Warm start used by the batched driver: thrust balancing gravity along the body axis."""
     U = np.zeros((N, NU)); U[:, 0] = x0[0] * 1.0

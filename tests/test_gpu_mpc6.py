@@ -73,6 +73,14 @@ def _structured_gp(env, n=400, M=40):
         dv = np.array([ogp.sparse_predict(f, zv)[0][0] for f in fits_v])
         dw = np.array([ogp.sparse_predict(f, zw)[0][0] for f in fits_w])
         return dv, dw
+
+    def predict_full(x, u):
+        zv = ogp.features_6dof_trans(x, u)[None]; zw = ogp.features_6dof_rot(x, u)[None]
+        pv = [ogp.sparse_predict(f, zv) for f in fits_v]
+        pw = [ogp.sparse_predict(f, zw) for f in fits_w]
+        return (np.array([r[0][0] for r in pv]), np.array([r[0][0] for r in pw]),
+                np.array([r[1][0] for r in pv]), np.array([r[1][0] for r in pw]))
+    predict.full = predict_full
     return sg, predict
 
 
@@ -156,3 +164,50 @@ def test_assembly_and_solve_match_oracle(env):
     ctl1 = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=N, max_sqp_iter=1, qp_max_iter=4000))
     one = ctl1.solve(X0[0], XT[0])
     np.testing.assert_allclose(one.u0, sol.u0[0], rtol=1e-9, atol=1e-12)
+
+
+def test_linear_uncertainty_propagation_14_state(env):
+    """Step 2 of GPMPC.solve on the 14-state model (gp_mpc.py:283-289 -> uncertainty_prop.py:117-177): covariance chain
+    along the GP-mean rollout, with the structured sparse GP's variances as process noise.  The chain kernel alone is
+    checked first on random stage matrices (1e-13: same products, summation order of a plain triple loop)."""
+    from oracle import mpc6 as o6
+    gp, mpc, dynamics, workloads = env
+    E = gp.engine
+    torch = E.torch_()
+    rng = np.random.default_rng(11)
+    B, N, nx = 5, 9, 14
+    A = rng.normal(size=(B, N, nx, 17)); A[..., :nx] = np.eye(nx) + 0.1 * A[..., :nx]
+    qd = rng.uniform(0, 1e-3, size=(B, N, nx))
+    covs = torch.zeros((B, N + 1, nx, nx), dtype=torch.float64, device="cuda")
+    act = torch.ones((B,), dtype=torch.int32, device="cuda"); act[3] = 0
+    Ad, qdd = E.to_dev(A), E.to_dev(qd)   # named: the buffers must outlive the asynchronous launch
+    E.call("gpmpc_propagate_cov", nx, B, N, E.ptr(Ad), 17, nx * 17, E.ptr(qdd), 1e-6, E.ptr(covs), E.ptr(act), E.stream())
+    covs = covs.cpu().numpy()
+    for b in range(B):
+        S = np.eye(nx) * 1e-6
+        for k in range(N):
+            if b != 3:
+                np.testing.assert_allclose(covs[b, k], S, rtol=1e-13, atol=1e-13 * np.max(np.abs(S)))
+            S = A[b, k, :, :nx] @ S @ A[b, k, :, :nx].T + np.diag(qd[b, k])
+    assert np.all(covs[3] == 0.0)   # inactive scenario untouched
+    # through the controller
+    sg, predict = _structured_gp(env)
+    dyn = dynamics.Rocket6DoFDynamics()
+    N, B = 12, 3
+    ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=N, max_sqp_iter=1))
+    X0, XT = workloads.sample_initial_conditions_6dof(0, B)
+    ctl.solve_batch(X0, XT)
+    cg = ctl.last_covariances()
+    assert cg.shape == (B, N + 1, 14, 14)
+    p = o6.Rocket6DoFParams()
+    for b in range(B):
+        U0 = np.zeros((N, 3)); U0[:, 0] = X0[b, 0]
+        _, co = o6.propagate_linear6(X0[b], U0, 0.1, p, predict.full)
+        # FD Jacobian noise (5e-8 absolute on entries of A) and the sparse-GP variance parity (1e-7) enter linearly
+        assert np.max(np.abs(cg[b] - co)) < 1e-6 * np.max(np.abs(co)), np.max(np.abs(cg[b] - co)) / np.max(np.abs(co))
+        # positive semi-definite: the quaternion normalisation inside the step makes A_k singular along q
+        ev = np.linalg.eigvalsh(cg[b, -1])
+        assert ev[0] > -1e-12 * ev[-1]
+    off = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=N, max_sqp_iter=1, use_gp_uncertainty=False))
+    off.solve_batch(X0, XT)
+    assert off.last_covariances() is None
