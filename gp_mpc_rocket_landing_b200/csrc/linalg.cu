@@ -89,6 +89,51 @@ __global__ void __launch_bounds__(256) potrf_diag64_kernel(double* __restrict__ 
   }
 }
 
+// W = L_bb^{-1} for 64x64 diagonal blocks of an already factored L (the second half of potrf_diag64_kernel on its own):
+// used after rows were appended to a factor, when only the diagonal blocks that received new rows change.
+__global__ void __launch_bounds__(256) trinv64_kernel(const double* __restrict__ L, long lda, double* __restrict__ Wbase,
+                                                      int b0) {
+  extern __shared__ double trinv_sm[];
+  double(*S)[65] = reinterpret_cast<double(*)[65]>(trinv_sm);
+  double(*Wi)[65] = reinterpret_cast<double(*)[65]>(trinv_sm + 64 * 65);
+  const int blk = b0 + blockIdx.x, tid = threadIdx.x;
+  const double* A = L + (long)blk * 64 * lda + (long)blk * 64;
+  for (int idx = tid; idx < 4096; idx += 256) {
+    int i = idx >> 6, k = idx & 63;
+    S[i][k] = A[(long)i * lda + k];
+    Wi[i][k] = 0.0;
+  }
+  __syncthreads();
+  {
+    const int j = tid >> 2, q = tid & 3;
+    for (int i = 0; i < 64; ++i) {
+      double sacc = 0.0;
+      for (int k = j + ((q - j) & 3); k < i; k += 4) sacc = fma(S[i][k], Wi[k][j], sacc);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+      sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+      if (q == 0 && i >= j) Wi[i][j] = (i == j) ? 1.0 / S[j][j] : -sacc / S[i][i];
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+  double* W = Wbase + (long)blk * 4096;
+  for (int idx = tid; idx < 4096; idx += 256) W[idx] = Wi[idx >> 6][idx & 63];
+}
+
+extern "C" int gpmpc_trinv64_blocks(const double* L, int n_pad, long lda, double* Winv, int block_first, int block_last,
+                                    void* stream) {
+  GPMPC_REQUIRE(n_pad % 64 == 0 && block_first >= 0 && block_last < n_pad / 64 && block_first <= block_last,
+                "gpmpc_trinv64_blocks: bad block range");
+  const size_t smem = sizeof(double) * 2 * 64 * 65;
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(trinv64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = true;
+  }
+  trinv64_kernel<<<block_last - block_first + 1, 256, smem, (cudaStream_t)stream>>>(L, lda, Winv, block_first);
+  return gpmpc_check_launch("trinv64");
+}
+
 __global__ void zero_upper_kernel(double* __restrict__ A, int n, long lda, long strideA) {
   double* a = A + blockIdx.z * strideA;
   int j = blockIdx.x * blockDim.x + threadIdx.x;

@@ -160,6 +160,58 @@ class ExactFactor:
                 return self
         raise ValueError("Kernel matrix is not positive definite even with jitter")
 
+    def append(self, Xnew):
+        """Extend the factor by the rows of the new points instead of re-factorising (the reference refits from scratch
+        for every batch of new observations: online_update.py:361-408, sparse_gp.py:328-353).  With K' = [[K, k], [k', c]]:
+        L' = [[L, 0], [v', l]], v = L^{-1} k (the blocked DMMA TRSM of `predict`), l l' = c - v'v (a <= 128-point
+        Cholesky).  O(n^2 m) instead of O(n^3 / 3); the existing rows of L are untouched, so the result equals the
+        factor of a full refit up to the rounding of the last rows.  Raises ValueError when the Schur complement is not
+        positive definite (the caller then refits with the jitter escalation of exact_gp.py:163-175)."""
+        torch = torch_()
+        if self.kind is None:
+            raise ValueError("ExactFactor.append: needs one of the fused ARD kernels")
+        Xnew = to_dev(Xnew)
+        if Xnew.dim() == 1:
+            Xnew = Xnew.reshape(1, -1)
+        for s0 in range(0, Xnew.shape[0], 128):
+            self._append_chunk(Xnew[s0:s0 + 128].contiguous())
+        return self
+
+    def _append_chunk(self, Xnew):
+        torch = torch_()
+        m, n = Xnew.shape[0], self.n
+        n2 = n + m
+        dev = self.L.device
+        if n2 > self.n_pad:   # grow the padded buffers by whole 128-blocks (unit diagonal in the padding)
+            np2 = pad_to(n2, 128)
+            L2 = torch.eye(np2, dtype=torch.float64, device=dev)
+            L2[: self.n_pad, : self.n_pad] = self.L
+            W2 = torch.eye(64, dtype=torch.float64, device=dev).repeat(1, np2 // 64, 1, 1)
+            W2[:, : self.n_pad // 64] = self.Winv
+            self.L, self.Winv, self.n_pad = L2, W2.contiguous(), np2
+        Xall = torch.cat([self.X, Xnew], dim=0)
+        Xs_all, sq_all = scale_inputs(Xall, self.ls, n_pad=self.n_pad, DP=self.DP)
+        Xs_new, sq_new = scale_inputs(Xnew, self.ls, DP=self.DP)
+        Kx = gram_scaled(self.kind, Xs_new, sq_new, m, Xs_all, sq_all, n2, self.sv)        # (128, n_pad)
+        V = Kx.clone()
+        V[:, n:] = 0.0
+        self.sumsq_inplace(V)                                                             # rows: v' = (L^{-1} k)'
+        VVt = torch.empty((128, 128), dtype=torch.float64, device=dev)
+        call("gpmpc_dgemm_nt", ptr(V), V.stride(0), ptr(V), V.stride(0), ptr(VVt), 128, 128, 128, self.n_pad, 1.0, 0.0, 0,
+             stream())
+        S = torch.eye(128, dtype=torch.float64, device=dev)
+        S[:m, :m] = Kx[:m, n:n2] - VVt[:m, :m]
+        S.diagonal()[:m].add_(self.noise + self.jitter)
+        _, info = potrf(S)
+        if int(info.item()) != 0:
+            raise ValueError("ExactFactor.append: Schur complement of the new points is not positive definite")
+        self.L[n:n2, :n] = V[:m, :n]
+        self.L[n:n2, n:n2] = S[:m, :m]
+        call("gpmpc_trinv64_blocks", ptr(self.L), self.n_pad, self.L.stride(0), ptr(self.Winv), n // 64, (n2 - 1) // 64,
+             stream())
+        self.X, self.Xs, self.sq, self.n = Xall, Xs_all, sq_all, n2
+        self.Linv = None
+
     def solve(self, Bm):
         """cho_solve for the rows of Bm (nrhs, n_pad), in place."""
         call("gpmpc_potrs", ptr(self.L), self.n_pad, self.L.stride(0), 0, ptr(self.Winv), ptr(Bm), Bm.shape[0], 1,

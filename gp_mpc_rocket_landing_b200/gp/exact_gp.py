@@ -112,6 +112,41 @@ class ExactGP:
                      float(model.ystd[0].item()), float(model.lml[0].item()))
         return self
 
+    def update(self, X_new, y_new) -> "ExactGP":
+        """Add observations (the exact-GP counterpart of SparseGP.update, sparse_gp.py:328-353, which refits on the
+        augmented data).  Same result as `fit` on the concatenated data -- targets are re-normalised, alpha and the LML
+        recomputed -- but the factor is EXTENDED by the new rows (ExactFactor.append, O(n^2 m)) when the
+        hyper-parameters are those of the cached factor; otherwise, or when the extension is not positive definite, this
+        is a full refit."""
+        if self._model is None:
+            return self.fit(X_new, y_new)
+        dev_x = _is_dev(self.X_train)
+        Xn = X_new if _is_dev(X_new) else np.atleast_2d(np.asarray(X_new, dtype=np.float64))
+        yn = _host(y_new).flatten() if _is_dev(y_new) else np.atleast_1d(np.asarray(y_new, dtype=np.float64)).flatten()
+        y_all = np.concatenate([self.y_train * self._y_std + self._y_mean, yn])
+        if dev_x:
+            X_all = E.torch_().cat([self.X_train, E.to_dev(Xn)], dim=0)
+        else:
+            X_all = np.vstack([self.X_train, _host(Xn) if _is_dev(Xn) else Xn])
+        f = self._model.f
+        k = self.kernel
+        same = (f.kind is not None and getattr(k, "kind", None) == f.kind and f.noise == float(self._noise_variance)
+                and f.sv == float(k.signal_variance) and np.array_equal(f.ls_host, np.asarray(k.lengthscales, dtype=np.float64))
+                and self._model.P == 1)
+        if not same:
+            return self.fit(X_all, y_all)
+        try:
+            f.append(Xn)
+        except ValueError:
+            return self.fit(X_all, y_all)
+        pm = None
+        if self.mean_function is not None:
+            pm = np.asarray(self.mean_function(_host(X_all) if dev_x else X_all), dtype=np.float64)
+        model = E.ExactModelDev(f).fit_targets(y_all, normalize=self.normalize_y, prior_mean=pm)
+        self._attach(model, 0, X_all, _host(model.Yn[0, : f.n]), float(model.ymean[0].item()),
+                     float(model.ystd[0].item()), float(model.lml[0].item()))
+        return self
+
     @property
     def log_marginal_likelihood(self) -> float:
         if self._log_marginal_likelihood is None:

@@ -118,6 +118,10 @@ class GPMPC6DoF:
         self._single = None
         self._models = (None, None)
         self._is_setup = False
+        self.timers: Optional[me.PhaseTimers] = None   # set by the bench tools: CUDA-event phase attribution
+
+    def _span(self, name):
+        return self.timers.span(name) if self.timers is not None else me.NULL_SPAN
 
     def setup(self) -> None:
         """Fetch the device models of the structured GP (fits it lazily, structured_gp.py:245-253)."""
@@ -172,29 +176,38 @@ class GPMPC6DoF:
         st.n_iter.zero_()
         st.qp_iters.zero_()
         st.converged.zero_()
-        self._rollout(st, x0, st.U, st.X, st.dmean if use_mean else None)
+        with self._span("rollout"):
+            self._rollout(st, x0, st.U, st.X, st.dmean if use_mean else None)
         st.has_cov = False
         if use_unc:
-            self._propagate(st, st.X)
+            with self._span("uncertainty"):
+                self._propagate(st, st.X)
         S = self._settings()
         ldx = 0 if x_ref.dim() == 2 else x_ref.stride(0)
         for it in range(c.max_sqp_iter):
             if use_mean and it > 0:  # GP means at the new linearisation points (gp_mpc.py:309-314)
-                self._gp_points(st)
+                with self._span("gp_mean"):
+                    self._gp_points(st)
+            sp = self._span("assemble"); sp.__enter__()
             ge.call("gpmpc_qp_assemble_6dof", C.byref(self._dyn), st.B, N, ge.ptr(st.X), ge.ptr(st.U), ge.ptr(x0),
                     ge.ptr(x_ref), ldx, ge.ptr(st.dmean) if use_mean else None, ge.ptr(self._qp.Qd), ge.ptr(self._qp.Qfd),
                     ge.ptr(st.AB), ge.ptr(st.beq), ge.ptr(st.q), ge.ptr(st.active), ge.stream())
             ge.call("gpmpc_pack_traj", NX6, NU6, st.B, N, ge.ptr(st.X), ge.ptr(st.U), ge.ptr(st.ws.x), ge.stream())
-            me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active)
+            sp.__exit__(None, None, None)
+            with self._span("admm"):
+                me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active)
+            sp = self._span("update"); sp.__enter__()
             st.qp_iters += st.ws.iters * st.active
             ge.call("gpmpc_mpc_update", NX6, NU6, st.B, N, 1, ge.ptr(st.ws.x), ge.ptr(st.ws.status), ge.ptr(x_ref), ldx,
                     ge.ptr(self._qp.Qd), ge.ptr(self._qp.Qfd), ge.ptr(self._qp.Rd), ge.ptr(st.X), ge.ptr(st.U), None, None,
                     ge.ptr(st.cost), ge.ptr(st.converged), ge.ptr(st.active), ge.ptr(st.n_iter), ge.stream())
+            sp.__exit__(None, None, None)
             if it == c.max_sqp_iter - 1 or int(st.active.sum().item()) == 0:
                 break
             if use_unc and c.repropagate_uncertainty:  # gp_mpc.py:347-353: chain along the rollout of the new controls
-                self._rollout(st, x0, st.U, st.Xr, st.dmean_r if use_mean else None)
-                self._propagate(st, st.Xr)
+                with self._span("uncertainty"):
+                    self._rollout(st, x0, st.U, st.Xr, st.dmean_r if use_mean else None)
+                    self._propagate(st, st.Xr)
         st.U_warm.copy_(st.U)
         st.has_warm = True
 

@@ -58,6 +58,12 @@ int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int batch, double*
 int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B, int nrhs, int batch,
                 void* stream);
 
+/* Winv[b] = (64x64 diagonal block b of the factored L)^{-1} for b in [block_first, block_last]: refreshes the cached
+ * block inverses after rows were appended to a factor in place (incremental alternative to the full refit of
+ * online_update.py:361-408 / sparse_gp.py:328-353, which re-factorise from scratch for every batch of new points). */
+int gpmpc_trinv64_blocks(const double* L, int n_pad, long lda, double* Winv, int block_first, int block_last,
+                         void* stream);
+
 /* Target normalisation, exact_gp.py:141-150: Yn[p*n_pad + i] = (Y[i*ldy + p] - mean_p) / std_p. */
 int gpmpc_normalize_targets(const double* Y, int n, int P, long ldy, int n_pad, int normalize, double* Yn,
                             double* ymean, double* ystd, void* stream);

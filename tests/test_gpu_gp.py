@@ -227,3 +227,47 @@ def test_optimize_hyperparameters_with_device_gradients(eng):
     # the finite-difference run stops on its noisier gradient a little earlier: same optimum to a few per cent
     np.testing.assert_allclose(res[True][1][:3], res[False][1][:3], rtol=0.1)
     assert res[True][0] >= res[False][0] - 1e-6 * abs(res[False][0])
+
+
+@pytest.mark.parametrize("n0,adds", [(100, (1, 27, 1)), (250, (6, 130)), (126, (2, 3))])
+def test_incremental_factor_append_equals_refit(eng, n0, adds):
+    """ExactGP.update: the factor extended row-wise (ExactFactor.append) against a from-scratch fit on the concatenated
+    data and against the oracle (exact_gp.py:118-204).  Crossing a 64-block, a 128-pad boundary (buffers grow) and a chunk
+    of more than 128 points are covered.  The old rows of L are bit-identical; the new rows, alpha, LML and predictions
+    agree to FP64 rounding scaled by cond(K) (1e-9 here, noise 1e-2)."""
+    from oracle import gp as og
+    from gp_mpc_rocket_landing_b200.gp import ExactGP, SquaredExponentialARD
+    rng = np.random.default_rng(n0)
+    D = 6
+    ntot = n0 + sum(adds)
+    X = rng.normal(size=(ntot, D))
+    y = np.sin(X[:, 0]) + 0.2 * X[:, 1] ** 2 + 0.05 * rng.normal(size=ntot)
+    Xq = rng.normal(size=(40, D))
+
+    def kern():
+        k = SquaredExponentialARD(D)
+        k.set_params(np.log(np.concatenate([[1.4], np.linspace(1.5, 2.5, D)])))
+        return k
+    inc = ExactGP(kern(), noise_variance=1e-2).fit(X[:n0], y[:n0])
+    L0 = inc._L.copy()
+    n = n0
+    for m in adds:
+        inc.update(X[n:n + m], y[n:n + m])
+        n += m
+        assert inc.n_train == n
+    full = ExactGP(kern(), noise_variance=1e-2).fit(X, y)
+    Li, Lf = inc._L, full._L
+    assert np.array_equal(Li[:n0, :n0], L0)            # existing rows untouched
+    assert np.array_equal(np.triu(Li, 1), np.zeros_like(Li))
+    np.testing.assert_allclose(Li, Lf, rtol=0, atol=1e-11 * np.abs(Lf).max())
+    ref = og.exact_fit(0, X, y, inc.kernel.lengthscales, inc.kernel.signal_variance, 1e-2)
+    assert relerr(inc._alpha, ref.alpha) < 1e-9
+    assert abs(inc.log_marginal_likelihood - ref.lml) < 1e-9 * abs(ref.lml)
+    pi, pf = inc.predict(Xq), full.predict(Xq)
+    mo, vo = og.exact_predict(ref, Xq)[:2]
+    assert relerr(pi.mean, mo) < 1e-9 and relerr(pi.variance, vo) < 1e-8
+    assert relerr(pi.mean, pf.mean) < 1e-10 and relerr(pi.variance, pf.variance) < 1e-9
+    # changed hyper-parameters: update falls back to a full refit with the new ones
+    inc.kernel.set_params(inc.kernel.get_params() + 0.1)
+    inc.update(X[:3] + 0.5, y[:3])
+    assert inc.n_train == ntot + 3 and np.allclose(inc._model.f.ls_host, inc.kernel.lengthscales)

@@ -37,6 +37,8 @@ def main():
     for _ in range(a.warmup):
         step()
     torch.cuda.synchronize()
+    from gp_mpc_rocket_landing_b200.mpc import engine as me
+    ctl.timers = me.PhaseTimers()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):
@@ -49,6 +51,7 @@ def main():
             "solves_per_s": a.batch / (ms * 1e-3), "mean_admm_iters_per_solve": float(np.mean(its)),
             "qp": "n=524 m=958, admm_stage_kernel<14,3,30,3,256,1> (one QP per SM, 220 KB shared memory)",
             "solved_fraction_last_step": float((s.qp_status == 1).double().mean().item()), "dtype": "f64"}
+    line["phase_ms_per_step"] = {k: round(v[0] / a.steps, 3) for k, v in ctl.timers.totals().items()}
     if a.cpu:
         from oracle import gp as ogp, mpc as ompc, mpc6 as o6
         p = o6.Rocket6DoFParams()

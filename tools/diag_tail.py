@@ -1,0 +1,68 @@
+"""Diagnostic (not part of the product): how much of the ADMM launch is tail?  Collects the per-QP iteration counts of a
+few closed-loop steps and simulates the CTA schedule (greedy, `slots` QPs resident) for three launch orders: scenario
+index (what the kernel does today), sorted by the previous step's iteration count (known before the launch), and sorted
+by the true count (lower bound for any order)."""
+import heapq, json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+
+
+def makespan(iters, slots, setup):
+    h = [0.0] * slots
+    heapq.heapify(h)
+    for it in iters:
+        t = heapq.heappop(h)
+        heapq.heappush(h, t + setup + it)
+    return max(h)
+
+
+def report(name, hist, slots, setup):
+    out = []
+    for prev, cur in zip(hist[:-1], hist[1:]):
+        idx = makespan(cur, slots, setup)
+        by_prev = makespan(cur[np.argsort(-prev, kind="stable")], slots, setup)
+        best = makespan(np.sort(cur)[::-1], slots, setup)
+        out.append((idx, by_prev, best, float(cur.sum() + setup * len(cur)) / slots, int(cur.max())))
+    a = np.array(out)
+    print(json.dumps({"case": name, "slots": slots, "setup_iters_equiv": setup,
+                      "makespan_index_order": a[:, 0].mean(), "makespan_sorted_by_previous": a[:, 1].mean(),
+                      "makespan_sorted_by_true": a[:, 2].mean(), "perfect_balance": a[:, 3].mean(),
+                      "max_iters_mean": a[:, 4].mean()}))
+
+
+def three_dof():
+    import bench
+    class A: pass
+    a = A(); a.batch = 4096; a.sqp_iters = 1; a.qp_max_iter = 1000
+    dyn, gp, ctl, mc = bench.build_problem(a, 0)
+    hist = []
+    for k in range(60):
+        mc.step()
+        if k >= 20:
+            hist.append(ctl._batch.ws.iters.cpu().numpy().astype(np.float64).copy())
+    report("3dof B=4096", hist, 444, 15.0)   # set-up 0.6 ms ~ 15 iterations of 39.6 us
+
+
+def six_dof():
+    import gp_mpc_rocket_landing_b200.gp as gp
+    import gp_mpc_rocket_landing_b200.mpc as mpc
+    from gp_mpc_rocket_landing_b200 import dynamics, workloads
+    X, U, Dv, Dw = workloads.residual_dataset_6dof(1000, seed=0)
+    sg = gp.StructuredRocketGP(gp.StructuredGPConfig(n_inducing=100, use_sparse=True, noise_variance=1e-3))
+    sg.add_data(X, U, Dv, Dw); sg.fit()
+    dyn = dynamics.Rocket6DoFDynamics()
+    ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=30, max_sqp_iter=1, use_gp_uncertainty=False))
+    X0, XT = workloads.sample_initial_conditions_6dof(0, 1024)
+    x = gp.engine.to_dev(X0); xt = gp.engine.to_dev(XT)
+    hist = []
+    for k in range(23):
+        s = ctl.solve_batch(x, xt)
+        x = dyn.step_batch(x, s.u0.contiguous(), 0.1)
+        if k >= 3:
+            hist.append(ctl._batch.ws.iters.cpu().numpy().astype(np.float64).copy())
+    report("6dof B=1024", hist, 148, 21.0)   # set-up 1.18 ms / 55 us per iteration
+
+
+three_dof()
+six_dof()
