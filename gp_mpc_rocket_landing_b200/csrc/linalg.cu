@@ -258,10 +258,135 @@ __global__ void __launch_bounds__(256) potrs_kernel(const double* __restrict__ L
   for (int i = tid; i < n_pad; i += 256) b[i] = y[i];
 }
 
+// Large n, few right-hand sides: the single-CTA solve above streams the whole factor through one SM (42 ms at
+// n = 8000).  Blocked right-looking substitution instead, one launch per 64-block: every CTA recomputes the small
+// solved block (64 x 64 product with the cached inverse), CTA 0 stores it, and the CTAs together subtract its
+// contribution from the not-yet-solved part -- a tall GEMV spread over all SMs.  The launch boundary is the dependency.
+__global__ void __launch_bounds__(256) potrs_fwd_step_kernel(const double* __restrict__ Lbase, int n_pad, long lda,
+                                                             long strideL, const double* __restrict__ Wbase,
+                                                             double* __restrict__ Bbase, double* __restrict__ Ybase,
+                                                             int nrhs, int j0) {
+  __shared__ double bj[64], yj[64], part[4][64];
+  const int f = blockIdx.y / nrhs;
+  const double* L = Lbase + f * strideL;
+  const double* W = Wbase + ((long)f * (n_pad / 64) + j0 / 64) * 4096;
+  double* b = Bbase + (long)blockIdx.y * n_pad;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid < 64) bj[tid] = b[j0 + tid];
+  __syncthreads();
+  {
+    const int i = tid & 63, q = tid >> 6;
+    double s = 0.0;
+    for (int k = q; k <= i; k += 4) s += W[i * 64 + k] * bj[k];
+    part[q][i] = s;
+  }
+  __syncthreads();
+  if (tid < 64) {
+    const double v = (part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid]);
+    yj[tid] = v;
+    if (blockIdx.x == 0) Ybase[(long)blockIdx.y * n_pad + j0 + tid] = v;
+  }
+  __syncthreads();
+  const double y0 = yj[2 * lane], y1 = yj[2 * lane + 1];
+  // 64 rows per CTA (n_pad - j0 - 64 is a multiple of 64), 8 per warp, 4 in flight: loads and reductions overlap
+  if (j0 + 64 + ((int)blockIdx.x + 1) * 64 > n_pad) return;   // last block: nothing left to update
+  const int r0 = j0 + 64 + blockIdx.x * 64 + warp * 8;
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
+    double sv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const double2 l2 = *reinterpret_cast<const double2*>(L + (long)(r0 + g * 4 + u) * lda + j0 + 2 * lane);
+      sv[u] = l2.x * y0 + l2.y * y1;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) sv[u] += __shfl_xor_sync(0xffffffffu, sv[u], o);
+    }
+    if (lane < 4) {
+      const double v = lane == 0 ? sv[0] : (lane == 1 ? sv[1] : (lane == 2 ? sv[2] : sv[3]));
+      b[r0 + g * 4 + lane] -= v;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) potrs_bwd_step_kernel(const double* __restrict__ Lbase, int n_pad, long lda,
+                                                             long strideL, const double* __restrict__ Wbase,
+                                                             double* __restrict__ Ybase, double* __restrict__ Xbase,
+                                                             int nrhs, int j0) {
+  __shared__ double rj[64], xj[64], part[4][64];
+  const int f = blockIdx.y / nrhs;
+  const double* L = Lbase + f * strideL;
+  const double* W = Wbase + ((long)f * (n_pad / 64) + j0 / 64) * 4096;
+  double* y = Ybase + (long)blockIdx.y * n_pad;
+  const int tid = threadIdx.x;
+  if (tid < 64) rj[tid] = y[j0 + tid];
+  __syncthreads();
+  {
+    const int c = tid & 63, q = tid >> 6;
+    double s = 0.0;
+    for (int k = c + q; k < 64; k += 4) s += W[k * 64 + c] * rj[k];   // x_j = W_j' r_j
+    part[q][c] = s;
+  }
+  __syncthreads();
+  if (tid < 64) {
+    const double v = (part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid]);
+    xj[tid] = v;
+    if (blockIdx.x == 0) Xbase[(long)blockIdx.y * n_pad + j0 + tid] = v;
+  }
+  __syncthreads();
+  const int c = blockIdx.x * 256 + tid;
+  if (c < j0) {
+    const double* col = L + (long)j0 * lda + c;
+    double s0 = 0.0, s1 = 0.0;
+#pragma unroll 8
+    for (int r = 0; r < 64; r += 2) {
+      s0 += col[(long)r * lda] * xj[r];
+      s1 += col[(long)(r + 1) * lda] * xj[r + 1];
+    }
+    y[c] -= s0 + s1;
+  }
+}
+
+static int potrs_blocked_min() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GPMPC_POTRS_BLOCKED_MIN");   // measurement knob; 0 disables the blocked path
+    v = e ? atoi(e) : 2048;
+    if (v <= 0) v = 1 << 30;
+  }
+  return v;
+}
+
+static int potrs_blocked(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B, int nrhs,
+                         int batch, cudaStream_t stream) {
+  double* Y = nullptr;
+  if (cudaMallocAsync(&Y, sizeof(double) * (size_t)batch * nrhs * n_pad, stream) != cudaSuccess) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_potrs: scratch allocation failed");
+    return GPMPC_ERR_CUDA;
+  }
+  const int nv = batch * nrhs;
+  for (int j0 = 0; j0 < n_pad; j0 += 64) {
+    const int rest = n_pad - j0 - 64;
+    dim3 grid(rest > 0 ? rest / 64 : 1, nv);
+    potrs_fwd_step_kernel<<<grid, 256, 0, stream>>>(L, n_pad, lda, strideL, Winv, B, Y, nrhs, j0);
+  }
+  for (int j0 = n_pad - 64; j0 >= 0; j0 -= 64) {
+    dim3 grid(j0 > 0 ? (j0 + 255) / 256 : 1, nv);
+    potrs_bwd_step_kernel<<<grid, 256, 0, stream>>>(L, n_pad, lda, strideL, Winv, Y, B, nrhs, j0);
+  }
+  cudaFreeAsync(Y, stream);
+  return gpmpc_check_launch("potrs_blocked");
+}
+
 extern "C" int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B,
                            int nrhs, int batch, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   GPMPC_REQUIRE(n_pad % 128 == 0 && n_pad > 0, "gpmpc_potrs: n_pad must be a multiple of 128");
+  if (n_pad >= potrs_blocked_min() && (long)batch * nrhs <= 64 && (lda & 1) == 0)
+    return potrs_blocked(L, n_pad, lda, strideL, Winv, B, nrhs, batch, stream);
   size_t smem = sizeof(double) * (n_pad + 64 + 256);
   GPMPC_REQUIRE(smem <= 200 * 1024, "gpmpc_potrs: n_pad too large for the shared-memory solve");
   static bool configured = false;
@@ -472,6 +597,37 @@ extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const d
   GPMPC_PREFER_SHARED(sum_parts_kernel);
   sum_parts_kernel<<<(q_pad + 255) / 256, 256, 0, stream>>>(work, n_pad / 64, q_pad, q_pad, sumsq);
   return gpmpc_check_launch("linv_sumsq");
+}
+
+// Right-looking form of the row solve V <- (L^{-1} V')' for FEW rows (q_pad = 128..512): per 64-block one in-place product
+// with the cached inverse block and one rank-64 update of all columns to the right, which spreads over n/128 CTAs.  The
+// left-looking gpmpc_trsm_sumsq is built for many query rows (its k-loop grows with the solved part and its grid with
+// the rows: with 128 rows that is one long serial CTA per step -- 43 ms at n = 8000 against 2 ms here).
+extern "C" int gpmpc_trsm_right(const double* L, int n_pad, long lda, const double* Winv, double* V, int q_pad, long ldv,
+                                void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0 && q_pad > 0, "gpmpc_trsm_right: n_pad, q_pad must be multiples of 128");
+  GPMPC_REQUIRE((lda & 1) == 0 && (ldv & 1) == 0 && ldv >= n_pad, "gpmpc_trsm_right: leading dimensions must be even");
+  for (int j0 = 0; j0 < n_pad; j0 += 64) {
+    GemmParams a{};                                   // V[:, j0:j0+64] <- V[:, j0:j0+64] W_j'   (in place: K = N = 64)
+    a.A = V + j0; a.lda = ldv;
+    a.B = Winv + (long)(j0 / 64) * 4096; a.ldb = 64;
+    a.C = V + j0; a.ldc = ldv;
+    a.M = q_pad; a.N = 64; a.K = 64; a.alpha = 1.0; a.beta = 0.0; a.epi = EPI_STORE;
+    int rc = launch_dgemm_nt<128, 64, 4, 2>(a, 1, stream);
+    if (rc) return rc;
+    if (j0 + 64 >= n_pad) break;
+    const int o = ((j0 + 64) / 128) * 128;            // 128-aligned origin; columns below j0 + 64 are masked
+    GemmParams u{};                                   // V[:, j0+64:] -= V[:, j0:j0+64] L[j0+64:, j0:j0+64]'
+    u.A = V + j0; u.lda = ldv;
+    u.B = L + (long)o * lda + j0; u.ldb = lda;
+    u.C = V + o; u.ldc = ldv;
+    u.M = q_pad; u.N = n_pad - o; u.K = 64; u.alpha = -1.0; u.beta = 1.0; u.epi = EPI_STORE;
+    u.col_min = j0 + 64 - o;
+    rc = launch_dgemm_nt<128, 128, 2, 4>(u, 1, stream);
+    if (rc) return rc;
+  }
+  return GPMPC_OK;
 }
 
 // ------------------------------------------------------------------------------------------------ small-M TRSM

@@ -7,6 +7,8 @@ from .features import (AtmosphereModel, CombinedFeatureExtractor, RocketFeatureE
                        Simple3DoFFeatureExtractor, TranslationalFeatureExtractor)
 from .kernels import (RBF, SE_ARD, Kernel, Matern32, Matern52, ProductKernel, SquaredExponential,
                       SquaredExponentialARD, SumKernel, WhiteNoise, create_matern_kernel, create_se_ard_kernel)
+from .online_update import (DataBuffer, DataPoint, OnlineGPUpdater, OnlineStructuredGPUpdater, OnlineUpdateConfig,
+                            ResidualCollector)
 from .sparse_gp import MultiOutputSparseGP, SparseGP
 from .structured_gp import Simple3DoFGP, StructuredGPConfig, StructuredRocketGP
 
@@ -17,4 +19,5 @@ __all__ = [
     "SquaredExponential", "SquaredExponentialARD", "SumKernel", "WhiteNoise", "create_matern_kernel",
     "create_se_ard_kernel", "MultiOutputSparseGP", "SparseGP", "CachedGPPredictor", "FastGPConfig",
     "FastGPPredictor", "NumbaGPPredictor", "SparseGPPredictor", "create_fast_gp", "Simple3DoFGP", "StructuredGPConfig", "StructuredRocketGP",
+    "DataBuffer", "DataPoint", "OnlineGPUpdater", "OnlineStructuredGPUpdater", "OnlineUpdateConfig", "ResidualCollector",
 ]

@@ -195,7 +195,8 @@ class ExactFactor:
         Kx = gram_scaled(self.kind, Xs_new, sq_new, m, Xs_all, sq_all, n2, self.sv)        # (128, n_pad)
         V = Kx.clone()
         V[:, n:] = 0.0
-        self.sumsq_inplace(V)                                                             # rows: v' = (L^{-1} k)'
+        call("gpmpc_trsm_right", ptr(self.L), self.n_pad, self.L.stride(0), ptr(self.Winv), ptr(V), 128, V.stride(0),
+             stream())                                                                    # rows: v' = (L^{-1} k)'
         VVt = torch.empty((128, 128), dtype=torch.float64, device=dev)
         call("gpmpc_dgemm_nt", ptr(V), V.stride(0), ptr(V), V.stride(0), ptr(VVt), 128, 128, 128, self.n_pad, 1.0, 0.0, 0,
              stream())

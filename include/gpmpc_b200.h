@@ -58,6 +58,11 @@ int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int batch, double*
 int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* B, int nrhs, int batch,
                 void* stream);
 
+/* V (q_pad x n_pad rows, ldv) <- (L^{-1} V')' in place, right-looking: the form for FEW rows (appending points to a
+ * factor); gpmpc_trsm_sumsq is the form for many query rows.  Same mathematics as solve_triangular at exact_gp.py:260. */
+int gpmpc_trsm_right(const double* L, int n_pad, long lda, const double* Winv, double* V, int q_pad, long ldv,
+                     void* stream);
+
 /* Winv[b] = (64x64 diagonal block b of the factored L)^{-1} for b in [block_first, block_last]: refreshes the cached
  * block inverses after rows were appended to a factor in place (incremental alternative to the full refit of
  * online_update.py:361-408 / sparse_gp.py:328-353, which re-factorise from scratch for every batch of new points). */

@@ -69,12 +69,64 @@ def query_fixture(X, U, nq, seed):
     return X[idx] + rng.normal(0, 0.05, (nq, 7)), U[idx] + rng.normal(0, 0.05, (nq, 3))
 
 
+def online_fixture(G, save):
+    """11. online data path (reference src/gp/online_update.py): DataBuffer ring semantics, and the accept / update
+    sequence of OnlineGPUpdater around a reference SparseGP with injected inducing points (no RNG dependence)."""
+    import src.gp.online_update as OU
+    rng = np.random.default_rng(21)
+    F = rng.normal(size=(40, 3)); F[7] = F[6] + 1e-3; F[20] = F[15] + 2e-2
+    T = rng.normal(size=(40, 2)); nov = rng.uniform(0, 1, 40)
+    buf = OU.DataBuffer(max_size=12, feature_dim=3, target_dim=2)
+    acc = np.array([buf.add_if_novel(F[i], T[i], float(nov[i]), threshold=0.3, min_distance=0.05) for i in range(40)])
+    st = buf.get_statistics()
+    rZ, rD = buf.get_recent(5)
+    out = dict(buf_F=F, buf_T=T, buf_nov=nov, buf_accepted=acc, buf_Z=buf.get_features(), buf_D=buf.get_targets(),
+               buf_recent_Z=rZ, buf_recent_D=rD,
+               buf_stats=np.array([st["size"], st["total_added"], st["total_rejected"], st["acceptance_rate"],
+                                   st["mean_novelty"]]))
+    n = 160
+    X = rng.normal(size=(n, 4)); U = rng.normal(size=(n, 2))
+    d = np.sin(X[:, 0]) + 0.3 * U[:, 1] + 0.05 * rng.normal(size=n)
+    ls = np.full(6, 3.0)
+    Zind = rng.normal(size=(20, 6))
+    gp = G.SparseGP(G.SquaredExponentialARD(6, 1.0, ls), n_inducing=20, noise_variance=1e-2, inducing_points=Zind.copy())
+    cfg = OU.OnlineUpdateConfig(buffer_size=60, min_data_for_fit=20, update_interval=10, novelty_threshold=0.05,
+                                min_distance=0.01)
+    up = OU.OnlineGPUpdater(gp, cfg)
+    accepted, novelty, updates = [], [], []
+    for i in range(n):
+        accepted.append(up.add_observation(X[i], U[i], d[i]))
+        if up.should_update():
+            r = up.update()
+            updates.append([i, r["n_data"], r["total_updates"], float(r["status"] == "success")])
+    Zb, Db = up._buffer.get_data()
+    Xq = rng.normal(size=(16, 6))
+    pred = gp.predict(Xq)
+    stt = up.get_statistics()
+    out.update(X=X, U=U, d=d, ls=ls, Zind=Zind, accepted=np.array(accepted), updates=np.array(updates), final_Z=Zb,
+               final_D=Db, Xq=Xq, pred_mean=pred.mean, pred_var=pred.variance,
+               stats=np.array([stt["total_updates"], stt["points_since_update"], stt["size"], stt["total_added"],
+                               stt["total_rejected"]]))
+    # ResidualCollector with an analytic nominal model
+    rc = OU.ResidualCollector(lambda x, u, dt: x + dt * np.concatenate([[0.0], x[4:7], u, 0.5 * x[7:14]]),
+                              max_samples=25)
+    Xs = rng.normal(size=(30, 14)); Us = rng.normal(size=(30, 3)); Xn = Xs + 0.1 * rng.normal(size=(30, 14))
+    for i in range(30):
+        rc.record(Xs[i], Us[i], Xn[i], 0.1)
+    a, b, c, e = rc.get_training_data()
+    out.update(rc_X=Xs, rc_U=Us, rc_Xn=Xn, rc_states=a, rc_controls=b, rc_dv=c, rc_dw=e)
+    save("online_update.npz", **out)
+
+
 def main():
     Stub = install_shim()
     import src.gp as G
     from src.gp.fast_gp import FastGPPredictor
     os.makedirs(OUT, exist_ok=True)
     save = lambda name, **kw: np.savez_compressed(os.path.join(OUT, name), **kw)
+    if "--only-online" in sys.argv:   # add the newest fixture without rewriting the others
+        online_fixture(G, save)
+        return
 
     # ---- 1. kernels ------------------------------------------------------------------
     rng = np.random.default_rng(10)
@@ -260,6 +312,7 @@ def main():
     states = rng.normal(0, 1, (200, 7)) * np.array([0.3, 1.0, 4, 4, 2, 1, 1]) + np.array([1.6, 0.3, 0, 0, -1, 0, 0])
     ok = np.array([lc.check_landing(s, 2.0)[0] for s in states])
     save("monte_carlo.npz", ics=ics, states=states, landing_ok=ok)
+    online_fixture(G, save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

@@ -271,3 +271,43 @@ def test_incremental_factor_append_equals_refit(eng, n0, adds):
     inc.kernel.set_params(inc.kernel.get_params() + 0.1)
     inc.update(X[:3] + 0.5, y[:3])
     assert inc.n_train == ntot + 3 and np.allclose(inc._model.f.ls_host, inc.kernel.lengthscales)
+
+
+def test_blocked_potrs_large_n_few_rhs(eng):
+    """gpmpc_potrs switches to the blocked multi-CTA substitution for n_pad >= 2048 with few right-hand sides (one launch
+    per 64-block, all SMs on the update): batch of two factors x three right-hand sides against numpy's cho_solve, and the
+    exact-GP alpha / LML at n = 2100 against the oracle (1e-8: cond(K) ~ n s2 / noise = 2e5; the backward error is 1e-13)."""
+    from oracle import gp as og
+    torch = eng.torch_()
+    rng = np.random.default_rng(2)
+    n, n_pad = 2100, 2176
+    Ls, Ws = [], []
+    A = torch.zeros((2, n_pad, n_pad), dtype=torch.float64, device="cuda")
+    Kh = []
+    for b in range(2):
+        X = rng.normal(size=(n, 5))
+        K = og.gram(0, X, None, np.full(5, 2.0 + b), 1.0) + 1e-2 * np.eye(n)
+        Kh.append(K)
+        A[b] = torch.eye(n_pad, dtype=torch.float64, device="cuda")
+        A[b, :n, :n] = eng.to_dev(K)
+    Winv, info = eng.potrf(A, batch=2)
+    assert int(info.abs().sum().item()) == 0
+    Bh = rng.normal(size=(2, 3, n))
+    B = torch.zeros((2, 3, n_pad), dtype=torch.float64, device="cuda")
+    B[:, :, :n] = eng.to_dev(Bh)
+    eng.call("gpmpc_potrs", eng.ptr(A), n_pad, n_pad, n_pad * n_pad, eng.ptr(Winv), eng.ptr(B), 3, 2, eng.stream())
+    Xs = B.cpu().numpy()
+    for b in range(2):
+        # backward error (the forward error scales with cond(K) ~ 1e5 for either solver): |K x - b| <= 1e-13 |K| |x|
+        res = np.abs(Kh[b] @ Xs[b, :, :n].T - Bh[b].T)
+        assert np.max(res / (np.abs(Kh[b]) @ np.abs(Xs[b, :, :n].T))) < 1e-13
+        assert relerr(Xs[b, :, :n], np.linalg.solve(Kh[b], Bh[b].T).T) < 1e-7
+        assert np.all(Xs[b, :, n:] == 0.0)
+    X = rng.normal(size=(n, 5))
+    Y = np.stack([np.sin(X[:, 0]), X[:, 1] * X[:, 2]], 1)
+    f = eng.ExactFactor(0, np.full(5, 2.0), 1.0, 1e-2).fit(X)
+    m = eng.ExactModelDev(f).fit_targets(Y)
+    for p in range(2):
+        ref = og.exact_fit(0, X, Y[:, p], np.full(5, 2.0), 1.0, 1e-2)
+        assert relerr(m.alpha[p, :n].cpu().numpy(), ref.alpha) < 1e-8
+        assert abs(m.lml[p].item() - ref.lml) < 1e-10 * abs(ref.lml)
