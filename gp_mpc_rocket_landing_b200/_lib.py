@@ -70,6 +70,7 @@ _PROTOS = {
     "gpmpc_potrf": (c_int, [c_dp, c_int, c_long, c_long, c_int, c_dp, c_dp, c_dp]),
     "gpmpc_potrs": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp]),
     "gpmpc_trsm_right": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp]),
+    "gpmpc_trsm_right_batched": (c_int, [c_dp, c_int, c_long, c_long, c_dp, c_dp, c_int, c_long, c_long, c_int, c_dp]),
     "gpmpc_trinv64_blocks": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_int, c_dp]),
     "gpmpc_normalize_targets": (c_int, [c_dp, c_int, c_int, c_long, c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_lml": (c_int, [c_dp, c_int, c_int, c_long, c_long, c_dp, c_dp, c_int, c_int, c_dp, c_dp]),

@@ -603,31 +603,38 @@ extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const d
 // with the cached inverse block and one rank-64 update of all columns to the right, which spreads over n/128 CTAs.  The
 // left-looking gpmpc_trsm_sumsq is built for many query rows (its k-loop grows with the solved part and its grid with
 // the rows: with 128 rows that is one long serial CTA per step -- 43 ms at n = 8000 against 2 ms here).
-extern "C" int gpmpc_trsm_right(const double* L, int n_pad, long lda, const double* Winv, double* V, int q_pad, long ldv,
-                                void* stream_) {
+extern "C" int gpmpc_trsm_right_batched(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* V,
+                                        int q_pad, long ldv, long strideV, int batch, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
-  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0 && q_pad > 0, "gpmpc_trsm_right: n_pad, q_pad must be multiples of 128");
+  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0 && q_pad > 0 && batch >= 1,
+                "gpmpc_trsm_right: n_pad, q_pad must be multiples of 128");
   GPMPC_REQUIRE((lda & 1) == 0 && (ldv & 1) == 0 && ldv >= n_pad, "gpmpc_trsm_right: leading dimensions must be even");
+  const long strideW = (long)(n_pad / 64) * 4096;
   for (int j0 = 0; j0 < n_pad; j0 += 64) {
     GemmParams a{};                                   // V[:, j0:j0+64] <- V[:, j0:j0+64] W_j'   (in place: K = N = 64)
-    a.A = V + j0; a.lda = ldv;
-    a.B = Winv + (long)(j0 / 64) * 4096; a.ldb = 64;
-    a.C = V + j0; a.ldc = ldv;
+    a.A = V + j0; a.lda = ldv; a.strideA = strideV;
+    a.B = Winv + (long)(j0 / 64) * 4096; a.ldb = 64; a.strideB = strideW;
+    a.C = V + j0; a.ldc = ldv; a.strideC = strideV;
     a.M = q_pad; a.N = 64; a.K = 64; a.alpha = 1.0; a.beta = 0.0; a.epi = EPI_STORE;
-    int rc = launch_dgemm_nt<128, 64, 4, 2>(a, 1, stream);
+    int rc = launch_dgemm_nt<128, 64, 4, 2>(a, batch, stream);
     if (rc) return rc;
     if (j0 + 64 >= n_pad) break;
     const int o = ((j0 + 64) / 128) * 128;            // 128-aligned origin; columns below j0 + 64 are masked
     GemmParams u{};                                   // V[:, j0+64:] -= V[:, j0:j0+64] L[j0+64:, j0:j0+64]'
-    u.A = V + j0; u.lda = ldv;
-    u.B = L + (long)o * lda + j0; u.ldb = lda;
-    u.C = V + o; u.ldc = ldv;
+    u.A = V + j0; u.lda = ldv; u.strideA = strideV;
+    u.B = L + (long)o * lda + j0; u.ldb = lda; u.strideB = strideL;
+    u.C = V + o; u.ldc = ldv; u.strideC = strideV;
     u.M = q_pad; u.N = n_pad - o; u.K = 64; u.alpha = -1.0; u.beta = 1.0; u.epi = EPI_STORE;
     u.col_min = j0 + 64 - o;
-    rc = launch_dgemm_nt<128, 128, 2, 4>(u, 1, stream);
+    rc = launch_dgemm_nt<128, 128, 2, 4>(u, batch, stream);
     if (rc) return rc;
   }
   return GPMPC_OK;
+}
+
+extern "C" int gpmpc_trsm_right(const double* L, int n_pad, long lda, const double* Winv, double* V, int q_pad, long ldv,
+                                void* stream_) {
+  return gpmpc_trsm_right_batched(L, n_pad, lda, 0, Winv, V, q_pad, ldv, 0, 1, stream_);
 }
 
 // ------------------------------------------------------------------------------------------------ small-M TRSM

@@ -571,11 +571,11 @@ class ExactSweep:
             if not ok:
                 jitter[g] = np.nan
         # y' K^-1 y = |L^-1 y|^2: forward solve only, all candidates in one batched DMMA TRSM with the P targets as rows
+        # (right-looking: few rows, so the parallelism has to come from the columns still to be updated)
         V = torch.zeros((G, 128, npad), dtype=torch.float64, device=dev)
         V[:, : self.P] = self.Yn[None]
-        ss = torch.empty((G, 128), dtype=torch.float64, device=dev)
-        call("gpmpc_trsm_sumsq_batched", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(V), 128, npad, 128 * npad, ptr(ss),
-             G, stream())
+        call("gpmpc_trsm_right_batched", ptr(L), npad, npad, npad * npad, ptr(Winv), ptr(V), 128, npad, 128 * npad, G,
+             stream())
         Vp = V[:, : self.P].contiguous()
         lml = torch.empty((G, self.P), dtype=torch.float64, device=dev)
         call("gpmpc_lml", ptr(L), self.n, npad, npad, npad * npad, ptr(Vp), ptr(Vp), self.P, G, ptr(lml), stream())

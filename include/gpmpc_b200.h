@@ -62,6 +62,8 @@ int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, const double
  * factor); gpmpc_trsm_sumsq is the form for many query rows.  Same mathematics as solve_triangular at exact_gp.py:260. */
 int gpmpc_trsm_right(const double* L, int n_pad, long lda, const double* Winv, double* V, int q_pad, long ldv,
                      void* stream);
+int gpmpc_trsm_right_batched(const double* L, int n_pad, long lda, long strideL, const double* Winv, double* V, int q_pad,
+                             long ldv, long strideV, int batch, void* stream);
 
 /* Winv[b] = (64x64 diagonal block b of the factored L)^{-1} for b in [block_first, block_last]: refreshes the cached
  * block inverses after rows were appended to a factor in place (incremental alternative to the full refit of
