@@ -78,6 +78,8 @@ _PROTOS = {
     "gpmpc_lml_grad_se": (c_int, [c_dp, c_int, c_int, c_int, c_int, c_double, c_double, c_dp, c_long, c_dp, c_long, c_int,
                                   c_dp, c_dp, c_dp]),
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_ut_sigma_3dof": (c_int, [c_int, c_double, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_ut_combine_3dof": (c_int, [c_int, c_int, c_double, c_double, c_double, c_dp, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_propagate_cov": (c_int, [c_int, c_int, c_int, c_dp, c_long, c_long, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_step_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linearize_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),

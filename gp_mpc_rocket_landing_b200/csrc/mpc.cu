@@ -413,6 +413,123 @@ __global__ void __launch_bounds__(128) propagate_cov3_kernel(GpmpcDyn3 dyn, int 
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------ unscented transform
+// uncertainty_prop.py:179-264 for the 7-state model.  The reference class carries 14 states: n = 14 fixes lambda and the
+// weights, and of its 29 sigma points the 14 that perturb only the 7 inert states propagate exactly like the centre
+// (their block of Sigma never couples with the first 7).  Per stage: ut_sigma3_kernel (7x7 Cholesky of
+// (n + lambda) Sigma + 1e-10 I, 15 distinct points), the N = 1 rollout kernel images them (step + GP mean, and the
+// cross-covariance row of the centre for the variance), ut_combine3_kernel recombines in the reference's term order.
+__global__ void __launch_bounds__(128) ut_sigma3_kernel(int nbatch, double scale, const double* __restrict__ xk,
+                                                        const double* __restrict__ Sk, const double* __restrict__ U,
+                                                        long ldu, double* __restrict__ SP, double* __restrict__ Usp,
+                                                        int* __restrict__ info) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  double L[NX][NX], x[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {
+    x[i] = xk[(long)b * NX + i];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) L[i][j] = scale * Sk[((long)b * NX + i) * NX + j] + ((i == j) ? 1e-10 : 0.0);
+  }
+#pragma unroll
+  for (int j = 0; j < NX; ++j) {
+    double d = L[j][j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= L[j][k] * L[j][k];
+    if (!(d > 0.0)) {
+      if (info[0] == 0) info[0] = b + 1;   // np.linalg.cholesky raises LinAlgError; the host checks this flag
+      d = 1.0;
+    }
+    const double dj = sqrt(d);
+    L[j][j] = dj;
+#pragma unroll
+    for (int i = j + 1; i < NX; ++i) {
+      double v = L[i][j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) v -= L[i][k] * L[j][k];
+      L[i][j] = v / dj;
+    }
+#pragma unroll
+    for (int i = 0; i < j; ++i) L[i][j] = 0.0;
+  }
+  double* sp = SP + (long)b * 15 * NX;
+  double* us = Usp + (long)b * 15 * NU;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) sp[i] = x[i];
+#pragma unroll
+  for (int c = 0; c < NX; ++c) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      sp[(1 + c) * NX + i] = x[i] + L[i][c];
+      sp[(1 + NX + c) * NX + i] = x[i] - L[i][c];
+    }
+  }
+  const double u0 = U[(long)b * ldu], u1 = U[(long)b * ldu + 1], u2 = U[(long)b * ldu + 2];
+  for (int s = 0; s < 15; ++s) {
+    us[s * NU] = u0; us[s * NU + 1] = u1; us[s * NU + 2] = u2;
+  }
+}
+
+// Xn: images of the sigma points, (nbatch * 15) x 2 x 7 (the N = 1 rollout layout: row 1 of each pair).
+__global__ void __launch_bounds__(128) ut_combine3_kernel(int nbatch, int n_inert, double wm0, double wc0, double wi,
+                                                          const double* __restrict__ Xn, const double* __restrict__ var,
+                                                          double dt, double* __restrict__ xnext,
+                                                          double* __restrict__ Snext) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  const double* base = Xn + (long)b * 15 * 2 * NX + NX;   // image of point s at base + s * 2 * NX
+  double c[NX], xn[NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {
+    c[i] = base[i];
+    xn[i] = wm0 * c[i];
+  }
+  // rows 0..28 of the reference's sigma-point array: centre, +real (7), +inert, -real (7), -inert
+  for (int s = 1; s <= NX; ++s)
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xn[i] = xn[i] + wi * base[(long)s * 2 * NX + i];
+  for (int s = 0; s < n_inert; ++s)
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xn[i] = xn[i] + wi * c[i];
+  for (int s = NX + 1; s <= 2 * NX; ++s)
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xn[i] = xn[i] + wi * base[(long)s * 2 * NX + i];
+  for (int s = 0; s < n_inert; ++s)
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xn[i] = xn[i] + wi * c[i];
+  double S[NX][NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i)
+#pragma unroll
+    for (int j = 0; j < NX; ++j) S[i][j] = 0.0;
+  auto add = [&](const double* q, double w) {
+    double df[NX];
+#pragma unroll
+    for (int i = 0; i < NX; ++i) df[i] = q[i] - xn[i];
+#pragma unroll
+    for (int i = 0; i < NX; ++i)
+#pragma unroll
+      for (int j = 0; j < NX; ++j) S[i][j] = S[i][j] + w * (df[i] * df[j]);
+  };
+  add(c, wc0);
+  for (int s = 1; s <= NX; ++s) add(base + (long)s * 2 * NX, wi);
+  for (int s = 0; s < n_inert; ++s) add(c, wi);
+  for (int s = NX + 1; s <= 2 * NX; ++s) add(base + (long)s * 2 * NX, wi);
+  for (int s = 0; s < n_inert; ++s) add(c, wi);
+  if (var) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) S[4 + i][4 + i] += var[(long)b * 3 + i] * (dt * dt);
+  }
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {
+    xnext[(long)b * NX + i] = xn[i];
+#pragma unroll
+    for (int j = 0; j < NX; ++j) Snext[((long)b * NX + i) * NX + j] = S[i][j];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ QP assembly
 // One thread per (scenario, stage); stage N writes the initial-state rows and the terminal cost vector.
 __global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nbatch, int N, int lin_mode, int rhs_mode,
@@ -715,6 +832,23 @@ extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double*
   GPMPC_PREFER_SHARED(pack_traj3_kernel);
   pack_traj3_kernel<<<(int)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, N, X, U, z, active);
   return gpmpc_check_launch("pack_traj_3dof");
+}
+
+extern "C" int gpmpc_ut_sigma_3dof(int B, double scale, const double* xk, const double* Sk, const double* U, long ldu,
+                                   double* SP, double* Usp, int* info, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && xk && Sk && U && SP && Usp && info, "gpmpc_ut_sigma_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  ut_sigma3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(B, scale, xk, Sk, U, ldu, SP, Usp, info);
+  return gpmpc_check_launch("ut_sigma_3dof");
+}
+
+extern "C" int gpmpc_ut_combine_3dof(int B, int n_inert, double wm0, double wc0, double wi, const double* Xn,
+                                     const double* var, double dt, double* xnext, double* Snext, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && n_inert >= 0 && Xn && xnext && Snext, "gpmpc_ut_combine_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  ut_combine3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(B, n_inert, wm0, wc0, wi, Xn, var, dt, xnext,
+                                                                        Snext);
+  return gpmpc_check_launch("ut_combine_3dof");
 }
 
 extern "C" int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U,

@@ -1,8 +1,10 @@
 """Horizon uncertainty propagation with the reference's API (src/mpc/uncertainty_prop.py:34-177), 7-state model.
 
 `propagate` = GP-augmented mean rollout + GP variance (blocked DMMA TRSM) + Sigma_{k+1} = A Sigma A' + Q_gp, all on
-the device (`gpmpc_rollout_3dof`, `gpmpc_trsm_sumsq`, `gpmpc_propagate_cov_3dof`).  Only the "linear" method is on
-the hot path; "unscented" / "monte_carlo" (uncertainty_prop.py:179-319) are SURVEY 8(f) "next" rows and raise.
+the device (`gpmpc_rollout_3dof`, `gpmpc_trsm_sumsq`, `gpmpc_propagate_cov_3dof`).  "unscented"
+(uncertainty_prop.py:179-264) runs stage by stage: sigma points, their images through the N = 1 rollout kernel (step +
+GP mean), the GP variance at the centre, recombination (`gpmpc_ut_sigma_3dof`, `gpmpc_ut_combine_3dof`).
+"monte_carlo" (:266-319, global-RNG particles) is not built and raises.
 """
 from __future__ import annotations
 
@@ -52,8 +54,10 @@ class UncertaintyPropagator:
     def propagate_batch(self, X0, U, Sigma_0: Optional[float] = None, dt: float = 0.1):
         """X0 (B,7), U (B,N,3) -> means (B,N+1,7), covs (B,N+1,7,7), dmean (B,N,3), dvar (B,N,3) as CUDA tensors.
         Sigma_0: scalar s for Sigma_0 = s*I (default 1e-6, uncertainty_prop.py:133-134)."""
+        if self.method == "unscented":
+            return self._propagate_unscented_batch(X0, U, Sigma_0, dt)
         if self.method != "linear":
-            raise _lib.GpmpcError(f"propagation method {self.method!r} is not on the device hot path (linear only)")
+            raise _lib.GpmpcError(f"propagation method {self.method!r} is not built (linear and unscented only)")
         torch = ge.torch_()
         x0, Ud = ge.to_dev(X0), ge.to_dev(U)
         B, N = Ud.shape[0], Ud.shape[1]
@@ -78,6 +82,70 @@ class UncertaintyPropagator:
                 ge.stream())
         me.propagate_cov(dyn, X, Ud, dvar, covs, sigma0=s0)
         return X, covs, dmean, dvar[: B * N].reshape(B, N, 3)
+
+    N_REFERENCE_STATES = 14   # uncertainty_prop.py:86: the reference class is written for 14 states; this fixes lambda
+
+    def _propagate_unscented_batch(self, X0, U, Sigma_0, dt):
+        """uncertainty_prop.py:179-264 for B scenarios at once; same return as the linear method."""
+        torch = ge.torch_()
+        x0, Ud = ge.to_dev(X0), ge.to_dev(U)
+        B, N = Ud.shape[0], Ud.shape[1]
+        model = self.gp.device_model() if self.gp is not None else None
+        dyn = self._dyn(dt)
+        f64 = dict(dtype=torch.float64, device=x0.device)
+        n = self.N_REFERENCE_STATES
+        a, beta, kappa = 1e-3, 2, 0
+        lam = a**2 * (n + kappa) - n
+        wm0 = lam / (n + lam)
+        wc0 = lam / (n + lam) + (1 - a**2 + beta)
+        wi = 1 / (2 * (n + lam))
+        s0 = 1e-6 if Sigma_0 is None else float(Sigma_0)
+        means = torch.zeros((B, N + 1, 7), **f64)
+        covs = torch.zeros((B, N + 1, 7, 7), **f64)
+        dmean = torch.zeros((B, N, 3), **f64)
+        dvar = torch.zeros((B, N, 3), **f64)
+        means[:, 0] = x0
+        covs[:, 0] = torch.eye(7, **f64) * s0
+        SP = torch.empty((B * 15, 7), **f64)
+        Usp = torch.empty((B * 15, 1, 3), **f64)
+        Xn = torch.empty((B * 15, 2, 7), **f64)
+        dm = torch.zeros((B * 15, 1, 3), **f64)
+        info = torch.zeros((1,), dtype=torch.int32, device=x0.device)
+        xk, Sk = x0.clone(), covs[:, 0].clone()
+        xn, Sn = torch.empty_like(xk), torch.empty_like(Sk)
+        if model is not None:
+            f = model.f
+            Ks = torch.zeros((ge.pad_to(B * 15, 128), f.n_pad), **f64)
+            Kc = torch.zeros((ge.pad_to(B, 128), f.n_pad), **f64)
+            var = torch.zeros((Kc.shape[0], 3), **f64)
+            ms = model.struct()
+        for k in range(N):
+            Uk = Ud[:, k].contiguous()
+            ge.call("gpmpc_ut_sigma_3dof", B, n + lam, ge.ptr(xk), ge.ptr(Sk), ge.ptr(Uk), Uk.stride(0), ge.ptr(SP),
+                    ge.ptr(Usp), ge.ptr(info), ge.stream())
+            if model is None:
+                me.rollout(None, dyn, SP, Usp, Xn)
+                vk = None
+            else:
+                me.rollout(ms, dyn, SP, Usp, Xn, dm, Ks)
+                Kc[:B] = Ks[0:B * 15:15]                     # cross-covariance rows of the centre points
+                sumsq = f.sumsq_inplace(Kc)
+                ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, B, 3, f.sv, 1e-10, ge.ptr(model.ystd), ge.ptr(var), 3, 0,
+                        ge.stream())
+                vk = var
+                dmean[:, k] = dm[0:B * 15:15, 0]
+                dvar[:, k] = var[:B]
+            ge.call("gpmpc_ut_combine_3dof", B, n - 7, wm0, wc0, wi, ge.ptr(Xn), ge.ptr(vk), float(dt), ge.ptr(xn),
+                    ge.ptr(Sn), ge.stream())
+            means[:, k + 1] = xn
+            covs[:, k + 1] = Sn
+            xk, xn = xn, xk
+            Sk, Sn = Sn, Sk
+        bad = int(info.item())
+        if bad:
+            raise np.linalg.LinAlgError(f"unscented propagation: (n + lambda) Sigma + 1e-10 I of scenario {bad - 1} is not "
+                                        "positive definite")
+        return means, covs, dmean, dvar
 
     def propagate(self, x0, U, Sigma_0=None, dt: float = 0.1) -> PropagatedUncertainty:
         s0 = None

@@ -240,6 +240,17 @@ int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_ste
 /* z = [x_0,u_0,...,x_N] from (X, U): OSQPRTIMPC._solution_to_vector, osqp_rti.py:601-614 (primal warm start). */
 int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active, void* stream);
 
+/* Unscented propagation (uncertainty_prop.py:179-264), 7-state model, one stage at a time:
+ * gpmpc_ut_sigma_3dof: SP[b] (15 x 7) = x_k, x_k + columns, x_k - columns of chol(scale * Sigma_k + 1e-10 I), and the stage
+ * control repeated 15 times in Usp (the layout gpmpc_rollout_3dof takes with N = 1); info[0] = b + 1 of a scenario whose
+ * matrix is not positive definite (np.linalg.cholesky raises).  gpmpc_ut_combine_3dof: x_{k+1} = sum w_m image_i,
+ * Sigma_{k+1} = sum w_c (image_i - x_{k+1})(...)' + dt^2 diag(var) in rows 4:7, from the rollout's images Xn
+ * ((B*15) x 2 x 7); n_inert = the reference's extra states (14 - 7), whose sigma points coincide with the centre. */
+int gpmpc_ut_sigma_3dof(int B, double scale, const double* xk, const double* Sk, const double* U, long ldu, double* SP,
+                        double* Usp, int* info, void* stream);
+int gpmpc_ut_combine_3dof(int B, int n_inert, double wm0, double wc0, double wi, const double* Xn, const double* var,
+                          double dt, double* xnext, double* Snext, void* stream);
+
 /* Linear covariance propagation (uncertainty_prop.py:117-177, 7-state): Sigma_{k+1} = A_k Sigma_k A_k' + diag(var)dt^2
  * on the velocity block, A_k = analytic discrete Jacobian at (X[b,k],U[b,k]).  covs: B x (N+1) x 7 x 7. */
 int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U, const double* dvar,

@@ -118,6 +118,33 @@ def online_fixture(G, save):
     save("online_update.npz", **out)
 
 
+def unscented_fixture(G, save):
+    """12. UncertaintyPropagator(method="unscented") (uncertainty_prop.py:179-264) on the 14-state embedding of the 7-state
+    model, same GP / controls as propagation.npz."""
+    import src.mpc.uncertainty_prop as UP
+    from oracle.mpc import Rocket3DoFParams, step_3dof
+    X, U, Dres = gp_fixture(300, 11)
+    gp = G.Simple3DoFGP(use_sparse=False, noise_variance=1e-3); gp.add_data(X, U, Dres); gp.fit()
+    p = Rocket3DoFParams()
+
+    class Dyn14:
+        params = p
+
+        def step(self, x, u, dt):
+            xn = x.copy(); xn[:7] = step_3dof(x[:7], u, dt, p); return xn
+
+    class GP14:
+        def predict(self, x, u):
+            m, v = gp.predict(x[:7], u); return m, np.zeros(3), v, np.zeros(3)
+
+    x0_14 = np.zeros(14); x0_14[:7] = [1.9, 25, 1, -2, -3.2, 0.3, -0.1]; x0_14[7] = 1.0
+    rng = np.random.default_rng(12)
+    Useq = np.stack([rng.uniform(1.5, 2.5, 20), rng.uniform(-.3, .3, 20), rng.uniform(-.3, .3, 20)], 1)
+    pu = UP.UncertaintyPropagator(Dyn14(), GP14(), method="unscented").propagate(x0_14, Useq, np.eye(14) * 1e-6, dt=0.1)
+    save("propagation_unscented.npz", X=X, U=U, D=Dres, noise=1e-3, x0=x0_14[:7], Useq=Useq, means=pu.means[:, :7],
+         covs=pu.covariances[:, :7, :7], means_inert=pu.means[:, 7:], cov_cross_max=np.abs(pu.covariances[:, :7, 7:]).max())
+
+
 def main():
     Stub = install_shim()
     import src.gp as G
@@ -126,6 +153,9 @@ def main():
     save = lambda name, **kw: np.savez_compressed(os.path.join(OUT, name), **kw)
     if "--only-online" in sys.argv:   # add the newest fixture without rewriting the others
         online_fixture(G, save)
+        return
+    if "--only-unscented" in sys.argv:
+        unscented_fixture(G, save)
         return
 
     # ---- 1. kernels ------------------------------------------------------------------
@@ -313,6 +343,7 @@ def main():
     ok = np.array([lc.check_landing(s, 2.0)[0] for s in states])
     save("monte_carlo.npz", ics=ics, states=states, landing_ok=ok)
     online_fixture(G, save)
+    unscented_fixture(G, save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

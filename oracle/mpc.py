@@ -500,6 +500,53 @@ def propagate_linear(x0, U, Sigma0, dt, p, gp_predict):
     return means, covs, dm, dv
 
 
+def propagate_unscented(x0, U, Sigma0, dt, p, gp_predict, n_aug=14):
+    """uncertainty_prop.py:179-264 restricted to the 7 states of the 3-DoF model.  The reference class carries 14 states
+    (n = 14 fixes lambda and the weights; 29 sigma points); for the 3-DoF embedding the 7 extra states are inert, their
+    block of Sigma never couples with the first 7, and the 14 sigma points that perturb only them propagate exactly like
+    the centre point.  So: 7-state Cholesky, 15 distinct points, the centre counted 1 + 14 times, terms added in the
+    reference's order (rows 0..28 of its sigma-point array: centre, +real, +inert, -real, -inert).
+    alpha = 1e-3 makes w_m[0] ~ -1e6: rounding in the sigma-point images is amplified by 1e6 in the mean."""
+    N = len(U)
+    n = n_aug
+    ni = n_aug - NX
+    if Sigma0 is None:
+        Sigma0 = np.eye(NX) * 1e-6
+    alpha, beta, kappa = 1e-3, 2, 0
+    lam = alpha**2 * (n + kappa) - n
+    wm0 = lam / (n + lam)
+    wc0 = lam / (n + lam) + (1 - alpha**2 + beta)
+    wi = 1 / (2 * (n + lam))
+    means = np.zeros((N + 1, NX)); covs = np.zeros((N + 1, NX, NX))
+    means[0] = x0; covs[0] = Sigma0
+    xk, Sk = np.array(x0, float), Sigma0.copy()
+
+    def image(x, u):
+        xn = step_3dof(x, u, dt, p)
+        d, _ = gp_predict(x, u)
+        xn[4:7] += d * dt
+        return xn
+
+    for k in range(N):
+        Ls = np.linalg.cholesky((n + lam) * Sk + 1e-10 * np.eye(NX))
+        c = image(xk, U[k])
+        plus = [image(xk + Ls[:, i], U[k]) for i in range(NX)]
+        minus = [image(xk - Ls[:, i], U[k]) for i in range(NX)]
+        pts = [c] + plus + [c] * ni + minus + [c] * ni
+        xn = wm0 * pts[0]
+        for q in pts[1:]:
+            xn = xn + wi * q
+        Sn = np.zeros((NX, NX))
+        for i, q in enumerate(pts):
+            df = q - xn
+            Sn = Sn + (wc0 if i == 0 else wi) * np.outer(df, df)
+        _, var = gp_predict(xk, U[k])
+        Sn[4:7, 4:7] += np.diag(var) * dt**2
+        means[k + 1] = xn; covs[k + 1] = Sn
+        xk, Sk = xn, Sn
+    return means, covs
+
+
 # --------------------------------------------------------------------------- GP-MPC (composed 3-DoF path)
 @dataclass
 class MPCSolutionOracle:

@@ -311,3 +311,43 @@ def test_mpc_update_semantics(E):
     me.mpc_update(qp, 0, t(z), t(status, torch.int32), t(x_ref), Xd2, t(U), Xp2, t(U), cost, conv, None, None)
     assert conv.cpu().tolist() == [1, 1, 1, 0]
     np.testing.assert_array_equal(Xd2[3].cpu().numpy(), X[3]); np.testing.assert_array_equal(Xp2[3].cpu().numpy(), 2 * X[3])
+
+
+def test_unscented_propagation_matches_reference(E):
+    """UncertaintyPropagator(method="unscented") (uncertainty_prop.py:179-264) on the device against the golden output of
+    the reference class and the oracle.  alpha = 1e-3 gives w_m[0] ~ -1e6: last-bit differences of the GP means (1e-13
+    relative, different summation order of K* alpha) are amplified to ~1e-7 in the mean and ~1e-7 relative in Sigma, hence
+    the tolerances 2e-6 absolute / 1e-5 relative."""
+    from oracle import gp as ogp, mpc as ompc
+    from gp_mpc_rocket_landing_b200.dynamics import Rocket3DoFDynamics
+    from gp_mpc_rocket_landing_b200.gp import Simple3DoFGP
+    from gp_mpc_rocket_landing_b200.mpc.uncertainty_prop import UncertaintyPropagator
+    g = load_golden("propagation_unscented.npz")
+    gp = Simple3DoFGP(noise_variance=float(g["noise"]), use_sparse=False)
+    gp.add_data(g["X"], g["U"], g["D"]); gp.fit()
+    up = UncertaintyPropagator(Rocket3DoFDynamics(), gp, method="unscented")
+    r = up.propagate(g["x0"], g["Useq"], np.eye(7) * 1e-6, dt=0.1)
+    np.testing.assert_allclose(r.means, g["means"], rtol=0, atol=2e-6)
+    np.testing.assert_allclose(r.covariances, g["covs"], rtol=1e-5, atol=1e-5 * np.abs(g["covs"]).max())
+    # batch: perturbed initial states / controls against the oracle, scenario by scenario
+    rng = np.random.default_rng(4)
+    B, N = 5, g["Useq"].shape[0]
+    x0 = np.tile(g["x0"], (B, 1)); U = np.tile(g["Useq"], (B, 1, 1))
+    x0[1:] += 0.05 * rng.normal(size=(B - 1, 7)); U[1:] += 0.05 * rng.normal(size=(B - 1, N, 3))
+    means, covs, dmean, dvar = up.propagate_batch(x0, U, None, 0.1)
+    means, covs = means.cpu().numpy(), covs.cpu().numpy()
+    np.testing.assert_allclose(means[0], r.means, rtol=0, atol=0)
+    o = ogp.Simple3DoFGPOracle(noise_variance=float(g["noise"]))
+    o.add_data(g["X"], g["U"], g["D"]); o.fit()
+    for b in (1, 4):
+        mo, co = ompc.propagate_unscented(x0[b], U[b], np.eye(7) * 1e-6, 0.1, ompc.Rocket3DoFParams(), o.predict)
+        np.testing.assert_allclose(means[b], mo, rtol=0, atol=2e-6)
+        np.testing.assert_allclose(covs[b], co, rtol=1e-5, atol=1e-5 * np.abs(co).max())
+    # no GP: the transform of the nominal model alone
+    r0 = UncertaintyPropagator(Rocket3DoFDynamics(), None, method="unscented").propagate(g["x0"], g["Useq"], None, dt=0.1)
+    mo, co = ompc.propagate_unscented(g["x0"], g["Useq"], None, 0.1, ompc.Rocket3DoFParams(),
+                                      lambda x, u: (np.zeros(3), np.zeros(3)))
+    np.testing.assert_allclose(r0.means, mo, rtol=0, atol=1e-9)
+    np.testing.assert_allclose(r0.covariances, co, rtol=1e-7, atol=1e-16)
+    with pytest.raises(Exception):
+        UncertaintyPropagator(Rocket3DoFDynamics(), gp, method="monte_carlo").propagate(g["x0"], g["Useq"])

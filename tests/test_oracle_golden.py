@@ -146,6 +146,18 @@ def test_propagation_matches_reference():
     np.testing.assert_allclose(covs, g["covs"], rtol=1e-9, atol=1e-18)
 
 
+def test_unscented_propagation_matches_reference():
+    """uncertainty_prop.py:179-264 through the reference's own class (14-state embedding) against the 7-state
+    restatement: identical term order, so the match is to the last bit although w_m[0] ~ -1e6."""
+    g = load_golden("propagation_unscented.npz")
+    o = ogp.Simple3DoFGPOracle(noise_variance=float(g["noise"]))
+    o.add_data(g["X"], g["U"], g["D"]); o.fit()
+    means, covs = ompc.propagate_unscented(g["x0"], g["Useq"], np.eye(7) * 1e-6, 0.1, ompc.Rocket3DoFParams(), o.predict)
+    np.testing.assert_allclose(means, g["means"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(covs, g["covs"], rtol=1e-7, atol=1e-16)
+    assert float(g["cov_cross_max"]) < 1e-12     # the inert block of the 14-state class never couples with the first 7
+
+
 def test_monte_carlo_sampling_and_landing():
     g = load_golden("monte_carlo.npz")
     cfg = ompc.SimConfig()
