@@ -6,10 +6,11 @@ from .gp_mpc import GPMPC, GPMPCConfig
 from .gp_mpc6 import GPMPC6DoF, GPMPC6DoFConfig
 from .nominal_mpc import BatchMPCSolution, MPCConfig, MPCSolution, NominalMPC3DoF
 from .osqp_rti import BatchRTISolution, FastRTI3DoF, OSQPRTIConfig, OSQPRTIMPC, OSQPRTISolution
-from .uncertainty_prop import PropagatedUncertainty, UncertaintyPropagator
+from .uncertainty_prop import (ConstraintTightening, PropagatedUncertainty, TubeBasedRobustness,
+                               UncertaintyPropagator)
 
 __all__ = [
     "ConstraintParams", "TightenedConstraints", "CostWeights", "GPMPC", "GPMPCConfig", "GPMPC6DoF", "GPMPC6DoFConfig", "BatchMPCSolution", "MPCConfig",
     "MPCSolution", "NominalMPC3DoF", "BatchRTISolution", "FastRTI3DoF", "OSQPRTIConfig", "OSQPRTIMPC",
-    "OSQPRTISolution", "PropagatedUncertainty", "UncertaintyPropagator",
+    "OSQPRTISolution", "PropagatedUncertainty", "UncertaintyPropagator", "ConstraintTightening", "TubeBasedRobustness",
 ]

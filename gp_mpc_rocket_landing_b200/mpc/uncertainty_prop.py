@@ -157,3 +157,66 @@ class UncertaintyPropagator:
         X, covs, _, _ = self.propagate_batch(np.asarray(x0, dtype=np.float64)[None], np.asarray(U, dtype=np.float64)[None],
                                              s0, dt)
         return PropagatedUncertainty(means=X[0].cpu().numpy(), covariances=covs[0].cpu().numpy())
+
+
+class ConstraintTightening:
+    """uncertainty_prop.py:322-416: Gaussian chance-constraint back-offs kappa * sqrt(g' Sigma g), kappa = Phi^{-1}(p)."""
+
+    def __init__(self, confidence: float = 0.95):
+        from scipy.stats import norm
+        self.confidence = confidence
+        self.kappa = norm.ppf(confidence)
+
+    def tighten_linear_constraint(self, a, b: float, mu, Sigma) -> float:  # noqa: ARG002 (mu unused, as in the reference)
+        a = np.asarray(a, dtype=np.float64)
+        return b + self.kappa * np.sqrt(a @ np.asarray(Sigma) @ a)
+
+    def tighten_quadratic_constraint(self, x_mu, x_Sigma, constraint_func, n_samples: int = 100) -> float:
+        """Sampling estimate from the global numpy RNG (uncertainty_prop.py:367-387)."""
+        samples = np.random.multivariate_normal(x_mu, x_Sigma, n_samples)
+        g = np.array([constraint_func(s) for s in samples])
+        return np.percentile(g, (1 - self.confidence) * 100)
+
+    def compute_back_offs(self, uncertainty: PropagatedUncertainty, constraint_gradients) -> np.ndarray:
+        N = len(uncertainty.means) - 1
+        nc = len(constraint_gradients[0]) if constraint_gradients else 0
+        out = np.zeros((N, nc))
+        for k in range(min(N, len(constraint_gradients))):
+            S = np.asarray(uncertainty.covariances[k])
+            for j, g in enumerate(constraint_gradients[k]):
+                g = np.asarray(g, dtype=np.float64)
+                out[k, j] = self.kappa * np.sqrt(g @ S @ g)
+        return out
+
+    def compute_back_offs_batch(self, covs, gradients):
+        """All scenarios and stages at once: covs (B, N+1, n, n) as returned by `propagate_batch` (CUDA tensor or numpy),
+        gradients (J, n) shared by all stages -> (B, N, J) back-offs kappa * sqrt(g_j' Sigma_{b,k} g_j)."""
+        if hasattr(covs, "is_cuda"):
+            torch = ge.torch_()
+            G = ge.to_dev(np.asarray(gradients, dtype=np.float64))
+            q = torch.einsum("ji,bkil,jl->bkj", G, covs[:, :-1], G)
+            return self.kappa * q.clamp_min(0.0).sqrt()
+        G = np.asarray(gradients, dtype=np.float64)
+        q = np.einsum("ji,bkil,jl->bkj", G, np.asarray(covs)[:, :-1], G)
+        return self.kappa * np.sqrt(np.maximum(q, 0.0))
+
+
+class TubeBasedRobustness:
+    """uncertainty_prop.py:419-470: w_{k+1} = |A_k| w_k + d_max dt in the velocity (and, for 14 states, body-rate) rows."""
+
+    def __init__(self, dynamics, d_max: float = 0.1):
+        self.dynamics = dynamics
+        self.d_max = d_max
+
+    def compute_tube(self, X_nom, U_nom, dt: float) -> np.ndarray:
+        X_nom, U_nom = np.asarray(X_nom, dtype=np.float64), np.asarray(U_nom, dtype=np.float64)
+        N, n_x = len(U_nom), X_nom.shape[1]
+        widths = np.zeros((N + 1, n_x))
+        w = np.zeros(n_x)
+        for k in range(N):
+            A_d, _ = self.dynamics.linearize(X_nom[k], U_nom[k], dt=dt)
+            w = np.abs(np.asarray(A_d)) @ w
+            w[4:7] += self.d_max * dt
+            w[11:14] += self.d_max * dt     # empty slice for the 7-state model
+            widths[k + 1] = w
+        return widths

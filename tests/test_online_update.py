@@ -141,3 +141,40 @@ def test_online_updater_sequence_matches_reference():
     pe, pf = ex.predict(g["Xq"]), fresh.predict(g["Xq"])
     assert relerr(pe.mean, pf.mean) < 1e-10 and relerr(pe.variance, pf.variance) < 1e-9
     assert abs(ex.log_marginal_likelihood - fresh.log_marginal_likelihood) < 1e-9 * abs(fresh.log_marginal_likelihood)
+
+
+def test_constraint_tightening_and_tube_host_classes():
+    """uncertainty_prop.py:322-470 (host arithmetic): back-offs kappa sqrt(g' Sigma g) and the |A| tube recursion against
+    direct evaluation; the batch form equals the per-stage loop."""
+    from scipy.stats import norm
+    from gp_mpc_rocket_landing_b200.mpc.uncertainty_prop import (ConstraintTightening, PropagatedUncertainty,
+                                                                 TubeBasedRobustness)
+    rng = np.random.default_rng(1)
+    N, n = 6, 7
+    M = rng.normal(size=(N + 1, n, n))
+    covs = M @ M.transpose(0, 2, 1) * 1e-3
+    pu = PropagatedUncertainty(means=rng.normal(size=(N + 1, n)), covariances=covs)
+    ct = ConstraintTightening(0.95)
+    assert abs(ct.kappa - norm.ppf(0.95)) < 1e-15
+    a = rng.normal(size=n)
+    assert abs(ct.tighten_linear_constraint(a, 0.3, pu.means[2], covs[2]) - (0.3 + ct.kappa * np.sqrt(a @ covs[2] @ a))) < 1e-15
+    G = rng.normal(size=(3, n))
+    bo = ct.compute_back_offs(pu, [list(G)] * N)
+    assert bo.shape == (N, 3)
+    np.testing.assert_allclose(bo[4, 1], ct.kappa * np.sqrt(G[1] @ covs[4] @ G[1]), rtol=1e-14)
+    np.testing.assert_allclose(ct.compute_back_offs_batch(covs[None], G)[0], bo, rtol=1e-12)
+    lo, hi = pu.get_confidence_bounds(3)
+    np.testing.assert_allclose(hi - lo, 2 * norm.ppf(0.975) * np.sqrt(np.diag(covs[3])), rtol=1e-14)
+
+    class Dyn:
+        def linearize(self, x, u, dt=None):
+            A = np.eye(n); A[1:4, 4:7] = dt * np.eye(3); A[4:7, 0] = -u * dt
+            return A, np.zeros((n, 3))
+    X, U = rng.normal(size=(N + 1, n)), rng.normal(size=(N, 3))
+    W = TubeBasedRobustness(Dyn(), d_max=0.2).compute_tube(X, U, 0.1)
+    w = np.zeros(n)
+    for k in range(N):
+        w = np.abs(Dyn().linearize(X[k], U[k], dt=0.1)[0]) @ w
+        w[4:7] += 0.02
+        np.testing.assert_allclose(W[k + 1], w, rtol=1e-15)
+    assert np.all(W[0] == 0)
