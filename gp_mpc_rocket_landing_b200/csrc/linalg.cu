@@ -547,15 +547,10 @@ extern "C" int gpmpc_tri_inverse(const double* L, int n_pad, long lda, const dou
   GPMPC_REQUIRE(n_pad % 128 == 0, "gpmpc_tri_inverse: n_pad must be a multiple of 128");
   const long tot = (long)n_pad * n_pad;
   set_identity_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, stream>>>(Linv, n_pad, ldi);
-  double* ss = nullptr;
-  if (cudaMallocAsync(&ss, sizeof(double) * n_pad, stream) != cudaSuccess) {
-    cudaGetLastError();
-    gpmpc_set_error("gpmpc_tri_inverse: scratch allocation failed");
-    return GPMPC_ERR_CUDA;
-  }
-  // rows of the identity solved in place: row q <- (L^{-1} e_q)' = column q of L^{-1}, i.e. the result is W'
-  int rc = gpmpc_trsm_sumsq_batched(L, n_pad, lda, 0, Winv, Linv, n_pad, ldi, 0, ss, 1, stream_);
-  cudaFreeAsync(ss, stream);
+  // rows of the identity solved in place: row q <- (L^{-1} e_q)' = column q of L^{-1}, i.e. the result is W'.
+  // Right-looking form: its rank-64 updates cover all remaining columns at once (2x faster here than the left-looking
+  // solve that `predict` uses for many query rows).
+  int rc = gpmpc_trsm_right_batched(L, n_pad, lda, 0, Winv, Linv, n_pad, ldi, 0, 1, stream_);
   if (rc) return rc;
   transpose_inplace_kernel<<<dim3(n_pad / 32, n_pad / 32), 256, 0, stream>>>(Linv, n_pad, ldi);
   return gpmpc_check_launch("tri_inverse");

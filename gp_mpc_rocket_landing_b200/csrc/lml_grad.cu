@@ -5,7 +5,7 @@
 // (dK/dlog s2 = K, dK/dlog l_d = K (x_d - x'_d)^2 / l_d^2); with alpha = K^{-1} y and W = alpha alpha' - K^{-1}
 //     dLML/dtheta = 1/2 sum_ij W_ij (dK/dtheta)_ij                         (Rasmussen & Williams eq. 5.9)
 // so all D + 2 components come from ONE pass over the n x n pairs: the kernel value is recomputed from the scaled inputs
-// (never stored), K^{-1} is read once (n^2 doubles: the algorithmic HBM traffic of the pass).
+// (never stored), the lower triangle of K^{-1} is read once (n^2 / 2 doubles: the algorithmic HBM traffic of the pass).
 #include "common.cuh"
 
 namespace {
@@ -22,6 +22,14 @@ __global__ void __launch_bounds__(128) lml_grad_se_kernel(const double* __restri
   __shared__ double red[4][DP + 2];
   const int t = threadIdx.x, p = blockIdx.z;
   const int i = blockIdx.y * 128 + t, j0 = blockIdx.x * 128;
+  // W and dK/dtheta are symmetric: only the tiles with column tile >= row tile are visited (they read the LOWER triangle
+  // of K^{-1}, entry (j, i) with j >= i tile-wise) and the off-diagonal ones count twice
+  const long blk = ((long)p * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (blockIdx.x < blockIdx.y) {
+    if (t < DP + 2) part[blk * (DP + 2) + t] = 0.0;
+    return;
+  }
+  const double sym = (blockIdx.x > blockIdx.y) ? 2.0 : 1.0;
   for (int idx = t; idx < 128 * DP; idx += 128) xj[idx] = Xs[(long)j0 * DP + idx];
   aj[t] = alpha[(long)p * lda + j0 + t];
   double xi[DP], acc[DP + 2];
@@ -42,7 +50,7 @@ __global__ void __launch_bounds__(128) lml_grad_se_kernel(const double* __restri
         s += d2[d];
       }
       // K^{-1} is symmetric: read (j, i) so that consecutive threads read consecutive addresses
-      const double w = (ai * aj[c] - Kinv[(long)(j0 + c) * ldk + i]) * (sv * exp(-0.5 * s));
+      const double w = sym * (ai * aj[c] - Kinv[(long)(j0 + c) * ldk + i]) * (sv * exp(-0.5 * s));
       acc[0] += w;
 #pragma unroll
       for (int d = 0; d < DP; ++d) acc[1 + d] += w * d2[d];
@@ -56,10 +64,7 @@ __global__ void __launch_bounds__(128) lml_grad_se_kernel(const double* __restri
     if ((t & 31) == 0) red[t >> 5][d] = v;
   }
   __syncthreads();
-  if (t < DP + 2) {
-    const long blk = ((long)p * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-    part[blk * (DP + 2) + t] = (red[0][t] + red[1][t]) + (red[2][t] + red[3][t]);
-  }
+  if (t < DP + 2) part[blk * (DP + 2) + t] = (red[0][t] + red[1][t]) + (red[2][t] + red[3][t]);
 }
 
 // grad[p * (D + 2) + c] = 1/2 * sum over tiles, in a fixed order (bit-reproducible)

@@ -303,7 +303,7 @@ class ExactModelDev:
 
     def lml_gradient(self):
         """d LML_p / d[log s2, log l_1..l_D, log noise] -> (P, D + 2) CUDA tensor, for the SE-ARD kernel.
-        K^{-1} comes from cho_solve of the identity on the cached factor; the D + 2 contractions with
+        K^{-1} = L^{-T} L^{-1} comes from the explicit inverse factor (one triangular GEMM); the D + 2 contractions with
         W = alpha alpha' - K^{-1} run as one fused pass (gpmpc_lml_grad_se).  The LML is the one of the normalised
         targets (exact_gp.py:186-204), so this is the gradient of `self.lml`."""
         torch = torch_()
@@ -313,8 +313,13 @@ class ExactModelDev:
         if f.DP > 32:
             raise ValueError("lml_gradient: input dimension > 32")
         dev = f.L.device
-        Kinv = torch.eye(f.n_pad, dtype=torch.float64, device=dev)
-        f.solve(Kinv)
+        # K^{-1} = W'W with the explicit inverse factor W = L^{-1}: a right-looking DMMA TRSM of the identity (gives W'
+        # row-major, the operand layout of the NT GEMM) and one lower-triangular GEMM, instead of n cho_solves
+        Wt = torch.eye(f.n_pad, dtype=torch.float64, device=dev)   # rows solved in place: row q <- column q of L^{-1}
+        call("gpmpc_trsm_right", ptr(f.L), f.n_pad, f.L.stride(0), ptr(f.Winv), ptr(Wt), f.n_pad, Wt.stride(0), stream())
+        Kinv = torch.empty((f.n_pad, f.n_pad), dtype=torch.float64, device=dev)
+        call("gpmpc_dgemm_nt", ptr(Wt), Wt.stride(0), ptr(Wt), Wt.stride(0), ptr(Kinv), Kinv.stride(0), f.n_pad, f.n_pad,
+             f.n_pad, 1.0, 0.0, 1, stream())
         nwork = int(_lib.lib.gpmpc_lml_grad_se_work_doubles(f.n_pad, f.DP, self.P))
         work = torch.empty((nwork,), dtype=torch.float64, device=dev)
         grad = torch.empty((self.P, f.D + 2), dtype=torch.float64, device=dev)

@@ -83,7 +83,8 @@ int gpmpc_lml(const double* L, int n, int n_pad, long lda, long strideL, const d
  * grad[p*(D+2) + c], c = 0: log signal variance, 1..D: log lengthscales, D+1: log noise variance, for P outputs that
  * share one factor.  dLML/dtheta = 1/2 sum_ij (alpha_i alpha_j - K^{-1}_ij) (dK/dtheta)_ij with the kernel derivatives of
  * kernels.py:279-318 and d(noise I)/dlog noise = noise I.  Xs: inputs scaled by 1/l (gpmpc_scale_inputs), Kinv: the
- * symmetric n_pad x n_pad inverse (gpmpc_potrs on the identity), alpha: P x lda.  work: gpmpc_lml_grad_se_work_doubles.
+ * n_pad x n_pad inverse, of which only the lower triangle (by 128-tiles) is read -- e.g. W'W with W = L^{-1} from
+ * gpmpc_tri_inverse, or gpmpc_potrs on the identity; alpha: P x lda.  work: gpmpc_lml_grad_se_work_doubles.
  * Replaces the finite-difference gradient of scipy's L-BFGS-B in ExactGP.optimize_hyperparameters (exact_gp.py:357-421:
  * D + 3 refits per gradient) with one refit + one pass. */
 size_t gpmpc_lml_grad_se_work_doubles(int n_pad, int DP, int P);

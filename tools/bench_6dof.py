@@ -23,6 +23,7 @@ def main():
     ge = gp.engine
     X, U, Dv, Dw = workloads.residual_dataset_6dof(1000, seed=0)
     sg = gp.StructuredRocketGP(gp.StructuredGPConfig(n_inducing=a.inducing, use_sparse=True, noise_variance=1e-3))
+    np.random.seed(0)   # the inducing points are drawn from the global numpy RNG (sparse_gp.py:122-148)
     sg.add_data(X, U, Dv, Dw); sg.fit()
     dyn = dynamics.Rocket6DoFDynamics()
     ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=30, max_sqp_iter=a.sqp_iters))

@@ -12,6 +12,8 @@ from gp_mpc_rocket_landing_b200.mpc import engine as me
 B = int(os.environ.get("B", 1024))
 X, U, Dv, Dw = workloads.residual_dataset_6dof(1000, seed=0)
 sg = gp.StructuredRocketGP(gp.StructuredGPConfig(n_inducing=100, use_sparse=True, noise_variance=1e-3))
+import numpy as np
+np.random.seed(0)
 sg.add_data(X, U, Dv, Dw); sg.fit()
 dyn = dynamics.Rocket6DoFDynamics()
 ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=30, max_sqp_iter=1, use_gp_uncertainty=False))
