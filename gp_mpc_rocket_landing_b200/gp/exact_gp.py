@@ -118,6 +118,8 @@ class ExactGP:
         recomputed -- but the factor is EXTENDED by the new rows (ExactFactor.append, O(n^2 m)) when the
         hyper-parameters are those of the cached factor; otherwise, or when the extension is not positive definite, this
         is a full refit."""
+        if np.size(_host(y_new) if _is_dev(y_new) else y_new) == 0:
+            return self                      # nothing to add
         if self._model is None:
             return self.fit(X_new, y_new)
         dev_x = _is_dev(self.X_train)

@@ -221,6 +221,8 @@ class OnlineGPUpdater:
         come from one batched variance query; the threshold / minimum-distance rules are then applied in row order, so
         the accepted set equals that of the row-by-row calls (the GP does not change between them)."""
         X, U = np.atleast_2d(np.asarray(X, dtype=np.float64)), np.atleast_2d(np.asarray(U, dtype=np.float64))
+        if X.size == 0:
+            return np.zeros(0, dtype=bool)
         D = np.asarray(D, dtype=np.float64).reshape(X.shape[0], -1)
         Z = np.stack([np.asarray(self.feature_extractor(X[i], U[i]), dtype=np.float64) for i in range(X.shape[0])])
         self._ensure_buffer(Z.shape[1], D.shape[1])

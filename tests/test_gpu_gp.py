@@ -267,6 +267,7 @@ def test_incremental_factor_append_equals_refit(eng, n0, adds):
     mo, vo = og.exact_predict(ref, Xq)[:2]
     assert relerr(pi.mean, mo) < 1e-9 and relerr(pi.variance, vo) < 1e-8
     assert relerr(pi.mean, pf.mean) < 1e-10 and relerr(pi.variance, pf.variance) < 1e-9
+    assert inc.update(np.zeros((0, D)), np.zeros(0)) is inc and inc.n_train == ntot      # empty update: no-op
     # changed hyper-parameters: update falls back to a full refit with the new ones
     inc.kernel.set_params(inc.kernel.get_params() + 0.1)
     inc.update(X[:3] + 0.5, y[:3])

@@ -91,6 +91,7 @@ def test_updater_schedule_and_incremental_routing():
     a.config = b.config = OnlineUpdateConfig(buffer_size=50, min_distance=0.01)
     one = np.array([a.add_observation(X[i], U[i], D[i]) for i in range(20)])
     assert np.array_equal(b.add_observations(X, U, D), one) and not one[5] and one.sum() == 19
+    assert b.add_observations(np.zeros((0, 3)), np.zeros((0, 2)), np.zeros(0)).shape == (0,)   # empty batch: no-op
 
 
 @pytest.mark.gpu
