@@ -312,3 +312,27 @@ def test_blocked_potrs_large_n_few_rhs(eng):
         ref = og.exact_fit(0, X, Y[:, p], np.full(5, 2.0), 1.0, 1e-2)
         assert relerr(m.alpha[p, :n].cpu().numpy(), ref.alpha) < 1e-8
         assert abs(m.lml[p].item() - ref.lml) < 1e-10 * abs(ref.lml)
+
+
+def test_sweep_then_gradient_refinement_shared_hyperparameters(eng):
+    """refit.sweep_and_refine: the best grid candidate of the batched sweep refined by L-BFGS-B on the summed LML of the
+    three outputs with the device gradient (one fit + one gradient pass per evaluation).  The refined LML is at least the
+    grid's, the gradient at the optimum vanishes (interior components), and the oracle agrees on the LML there."""
+    from oracle import gp as og
+    from gp_mpc_rocket_landing_b200.gp import refit
+    rng = np.random.default_rng(8)
+    n, D = 400, 4
+    X = rng.uniform(-2, 2, size=(n, D))
+    Y = np.stack([np.sin(2 * X[:, 0]) + 0.3 * X[:, 1], np.cos(X[:, 1]) * X[:, 2], 0.5 * X[:, 3] ** 2], 1)
+    Y += 0.05 * rng.normal(size=Y.shape)
+    r = refit.sweep_and_refine(X, Y)
+    assert r["lml"].shape == (3,) and r["lml"].sum() >= r["grid_best_lml"].sum() - 1e-9
+    assert r["lml"].sum() > r["grid_best_lml"].sum() + 1.0          # the grid is coarse: the refinement moves
+    f = eng.ExactFactor(0, r["lengthscales"], r["signal_variance"], r["noise_variance"]).fit(X)
+    m = eng.ExactModelDev(f).fit_targets(Y)
+    g = m.lml_gradient().sum(dim=0).cpu().numpy()
+    assert np.max(np.abs(g)) < 1e-2 * max(1.0, abs(r["lml"].sum()))
+    for p in range(3):
+        ref = og.exact_fit(0, X, Y[:, p], r["lengthscales"], r["signal_variance"], r["noise_variance"])
+        assert abs(ref.lml - r["lml"][p]) < 1e-8 * abs(ref.lml)
+    assert r["n_evaluations"] < 120      # the differenced optimiser needs (D + 3) fits per gradient
