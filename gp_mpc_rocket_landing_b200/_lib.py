@@ -25,14 +25,15 @@ class AdmmSettings(C.Structure):
         ("max_iter", c_int), ("scaling", c_int), ("check_every", c_int),
         ("adaptive_rho", c_int), ("adaptive_rho_interval", c_int),
         ("warm_x", c_int), ("warm_y", c_int), ("rho_from_input", c_int),
-        ("commit_y_solved_only", c_int), ("kernel_variant", c_int),
+        ("commit_y_solved_only", c_int), ("kernel_variant", c_int), ("bound_stride", c_int),
     ]
 
     @classmethod
     def reference_defaults(cls, **over):
         s = cls(rho=0.1, sigma=1e-6, alpha=1.6, eps_abs=1e-4, eps_rel=1e-4, eps_prim_inf=1e-4, eps_dual_inf=1e-4,
                 adaptive_rho_tolerance=5.0, max_iter=50, scaling=3, check_every=25, adaptive_rho=1,
-                adaptive_rho_interval=25, warm_x=0, warm_y=0, rho_from_input=0, commit_y_solved_only=0, kernel_variant=0)
+                adaptive_rho_interval=25, warm_x=0, warm_y=0, rho_from_input=0, commit_y_solved_only=0, kernel_variant=0,
+                bound_stride=0)
         for k, v in over.items():
             setattr(s, k, v)
         return s
@@ -80,6 +81,7 @@ _PROTOS = {
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_ut_sigma_3dof": (c_int, [c_int, c_double, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_combine_3dof": (c_int, [c_int, c_int, c_double, c_double, c_double, c_dp, c_dp, c_double, c_dp, c_dp, c_dp]),
+    "gpmpc_tighten_bounds": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_double, c_double, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_propagate_cov": (c_int, [c_int, c_int, c_int, c_dp, c_long, c_long, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_step_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linearize_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),

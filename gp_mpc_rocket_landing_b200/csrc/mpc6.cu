@@ -444,6 +444,48 @@ __global__ void __launch_bounds__(256) propagate_cov_kernel(int nx, int N, const
   }
 }
 
+// lb' = lb + kappa sigma, ub' = ub - kappa sigma for the states of stages k >= 1; one thread per (scenario, variable).
+__global__ void __launch_bounds__(256) tighten_bounds_kernel(int nx, int nu, int N, long total, const double* __restrict__ lb,
+                                                             const double* __restrict__ ub,
+                                                             const double* __restrict__ covs, double kappa,
+                                                             double max_variance, double* __restrict__ lbo,
+                                                             double* __restrict__ ubo, const int* __restrict__ active) {
+  const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int ns = nx + nu, n = N * ns + nx;
+  const int b = (int)(idx / n), j = (int)(idx - (long)b * n);
+  if (active && !active[b]) return;
+  const int k = j / ns, i = j - k * ns;
+  double l = lb[j], u = ub[j];
+  if (k >= 1 && i < nx) {
+    const double* Sk = covs + ((long)b * (N + 1) + k) * nx * nx;
+    // gp_mpc.py:206-208: no tightening when the stage is too uncertain (there: the mean velocity std; here: any variance)
+    bool ok = true;
+    for (int d = 0; d < nx; ++d) ok = ok && (Sk[d * nx + d] <= max_variance);
+    if (ok) {
+      const double back = kappa * sqrt(fmax(Sk[i * nx + i], 0.0));
+      const bool lf = l > -1e20, uf = u < 1e20;
+      if (lf) l += back;
+      if (uf) u -= back;
+      if (lf && uf && l > u) l = u = 0.5 * (l + u);
+    }
+  }
+  lbo[idx] = l;
+  ubo[idx] = u;
+}
+
+extern "C" int gpmpc_tighten_bounds(int nx, int nu, int B, int N, const double* lb, const double* ub, const double* covs,
+                                    double kappa, double max_variance, double* lb_out, double* ub_out, const int* active,
+                                    void* stream) {
+  GPMPC_REQUIRE(nx >= 1 && nu >= 0 && B >= 0 && N >= 1 && lb && ub && covs && lb_out && ub_out,
+                "gpmpc_tighten_bounds: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  const long total = (long)B * (N * (nx + nu) + nx);
+  tighten_bounds_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      nx, nu, N, total, lb, ub, covs, kappa, max_variance, lb_out, ub_out, active);
+  return gpmpc_check_launch("tighten_bounds");
+}
+
 extern "C" int gpmpc_propagate_cov(int nx, int B, int N, const double* A, long ld_row, long stage_stride,
                                    const double* qdiag, double sigma0, double* covs, const int* active, void* stream) {
   GPMPC_REQUIRE(nx >= 1 && nx <= 16 && B >= 0 && N >= 1, "gpmpc_propagate_cov: need 1 <= nx <= 16, N >= 1");

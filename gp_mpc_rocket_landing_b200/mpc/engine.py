@@ -136,8 +136,11 @@ class AdmmWorkspace:
         self.iters = torch.zeros((B,), dtype=torch.int32, device=kw["device"])
 
 
-def admm_solve(qp: QPData, AB, beq, q, settings: AdmmSettings, ws: AdmmWorkspace, active=None):
-    call("gpmpc_admm_solve", ws.nx, ws.nu, qp.N, ws.B, ptr(AB), ptr(beq), ptr(q), ptr(qp.Pdiag), ptr(qp.lb), ptr(qp.ub),
+def admm_solve(qp: QPData, AB, beq, q, settings: AdmmSettings, ws: AdmmWorkspace, active=None, lb=None, ub=None):
+    """lb, ub: optional per-scenario boxes (B, n) replacing the shared qp.lb / qp.ub (settings.bound_stride)."""
+    settings.bound_stride = 0 if lb is None else int(lb.stride(0))
+    lb, ub = (qp.lb, qp.ub) if lb is None else (lb, ub)
+    call("gpmpc_admm_solve", ws.nx, ws.nu, qp.N, ws.B, ptr(AB), ptr(beq), ptr(q), ptr(qp.Pdiag), ptr(lb), ptr(ub),
          C.byref(settings), ptr(active), ptr(ws.x), ptr(ws.y), ptr(ws.rho), ptr(ws.status), ptr(ws.iters),
          ptr(ws.obj), ptr(ws.pri), ptr(ws.dua), stream())
     return ws
@@ -166,6 +169,13 @@ def linearize(dyn, X, U, AB, lin_mode=0):
     """[A_d | B_d] at the flattened points of X (...,7), U (...,3) -> AB (...,7,10)."""
     npts = X.numel() // NX
     call("gpmpc_linearize_3dof", C.byref(dyn), npts, lin_mode, ptr(X), ptr(U), ptr(AB), stream())
+
+
+def tighten_bounds(qp: QPData, covs, kappa, max_variance, lb_out, ub_out, nx=NX, nu=NU, active=None):
+    """Per-scenario boxes lb + kappa sigma_k, ub - kappa sigma_k for the states of stages k >= 1 (gpmpc_tighten_bounds)."""
+    B = covs.shape[0]
+    call("gpmpc_tighten_bounds", nx, nu, B, qp.N, ptr(qp.lb), ptr(qp.ub), ptr(covs), float(kappa), float(max_variance),
+         ptr(lb_out), ptr(ub_out), ptr(active), stream())
 
 
 def propagate_cov(dyn, X, U, dvar, covs, sigma0=1e-6, active=None):

@@ -42,6 +42,11 @@ class GPMPCConfig(MPCConfig):
     max_sqp_iter: int = 10            # gp_mpc.py:293 `max_iters = 10`
     sqp_tol: float = 1e-4             # gp_mpc.py:343 (the device kernel implements exactly this constant)
     repropagate_uncertainty: bool = True  # gp_mpc.py:348-353 (computed and discarded by the reference)
+    confidence_level: float = 0.95        # gp_mpc.py:57
+    max_variance_for_constraint: float = 1.0  # gp_mpc.py:60: no tightening for a stage more uncertain than this
+    # Extension (off = reference behaviour, which prepares the tightening and applies it at k = 0 only, gp_mpc.py:414):
+    # tighten the state box of every stage k >= 1 of every scenario by kappa * sqrt(diag Sigma_k), kappa = Phi^-1(level)
+    tighten_state_bounds: bool = False
     qp_max_iter: int = 1000           # config/mpc_params.yaml:48 (osqp_rti.py:53 uses 50, which rarely converges)
     qp_eps_abs: float = 1e-4          # osqp_rti.py:54
     qp_eps_rel: float = 1e-4          # osqp_rti.py:55
@@ -87,6 +92,8 @@ class _BatchState:
         self.Ks = torch.zeros((self.q_pad, model.f.n_pad), **f64) if model is not None else None
         self.var_work = None  # scratch of the explicit-inverse variance path (allocated on first use)
         self.covs = torch.zeros((B, N + 1, NX, NX), **f64)
+        self.lb_t = None   # per-scenario tightened boxes (tighten_state_bounds)
+        self.ub_t = None
         self.AB = torch.zeros((B, N, NX, NX + NU), **f64)
         self.beq = torch.zeros((B, NX * (N + 1)), **f64)
         self.q = torch.zeros((B, n), **f64)
@@ -291,7 +298,19 @@ class GPMPC:
             launches += self._fork_uncertainty(st, st.X, st.U, st.active)
         # --- 3. SQP iterations
         S = self._settings()
+        tighten = use_unc and c.tighten_state_bounds
+        if tighten:
+            from scipy.stats import norm
+            kappa = float(norm.ppf(c.confidence_level))
+            if st.lb_t is None:
+                n_var = self._qp.lb.shape[0]
+                st.lb_t = ge.torch_().empty((st.B, n_var), dtype=self._qp.lb.dtype, device=self._qp.lb.device)
+                st.ub_t = ge.torch_().empty_like(st.lb_t)
         for it in range(c.max_sqp_iter):
+            if tighten:   # boxes from the latest covariance chain (initial propagation or the re-propagation below)
+                self._join_uncertainty(st)
+                me.tighten_bounds(self._qp, st.covs, kappa, c.max_variance_for_constraint, st.lb_t, st.ub_t)
+                launches += 1
             if use_mean and it > 0:
                 with self._span("gp_mean"):
                     me.gp_mean_points(self._model_struct, st.X, st.U, st.dmean, None, active=st.active)
@@ -301,7 +320,8 @@ class GPMPC:
                                c_gp=st.dmean if use_mean else None, lin_mode=0, rhs_mode=1, active=st.active)
                 me.pack_traj(st.X, st.U, st.ws.x, active=st.active)
             with self._span("admm"):
-                me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active)
+                me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active,
+                              lb=st.lb_t if tighten else None, ub=st.ub_t if tighten else None)
             with self._span("update"):
                 st.qp_iters += st.ws.iters * st.active
                 me.mpc_update(self._qp, 1, st.ws.x, st.ws.status, x_ref, st.X, st.U, None, None, st.cost,

@@ -179,6 +179,8 @@ typedef struct GpmpcAdmmSettings {
   int commit_y_solved_only; /* write y back only when status == SOLVED (GP-MPC SQP loop keeps the last good duals) */
   int kernel_variant;     /* 0: stage-parallel kernel (csrc/admm_stage.cu) when the problem fits it; 1: force the
                              first-generation one-chain kernel (csrc/admm.cu) */
+  int bound_stride;       /* 0: lb / ub (n) are shared by all QPs (the reference's fixed box, osqp_rti.py:197-200);
+                             > 0: QP b reads lb + b * bound_stride, ub + b * bound_stride (per-scenario tightened boxes) */
 } GpmpcAdmmSettings;
 
 /* 3-DoF Euler model parameters (nominal_mpc.py:579-605, rocket_3dof.py:33-65). */
@@ -307,6 +309,15 @@ int gpmpc_rollout_6dof(const GpmpcExactModel* gp_v, const GpmpcExactModel* gp_w,
 int gpmpc_qp_assemble_6dof(const GpmpcDyn6* dyn, int B, int N, const double* X_lin, const double* U_lin,
                            const double* x_init, const double* x_ref, long ldxref, const double* c_gp, const double* Qd,
                            const double* Qfd, double* AB, double* beq, double* q, const int* active, void* stream);
+
+/* Per-scenario, per-stage box tightening from the propagated covariances: for state i of stage k >= 1,
+ * lb' = lb + kappa sqrt(Sigma_k[i][i]), ub' = ub - kappa sqrt(Sigma_k[i][i]) (finite bounds only; a box that would invert
+ * collapses to its midpoint; variances above max_variance leave the stage untouched, gp_mpc.py:206-208).  Controls and
+ * stage 0 keep the shared box.  lb, ub: n = N (nx + nu) + nx shared entries; lb_out, ub_out: B x n.  This is the per-stage
+ * use of Sigma_k that gp_mpc.py:177-215,414 prepares and then applies at k = 0 only. */
+int gpmpc_tighten_bounds(int nx, int nu, int B, int N, const double* lb, const double* ub, const double* covs,
+                         double kappa, double max_variance, double* lb_out, double* ub_out, const int* active,
+                         void* stream);
 
 /* Linear covariance chain Sigma_0 = sigma0 I, Sigma_{k+1} = A_k Sigma_k A_k' + diag(qdiag[b,k]) for any nx <= 16:
  * uncertainty_prop.py:117-177 (the 14-state propagator GPMPC.solve calls at gp_mpc.py:283-289,347-351).  A: entry (i,j) of

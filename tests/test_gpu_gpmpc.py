@@ -111,3 +111,55 @@ def test_osqp_rti_step_matches_oracle(setup):
     one.initialize(X0[0], XT[0])
     s = one.step(X0[0])
     assert s.u0.shape == (3,) and s.X_opt.shape == (16, 7) and isinstance(s.success, bool)
+
+
+def test_per_stage_bound_tightening_extension(setup):
+    """GPMPCConfig.tighten_state_bounds (extension; the reference prepares the tightening from Sigma_k and applies it at
+    k = 0 only, gp_mpc.py:177-215,414): per-scenario boxes lb + kappa sqrt(diag Sigma_k), ub - kappa sqrt(diag Sigma_k) for
+    the states of stages k >= 1, read by the ADMM kernel through GpmpcAdmmSettings.bound_stride.  Checked: the boxes
+    against the covariances; the device solution against the dense OSQP restatement of the same QP with the same boxes."""
+    from scipy.stats import norm
+    from gp_mpc_rocket_landing_b200 import workloads
+    from gp_mpc_rocket_landing_b200.mpc import GPMPC, GPMPCConfig, engine as me
+    from oracle import mpc as ompc
+    dyn, gp, _ = setup
+    N, B = 20, 4
+    X0, XT = workloads.sample_initial_conditions(0, B)
+    X0[:, 4] = -49.5      # descent rate next to its -50 bound: the tightened box binds on the first stages
+    cfg = GPMPCConfig(N=N, dt=0.1, max_sqp_iter=1, qp_max_iter=4000, tighten_state_bounds=True, confidence_level=0.99)
+    mpc = GPMPC(dyn, gp, cfg); mpc.setup()
+    sol = mpc.solve_batch(X0, XT)
+    st = mpc._batch
+    covs = mpc.last_covariances()
+    kappa = norm.ppf(0.99)
+    lb0, ub0 = mpc._qp.lb.cpu().numpy(), mpc._qp.ub.cpu().numpy()
+    lbt, ubt = st.lb_t.cpu().numpy(), st.ub_t.cpu().numpy()
+    for b in range(B):
+        for k in range(N + 1):
+            sl = slice(k * 10, k * 10 + 7)
+            back = kappa * np.sqrt(np.diag(covs[b, k])) if k >= 1 else np.zeros(7)
+            fin_l, fin_u = lb0[sl] > -1e20, ub0[sl] < 1e20
+            np.testing.assert_allclose(lbt[b, sl][fin_l], (lb0[sl] + back)[fin_l], rtol=1e-14)
+            np.testing.assert_allclose(ubt[b, sl][fin_u], (ub0[sl] - back)[fin_u], rtol=1e-14)
+            assert np.array_equal(lbt[b, sl][~fin_l], lb0[sl][~fin_l])
+            if k < N:
+                assert np.array_equal(lbt[b, k * 10 + 7:k * 10 + 10], lb0[k * 10 + 7:k * 10 + 10])   # controls untouched
+    assert np.all(sol.qp_status == 1)
+    AB, beq, q = st.AB.cpu().numpy(), st.beq.cpu().numpy(), st.q.cpu().numpy()
+    Pd = mpc._qp.Pdiag.cpu().numpy()
+    z = st.ws.x.cpu().numpy()
+    for b in range(2):
+        A, l, u = me.dense_constraints(N, AB[b], beq[b], lbt[b], ubt[b])
+        r = ompc.OSQPOracle(Pd, q[b], A, l, u, ompc.OSQPSettings(max_iter=4000)).solve()
+        assert r.status == 1
+        obj_d = 0.5 * z[b] @ (Pd * z[b]) + q[b] @ z[b]
+        obj_o = 0.5 * r.x @ (Pd * r.x) + q[b] @ r.x
+        assert abs(obj_d - obj_o) < 1e-3 * max(1.0, abs(obj_o))
+        assert np.max(np.abs(z[b] - r.x)) < 5e-3 * max(1.0, np.max(np.abs(r.x)))      # two ADMM runs at eps = 1e-4
+        assert np.all(z[b] >= lbt[b] - 1e-2) and np.all(z[b] <= ubt[b] + 1e-2)   # ADMM primal tolerance (eps_rel |z|)
+        # the tightened box is active: the velocity of stage 1 sits above the ORIGINAL bound by about the back-off
+        assert z[b][10 + 4] >= lb0[14] + 0.5 * kappa * np.sqrt(covs[b, 1][4, 4])
+    # off (default) = the reference's fixed box
+    ref = GPMPC(dyn, gp, GPMPCConfig(N=N, dt=0.1, max_sqp_iter=1, qp_max_iter=4000)); ref.setup()
+    ref.solve_batch(X0, XT)
+    assert ref._batch.lb_t is None
