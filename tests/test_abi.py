@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_struct_layouts_match_header():
     from gp_mpc_rocket_landing_b200 import _lib
-    assert ctypes.sizeof(_lib.AdmmSettings) == 8 * 8 + 10 * 4
+    assert ctypes.sizeof(_lib.AdmmSettings) == 8 * 8 + 11 * 4 + 4      # 8 doubles, 11 ints, tail padding to 8 bytes
     assert ctypes.sizeof(_lib.Dyn3) == 5 * 8
     assert ctypes.sizeof(_lib.ExactModel) == 6 * 4 + 8 + 8 * 8
 
