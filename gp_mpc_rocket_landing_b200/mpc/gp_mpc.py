@@ -93,6 +93,7 @@ class _BatchState:
         self.var_work = None  # scratch of the explicit-inverse variance path (allocated on first use)
         self.covs = torch.zeros((B, N + 1, NX, NX), **f64)
         self.lb_t = None   # per-scenario tightened boxes (tighten_state_bounds)
+        self._pinned_in = {}
         self.ub_t = None
         self.AB = torch.zeros((B, N, NX, NX + NU), **f64)
         self.beq = torch.zeros((B, NX * (N + 1)), **f64)
@@ -108,6 +109,18 @@ class _BatchState:
         self.has_warm = False
         self._pinned = [{}, {}]   # two alternating sets of pinned staging buffers for the host results
         self._flip = 0
+
+    def from_host(self, key: str, arr):
+        """numpy -> device through a persistent pinned staging buffer (async H2D on the current stream).  Safe to reuse
+        on the next call: every numpy-in call ends with the stream synchronisation of `to_host`."""
+        torch = ge.torch_()
+        a = np.ascontiguousarray(np.asarray(arr, dtype=np.float64))
+        b = self._pinned_in.get(key)
+        if b is None or tuple(b.shape) != a.shape:
+            b = torch.empty(a.shape, dtype=torch.float64, device="cpu", pin_memory=True)
+            self._pinned_in[key] = b
+        b.numpy()[...] = a
+        return b.to("cuda", non_blocking=True)
 
     def to_host(self, tensors: dict) -> dict:
         """Device -> pinned host copies of the result tensors (async on the current stream, one synchronise).
@@ -374,11 +387,19 @@ class GPMPC:
         torch = ge.torch_()
         t0 = time.perf_counter()
         dev_in = _is_dev(X0)
-        x0 = ge.to_dev(X0)
-        if x0.dim() == 1:
-            x0 = x0[None, :]
-        B = x0.shape[0]
-        st = self._state_for(B, single=False)
+        if dev_in:
+            x0 = ge.to_dev(X0)
+            if x0.dim() == 1:
+                x0 = x0[None, :]
+            B = x0.shape[0]
+            st = self._state_for(B, single=False)
+        else:   # host buffers: H2D from pinned staging memory
+            X0h = np.atleast_2d(np.asarray(X0, dtype=np.float64))
+            B = X0h.shape[0]
+            st = self._state_for(B, single=False)
+            x0 = st.from_host("x0", X0h)
+            if X_ref is None and not _is_dev(x_target):
+                x_target = st.from_host("xt", x_target)
         x_ref = self._x_ref(x_target, X_ref, B)
         act = None if active is None else ge.to_dev(active, torch.int32)
         uref = None if U_ref is None else ge.to_dev(U_ref)
