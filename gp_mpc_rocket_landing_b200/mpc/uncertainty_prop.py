@@ -118,6 +118,7 @@ class UncertaintyPropagator:
             Ks = torch.zeros((ge.pad_to(B * 15, 128), f.n_pad), **f64)
             Kc = torch.zeros((ge.pad_to(B, 128), f.n_pad), **f64)
             var = torch.zeros((Kc.shape[0], 3), **f64)
+            var_work = torch.empty(((f.n_pad // 64) * Kc.shape[0],), **f64)
             ms = model.struct()
         for k in range(N):
             Uk = Ud[:, k].contiguous()
@@ -129,7 +130,7 @@ class UncertaintyPropagator:
             else:
                 me.rollout(ms, dyn, SP, Usp, Xn, dm, Ks)
                 Kc[:B] = Ks[0:B * 15:15]                     # cross-covariance rows of the centre points
-                sumsq = f.sumsq_inplace(Kc)
+                sumsq = f.sumsq_linv(Kc, var_work)            # one triangular GEMM against the explicit inverse factor
                 ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, B, 3, f.sv, 1e-10, ge.ptr(model.ystd), ge.ptr(var), 3, 0,
                         ge.stream())
                 vk = var
