@@ -817,7 +817,15 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
 // Launch shapes: 3-DoF (nx 7): 128 threads x 2 slots, 3 QPs per SM, horizon 20 compiled in;  6-DoF (nx 14, N = 30 needs
 // 220 KB of shared memory): 256 threads x 3 slots, one QP per SM, horizon 30 compiled in.
 template <int NX> struct StageShape { static constexpr int NSLOT = 2, NTHR = 128, MINB = ADMM_STAGE_MIN_CTAS, NFIX = 20; };
-template <> struct StageShape<14> { static constexpr int NSLOT = 3, NTHR = 256, MINB = 1, NFIX = 30; };
+// 6-DoF shape.  Measured on B200 (tools/prof_admm6.py, 1024 QPs): 3 slots x 256 threads 55.2 us per iteration of the batch,
+// 2 slots x 384 threads (168 registers) 56.6 us -- the iteration is bound by the two chain warps, not by the thread count.
+// (More than 8 warps also needs MAX_WARPS raised.)
+#ifndef ADMM_STAGE14_NSLOT
+#define ADMM_STAGE14_NSLOT 3
+#define ADMM_STAGE14_NTHR 256
+#endif
+static_assert(ADMM_STAGE14_NTHR / 32 <= MAX_WARPS, "raise MAX_WARPS for this block size");
+template <> struct StageShape<14> { static constexpr int NSLOT = ADMM_STAGE14_NSLOT, NTHR = ADMM_STAGE14_NTHR, MINB = 1, NFIX = 30; };
 
 // Launcher used by gpmpc_admm_solve (csrc/admm.cu).  Returns GPMPC_ERR_ARG without launching when the problem does not
 // fit this kernel (the caller then falls back to the first-generation kernel).  `scratch`: B x (n + m) doubles.
