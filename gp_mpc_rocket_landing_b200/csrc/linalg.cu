@@ -336,17 +336,22 @@ __global__ void __launch_bounds__(256) potrs_bwd_step_kernel(const double* __res
     if (blockIdx.x == 0) Xbase[(long)blockIdx.y * n_pad + j0 + tid] = v;
   }
   __syncthreads();
-  const int c = blockIdx.x * 256 + tid;
+  // 64 columns per CTA, the 64 rows of the block split over 4 thread groups (16 rows each, coalesced across columns)
+  const int cl = tid & 63, q = tid >> 6;
+  const int c = blockIdx.x * 64 + cl;
+  double s0 = 0.0, s1 = 0.0;
   if (c < j0) {
-    const double* col = L + (long)j0 * lda + c;
-    double s0 = 0.0, s1 = 0.0;
-#pragma unroll 8
-    for (int r = 0; r < 64; r += 2) {
-      s0 += col[(long)r * lda] * xj[r];
-      s1 += col[(long)(r + 1) * lda] * xj[r + 1];
+    const double* col = L + (long)(j0 + q * 16) * lda + c;
+#pragma unroll
+    for (int r = 0; r < 16; r += 2) {
+      s0 += col[(long)r * lda] * xj[q * 16 + r];
+      s1 += col[(long)(r + 1) * lda] * xj[q * 16 + r + 1];
     }
-    y[c] -= s0 + s1;
   }
+  __syncthreads();            // part[] was read above to form xj
+  part[q][cl] = s0 + s1;
+  __syncthreads();
+  if (tid < 64 && c < j0) y[c] -= (part[0][tid] + part[1][tid]) + (part[2][tid] + part[3][tid]);
 }
 
 static int potrs_blocked_min() {
@@ -374,7 +379,7 @@ static int potrs_blocked(const double* L, int n_pad, long lda, long strideL, con
     potrs_fwd_step_kernel<<<grid, 256, 0, stream>>>(L, n_pad, lda, strideL, Winv, B, Y, nrhs, j0);
   }
   for (int j0 = n_pad - 64; j0 >= 0; j0 -= 64) {
-    dim3 grid(j0 > 0 ? (j0 + 255) / 256 : 1, nv);
+    dim3 grid(j0 > 0 ? j0 / 64 : 1, nv);
     potrs_bwd_step_kernel<<<grid, 256, 0, stream>>>(L, n_pad, lda, strideL, Winv, Y, B, nrhs, j0);
   }
   cudaFreeAsync(Y, stream);
