@@ -82,6 +82,7 @@ _PROTOS = {
     "gpmpc_ut_sigma_3dof": (c_int, [c_int, c_double, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_combine_3dof": (c_int, [c_int, c_int, c_double, c_double, c_double, c_dp, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_tighten_bounds": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_double, c_double, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_propagate_tube": (c_int, [c_int, c_int, c_int, c_dp, c_long, c_long, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_propagate_cov": (c_int, [c_int, c_int, c_int, c_dp, c_long, c_long, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_step_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linearize_6dof": (c_int, [C.POINTER(Dyn6), c_int, c_dp, c_dp, c_dp, c_dp]),

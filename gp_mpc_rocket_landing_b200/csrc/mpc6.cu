@@ -444,6 +444,42 @@ __global__ void __launch_bounds__(256) propagate_cov_kernel(int nx, int N, const
   }
 }
 
+// Tube recursion e_{k+1} = |A_k| e_k + w_k (uncertainty_prop.py:435-470, safety/tube_mpc.py:104-183), any nx <= 32: one warp
+// per scenario, lane i owns component i; e_k is exchanged by shuffles.
+__global__ void __launch_bounds__(128) propagate_tube_kernel(int nx, int nbatch, int N, const double* __restrict__ A,
+                                                             long ld_row, long stage_stride,
+                                                             const double* __restrict__ w, double* __restrict__ tubes,
+                                                             const int* __restrict__ active) {
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  double e = 0.0;
+  double* out = tubes + (long)b * (N + 1) * nx;
+  if (lane < nx) out[lane] = 0.0;
+  for (int k = 0; k < N; ++k) {
+    const double* Ak = A + ((long)b * N + k) * stage_stride + (long)lane * ld_row;
+    double s = 0.0;
+    for (int j = 0; j < nx; ++j) {
+      const double ej = __shfl_sync(0xffffffffu, e, j);
+      if (lane < nx) s += fabs(Ak[j]) * ej;
+    }
+    if (lane < nx) {
+      s += w[((long)b * N + k) * nx + lane];
+      out[(long)(k + 1) * nx + lane] = s;
+    }
+    e = (lane < nx) ? s : 0.0;
+  }
+}
+
+extern "C" int gpmpc_propagate_tube(int nx, int B, int N, const double* A, long ld_row, long stage_stride, const double* w,
+                                    double* tubes, const int* active, void* stream) {
+  GPMPC_REQUIRE(nx >= 1 && nx <= 32 && B >= 0 && N >= 1 && A && w && tubes && ld_row >= nx,
+                "gpmpc_propagate_tube: need 1 <= nx <= 32, N >= 1, ld_row >= nx");
+  if (B == 0) return GPMPC_OK;
+  propagate_tube_kernel<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream>>>(nx, B, N, A, ld_row, stage_stride, w, tubes, active);
+  return gpmpc_check_launch("propagate_tube");
+}
+
 // lb' = lb + kappa sigma, ub' = ub - kappa sigma for the states of stages k >= 1; one thread per (scenario, variable).
 __global__ void __launch_bounds__(256) tighten_bounds_kernel(int nx, int nu, int N, long total, const double* __restrict__ lb,
                                                              const double* __restrict__ ub,

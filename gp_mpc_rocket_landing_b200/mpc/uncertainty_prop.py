@@ -221,3 +221,41 @@ class TubeBasedRobustness:
             w[11:14] += self.d_max * dt     # empty slice for the 7-state model
             widths[k + 1] = w
         return widths
+
+    # ---- batched device forms (7-state model) -----------------------------------------------------------------------
+    def _device_tube(self, X_nom, U_nom, dt, W):
+        torch = ge.torch_()
+        X, U = ge.to_dev(X_nom), ge.to_dev(U_nom)
+        B, N = U.shape[0], U.shape[1]
+        p = self.dynamics.params
+        g_vec = getattr(p, "g_vec", None)
+        dyn = me.make_dyn(p.alpha, np.asarray(g_vec if g_vec is not None else p.g_I, dtype=np.float64), dt)
+        Xp = X[:, :N].reshape(B * N, 7).contiguous()
+        Up = U.reshape(B * N, 3).contiguous()
+        AB = torch.empty((B * N, 7, 10), dtype=torch.float64, device=X.device)
+        me.linearize(dyn, Xp, Up, AB)
+        tubes = torch.empty((B, N + 1, 7), dtype=torch.float64, device=X.device)
+        ge.call("gpmpc_propagate_tube", 7, B, N, ge.ptr(AB), 10, 70, ge.ptr(W), ge.ptr(tubes), None, ge.stream())
+        return tubes
+
+    def compute_tube_batch(self, X_nom, U_nom, dt: float):
+        """`compute_tube` for B trajectories at once: X_nom (B,N+1,7), U_nom (B,N,3) -> (B,N+1,7) CUDA tensor
+        (Jacobians by `gpmpc_linearize_3dof`, recursion by `gpmpc_propagate_tube`)."""
+        torch = ge.torch_()
+        U = ge.to_dev(U_nom)
+        W = torch.zeros((U.shape[0], U.shape[1], 7), dtype=torch.float64, device=U.device)
+        W[:, :, 4:7] = self.d_max * dt
+        return self._device_tube(X_nom, U, dt, W)
+
+    def propagate_with_gp_batch(self, X_nom, U_nom, dt: float, gp_model, n_sigma: float = 2.0):
+        """GP-variance tubes (safety/tube_mpc.py:118-183) for B trajectories: w_k = n_sigma * sqrt(var_k) in the velocity rows,
+        variances from one batched `gp_model.predict_batch` over all (scenario, stage) points.
+        -> (tubes (B,N+1,7), gp_vars (B,N,3)) CUDA tensors."""
+        torch = ge.torch_()
+        X, U = ge.to_dev(X_nom), ge.to_dev(U_nom)
+        B, N = U.shape[0], U.shape[1]
+        _, var = gp_model.predict_batch(X[:, :N].reshape(B * N, 7).contiguous(), U.reshape(B * N, 3).contiguous())
+        var = ge.to_dev(var).reshape(B, N, 3)
+        W = torch.zeros((B, N, 7), dtype=torch.float64, device=U.device)
+        W[:, :, 4:7] = n_sigma * var.sqrt()
+        return self._device_tube(X, U, dt, W), var

@@ -319,6 +319,12 @@ int gpmpc_tighten_bounds(int nx, int nu, int B, int N, const double* lb, const d
                          double kappa, double max_variance, double* lb_out, double* ub_out, const int* active,
                          void* stream);
 
+/* Tube half-widths e_0 = 0, e_{k+1} = |A_k| e_k + w_k for B trajectories (uncertainty_prop.py:435-470 with
+ * w = d_max dt in the velocity / rate rows; safety/tube_mpc.py:118-183 with w = n_sigma * GP standard deviations).
+ * A as in gpmpc_propagate_cov; w: (B,N,nx); tubes: (B,N+1,nx). */
+int gpmpc_propagate_tube(int nx, int B, int N, const double* A, long ld_row, long stage_stride, const double* w,
+                         double* tubes, const int* active, void* stream);
+
 /* Linear covariance chain Sigma_0 = sigma0 I, Sigma_{k+1} = A_k Sigma_k A_k' + diag(qdiag[b,k]) for any nx <= 16:
  * uncertainty_prop.py:117-177 (the 14-state propagator GPMPC.solve calls at gp_mpc.py:283-289,347-351).  A: entry (i,j) of
  * the stage-(b,k) Jacobian at A[(b*N+k)*stage_stride + i*ld_row + j] (e.g. the [A|B] blocks of gpmpc_linearize_6dof with

@@ -351,3 +351,43 @@ def test_unscented_propagation_matches_reference(E):
     np.testing.assert_allclose(r0.covariances, co, rtol=1e-7, atol=1e-16)
     with pytest.raises(Exception):
         UncertaintyPropagator(Rocket3DoFDynamics(), gp, method="monte_carlo").propagate(g["x0"], g["Useq"])
+
+
+def test_tube_recursion_batched(E):
+    """gpmpc_propagate_tube (e_{k+1} = |A_k| e_k + w_k) against the host loop of uncertainty_prop.py:435-470, and the
+    GP-variance tubes of safety/tube_mpc.py:118-183 (w = n_sigma sqrt(var)) against the same loop fed the oracle variances."""
+    from oracle import gp as ogp, mpc as ompc
+    from gp_mpc_rocket_landing_b200 import workloads
+    from gp_mpc_rocket_landing_b200.dynamics import Rocket3DoFDynamics
+    from gp_mpc_rocket_landing_b200.gp import Simple3DoFGP
+    from gp_mpc_rocket_landing_b200.mpc.uncertainty_prop import TubeBasedRobustness
+    ge, me = E
+    rng = np.random.default_rng(6)
+    B, N = 6, 12
+    X0, _ = workloads.sample_initial_conditions(0, B)
+    X = np.zeros((B, N + 1, 7)); U = np.zeros((B, N, 3))
+    p = ompc.Rocket3DoFParams()
+    for b in range(B):
+        X[b, 0] = X0[b]
+        for k in range(N):
+            U[b, k] = [X0[b, 0] + 0.2 * rng.normal(), 0.2 * rng.normal(), 0.2 * rng.normal()]
+            X[b, k + 1] = ompc.step_3dof(X[b, k], U[b, k], 0.1, p)
+    dyn = Rocket3DoFDynamics()
+    tb = TubeBasedRobustness(dyn, d_max=0.3)
+    T = tb.compute_tube_batch(X, U, 0.1).cpu().numpy()
+    for b in range(B):
+        np.testing.assert_allclose(T[b], tb.compute_tube(X[b], U[b], 0.1), rtol=1e-13, atol=1e-16)
+    Xr, Ur, Dr = workloads.residual_dataset(200, seed=2)
+    gp = Simple3DoFGP(noise_variance=1e-2, use_sparse=False); gp.add_data(Xr, Ur, Dr); gp.fit()
+    o = ogp.Simple3DoFGPOracle(noise_variance=1e-2); o.add_data(Xr, Ur, Dr); o.fit()
+    Tg, var = tb.propagate_with_gp_batch(X, U, 0.1, gp, n_sigma=2.0)
+    Tg, var = Tg.cpu().numpy(), var.cpu().numpy()
+    for b in (0, 3, 5):
+        e = np.zeros(7)
+        for k in range(N):
+            A, _ = ompc.linearize_3dof(X[b, k], U[b, k], 0.1, p)
+            _, v = o.predict(X[b, k], U[b, k])
+            np.testing.assert_allclose(var[b, k], v, rtol=1e-8)
+            w = np.zeros(7); w[4:7] = 2.0 * np.sqrt(v)
+            e = np.abs(A) @ e + w
+            np.testing.assert_allclose(Tg[b, k + 1], e, rtol=1e-8, atol=1e-14)
