@@ -315,7 +315,7 @@ def run_b200_arm(args):
         barrier()
         t0 = time.perf_counter()
         for _ in range(Ke):
-            s = ctl.solve_batch(x, XT)          # H2D: x, XT ; D2H: u0, X_opt, U_opt, cost, flags
+            s = ctl.solve_batch(x, XT)          # H2D: x, XT ; D2H: u0, cost, flags (X_opt / U_opt on request)
             x = dyn.step_batch(x, s.u0, DT)     # H2D: x, u0 ; D2H: x_next
             # the termination rules of the Monte Carlo loop (experiments/monte_carlo.py:460-488), on the host copy:
             # finished scenarios restart from their initial condition, exactly as the device-resident loop respawns them
@@ -329,9 +329,12 @@ def run_b200_arm(args):
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
         h2d = B * (7 + 7 + 7 + 3) * 8
-        d2h = B * ((N_HORIZON + 1) * 7 + N_HORIZON * 3 + 1) * 8 + B * (4 + 1 + 1 + 4 + 4) + B * 7 * 8
+        # u0 (3) + cost (1) doubles, iteration / status / flag arrays, and the next state from step_batch; the planned
+        # trajectories X_opt / U_opt stay on the device until the caller reads them (BatchMPCSolution defers that copy)
+        d2h = B * (3 + 1) * 8 + B * (4 + 1 + 1 + 4 + 4) + B * 7 * 8
         e2e = {"value": world * B * Ke / float(te.item()), "unit": "solves/s", "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "steps": Ke, "timer": "host wall clock around synchronised steps"}
+               "d2h_bytes_per_step": d2h, "steps": Ke, "timer": "host wall clock around synchronised steps",
+               "result_read": "u0, cost, status / iteration flags, next state (trajectories on request)"}
 
     if rank == 0:
         # ---- rooflines: algorithmic work per launch / measured launch time ------------------------

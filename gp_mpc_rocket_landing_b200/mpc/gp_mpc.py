@@ -24,7 +24,7 @@ from ..gp import engine as ge
 from . import engine as me
 from .constraints import ConstraintParams, TightenedConstraints
 from .cost_functions import CostWeights
-from .nominal_mpc import BatchMPCSolution, MPCConfig, MPCSolution
+from .nominal_mpc import BatchMPCSolution, DeferredHostArray, MPCConfig, MPCSolution
 
 NX, NU = 7, 3
 
@@ -47,6 +47,8 @@ class GPMPCConfig(MPCConfig):
     # Extension (off = reference behaviour, which prepares the tightening and applies it at k = 0 only, gp_mpc.py:414):
     # tighten the state box of every stage k >= 1 of every scenario by kappa * sqrt(diag Sigma_k), kappa = Phi^-1(level)
     tighten_state_bounds: bool = False
+    # numpy-in calls: copy u0 / cost / flags to the host at once and X_opt / U_opt on first access (BatchMPCSolution)
+    defer_trajectory_copy: bool = True
     qp_max_iter: int = 1000           # config/mpc_params.yaml:48 (osqp_rti.py:53 uses 50, which rarely converges)
     qp_eps_abs: float = 1e-4          # osqp_rti.py:54
     qp_eps_rel: float = 1e-4          # osqp_rti.py:55
@@ -418,13 +420,21 @@ class GPMPC:
                 qp_status=st.ws.status.clone(), qp_iterations=st.qp_iters.clone(),
                 covariances=st.covs.clone() if has_cov else None)
         else:
-            t = dict(X=st.X, U=st.U, cost=st.cost, it=st.n_iter, ok=success, status=status, qs=st.ws.status,
-                     qi=st.qp_iters)
+            defer = self.config.defer_trajectory_copy and not with_cov
+            t = dict(cost=st.cost, it=st.n_iter, ok=success, status=status, qs=st.ws.status, qi=st.qp_iters)
+            if defer:
+                t["u0"] = st.U[:, 0].contiguous()
+            else:
+                t["X"], t["U"] = st.X, st.U
             if has_cov and with_cov:
                 t["cov"] = st.covs
             h = st.to_host(t)
+            if defer:
+                h["X"], h["U"] = DeferredHostArray(st.X.clone()), DeferredHostArray(st.U.clone())
+            else:
+                h["u0"] = h["U"][:, 0]
             sol = BatchMPCSolution(
-                u0=h["U"][:, 0], X_opt=h["X"], U_opt=h["U"], cost=h["cost"], iterations=h["it"], success=h["ok"],
+                u0=h["u0"], X_opt=h["X"], U_opt=h["U"], cost=h["cost"], iterations=h["it"], success=h["ok"],
                 status=h["status"], solve_time=0.0, qp_status=h["qs"], qp_iterations=h["qi"],
                 covariances=h.get("cov"))
         sol.solve_time = time.perf_counter() - t0

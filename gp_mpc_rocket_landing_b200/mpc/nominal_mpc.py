@@ -43,6 +43,16 @@ class MPCSolution:
         return self.U_opt[0]
 
 
+class DeferredHostArray:
+    """A device snapshot that becomes a numpy array the first time the owning solution's attribute is read."""
+
+    def __init__(self, tensor):
+        self.tensor = tensor
+
+    def fetch(self):
+        return self.tensor.cpu().numpy()
+
+
 @dataclass
 class BatchMPCSolution:
     """Result of `solve_batch` (new entry point): B independent `MPCSolution`s as arrays.
@@ -50,7 +60,9 @@ class BatchMPCSolution:
     u0 (B,3), X_opt (B,N+1,7), U_opt (B,N,3), cost (B,), iterations (B,) int, success (B,) bool,
     status (B,) int8 (1 = "Converged", 0 = "Max iterations"), qp_status (B,) int (OSQP code of the last QP),
     qp_iterations (B,) int (ADMM iterations summed over the SQP loop), covariances (B,N+1,7,7) or None.
-    numpy arrays when the inputs were numpy, CUDA tensors when they were CUDA tensors."""
+    numpy arrays when the inputs were numpy, CUDA tensors when they were CUDA tensors.  For numpy calls u0, cost and the
+    flags are copied to the host at once; X_opt / U_opt (7 MB at B = 4096) are device snapshots that turn into numpy arrays
+    on first access (`GPMPCConfig.defer_trajectory_copy`), since a closed loop reads u0 only."""
 
     u0: Any
     X_opt: Any
@@ -63,6 +75,15 @@ class BatchMPCSolution:
     qp_status: Any = None
     qp_iterations: Any = None
     covariances: Any = None
+
+    _DEFERRABLE = ("X_opt", "U_opt")
+
+    def __getattribute__(self, name):
+        v = object.__getattribute__(self, name)
+        if name in BatchMPCSolution._DEFERRABLE and isinstance(v, DeferredHostArray):
+            v = v.fetch()                       # host-buffer calls: the trajectories cross PCIe only when they are read
+            object.__setattr__(self, name, v)
+        return v
 
     def __len__(self):
         return self.u0.shape[0]
