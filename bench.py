@@ -284,7 +284,7 @@ def run_b200_arm(args):
     e0.record()
     for _ in range(K):
         sol = mc.step()
-        launches += ctl.last_kernel_launches + 1
+        launches += ctl.last_kernel_launches + 2   # + mc_step3_kernel + reset_scenarios_kernel (respawn)
         qp_it += sol.qp_iterations.sum()     # stays on the device: no host synchronisation inside the timed region
     e1.record()
     barrier()

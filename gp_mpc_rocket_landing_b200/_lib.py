@@ -79,6 +79,7 @@ _PROTOS = {
     "gpmpc_lml_grad_se": (c_int, [c_dp, c_int, c_int, c_int, c_int, c_double, c_double, c_dp, c_long, c_dp, c_long, c_int,
                                   c_dp, c_dp, c_dp]),
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_reset_scenarios": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_sigma_3dof": (c_int, [c_int, c_double, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_combine_3dof": (c_int, [c_int, c_int, c_double, c_double, c_double, c_dp, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_tighten_bounds": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_double, c_double, c_dp, c_dp, c_dp, c_dp]),

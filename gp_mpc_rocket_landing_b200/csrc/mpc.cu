@@ -834,6 +834,32 @@ extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double*
   return gpmpc_check_launch("pack_traj_3dof");
 }
 
+// Per-scenario controller reset (a fresh GPMPC instance for a respawned Monte Carlo run): hover warm start, zero duals,
+// rho back to "unset".  One thread per (scenario, element) of the longest array.
+__global__ void __launch_bounds__(256) reset_scenarios_kernel(int nbatch, int N, int nu, int m, const int* __restrict__ mask,
+                                                              const double* __restrict__ hover0, double* __restrict__ Uw,
+                                                              double* __restrict__ y, double* __restrict__ rho) {
+  const int per = max(m, N * nu);
+  const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (long)nbatch * per) return;
+  const int b = (int)(idx / per), e = (int)(idx - (long)b * per);
+  if (!mask[b]) return;
+  if (e < N * nu) Uw[(long)b * N * nu + e] = (e % nu == 0) ? hover0[b] : 0.0;
+  if (e < m) y[(long)b * m + e] = 0.0;
+  if (e == 0) rho[b] = 0.0;
+}
+
+extern "C" int gpmpc_reset_scenarios(int B, int N, int nu, int m, const int* mask, const double* hover0, double* U_warm,
+                                     double* y, double* rho, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && N >= 1 && nu >= 1 && m >= 1 && mask && hover0 && U_warm && y && rho,
+                "gpmpc_reset_scenarios: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  const long total = (long)B * (m > N * nu ? m : N * nu);
+  reset_scenarios_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, N, nu, m, mask, hover0, U_warm,
+                                                                                            y, rho);
+  return gpmpc_check_launch("reset_scenarios");
+}
+
 extern "C" int gpmpc_ut_sigma_3dof(int B, double scale, const double* xk, const double* Sk, const double* U, long ldu,
                                    double* SP, double* Usp, int* info, void* stream) {
   GPMPC_REQUIRE(B >= 0 && xk && Sk && U && SP && Usp && info, "gpmpc_ut_sigma_3dof: bad arguments");

@@ -215,12 +215,17 @@ class GPMPC:
         if st is None or not st.has_warm:
             return
         torch = ge.torch_()
-        mask = ge.to_dev(mask, torch.bool)
-        hover = torch.zeros_like(st.U_warm)
-        hover[:, :, 0] = (ge.to_dev(X0)[:, 0] * float(self.dynamics.params.g0))[:, None]
-        st.U_warm = torch.where(mask[:, None, None], hover, st.U_warm).contiguous()
-        st.ws.y.masked_fill_(mask[:, None], 0.0)
-        st.ws.rho.masked_fill_(mask, 0.0)
+        g0 = float(self.dynamics.params.g0)
+        if _is_dev(mask):
+            mask_d = mask.to(torch.int32).contiguous()
+            hover0 = (ge.to_dev(X0)[:, 0] * g0).contiguous()
+        else:   # host arrays: two small pinned H2D copies, one launch
+            mask_d = st.from_host("reset_mask", np.asarray(mask) != 0).to(torch.int32)
+            hover0 = st.from_host("reset_hover", np.asarray(X0, dtype=np.float64)[:, 0] * g0)
+        if not st.U_warm.is_contiguous():
+            st.U_warm = st.U_warm.contiguous()
+        ge.call("gpmpc_reset_scenarios", st.B, st.N, NU, st.ws.y.shape[1], ge.ptr(mask_d), ge.ptr(hover0),
+                ge.ptr(st.U_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), ge.stream())
 
     def _settings(self):
         c = self.config

@@ -243,6 +243,12 @@ int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_ste
 /* z = [x_0,u_0,...,x_N] from (X, U): OSQPRTIMPC._solution_to_vector, osqp_rti.py:601-614 (primal warm start). */
 int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active, void* stream);
 
+/* Per-scenario reset of the batched controller state for respawned Monte Carlo runs (a new GPMPC per run in the reference,
+ * monte_carlo.py:606-616): where mask[b] != 0, U_warm[b] <- hover (first control component hover0[b], others 0), the ADMM
+ * duals y[b] (m) <- 0 and rho[b] <- 0 (= take the configured default). */
+int gpmpc_reset_scenarios(int B, int N, int nu, int m, const int* mask, const double* hover0, double* U_warm, double* y,
+                          double* rho, void* stream);
+
 /* Unscented propagation (uncertainty_prop.py:179-264), 7-state model, one stage at a time:
  * gpmpc_ut_sigma_3dof: SP[b] (15 x 7) = x_k, x_k + columns, x_k - columns of chol(scale * Sigma_k + 1e-10 I), and the stage
  * control repeated 15 times in Usp (the layout gpmpc_rollout_3dof takes with N = 1); info[0] = b + 1 of a scenario whose
