@@ -13,20 +13,6 @@ X0, XT = workloads.sample_initial_conditions(0, a.batch)
 x = X0.copy()
 for _ in range(10):
     s = ctl.solve_batch(x, XT); x = dyn.step_batch(x, s.u0, bench.DT)
-from gp_mpc_rocket_landing_b200.gp import engine as ge
-lines = {}
-def reset_timed(mask):
-    st = ctl._batch
-    marks = [time.perf_counter()]
-    m = ge.to_dev(mask, torch.bool); marks.append(time.perf_counter())
-    hover = torch.zeros_like(st.U_warm); marks.append(time.perf_counter())
-    xd = ge.to_dev(X0); marks.append(time.perf_counter())
-    hover[:, :, 0] = (xd[:, 0] * 1.0)[:, None]; marks.append(time.perf_counter())
-    st.U_warm = torch.where(m[:, None, None], hover, st.U_warm).contiguous(); marks.append(time.perf_counter())
-    st.ws.y.masked_fill_(m[:, None], 0.0); marks.append(time.perf_counter())
-    st.ws.rho.masked_fill_(m, 0.0); marks.append(time.perf_counter())
-    for i, nm in enumerate(["mask", "zeros", "x0", "fill", "where", "y", "rho"]):
-        lines[nm] = lines.get(nm, 0.0) + marks[i + 1] - marks[i]
 t = {"solve_batch": 0.0, "step_batch": 0.0, "respawn": 0.0}
 K = 40
 torch.cuda.synchronize(); T0 = time.perf_counter()
@@ -45,4 +31,3 @@ for _ in range(K):
     t["reset_scenarios"] = t.get("reset_scenarios", 0.0) + t3 - t2c; t["n_done"] = t.get("n_done", 0) + int(done.sum()) / 1e3 * K
 tot = time.perf_counter() - T0
 print({k: round(1e3 * v / K, 3) for k, v in t.items()}, "total ms/step", round(1e3 * tot / K, 3))
-print({k: round(1e3 * v / K, 3) for k, v in lines.items()})
