@@ -157,7 +157,7 @@ extern "C" int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int bat
   // Two-level blocking: 64-wide right-looking steps INSIDE a 256-wide outer panel (their rank-64 updates touch the panel
   // columns only), then ONE rank-256 update of the trailing matrix per outer panel.  The trailing matrix is streamed
   // through HBM n/256 times instead of n/64 times and its GEMM runs a 16-step k-loop instead of 4.
-  constexpr int NB = 512;
+  constexpr int NB = 512;   // measured at n = 8000, 16 matrices: NB 256 / 512 / 1024 -> 129.8 / 123.6 / 126.6 ms
   for (int K0 = 0; K0 < n_pad; K0 += NB) {
     const int Kend = (K0 + NB < n_pad) ? K0 + NB : n_pad;
     for (int k0 = K0; k0 < Kend; k0 += 64) {
