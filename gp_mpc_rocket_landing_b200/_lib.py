@@ -60,6 +60,43 @@ class ExactModel(C.Structure):
     ]
 
 
+class Solve3(C.Structure):
+    """GpmpcSolve3: the plan of one fused batched solve (gpmpc_solve_batch_3dof); field order = include/gpmpc_b200.h."""
+    _fields_ = [
+        ("B", c_int), ("N", c_int), ("max_sqp_iter", c_int), ("use_gp_mean", c_int), ("use_gp_uncertainty", c_int),
+        ("repropagate", c_int), ("target_mode", c_int), ("has_model", c_int),
+        ("dyn", Dyn3), ("g0", c_double), ("admm", AdmmSettings), ("model", ExactModel),
+        ("Linv", c_dp), ("ldi", c_long), ("tighten_kappa", c_double), ("tighten_max_variance", c_double),
+        ("x0", c_dp), ("x_target", c_dp), ("X_ref", c_dp), ("ld_xref_in", c_long), ("U_ref", c_dp), ("ld_uref", c_long),
+        ("active_in", c_dp),
+        ("Pdiag", c_dp), ("lb", c_dp), ("ub", c_dp), ("Qd", c_dp), ("Qfd", c_dp), ("Rd", c_dp),
+        ("x_ref", c_dp), ("X", c_dp), ("U", c_dp), ("Xs", c_dp), ("dmean", c_dp), ("dmean_s", c_dp),
+        ("Ks", c_dp), ("ldk", c_long), ("q_pad", c_int),
+        ("var_work", c_dp), ("sumsq", c_dp), ("dvar", c_dp), ("covs", c_dp), ("lb_t", c_dp), ("ub_t", c_dp),
+        ("AB", c_dp), ("beq", c_dp), ("q", c_dp),
+        ("cost", c_dp), ("converged", c_dp), ("active", c_dp), ("n_iter", c_dp), ("qp_iters", c_dp),
+        ("z", c_dp), ("y", c_dp), ("rho", c_dp), ("obj", c_dp), ("pri", c_dp), ("dua", c_dp), ("qp_status", c_dp),
+        ("qp_it", c_dp),
+        ("U_warm", c_dp), ("X_warm", c_dp), ("has_warm", c_dp),
+        ("events", C.POINTER(C.c_void_p)), ("event_phase", C.POINTER(c_int)), ("event_cap", c_int),
+        ("event_count", C.POINTER(c_int)),
+    ]
+
+
+class McStep3(C.Structure):
+    """GpmpcMcStep3: arguments of gpmpc_mc_advance_3dof."""
+    _fields_ = [
+        ("B", c_int), ("N", c_int), ("m", c_int), ("dyn", Dyn3), ("drag_cda", c_double),
+        ("max_steps", c_int), ("fail_policy", c_int), ("respawn", c_int), ("classify_only", c_int),
+        ("x", c_dp), ("u", c_dp), ("ldu", c_long), ("success", c_dp), ("m0", c_dp), ("x_init", c_dp),
+        ("t_step", c_dp), ("active", c_dp), ("outcome", c_dp), ("fail_steps", c_dp), ("x_final", c_dp), ("counts", c_dp),
+        ("has_warm", c_dp), ("y", c_dp), ("rho", c_dp),
+    ]
+
+
+PHASE_NAMES = ("begin", "prologue", "rollout", "gp_variance", "cov", "gp_mean", "assemble", "admm", "update", "mc")
+
+
 _PROTOS = {
     "gpmpc_version": (c_int, []),
     "gpmpc_last_error": (C.c_char_p, []),
@@ -79,7 +116,7 @@ _PROTOS = {
     "gpmpc_lml_grad_se": (c_int, [c_dp, c_int, c_int, c_int, c_int, c_double, c_double, c_dp, c_long, c_dp, c_long, c_int,
                                   c_dp, c_dp, c_dp]),
     "gpmpc_trsm_sumsq": (c_int, [c_dp, c_int, c_long, c_dp, c_dp, c_int, c_long, c_dp, c_dp]),
-    "gpmpc_reset_scenarios": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_reset_scenarios": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_sigma_3dof": (c_int, [c_int, c_double, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_ut_combine_3dof": (c_int, [c_int, c_int, c_double, c_double, c_double, c_dp, c_dp, c_double, c_dp, c_dp, c_dp]),
     "gpmpc_tighten_bounds": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_double, c_double, c_dp, c_dp, c_dp, c_dp]),
@@ -124,6 +161,13 @@ _PROTOS = {
                                          c_dp]),
     "gpmpc_qp_assemble_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long,
                                        c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_linv_sumsq_parts": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_solve_batch_3dof": (c_int, [C.POINTER(Solve3), C.POINTER(c_int), c_dp]),
+    "gpmpc_mc_advance_3dof": (c_int, [C.POINTER(McStep3), c_dp]),
+    "gpmpc_struct_layout": (c_long, [c_int, c_int]),
+    "gpmpc_events_create": (c_int, [c_int, C.POINTER(C.c_void_p)]),
+    "gpmpc_events_destroy": (c_int, [c_int, C.POINTER(C.c_void_p)]),
+    "gpmpc_events_elapsed_ms": (c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]),
     "gpmpc_mpc_update_3dof": (c_int, [c_int, c_int, c_int, c_dp, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp,
                                       c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
 }

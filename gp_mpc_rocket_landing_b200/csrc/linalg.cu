@@ -569,6 +569,20 @@ __global__ void sum_parts_kernel(const double* __restrict__ part, int nparts, lo
   out[i] = s;
 }
 
+// The triangular GEMM alone: per-tile partial sums work[t * q_pad + q], t < n_pad / 64 (the fused step reduces them inside
+// its variance / covariance kernel, in the same fixed order as sum_parts_kernel).
+extern "C" int gpmpc_linv_sumsq_parts(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk,
+                                      double* work, void* stream_) {
+  GPMPC_REQUIRE(n_pad % 128 == 0 && q_pad % 128 == 0, "gpmpc_linv_sumsq_parts: n_pad and q_pad must be multiples of 128");
+  GPMPC_REQUIRE(Linv && Ks && work, "gpmpc_linv_sumsq_parts: NULL buffer");
+  GemmParams p{};
+  p.A = Linv; p.lda = ldi;
+  p.B = Ks; p.ldb = ldk;
+  p.M = n_pad; p.N = q_pad; p.K = n_pad; p.alpha = 1.0; p.beta = 0.0;
+  p.k_tri = 1; p.m_fast = 1; p.epi = EPI_SUMSQ_PART; p.sumsq = work; p.part_stride = q_pad;
+  return launch_dgemm_nt<64, 128, 2, 4>(p, 1, (cudaStream_t)stream_);
+}
+
 extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk,
                                 double* work, double* sumsq, int one_cta_per_sm, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

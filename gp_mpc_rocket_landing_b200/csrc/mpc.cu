@@ -541,7 +541,8 @@ __global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nb
                                                            const double* __restrict__ Qd,
                                                            const double* __restrict__ Qfd, double* __restrict__ AB,
                                                            double* __restrict__ beq, double* __restrict__ q,
-                                                           const int* __restrict__ active) {
+                                                           const int* __restrict__ active,
+                                                           double* __restrict__ zpack) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= nbatch * (N + 1)) return;
   const int b = idx / (N + 1), k = idx - b * (N + 1);
@@ -549,6 +550,14 @@ __global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nb
   const int n = N * NS + NX, neq = NX * (N + 1);
   const double* xr = x_ref + (long)b * ldxref + (long)k * NX;
   double* qb = q + (long)b * n + (long)k * NS;
+  if (zpack) {  // primal warm start z = [x_0,u_0,...,x_N] (osqp_rti.py:601-614), fused: one launch less per SQP iteration
+    double* zb = zpack + (long)b * n + (long)k * NS;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) zb[i] = X_lin[((long)b * (N + 1) + k) * NX + i];
+    if (k < N)
+#pragma unroll
+      for (int i = 0; i < NU; ++i) zb[NX + i] = U_lin[((long)b * N + k) * NU + i];
+  }
   if (k == N) {
 #pragma unroll
     for (int i = 0; i < NX; ++i) {
@@ -685,24 +694,18 @@ __global__ void __launch_bounds__(128) mc_step3_kernel(GpmpcDyn3 dyn, int nbatch
 
 // ------------------------------------------------------------------------------------------------ post-QP update
 // One warp per scenario.  mode 0 = RTI (osqp_rti.py:532-552), mode 1 = GP-MPC SQP iteration (gp_mpc.py:336-345).
-__global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int mode, const double* __restrict__ z,
-                                                          const int* __restrict__ qp_status,
-                                                          const double* __restrict__ x_ref, long ldxref,
-                                                          const double* __restrict__ Qd,
-                                                          const double* __restrict__ Qfd,
-                                                          const double* __restrict__ Rd, double* __restrict__ X,
-                                                          double* __restrict__ U, double* __restrict__ X_prev,
-                                                          double* __restrict__ U_prev, double* __restrict__ cost,
-                                                          int* __restrict__ converged, int* __restrict__ active,
-                                                          int* __restrict__ n_iter) {
-  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-  if (b >= nbatch) return;
-  if (active && !active[b]) return;
+__device__ __forceinline__ void mpc_update3_body(int b, int lane, int N, int mode, const double* __restrict__ z,
+                                                 const int* __restrict__ qp_status, const double* __restrict__ x_ref,
+                                                 long ldxref, const double* __restrict__ Qd,
+                                                 const double* __restrict__ Qfd, const double* __restrict__ Rd,
+                                                 double* __restrict__ Xb, double* __restrict__ Ub,
+                                                 double* __restrict__ X_prev, double* __restrict__ U_prev,
+                                                 double* __restrict__ cost, int* __restrict__ converged,
+                                                 int* __restrict__ active, int* __restrict__ n_iter,
+                                                 const int* __restrict__ qp_it, int* __restrict__ qp_iters) {
   const int n = N * NS + NX;
   const bool solved = qp_status[b] == GPMPC_QP_SOLVED;
   const double* zb = z + (long)b * n;
-  double* Xb = X + (long)b * (N + 1) * NX;
-  double* Ub = U + (long)b * N * NU;
   double dmaxx = 0.0, dmaxu = 0.0, cs = 0.0;
   if (solved) {
     for (int j = lane; j < n; j += 32) {
@@ -737,6 +740,7 @@ __global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int
   cs = warp_sum(cs);
   if (lane == 0) {
     cost[b] = solved ? cs : INFINITY;
+    if (qp_iters && qp_it) qp_iters[b] += qp_it[b];
     if (mode == 0) {
       converged[b] = solved ? 1 : 0;
     } else {
@@ -746,6 +750,231 @@ __global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int
       if (conv && active) active[b] = 0;
     }
   }
+}
+
+__global__ void __launch_bounds__(128) mpc_update3_kernel(int nbatch, int N, int mode, const double* __restrict__ z,
+                                                          const int* __restrict__ qp_status,
+                                                          const double* __restrict__ x_ref, long ldxref,
+                                                          const double* __restrict__ Qd,
+                                                          const double* __restrict__ Qfd,
+                                                          const double* __restrict__ Rd, double* __restrict__ X,
+                                                          double* __restrict__ U, double* __restrict__ X_prev,
+                                                          double* __restrict__ U_prev, double* __restrict__ cost,
+                                                          int* __restrict__ converged, int* __restrict__ active,
+                                                          int* __restrict__ n_iter,
+                                                          const int* __restrict__ qp_it, int* __restrict__ qp_iters,
+                                                          double* __restrict__ U_warm, double* __restrict__ X_warm,
+                                                          int* __restrict__ has_warm) {
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (b >= nbatch) return;
+  double* Xb = X + (long)b * (N + 1) * NX;
+  double* Ub = U + (long)b * N * NU;
+  const bool act = !(active && !active[b]);
+  if (U_warm) {  // last SQP iteration: the iterate of EVERY scenario becomes its next warm start (gp_mpc.py:355-357)
+    if (act) {
+      mpc_update3_body(b, lane, N, mode, z, qp_status, x_ref, ldxref, Qd, Qfd, Rd, Xb, Ub, X_prev, U_prev, cost, converged,
+                       active, n_iter, qp_it, qp_iters);
+      __syncwarp();
+    }
+    for (int j = lane; j < N * NU; j += 32) U_warm[(long)b * N * NU + j] = Ub[j];
+    if (X_warm)
+      for (int j = lane; j < (N + 1) * NX; j += 32) X_warm[(long)b * (N + 1) * NX + j] = Xb[j];
+    if (has_warm && lane == 0) has_warm[b] = 1;
+    return;
+  }
+  if (!act) return;
+  mpc_update3_body(b, lane, N, mode, z, qp_status, x_ref, ldxref, Qd, Qfd, Rd, Xb, Ub, X_prev, U_prev, cost, converged,
+                   active, n_iter, qp_it, qp_iters);
+}
+
+
+// ------------------------------------------------------------------------------------------------ fused-step kernels
+// Prologue of one batched solve, one thread per (scenario, stage row k <= N): the reference trajectory row (a given X_ref,
+// the tiled target of gp_mpc.py:236-245, or the per-step target the Monte Carlo loop derives for `.solve` controllers,
+// monte_carlo.py:497-499), the initial controls (warm start | U_ref | hover along axis 0, gp_mpc.py:266-275) and the
+// per-scenario flags.
+__global__ void __launch_bounds__(128) solve_prologue3_kernel(int nbatch, int N, int target_mode, double g0,
+                                                              const double* __restrict__ x0,
+                                                              const double* __restrict__ x_target,
+                                                              const double* __restrict__ X_ref, long ld_xref_in,
+                                                              const double* __restrict__ U_ref, long ld_uref,
+                                                              const int* __restrict__ active_in,
+                                                              const int* __restrict__ has_warm,
+                                                              const double* __restrict__ U_warm,
+                                                              double* __restrict__ x_ref, double* __restrict__ U,
+                                                              int* __restrict__ active, int* __restrict__ n_iter,
+                                                              int* __restrict__ qp_iters, int* __restrict__ converged) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nbatch * (N + 1)) return;
+  const int b = idx / (N + 1), k = idx - b * (N + 1);
+  double* xr = x_ref + ((long)b * (N + 1) + k) * NX;
+  if (X_ref) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xr[i] = X_ref[(long)b * ld_xref_in + (long)k * NX + i];
+  } else if (target_mode == 0) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) xr[i] = x_target[(long)b * NX + i];
+  } else {  // monte_carlo.py:497-499: x_target = x; x_target[4:7] = 0; x_target[1] = max(0.5, altitude - 2.0)
+    const double* x = x0 + (long)b * NX;
+    xr[0] = x[0];
+    xr[1] = fmax(0.5, x[1] - 2.0);
+    xr[2] = x[2];
+    xr[3] = x[3];
+    xr[4] = xr[5] = xr[6] = 0.0;
+  }
+  if (k < N) {
+    double* u = U + ((long)b * N + k) * NU;
+    if (has_warm && has_warm[b]) {
+#pragma unroll
+      for (int i = 0; i < NU; ++i) u[i] = U_warm[((long)b * N + k) * NU + i];
+    } else if (U_ref) {
+#pragma unroll
+      for (int i = 0; i < NU; ++i) u[i] = U_ref[(long)b * ld_uref + (long)k * NU + i];
+    } else {
+      u[0] = x0[(long)b * NX] * g0;
+      u[1] = 0.0;
+      u[2] = 0.0;
+    }
+  } else {
+    active[b] = active_in ? (active_in[b] != 0) : 1;
+    n_iter[b] = 0;
+    qp_iters[b] = 0;
+    converged[b] = 0;
+  }
+}
+
+// GP variances from the per-tile partial sums of |L^-1 k*|^2 (fixed summation order, as sum_parts_kernel), the floor and
+// the output scale of exact_gp.py:259-263 (as predict_var_kernel), then the covariance chain of propagate_cov3_kernel:
+// one launch instead of three, same arithmetic.
+__global__ void __launch_bounds__(128) var_cov3_kernel(GpmpcDyn3 dyn, int nbatch, int N, const double* __restrict__ part,
+                                                       int nparts, long part_stride, double prior, double floor_,
+                                                       const double* __restrict__ ystd, double sigma0,
+                                                       const double* __restrict__ X, const double* __restrict__ U,
+                                                       double* __restrict__ dvar, double* __restrict__ covs,
+                                                       const int* __restrict__ active) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  double S[NX][NX], Mx[NX][NX];
+#pragma unroll
+  for (int i = 0; i < NX; ++i)
+#pragma unroll
+    for (int j = 0; j < NX; ++j) S[i][j] = (i == j) ? sigma0 : 0.0;
+  double* out = covs + (long)b * (N + 1) * NX * NX;
+#pragma unroll
+  for (int i = 0; i < NX; ++i)
+#pragma unroll
+    for (int j = 0; j < NX; ++j) out[i * NX + j] = S[i][j];
+  double ys2[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) ys2[i] = ystd[i] * ystd[i];
+  for (int k = 0; k < N; ++k) {
+    const long qrow = (long)b * N + k;
+    double ss = 0.0;
+    for (int t = 0; t < nparts; ++t) ss += part[(long)t * part_stride + qrow];
+    const double vq = fmax(prior - ss, floor_);
+    double v[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      v[i] = vq * ys2[i];
+      dvar[qrow * 3 + i] = v[i];
+    }
+    const double* x = X + ((long)b * (N + 1) + k) * NX;
+    const double* u = U + ((long)b * N + k) * NU;
+    const double m = x[0];
+    double a[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) a[i] = -u[i] / (m * m) * dyn.dt;
+#pragma unroll
+    for (int j = 0; j < NX; ++j) {
+      Mx[0][j] = S[0][j];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        Mx[1 + i][j] = S[1 + i][j] + dyn.dt * S[4 + i][j];
+        Mx[4 + i][j] = a[i] * S[0][j] + S[4 + i][j];
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < NX; ++r) {
+      S[r][0] = Mx[r][0];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        S[r][1 + i] = Mx[r][1 + i] + Mx[r][4 + i] * dyn.dt;
+        S[r][4 + i] = Mx[r][0] * a[i] + Mx[r][4 + i];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 3; ++i) S[4 + i][4 + i] = S[4 + i][4 + i] + v[i] * (dyn.dt * dyn.dt);  // uncertainty_prop.py:157-160
+    double* o = out + (long)(k + 1) * NX * NX;
+#pragma unroll
+    for (int i = 0; i < NX; ++i)
+#pragma unroll
+      for (int j = 0; j < NX; ++j) o[i * NX + j] = S[i][j];
+  }
+}
+
+// Closed-loop advance (see GpmpcMcStep3 in the header), one thread per scenario.
+__global__ void __launch_bounds__(128) mc_advance3_kernel(GpmpcMcStep3 a) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= a.B) return;
+  if (!a.active[b]) return;
+  double xl[NX], xn[NX];
+#pragma unroll
+  for (int d = 0; d < NX; ++d) xl[d] = a.x[(long)b * NX + d];
+  int code = 0;
+  bool stepped = false;
+  if (a.classify_only) {
+    code = classify3(xl, a.m0[b]);
+#pragma unroll
+    for (int d = 0; d < NX; ++d) xn[d] = xl[d];
+  } else {
+    const bool ok = a.success == nullptr || a.success[b] != 0;
+    if (!ok && a.fail_steps) a.fail_steps[b] += 1;
+    if (!ok && a.fail_policy == 1) {  // monte_carlo.py:507-510: "MPC solve failed" -> DIVERGENCE, no plant step
+      code = 6;
+#pragma unroll
+      for (int d = 0; d < NX; ++d) xn[d] = xl[d];
+    } else {
+      double ul[NU];
+#pragma unroll
+      for (int d = 0; d < NU; ++d) ul[d] = a.u[(long)b * a.ldu + d];
+      step3(xl, ul, a.dyn, xn);
+      if (a.drag_cda != 0.0) {
+        const double rho = 1.225 * exp(-xl[1] / 8500.0);
+        const double sp = sqrt(xl[4] * xl[4] + xl[5] * xl[5] + xl[6] * xl[6]);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + a.dyn.dt * (-0.5 * rho * a.drag_cda * sp * xl[4 + i] / xl[0]);
+      }
+      stepped = true;
+      const int t = a.t_step[b] + 1;
+      a.t_step[b] = t;
+      // the reference classifies x_0 .. x_{max_steps-1} at the top of its loop; the state after the last plant step is
+      // not inspected: for/else -> TIMEOUT (monte_carlo.py:455,539-542)
+      code = (t >= a.max_steps) ? 5 : classify3(xn, a.m0[b]);
+    }
+  }
+  if (stepped)
+#pragma unroll
+    for (int d = 0; d < NX; ++d) a.x[(long)b * NX + d] = xn[d];
+  if (code == 0) return;
+  a.outcome[b] = code;
+  if (a.x_final)
+#pragma unroll
+    for (int d = 0; d < NX; ++d) a.x_final[(long)b * NX + d] = xn[d];
+  if (a.counts) atomicAdd(a.counts + code, 1ULL);
+  if (!a.respawn) {
+    a.active[b] = 0;
+    return;
+  }
+  // respawn: the next run of this slot starts from its initial condition with a fresh controller (monte_carlo.py:606-616
+  // builds the loop around run_single; GPMPC.reset_warm_start semantics per scenario)
+#pragma unroll
+  for (int d = 0; d < NX; ++d) a.x[(long)b * NX + d] = a.x_init[(long)b * NX + d];
+  a.t_step[b] = 0;
+  if (a.has_warm) a.has_warm[b] = 0;
+  if (a.rho) a.rho[b] = 0.0;
+  if (a.y)
+    for (int e = 0; e < a.m; ++e) a.y[(long)b * a.m + e] = 0.0;
 }
 
 }  // namespace
@@ -838,25 +1067,28 @@ extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double*
 // rho back to "unset".  One thread per (scenario, element) of the longest array.
 __global__ void __launch_bounds__(256) reset_scenarios_kernel(int nbatch, int N, int nu, int m, const int* __restrict__ mask,
                                                               const double* __restrict__ hover0, double* __restrict__ Uw,
-                                                              double* __restrict__ y, double* __restrict__ rho) {
+                                                              double* __restrict__ y, double* __restrict__ rho,
+                                                              int* __restrict__ has_warm) {
   const int per = max(m, N * nu);
   const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= (long)nbatch * per) return;
   const int b = (int)(idx / per), e = (int)(idx - (long)b * per);
   if (!mask[b]) return;
-  if (e < N * nu) Uw[(long)b * N * nu + e] = (e % nu == 0) ? hover0[b] : 0.0;
+  if (Uw && hover0 && e < N * nu) Uw[(long)b * N * nu + e] = (e % nu == 0) ? hover0[b] : 0.0;
   if (e < m) y[(long)b * m + e] = 0.0;
-  if (e == 0) rho[b] = 0.0;
+  if (e == 0) {
+    rho[b] = 0.0;
+    if (has_warm) has_warm[b] = 0;
+  }
 }
 
 extern "C" int gpmpc_reset_scenarios(int B, int N, int nu, int m, const int* mask, const double* hover0, double* U_warm,
-                                     double* y, double* rho, void* stream) {
-  GPMPC_REQUIRE(B >= 0 && N >= 1 && nu >= 1 && m >= 1 && mask && hover0 && U_warm && y && rho,
-                "gpmpc_reset_scenarios: bad arguments");
+                                     double* y, double* rho, int* has_warm, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && N >= 1 && nu >= 1 && m >= 1 && mask && y && rho, "gpmpc_reset_scenarios: bad arguments");
   if (B == 0) return GPMPC_OK;
   const long total = (long)B * (m > N * nu ? m : N * nu);
   reset_scenarios_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(B, N, nu, m, mask, hover0, U_warm,
-                                                                                            y, rho);
+                                                                                            y, rho, has_warm);
   return gpmpc_check_launch("reset_scenarios");
 }
 
@@ -898,7 +1130,8 @@ extern "C" int gpmpc_qp_assemble_3dof(const GpmpcDyn3* dyn, int B, int N, int li
   const int total = B * (N + 1);
   GPMPC_PREFER_SHARED(qp_assemble3_kernel);
   qp_assemble3_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-      *dyn, B, N, lin_mode, rhs_mode, X_lin, U_lin, x_init, x_ref, ldxref, c_gp, Qdiag, Qfdiag, AB, beq, q, active);
+      *dyn, B, N, lin_mode, rhs_mode, X_lin, U_lin, x_init, x_ref, ldxref, c_gp, Qdiag, Qfdiag, AB, beq, q, active,
+      nullptr);
   return gpmpc_check_launch("qp_assemble_3dof");
 }
 
@@ -911,6 +1144,220 @@ extern "C" int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, co
   GPMPC_PREFER_SHARED(mpc_update3_kernel);
   mpc_update3_kernel<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream>>>(B, N, mode, z, qp_status, x_ref, ldxref, Qdiag,
                                                                      Qfdiag, Rdiag, X, U, X_prev, U_prev, cost,
-                                                                     converged, active, n_iter);
+                                                                     converged, active, n_iter, nullptr, nullptr, nullptr,
+                                                                     nullptr, nullptr);
   return gpmpc_check_launch("mpc_update_3dof");
+}
+
+// ================================================================================================== fused step (C ABI)
+extern "C" int gpmpc_events_create(int n, void** events_out) {
+  GPMPC_REQUIRE(n >= 0 && (n == 0 || events_out), "gpmpc_events_create: bad arguments");
+  for (int i = 0; i < n; ++i) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) {
+      gpmpc_set_error("gpmpc_events_create: cudaEventCreate failed");
+      return GPMPC_ERR_CUDA;
+    }
+    events_out[i] = (void*)e;
+  }
+  return GPMPC_OK;
+}
+
+extern "C" int gpmpc_events_destroy(int n, void** events) {
+  for (int i = 0; i < n; ++i)
+    if (events && events[i]) cudaEventDestroy((cudaEvent_t)events[i]);
+  return GPMPC_OK;
+}
+
+extern "C" int gpmpc_events_elapsed_ms(void* a, void* b, float* ms_out) {
+  GPMPC_REQUIRE(a && b && ms_out, "gpmpc_events_elapsed_ms: bad arguments");
+  if (cudaEventSynchronize((cudaEvent_t)b) != cudaSuccess || cudaEventElapsedTime(ms_out, (cudaEvent_t)a, (cudaEvent_t)b) != cudaSuccess) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_events_elapsed_ms: event not recorded");
+    return GPMPC_ERR_CUDA;
+  }
+  return GPMPC_OK;
+}
+
+extern "C" int gpmpc_mc_advance_3dof(const GpmpcMcStep3* a, void* stream) {
+  GPMPC_REQUIRE(a != nullptr && a->B >= 0, "gpmpc_mc_advance_3dof: bad arguments");
+  GPMPC_REQUIRE(a->x && a->m0 && a->t_step && a->active && a->outcome, "gpmpc_mc_advance_3dof: NULL state buffer");
+  GPMPC_REQUIRE(a->classify_only || a->u, "gpmpc_mc_advance_3dof: u is NULL");
+  GPMPC_REQUIRE(!a->respawn || a->x_init, "gpmpc_mc_advance_3dof: respawn needs x_init");
+  if (a->B == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(mc_advance3_kernel);
+  mc_advance3_kernel<<<(a->B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*a);
+  return gpmpc_check_launch("mc_advance_3dof");
+}
+
+namespace {
+struct PhaseRec {
+  const GpmpcSolve3* p;
+  cudaStream_t s;
+  void mark(int phase) const {
+    if (!p->events || !p->event_count) return;
+    const int i = *p->event_count;
+    if (i >= p->event_cap) return;
+    cudaEventRecord((cudaEvent_t)p->events[i], s);
+    p->event_phase[i] = phase;
+    *p->event_count = i + 1;
+  }
+};
+}  // namespace
+
+extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, void* stream_) {
+  GPMPC_REQUIRE(p != nullptr && p->B >= 0 && p->N >= 1 && p->max_sqp_iter >= 1, "gpmpc_solve_batch_3dof: bad arguments");
+  GPMPC_REQUIRE(p->x0 && p->x_ref && p->X && p->U && p->AB && p->beq && p->q && p->z && p->y && p->rho,
+                "gpmpc_solve_batch_3dof: NULL state buffer");
+  GPMPC_REQUIRE(p->target_mode == 1 || p->x_target || p->X_ref, "gpmpc_solve_batch_3dof: no target");
+  cudaStream_t s = (cudaStream_t)stream_;
+  const int B = p->B, N = p->N;
+  int launches = 0;
+  if (n_launches) *n_launches = 0;
+  if (B == 0) return GPMPC_OK;
+  const bool use_mean = p->has_model && p->use_gp_mean;
+  const bool use_unc = p->has_model && p->use_gp_uncertainty;
+  GPMPC_REQUIRE(!use_unc || (p->Ks && p->sumsq && p->dvar && p->covs), "gpmpc_solve_batch_3dof: uncertainty buffers are NULL");
+  GPMPC_REQUIRE(!use_unc || p->Linv == nullptr || p->var_work, "gpmpc_solve_batch_3dof: var_work is NULL");
+  GPMPC_REQUIRE(!p->has_model || p->dmean, "gpmpc_solve_batch_3dof: dmean is NULL");
+  const bool tighten = use_unc && p->tighten_kappa > 0.0;
+  GPMPC_REQUIRE(!tighten || (p->lb_t && p->ub_t), "gpmpc_solve_batch_3dof: tightened boxes are NULL");
+  PhaseRec rec{p, s};
+  const int total = B * (N + 1);
+  int rc;
+  rec.mark(GPMPC_PHASE_BEGIN);
+  GPMPC_PREFER_SHARED(solve_prologue3_kernel);
+  solve_prologue3_kernel<<<(total + 127) / 128, 128, 0, s>>>(B, N, p->target_mode, p->g0, p->x0, p->x_target, p->X_ref,
+                                                             p->ld_xref_in, p->U_ref, p->ld_uref, p->active_in,
+                                                             p->has_warm, p->U_warm, p->x_ref, p->U, p->active, p->n_iter,
+                                                             p->qp_iters, p->converged);
+  if ((rc = gpmpc_check_launch("solve_prologue_3dof"))) return rc;
+  ++launches;
+  rec.mark(GPMPC_PHASE_PROLOGUE);
+  const GpmpcExactModel* mdl = p->has_model ? &p->model : nullptr;
+  // variances of the rows of Ks + covariance chain along (X, U)
+  auto uncertainty = [&](const double* Xt) -> int {
+    int r;
+    const double* part;
+    int nparts;
+    if (p->Linv) {
+      if ((r = gpmpc_linv_sumsq_parts(p->Linv, p->model.n_pad, p->ldi, p->Ks, p->q_pad, p->ldk, p->var_work, (void*)s)))
+        return r;
+      part = p->var_work;
+      nparts = p->model.n_pad / 64;
+      ++launches;
+    } else {
+      if ((r = gpmpc_trsm_sumsq(p->model.L, p->model.n_pad, p->model.n_pad, p->model.Winv, p->Ks, p->q_pad, p->ldk,
+                                p->sumsq, (void*)s)))
+        return r;
+      part = p->sumsq;
+      nparts = 1;
+      launches += 2 * (p->model.n_pad / 64);
+    }
+    rec.mark(GPMPC_PHASE_GP_VARIANCE);
+    GPMPC_PREFER_SHARED(var_cov3_kernel);
+    var_cov3_kernel<<<(B + 127) / 128, 128, 0, s>>>(p->dyn, B, N, part, nparts, (long)p->q_pad, p->model.signal_var, 1e-10,
+                                                    p->model.ystd, 1e-6, Xt, p->U, p->dvar, p->covs, p->active);
+    if ((r = gpmpc_check_launch("var_cov_3dof"))) return r;
+    ++launches;
+    rec.mark(GPMPC_PHASE_COV);
+    return GPMPC_OK;
+  };
+  // 1. rollout with the GP mean (gp_mpc.py:277-281)
+  rc = gpmpc_rollout_3dof((use_mean || use_unc) ? mdl : nullptr, &p->dyn, B, N, p->x0, p->U, p->X,
+                          p->has_model ? p->dmean : nullptr, use_unc ? p->Ks : nullptr, p->ldk, p->active, (void*)s);
+  if (rc) return rc;
+  ++launches;
+  if (p->has_model && !use_mean && use_unc) {  // uncertainty only: the GP mean must not enter the prediction
+    if ((rc = gpmpc_rollout_3dof(nullptr, &p->dyn, B, N, p->x0, p->U, p->X, nullptr, nullptr, 0, p->active, (void*)s))) return rc;
+    ++launches;
+  }
+  rec.mark(GPMPC_PHASE_ROLLOUT);
+  // 2. uncertainty propagation (gp_mpc.py:284-289)
+  if (use_unc && (rc = uncertainty(p->X))) return rc;
+  // 3. SQP iterations (gp_mpc.py:296-353)
+  GpmpcAdmmSettings S = p->admm;
+  S.bound_stride = tighten ? (N * NS + NX) : 0;
+  for (int it = 0; it < p->max_sqp_iter; ++it) {
+    const bool last = it == p->max_sqp_iter - 1;
+    if (tighten) {
+      if ((rc = gpmpc_tighten_bounds(NX, NU, B, N, p->lb, p->ub, p->covs, p->tighten_kappa, p->tighten_max_variance,
+                                     p->lb_t, p->ub_t, nullptr, (void*)s)))
+        return rc;
+      ++launches;
+    }
+    if (use_mean && it > 0) {
+      if ((rc = gpmpc_gp_mean_points_3dof(mdl, B, N, p->X, p->U, p->dmean, nullptr, 0, p->active, (void*)s))) return rc;
+      ++launches;
+      rec.mark(GPMPC_PHASE_GP_MEAN);
+    }
+    GPMPC_PREFER_SHARED(qp_assemble3_kernel);
+    qp_assemble3_kernel<<<(total + 127) / 128, 128, 0, s>>>(p->dyn, B, N, 0, 1, p->X, p->U, p->x0, p->x_ref,
+                                                            (long)(N + 1) * NX, use_mean ? p->dmean : nullptr, p->Qd,
+                                                            p->Qfd, p->AB, p->beq, p->q, p->active, p->z);
+    if ((rc = gpmpc_check_launch("qp_assemble_3dof"))) return rc;
+    ++launches;
+    rec.mark(GPMPC_PHASE_ASSEMBLE);
+    if ((rc = gpmpc_admm_solve(NX, NU, N, B, p->AB, p->beq, p->q, p->Pdiag, tighten ? p->lb_t : p->lb,
+                               tighten ? p->ub_t : p->ub, &S, p->active, p->z, p->y, p->rho, p->qp_status, p->qp_it, p->obj,
+                               p->pri, p->dua, (void*)s)))
+      return rc;
+    ++launches;
+    rec.mark(GPMPC_PHASE_ADMM);
+    GPMPC_PREFER_SHARED(mpc_update3_kernel);
+    mpc_update3_kernel<<<(B + 3) / 4, 128, 0, s>>>(B, N, 1, p->z, p->qp_status, p->x_ref, (long)(N + 1) * NX, p->Qd, p->Qfd,
+                                                   p->Rd, p->X, p->U, nullptr, nullptr, p->cost, p->converged, p->active,
+                                                   p->n_iter, p->qp_it, p->qp_iters, last ? p->U_warm : nullptr,
+                                                   last ? p->X_warm : nullptr, last ? p->has_warm : nullptr);
+    if ((rc = gpmpc_check_launch("mpc_update_3dof"))) return rc;
+    ++launches;
+    rec.mark(GPMPC_PHASE_UPDATE);
+    if (last) break;
+    if (use_unc && p->repropagate) {  // gp_mpc.py:347-353
+      GPMPC_REQUIRE(p->Xs && p->dmean_s, "gpmpc_solve_batch_3dof: re-propagation scratch is NULL");
+      if ((rc = gpmpc_rollout_3dof(mdl, &p->dyn, B, N, p->x0, p->U, p->Xs, p->dmean_s, p->Ks, p->ldk, p->active, (void*)s)))
+        return rc;
+      ++launches;
+      rec.mark(GPMPC_PHASE_ROLLOUT);
+      if ((rc = uncertainty(p->Xs))) return rc;
+    }
+  }
+  if (n_launches) *n_launches = launches;
+  return GPMPC_OK;
+}
+
+// Layout probes for the binding tests (tests/test_abi.py): which = 0 GpmpcSolve3, 1 GpmpcMcStep3, 2 GpmpcAdmmSettings,
+// 3 GpmpcExactModel; field < 0: sizeof, else the offset of a sentinel field.
+#include <stddef.h>
+extern "C" long gpmpc_struct_layout(int which, int field) {
+  if (which == 0) {
+    switch (field) {
+      case -1: return (long)sizeof(GpmpcSolve3);
+      case 0: return (long)offsetof(GpmpcSolve3, dyn);
+      case 1: return (long)offsetof(GpmpcSolve3, admm);
+      case 2: return (long)offsetof(GpmpcSolve3, model);
+      case 3: return (long)offsetof(GpmpcSolve3, Linv);
+      case 4: return (long)offsetof(GpmpcSolve3, x0);
+      case 5: return (long)offsetof(GpmpcSolve3, Ks);
+      case 6: return (long)offsetof(GpmpcSolve3, q_pad);
+      case 7: return (long)offsetof(GpmpcSolve3, var_work);
+      case 8: return (long)offsetof(GpmpcSolve3, U_warm);
+      case 9: return (long)offsetof(GpmpcSolve3, events);
+      case 10: return (long)offsetof(GpmpcSolve3, event_count);
+    }
+  } else if (which == 1) {
+    switch (field) {
+      case -1: return (long)sizeof(GpmpcMcStep3);
+      case 0: return (long)offsetof(GpmpcMcStep3, dyn);
+      case 1: return (long)offsetof(GpmpcMcStep3, max_steps);
+      case 2: return (long)offsetof(GpmpcMcStep3, x);
+      case 3: return (long)offsetof(GpmpcMcStep3, counts);
+      case 4: return (long)offsetof(GpmpcMcStep3, rho);
+    }
+  } else if (which == 2 && field < 0) {
+    return (long)sizeof(GpmpcAdmmSettings);
+  } else if (which == 3 && field < 0) {
+    return (long)sizeof(GpmpcExactModel);
+  }
+  return -1;
 }

@@ -2,9 +2,22 @@
 (src/experiments/monte_carlo.py:401-636) turned inside-out -- all B scenarios advance one control step per
 `controller.solve_batch` / `step_batch`, with per-scenario termination masks kept on the device.
 
+Loop semantics (all evaluated on the device, `gpmpc_mc_advance_3dof`):
+
+* `target_mode="per_step"` -- what the reference does for a controller that has `.solve` and no `.step` (GPMPC,
+  NominalMPC3DoF; monte_carlo.py:495-499): every step the target is re-derived from the current state,
+  x_target = x with v = 0 and altitude = max(0.5, altitude - 2).  `"fixed"` keeps the target [m0, 0, ...] of :428-429
+  (what a controller with `.step` sees through `initialize`).  Default: "per_step" for `.solve` controllers.
+* `on_solve_failure="divergence"` -- the reference's branch :507-510: a solve with `success == False` ends the run as
+  DIVERGENCE.  `"continue"` only counts the flag (what the reference does for `.step` controllers, :492-494).  Default:
+  "divergence" for `.solve` controllers, "continue" for RTI controllers.  NB: `GPMPC.success` is the SQP step-size test
+  (gp_mpc.py:337-345, 1e-4), which a real-time iteration (max_sqp_iter = 1) almost never meets, so throughput runs use
+  "continue" -- DESIGN.md section 11 has the outcome tables for both.
+* termination rules :460-488 on every state x_0 .. x_{max_steps-1}, TIMEOUT by the for/else (:539-542).
+
 Sharding: scenarios are independent, so rank r of W simulates the block [r*B/W, (r+1)*B/W) of the scenario
 index range; initial conditions are generated per index from `seed + i` (monte_carlo.py:606-616), so the results do
-not depend on W.  The only collectives are the stats gather and the hyper-parameter broadcast (parallel.py).
+not depend on W.  The only collectives are the stats gather and the hyper-parameter broadcast (distributed.py).
 """
 from __future__ import annotations
 
@@ -13,6 +26,7 @@ from typing import Any, Dict, Optional
 
 import numpy as np
 
+from . import _lib
 from .gp import engine as ge
 from .mpc import engine as me
 from .workloads import SimulationConfig, sample_initial_conditions
@@ -52,20 +66,26 @@ class BatchMonteCarloResults:
 class BatchedMonteCarlo:
     """Closed loop of B scenarios around a batched controller.
 
-    controller: `GPMPC` / `NominalMPC3DoF` (uses `solve_batch`, target x' = x with v = 0 is NOT re-derived per step:
-    the fixed target [m0, 0...] of monte_carlo.py:428-429 is used, as for controllers with `.step`) or
-    `OSQPRTIMPC` / `FastRTI3DoF` (uses `initialize_batch` + `step_batch`).
-    drag_cda: C_D*A of the "true" plant's drag residual (0 = the plant is the nominal model)."""
+    controller: `GPMPC` / `NominalMPC3DoF` (uses `solve_batch`) or `OSQPRTIMPC` / `FastRTI3DoF` (uses `initialize_batch` +
+    `step_batch`).  target_mode / on_solve_failure: see the module docstring (None = the reference's behaviour for the
+    controller's kind).  drag_cda: C_D*A of the "true" plant's drag residual (0 = the plant is the nominal model).
+    respawn: a finished scenario restarts from its initial condition with a fresh controller state, which keeps the
+    batch full (throughput runs); the outcome counters keep accumulating."""
 
     def __init__(self, dynamics, controller, sim_config: Optional[SimulationConfig] = None, drag_cda: float = 0.0,
-                 respawn: bool = False):
+                 respawn: bool = False, target_mode: Optional[str] = None, on_solve_failure: Optional[str] = None):
         self.dynamics = dynamics
         self.controller = controller
         self.cfg = sim_config or SimulationConfig()
         self.drag_cda = float(drag_cda)
         self.respawn = respawn
-        self.max_steps = int(round(self.cfg.max_time / self.cfg.dt))
+        self.max_steps = int(self.cfg.max_time / self.cfg.dt)    # monte_carlo.py:447
         self._rti = hasattr(controller, "step_batch")
+        self.target_mode = target_mode or ("fixed" if self._rti else "per_step")
+        self.on_solve_failure = on_solve_failure or ("continue" if self._rti else "divergence")
+        assert self.target_mode in ("fixed", "per_step") and self.on_solve_failure in ("divergence", "continue")
+        if self._rti and self.target_mode == "per_step":
+            raise ValueError("RTI controllers take their target in initialize_batch: target_mode must be 'fixed'")
 
     def reset(self, first: int, count: int, seed: int = 42):
         torch = ge.torch_()
@@ -92,32 +112,43 @@ class BatchedMonteCarlo:
             self.controller.initialize_batch(self.x0, self.xt)
         elif hasattr(self.controller, "reset_warm_start"):
             self.controller.reset_warm_start()
+        a = _lib.McStep3()
+        a.B, a.N, a.dyn, a.drag_cda = count, int(getattr(self.controller.config, "N", 0)), self._dyn, self.drag_cda
+        a.max_steps = self.max_steps
+        a.fail_policy = 1 if self.on_solve_failure == "divergence" else 0
+        a.respawn = 1 if self.respawn else 0
+        for name in ("x", "m0", "t_step", "active", "outcome", "fail_steps", "x_final", "counts"):
+            setattr(a, name, ge.ptr(getattr(self, name)))
+        a.x_init = ge.ptr(self.x0)
+        self._args = a
+        # the reference applies the termination rules to x0 before the first control (monte_carlo.py:455-488)
+        a.classify_only = 1
+        ge.call("gpmpc_mc_advance_3dof", _lib.C.byref(a), ge.stream())
+        a.classify_only = 0
         return self
 
     def step(self):
-        """One control step for every active scenario; returns the controller's batch solution."""
+        """One control step for every active scenario; returns the controller's batch solution (device views)."""
         torch = ge.torch_()
+        a = self._args
         if self._rti:
             sol = self.controller.step_batch(self.x, active=self.active)
+            self._u0 = sol.u0.contiguous()
+            self._ok = sol.success.to(torch.int32)
+            a.u, a.ldu, a.success = ge.ptr(self._u0), self._u0.stride(0), ge.ptr(self._ok)
+            a.has_warm = a.y = a.rho = None
         else:
-            sol = self.controller.solve_batch(self.x, self.xt, active=self.active)
-        self.fail_steps += (~sol.success).to(torch.int32) * self.active
-        u0 = sol.u0.contiguous()
-        ge.call("gpmpc_mc_step_3dof", me.C.byref(self._dyn), self.B, self.drag_cda, self.max_steps, ge.ptr(self.x),
-                ge.ptr(u0), ge.ptr(self.m0), ge.ptr(self.t_step), ge.ptr(self.active), ge.ptr(self.outcome),
-                ge.ptr(self.x_final), ge.ptr(self.counts), ge.stream())
-        if self.respawn:
-            done = self.active == 0
-            self._respawn(done)
+            sol = self.controller.solve_batch(self.x, self.xt, active=self.active,
+                                              per_step_target=self.target_mode == "per_step")
+            U = sol.U_opt                    # (B,N,3) view of the controller state: u0 = U[:,0]
+            a.u, a.ldu, a.success = U.data_ptr(), U.stride(0), ge.ptr(sol.success)
+            st = getattr(self.controller, "_batch", None)
+            if self.respawn and st is not None:   # controller state cleared on the device for respawned scenarios
+                a.has_warm, a.y, a.rho, a.m = ge.ptr(st.has_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), st.ws.y.shape[1]
+            else:
+                a.has_warm = a.y = a.rho = None
+        ge.call("gpmpc_mc_advance_3dof", _lib.C.byref(a), ge.stream())
         return sol
-
-    def _respawn(self, done):
-        """Restart finished scenarios from their initial condition (keeps the batch full for throughput runs)."""
-        if hasattr(self.controller, "reset_scenarios"):
-            self.controller.reset_scenarios(done, self.x0)
-        self.x = ge.torch_().where(done[:, None], self.x0, self.x).contiguous()
-        self.t_step.masked_fill_(done, 0)
-        self.active.fill_(1)
 
     def n_active(self) -> int:
         return int(self.active.sum().item())

@@ -61,6 +61,61 @@ class PhaseTimers:
         self.pairs = {}
 
 
+class EventTimers:
+    """CUDA-event phase attribution of the fused solve (`gpmpc_solve_batch_3dof` records one event per phase boundary
+    on the launching stream when a pool is attached).  Used by bench.py to time every kernel live, inside the timed region."""
+
+    def __init__(self, capacity: int = 4096):
+        torch_()
+        self.cap = int(capacity)
+        self.events = (C.c_void_p * self.cap)()
+        self.phase = (C.c_int * self.cap)()
+        self.count = C.c_int(0)
+        call("gpmpc_events_create", self.cap, self.events)
+
+    def attach(self, plan):
+        plan.events = C.cast(self.events, C.POINTER(C.c_void_p))
+        plan.event_phase = C.cast(self.phase, C.POINTER(C.c_int))
+        plan.event_cap = self.cap
+        plan.event_count = C.pointer(self.count)
+
+    def reset(self):
+        self.count.value = 0
+
+    def totals(self):
+        """phase name -> (total ms, number of spans); the time between the last event of one solve and the `begin` of
+        the next (plant step, respawn, host gaps) is reported as "between_solves".  Synchronises."""
+        torch_().cuda.synchronize()
+        out = {}
+        ms = C.c_float(0.0)
+        n = self.count.value
+        for i in range(1, n):
+            ph = self.phase[i]
+            name = "between_solves" if ph == 0 else _lib.PHASE_NAMES[ph]
+            call("gpmpc_events_elapsed_ms", self.events[i - 1], self.events[i], C.byref(ms))
+            t, c = out.get(name, (0.0, 0))
+            out[name] = (t + ms.value, c + 1)
+        return out
+
+    def step_times_ms(self):
+        """Per-solve wall time on the device: begin(i) -> begin(i+1) for consecutive solves (includes what runs between
+        them), for the p50 / p99 step latency."""
+        torch_().cuda.synchronize()
+        idx = [i for i in range(self.count.value) if self.phase[i] == 0]
+        ms = C.c_float(0.0)
+        out = []
+        for a, b in zip(idx[:-1], idx[1:]):
+            call("gpmpc_events_elapsed_ms", self.events[a], self.events[b], C.byref(ms))
+            out.append(ms.value)
+        return out
+
+    def __del__(self):
+        try:
+            _lib.lib.gpmpc_events_destroy(self.cap, self.events)
+        except Exception:  # noqa: BLE001
+            pass
+
+
 class _NullSpan:
     def __enter__(self):
         return None

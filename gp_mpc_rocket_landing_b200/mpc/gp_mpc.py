@@ -59,12 +59,6 @@ class GPMPCConfig(MPCConfig):
     variance_via_inverse: bool = True  # horizon variances |L^-1 k*|^2 as one triangular DMMA GEMM against the explicit
                                        # inverse factor (formed once per fit) instead of the blocked in-place solve
                                        # (31 dependent launches); same quantity, rounding differs by O(cond(L) eps)
-    overlap_uncertainty: bool = False  # GP variance + covariance chain on a side stream, concurrent with the QP (the QP
-                                       # does not read them: gp_mpc.py:414 evaluates the tightening at k = 0 only).  The
-                                       # variance GEMM then runs as a persistent one-CTA-per-SM grid so that two ADMM QPs
-                                       # fit next to it on every SM.  Measured on B200: the kernels do
-                                       # co-reside, but the step stays at 8.83 ms (8.89 ms serial) -- they contend for the
-                                       # same shared-memory / issue bandwidth.  Off by default: clean per-kernel timings.
 
 
 def _is_dev(a):
@@ -72,7 +66,8 @@ def _is_dev(a):
 
 
 class _BatchState:
-    """Device-resident state of B controller instances (buffers are allocated once and reused every step)."""
+    """Device-resident state of B controller instances (buffers are allocated once and reused every step) and the
+    `GpmpcSolve3` plan that hands their addresses to the fused C entry point."""
 
     def __init__(self, B: int, N: int, model, device="cuda"):
         torch = ge.torch_()
@@ -80,17 +75,15 @@ class _BatchState:
         i32 = dict(dtype=torch.int32, device=device)
         n, m = me.qp_dims(N)
         self.B, self.N = B, N
+        self.x_ref = torch.zeros((B, N + 1, NX), **f64)
         self.X = torch.zeros((B, N + 1, NX), **f64)
         self.U = torch.zeros((B, N, NU), **f64)
         self.Xs = torch.zeros((B, N + 1, NX), **f64)       # scratch rollout of the re-propagation
-        self.X_unc = torch.zeros((B, N + 1, NX), **f64)    # snapshot read by the side-stream covariance chain
-        self.U_unc = torch.zeros((B, N, NU), **f64)
-        self.active_unc = torch.ones((B,), **i32)
-        self.unc_event = None
         self.dmean = torch.zeros((B, N, 3), **f64)
         self.dmean_s = torch.zeros((B, N, 3), **f64)
         self.q_pad = ge.pad_to(B * N, 128)
         self.dvar = torch.zeros((self.q_pad, 3), **f64)
+        self.sumsq = torch.zeros((self.q_pad,), **f64)
         self.Ks = torch.zeros((self.q_pad, model.f.n_pad), **f64) if model is not None else None
         self.var_work = None  # scratch of the explicit-inverse variance path (allocated on first use)
         self.covs = torch.zeros((B, N + 1, NX, NX), **f64)
@@ -108,7 +101,10 @@ class _BatchState:
         self.ws = me.AdmmWorkspace(B, N, device=device)
         self.U_warm = torch.zeros((B, N, NU), **f64)
         self.X_warm = torch.zeros((B, N + 1, NX), **f64)
-        self.has_warm = False
+        self.has_warm = torch.zeros((B,), **i32)     # per scenario: 0 -> hover / U_ref initial guess
+        self.plan = None
+        self.generation = 0   # number of solves run on this state (DeferredHostArray checks it)
+        self.keep = None      # tensors referenced by the plan for the duration of a call
         self._pinned = [{}, {}]   # two alternating sets of pinned staging buffers for the host results
         self._flip = 0
 
@@ -118,11 +114,13 @@ class _BatchState:
         torch = ge.torch_()
         a = np.ascontiguousarray(np.asarray(arr, dtype=np.float64))
         b = self._pinned_in.get(key)
-        if b is None or tuple(b.shape) != a.shape:
-            b = torch.empty(a.shape, dtype=torch.float64, device="cpu", pin_memory=True)
+        if b is None or tuple(b[0].shape) != a.shape:
+            b = (torch.empty(a.shape, dtype=torch.float64, device="cpu", pin_memory=True),
+                 torch.empty(a.shape, dtype=torch.float64, device="cuda"))
             self._pinned_in[key] = b
-        b.numpy()[...] = a
-        return b.to("cuda", non_blocking=True)
+        b[0].numpy()[...] = a
+        b[1].copy_(b[0], non_blocking=True)
+        return b[1]
 
     def to_host(self, tensors: dict) -> dict:
         """Device -> pinned host copies of the result tensors (async on the current stream, one synchronise).
@@ -164,12 +162,8 @@ class GPMPC:
         self._qp = None
         self._dyn = None
         self._is_setup = False
-        self._side = None
         self.last_kernel_launches = 0
-        self.timers: Optional[me.PhaseTimers] = None   # set to me.PhaseTimers() to time the phases (bench.py)
-
-    def _span(self, name):
-        return self.timers.span(name) if self.timers is not None else me.NULL_SPAN
+        self.timers: Optional[me.EventTimers] = None   # set to me.EventTimers(n) to time the phases (bench.py)
 
     # ------------------------------------------------------------------------------------------------ setup
     def setup(self) -> None:
@@ -189,6 +183,9 @@ class GPMPC:
         """(Re)read the GP's fitted device state -- call after the GP was refit (e.g. new hyper-parameters)."""
         self._model = None
         self._model_struct = None
+        for st in (self._single, self._batch):
+            if st is not None:
+                st.plan = None
         if self.gp is not None and (self.config.use_gp_mean or self.config.use_gp_uncertainty):
             dm = self.gp.device_model() if hasattr(self.gp, "device_model") else None
             if dm is None and getattr(self.gp, "n_data", 0) > 0:
@@ -204,28 +201,23 @@ class GPMPC:
         self._U_warm = None
         for st in (self._single, self._batch):
             if st is not None:
-                st.has_warm = False
+                st.has_warm.zero_()
                 st.ws.y.zero_()
                 st.ws.rho.zero_()
 
-    def reset_scenarios(self, mask, X0) -> None:
+    def reset_scenarios(self, mask, X0=None) -> None:
         """Per-scenario `reset_warm_start` for the batched state: scenarios with mask != 0 restart from the hover
-        guess at mass X0[b,0] with zero duals (a fresh controller instance for a respawned Monte Carlo run)."""
+        guess with zero duals and the default rho (a fresh controller instance for a respawned Monte Carlo run)."""
         st = self._batch
-        if st is None or not st.has_warm:
+        if st is None:
             return
         torch = ge.torch_()
-        g0 = float(self.dynamics.params.g0)
         if _is_dev(mask):
             mask_d = mask.to(torch.int32).contiguous()
-            hover0 = (ge.to_dev(X0)[:, 0] * g0).contiguous()
-        else:   # host arrays: two small pinned H2D copies, one launch
-            mask_d = st.from_host("reset_mask", np.asarray(mask) != 0).to(torch.int32)
-            hover0 = st.from_host("reset_hover", np.asarray(X0, dtype=np.float64)[:, 0] * g0)
-        if not st.U_warm.is_contiguous():
-            st.U_warm = st.U_warm.contiguous()
-        ge.call("gpmpc_reset_scenarios", st.B, st.N, NU, st.ws.y.shape[1], ge.ptr(mask_d), ge.ptr(hover0),
-                ge.ptr(st.U_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), ge.stream())
+        else:   # host mask: one small pinned H2D copy, one launch
+            mask_d = st.from_host("reset_mask", (np.asarray(mask) != 0).astype(np.float64)).to(torch.int32)
+        ge.call("gpmpc_reset_scenarios", st.B, st.N, NU, st.ws.y.shape[1], ge.ptr(mask_d), None, None, ge.ptr(st.ws.y),
+                ge.ptr(st.ws.rho), ge.ptr(st.has_warm), ge.stream())
 
     def _settings(self):
         c = self.config
@@ -235,133 +227,83 @@ class GPMPC:
             warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1)
 
     # ------------------------------------------------------------------------------------------------ core
-    def _variance_and_cov(self, st: _BatchState, X, U, active):
-        """GP variances of the rows of st.Ks (blocked DMMA TRSM with fused sum of squares) -> covariance chain."""
-        f = self._model.f
-        with self._span("gp_variance"):
-            if self.config.variance_via_inverse:
-                if st.var_work is None:
-                    st.var_work = ge.torch_().empty(((f.n_pad // 64) * st.Ks.shape[0],), dtype=st.Ks.dtype,
-                                                    device=st.Ks.device)
-                sumsq = f.sumsq_linv(st.Ks, st.var_work, one_cta_per_sm=self.config.overlap_uncertainty)
-            else:
-                sumsq = f.sumsq_inplace(st.Ks)
-        with self._span("cov"):
-            ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, st.B * st.N, 3, f.sv, 1e-10, ge.ptr(self._model.ystd),
-                    ge.ptr(st.dvar), 3, 0, ge.stream())
-            me.propagate_cov(self._dyn, X, U, st.dvar, st.covs, sigma0=1e-6, active=active)
-        if self.config.variance_via_inverse:
-            return 4  # triangular GEMM + partial-sum reduction + var + cov
-        return 2 * (f.n_pad // 64) + 2  # launches: memset is not a kernel; (n/64 - 1) GEMM + n/64 W-GEMM + var + cov
-
-    def _fork_uncertainty(self, st: _BatchState, X, U, active):
-        """`_variance_and_cov` on the side stream: the blocked DMMA TRSM (tensor pipe) runs concurrently with the
-        latency-bound ADMM kernel of the main stream.  Inputs that the main stream later overwrites are snapshotted."""
+    def _make_plan(self, st: _BatchState) -> "_lib.Solve3":
+        """Fill the GpmpcSolve3 plan with the addresses of the state buffers (once per state / GP refresh)."""
         torch = ge.torch_()
-        if not self.config.overlap_uncertainty:
-            return self._variance_and_cov(st, X, U, active)
-        if self._side is None:
-            self._side = torch.cuda.Stream(priority=-1)
-        self._join_uncertainty(st)
-        st.X_unc.copy_(X)
-        st.U_unc.copy_(U)
-        st.active_unc.copy_(active)
-        main = torch.cuda.current_stream()
-        self._side.wait_stream(main)
-        with torch.cuda.stream(self._side):
-            n = self._variance_and_cov(st, st.X_unc, st.U_unc, st.active_unc)
-            st.unc_event = torch.cuda.Event()
-            st.unc_event.record(self._side)
-        return n + 3
-
-    def _join_uncertainty(self, st: _BatchState):
-        if st.unc_event is not None:
-            ge.torch_().cuda.current_stream().wait_event(st.unc_event)
-            st.unc_event = None
-
-    def _solve_device(self, st: _BatchState, x0, x_ref, U_ref=None, active_in=None):
-        """One GP-MPC solve for every scenario of `st` (all tensors on the device).  Returns #kernel launches."""
         c = self.config
-        N = c.N
         use_model = self._model is not None
-        use_mean = c.use_gp_mean and use_model
         use_unc = c.use_gp_uncertainty and use_model
-        launches = 0
-        # --- initial controls: warm start | U_ref | hover along the up axis (gp_mpc.py:266-275; the 3-DoF frame of
-        #     nominal_mpc.py:651-657 / osqp_rti.py:427-431 has "up" = axis 0)
-        if st.has_warm and c.warm_start:
-            st.U.copy_(st.U_warm)
-        elif U_ref is not None:
-            st.U.copy_(U_ref[..., :N, :].expand_as(st.U))
-        else:
-            st.U.zero_()
-            st.U[:, :, 0] = (x0[:, 0] * float(self.dynamics.params.g0))[:, None]
-        if active_in is None:
-            st.active.fill_(1)
-        else:
-            st.active.copy_(active_in)
-        st.n_iter.zero_()
-        st.qp_iters.zero_()
-        st.converged.zero_()
-        # --- 1. rollout with the GP mean
-        need_ks = use_unc
-        with self._span("rollout"):
-            me.rollout(self._model_struct if (use_mean or use_unc) else None, self._dyn, x0, st.U, st.X,
-                       st.dmean if use_model else None, st.Ks if need_ks else None, active=st.active)
-        launches += 1
-        if use_model and not use_mean:
-            # uncertainty only: the GP mean must not enter the prediction (use_gp_mean=False)
-            me.rollout(None, self._dyn, x0, st.U, st.X, None, None, active=st.active)
-            launches += 1
-        # --- 2. uncertainty propagation
-        if use_unc:
-            launches += self._fork_uncertainty(st, st.X, st.U, st.active)
-        # --- 3. SQP iterations
-        S = self._settings()
-        tighten = use_unc and c.tighten_state_bounds
-        if tighten:
+        p = _lib.Solve3()
+        p.B, p.N = st.B, st.N
+        p.use_gp_mean = 1 if (c.use_gp_mean and use_model) else 0
+        p.use_gp_uncertainty = 1 if use_unc else 0
+        p.repropagate = 1 if c.repropagate_uncertainty else 0
+        p.has_model = 1 if use_model else 0
+        p.dyn = self._dyn
+        p.g0 = float(self.dynamics.params.g0)
+        if use_model:
+            p.model = self._model_struct
+            f = self._model.f
+            if use_unc and c.variance_via_inverse:
+                W = f.ensure_linv()
+                p.Linv, p.ldi = ge.ptr(W), W.stride(0)
+                if st.var_work is None:
+                    st.var_work = torch.empty(((f.n_pad // 64) * st.q_pad,), dtype=torch.float64, device=st.Ks.device)
+                p.var_work = ge.ptr(st.var_work)
+            p.Ks, p.ldk = ge.ptr(st.Ks), st.Ks.stride(0)
+        p.q_pad = st.q_pad
+        if use_unc and c.tighten_state_bounds:
             from scipy.stats import norm
-            kappa = float(norm.ppf(c.confidence_level))
+            p.tighten_kappa = float(norm.ppf(c.confidence_level))
+            p.tighten_max_variance = float(c.max_variance_for_constraint)
             if st.lb_t is None:
                 n_var = self._qp.lb.shape[0]
-                st.lb_t = ge.torch_().empty((st.B, n_var), dtype=self._qp.lb.dtype, device=self._qp.lb.device)
-                st.ub_t = ge.torch_().empty_like(st.lb_t)
-        for it in range(c.max_sqp_iter):
-            if tighten:   # boxes from the latest covariance chain (initial propagation or the re-propagation below)
-                self._join_uncertainty(st)
-                me.tighten_bounds(self._qp, st.covs, kappa, c.max_variance_for_constraint, st.lb_t, st.ub_t)
-                launches += 1
-            if use_mean and it > 0:
-                with self._span("gp_mean"):
-                    me.gp_mean_points(self._model_struct, st.X, st.U, st.dmean, None, active=st.active)
-                launches += 1
-            with self._span("assemble"):
-                me.qp_assemble(self._dyn, self._qp, st.X, st.U, x0, x_ref, st.AB, st.beq, st.q,
-                               c_gp=st.dmean if use_mean else None, lin_mode=0, rhs_mode=1, active=st.active)
-                me.pack_traj(st.X, st.U, st.ws.x, active=st.active)
-            with self._span("admm"):
-                me.admm_solve(self._qp, st.AB, st.beq, st.q, S, st.ws, active=st.active,
-                              lb=st.lb_t if tighten else None, ub=st.ub_t if tighten else None)
-            with self._span("update"):
-                st.qp_iters += st.ws.iters * st.active
-                me.mpc_update(self._qp, 1, st.ws.x, st.ws.status, x_ref, st.X, st.U, None, None, st.cost,
-                              st.converged, active=st.active, n_iter=st.n_iter)
-            launches += 5
-            if it == c.max_sqp_iter - 1:
-                break
-            if int(st.active.sum().item()) == 0:
-                break
-            if use_unc and c.repropagate_uncertainty:  # gp_mpc.py:348-353
-                self._join_uncertainty(st)   # the rollout below overwrites Ks
-                with self._span("rollout"):
-                    me.rollout(self._model_struct, self._dyn, x0, st.U, st.Xs, st.dmean_s, st.Ks, active=st.active)
-                launches += 1 + self._fork_uncertainty(st, st.Xs, st.U, st.active)
-        self._join_uncertainty(st)
-        # --- 4. warm start for the next call (unshifted, gp_mpc.py:355-357)
-        st.U_warm.copy_(st.U)
-        st.X_warm.copy_(st.X)
-        st.has_warm = True
-        return launches
+                st.lb_t = torch.empty((st.B, n_var), dtype=self._qp.lb.dtype, device=self._qp.lb.device)
+                st.ub_t = torch.empty_like(st.lb_t)
+            p.lb_t, p.ub_t = ge.ptr(st.lb_t), ge.ptr(st.ub_t)
+        qp, ws = self._qp, st.ws
+        for name, t in (("Pdiag", qp.Pdiag), ("lb", qp.lb), ("ub", qp.ub), ("Qd", qp.Qd), ("Qfd", qp.Qfd), ("Rd", qp.Rd),
+                        ("x_ref", st.x_ref), ("X", st.X), ("U", st.U), ("Xs", st.Xs), ("dmean", st.dmean),
+                        ("dmean_s", st.dmean_s), ("sumsq", st.sumsq), ("dvar", st.dvar), ("covs", st.covs),
+                        ("AB", st.AB), ("beq", st.beq), ("q", st.q), ("cost", st.cost), ("converged", st.converged),
+                        ("active", st.active), ("n_iter", st.n_iter), ("qp_iters", st.qp_iters), ("z", ws.x),
+                        ("y", ws.y), ("rho", ws.rho), ("obj", ws.obj), ("pri", ws.pri), ("dua", ws.dua),
+                        ("qp_status", ws.status), ("qp_it", ws.iters), ("U_warm", st.U_warm), ("X_warm", st.X_warm)):
+            setattr(p, name, ge.ptr(t))
+        return p
+
+    def _solve_device(self, st: _BatchState, x0, x_target=None, X_ref=None, U_ref=None, active_in=None,
+                      per_step_target=False):
+        """One GP-MPC solve for every scenario of `st` (all tensors on the device): ONE call of the fused C entry point
+        `gpmpc_solve_batch_3dof` (8 kernel launches for S = 1, no host synchronisation).  Returns #kernel launches."""
+        c = self.config
+        if st.plan is None:
+            st.plan = self._make_plan(st)
+        p = st.plan
+        p.max_sqp_iter = int(c.max_sqp_iter)
+        p.admm = self._settings()
+        p.target_mode = 1 if per_step_target else 0
+        p.x0 = ge.ptr(x0)
+        p.x_target = ge.ptr(x_target) if x_target is not None else None
+        if X_ref is not None:
+            p.X_ref, p.ld_xref_in = ge.ptr(X_ref), (0 if X_ref.dim() == 2 else X_ref.stride(0))
+        else:
+            p.X_ref, p.ld_xref_in = None, 0
+        if U_ref is not None:
+            p.U_ref, p.ld_uref = ge.ptr(U_ref), (0 if U_ref.dim() == 2 else U_ref.stride(0))
+        else:
+            p.U_ref, p.ld_uref = None, 0
+        p.active_in = ge.ptr(active_in) if active_in is not None else None
+        p.has_warm = ge.ptr(st.has_warm) if c.warm_start else None
+        if self.timers is not None:
+            self.timers.attach(p)
+        else:
+            p.events, p.event_phase, p.event_cap, p.event_count = None, None, 0, None
+        st.keep = (x0, x_target, X_ref, U_ref, active_in)
+        st.generation += 1
+        n = _lib.c_int(0)
+        ge.call("gpmpc_solve_batch_3dof", _lib.C.byref(p), _lib.C.byref(n), ge.stream())
+        return n.value
 
     def _state_for(self, B: int, single: bool) -> _BatchState:
         attr = "_single" if single else "_batch"
@@ -371,24 +313,32 @@ class GPMPC:
             setattr(self, attr, st)
         return st
 
-    def _x_ref(self, x_target, X_ref, B):
-        torch = ge.torch_()
+    def _targets(self, st, x_target, X_ref, U_ref, B):
+        """Device views of the target / reference arguments in the layouts GpmpcSolve3 takes."""
         N = self.config.N
+        xr = ur = xt = None
         if X_ref is not None:
-            r = ge.to_dev(X_ref)
-            return r[..., : N + 1, :].contiguous()
-        t = ge.to_dev(x_target)
-        if t.dim() == 1:
-            return t[None, :].expand(N + 1, NX).contiguous()
-        return t[:, None, :].expand(B, N + 1, NX).contiguous()
+            xr = ge.to_dev(X_ref)[..., : N + 1, :].contiguous()
+        elif x_target is not None:
+            xt = ge.to_dev(x_target)
+            if xt.dim() == 1:
+                xt = xt[None, :].expand(B, NX)
+            xt = xt.contiguous()
+        if U_ref is not None:
+            ur = ge.to_dev(U_ref)[..., :N, :].contiguous()
+        return xt, xr, ur
 
     # ------------------------------------------------------------------------------------------------ public API
-    def solve_batch(self, X0, x_target, X_ref=None, U_ref=None, active=None) -> BatchMPCSolution:
+    def solve_batch(self, X0, x_target=None, X_ref=None, U_ref=None, active=None,
+                    per_step_target: bool = False) -> BatchMPCSolution:
         """B independent `solve` calls (each scenario keeps its own warm start between calls).
 
         X0 (B,7); x_target (7,) or (B,7); optional X_ref (N+1,7)|(B,N+1,7), U_ref (N,3)|(B,N,3); optional `active`
-        (B,) mask -- scenarios with 0 are skipped (their outputs repeat the previous call).  numpy in -> numpy out,
-        CUDA float64 tensors in -> CUDA tensors out."""
+        (B,) mask -- scenarios with 0 are skipped (their outputs repeat the previous call).  per_step_target=True derives
+        every scenario's target from its current state on the device, as the reference's Monte Carlo loop does for
+        controllers with `.solve` (monte_carlo.py:497-499: x_target = x, v = 0, altitude = max(0.5, altitude - 2));
+        x_target is then ignored.  numpy in -> numpy out; CUDA float64 tensors in -> CUDA tensors out, which are VIEWS of
+        the controller state, valid until the next call (clone what must survive it)."""
         if not self._is_setup:
             self.setup()
         torch = ge.torch_()
@@ -398,6 +348,7 @@ class GPMPC:
             x0 = ge.to_dev(X0)
             if x0.dim() == 1:
                 x0 = x0[None, :]
+            x0 = x0.contiguous()
             B = x0.shape[0]
             st = self._state_for(B, single=False)
         else:   # host buffers: H2D from pinned staging memory
@@ -405,28 +356,29 @@ class GPMPC:
             B = X0h.shape[0]
             st = self._state_for(B, single=False)
             x0 = st.from_host("x0", X0h)
-            if X_ref is None and not _is_dev(x_target):
-                x_target = st.from_host("xt", x_target)
-        x_ref = self._x_ref(x_target, X_ref, B)
-        act = None if active is None else ge.to_dev(active, torch.int32)
-        uref = None if U_ref is None else ge.to_dev(U_ref)
-        self.last_kernel_launches = self._solve_device(st, x0, x_ref, uref, act)
+            if X_ref is None and x_target is not None and not per_step_target and not _is_dev(x_target):
+                xth = np.asarray(x_target, dtype=np.float64)
+                x_target = st.from_host("xt", np.broadcast_to(xth, (B, NX)))
+        if per_step_target:
+            x_target = None
+        elif x_target is None and X_ref is None:
+            raise ValueError("solve_batch needs x_target, X_ref or per_step_target=True")
+        xt, xr, ur = self._targets(st, x_target, X_ref, U_ref, B)
+        act = None if active is None else ge.to_dev(active, torch.int32).contiguous()
+        self.last_kernel_launches = self._solve_device(st, x0, xt, xr, ur, act, per_step_target)
         return self._collect(st, dev_in, t0)
 
     def _collect(self, st: _BatchState, dev_in: bool, t0: float, with_cov: bool = False) -> BatchMPCSolution:
         torch = ge.torch_()
-        success = st.converged.to(torch.bool)
-        status = st.converged.to(torch.int8)
         has_cov = self._model is not None and self.config.use_gp_uncertainty
-        if dev_in:  # stream-ordered results, no host synchronisation (solve_time is then the launch time only)
+        if dev_in:  # stream-ordered views of the controller state: no copies, no host synchronisation
             sol = BatchMPCSolution(
-                u0=st.U[:, 0].clone(), X_opt=st.X.clone(), U_opt=st.U.clone(), cost=st.cost.clone(),
-                iterations=st.n_iter.clone(), success=success, status=status, solve_time=0.0,
-                qp_status=st.ws.status.clone(), qp_iterations=st.qp_iters.clone(),
-                covariances=st.covs.clone() if has_cov else None)
+                u0=st.U[:, 0], X_opt=st.X, U_opt=st.U, cost=st.cost, iterations=st.n_iter, success=st.converged,
+                status=st.converged, solve_time=0.0, qp_status=st.ws.status, qp_iterations=st.qp_iters,
+                covariances=st.covs if has_cov else None)
         else:
             defer = self.config.defer_trajectory_copy and not with_cov
-            t = dict(cost=st.cost, it=st.n_iter, ok=success, status=status, qs=st.ws.status, qi=st.qp_iters)
+            t = dict(cost=st.cost, it=st.n_iter, ok=st.converged, qs=st.ws.status, qi=st.qp_iters)
             if defer:
                 t["u0"] = st.U[:, 0].contiguous()
             else:
@@ -435,12 +387,13 @@ class GPMPC:
                 t["cov"] = st.covs
             h = st.to_host(t)
             if defer:
-                h["X"], h["U"] = DeferredHostArray(st.X.clone()), DeferredHostArray(st.U.clone())
+                h["X"], h["U"] = DeferredHostArray(st.X, st), DeferredHostArray(st.U, st)
             else:
                 h["u0"] = h["U"][:, 0]
+            ok = h["ok"] != 0
             sol = BatchMPCSolution(
-                u0=h["u0"], X_opt=h["X"], U_opt=h["U"], cost=h["cost"], iterations=h["it"], success=h["ok"],
-                status=h["status"], solve_time=0.0, qp_status=h["qs"], qp_iterations=h["qi"],
+                u0=h["u0"], X_opt=h["X"], U_opt=h["U"], cost=h["cost"], iterations=h["it"], success=ok,
+                status=ok.astype(np.int8), solve_time=0.0, qp_status=h["qs"], qp_iterations=h["qi"],
                 covariances=h.get("cov"))
         sol.solve_time = time.perf_counter() - t0
         return sol
@@ -461,9 +414,8 @@ class GPMPC:
         t0 = time.perf_counter()
         x0d = ge.to_dev(np.asarray(x0, dtype=np.float64)[None, :])
         st = self._state_for(1, single=True)
-        x_ref = self._x_ref(np.asarray(x_target, dtype=np.float64), X_ref, 1)
-        uref = None if U_ref is None else ge.to_dev(np.asarray(U_ref, dtype=np.float64))
-        self.last_kernel_launches = self._solve_device(st, x0d, x_ref, uref, None)
+        xt, xr, ur = self._targets(st, np.asarray(x_target, dtype=np.float64), X_ref, U_ref, 1)
+        self.last_kernel_launches = self._solve_device(st, x0d, xt, xr, ur, None, False)
         b = self._collect(st, False, t0, with_cov=True)
         b.X_opt, b.U_opt, b.u0 = b.X_opt.copy(), b.U_opt.copy(), b.u0.copy()   # detach from the pinned staging
         if b.covariances is not None:

@@ -44,12 +44,19 @@ class MPCSolution:
 
 
 class DeferredHostArray:
-    """A device snapshot that becomes a numpy array the first time the owning solution's attribute is read."""
+    """A device array that becomes a numpy array the first time the owning solution's attribute is read.  `owner` (the
+    controller's batch state) counts its solves: reading after a later solve overwrote the array is an error, not a
+    silent read of newer data."""
 
-    def __init__(self, tensor):
+    def __init__(self, tensor, owner=None):
         self.tensor = tensor
+        self.owner = owner
+        self.generation = getattr(owner, "generation", None)
 
     def fetch(self):
+        if self.owner is not None and self.owner.generation != self.generation:
+            raise RuntimeError("X_opt / U_opt of an earlier solve_batch were overwritten by a later call: read them before "
+                               "the next call, or set GPMPCConfig.defer_trajectory_copy=False")
         return self.tensor.cpu().numpy()
 
 
@@ -57,7 +64,8 @@ class DeferredHostArray:
 class BatchMPCSolution:
     """Result of `solve_batch` (new entry point): B independent `MPCSolution`s as arrays.
 
-    u0 (B,3), X_opt (B,N+1,7), U_opt (B,N,3), cost (B,), iterations (B,) int, success (B,) bool,
+    u0 (B,3), X_opt (B,N+1,7), U_opt (B,N,3), cost (B,), iterations (B,) int, success (B,) bool (numpy calls; 0/1 int32
+    for CUDA-tensor calls, whose results are views of the controller state valid until the next call),
     status (B,) int8 (1 = "Converged", 0 = "Max iterations"), qp_status (B,) int (OSQP code of the last QP),
     qp_iterations (B,) int (ADMM iterations summed over the SQP loop), covariances (B,N+1,7,7) or None.
     numpy arrays when the inputs were numpy, CUDA tensors when they were CUDA tensors.  For numpy calls u0, cost and the
@@ -117,10 +125,17 @@ class NominalMPC3DoF:
             self.setup()
         return self._impl.solve(x0, x_target)
 
-    def solve_batch(self, X0, x_target) -> BatchMPCSolution:
+    def solve_batch(self, X0, x_target=None, **kw) -> BatchMPCSolution:
         if not self._is_setup:
             self.setup()
-        return self._impl.solve_batch(X0, x_target)
+        return self._impl.solve_batch(X0, x_target, **kw)
+
+    @property
+    def _batch(self):
+        return self._impl._batch
 
     def reset_warm_start(self) -> None:
         self._impl.reset_warm_start()
+
+    def reset_scenarios(self, mask, X0=None) -> None:
+        self._impl.reset_scenarios(mask, X0)

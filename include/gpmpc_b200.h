@@ -114,6 +114,11 @@ int gpmpc_tri_inverse(const double* L, int n_pad, long lda, const double* Winv, 
 int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk, double* work,
                      double* sumsq, int one_cta_per_sm, void* stream);
 
+/* The triangular GEMM of gpmpc_linv_sumsq alone: work[t * q_pad + q], t < n_pad / 64, per-tile partial sums that the
+ * caller reduces in the order t = 0, 1, ... (gpmpc_solve_batch_3dof does so inside its variance / covariance kernel). */
+int gpmpc_linv_sumsq_parts(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk, double* work,
+                           void* stream);
+
 /* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
  * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
 int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, long ldb, int ncols, int b_colmajor, double* sumsq,
@@ -244,10 +249,11 @@ int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_ste
 int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active, void* stream);
 
 /* Per-scenario reset of the batched controller state for respawned Monte Carlo runs (a new GPMPC per run in the reference,
- * monte_carlo.py:606-616): where mask[b] != 0, U_warm[b] <- hover (first control component hover0[b], others 0), the ADMM
- * duals y[b] (m) <- 0 and rho[b] <- 0 (= take the configured default). */
+ * monte_carlo.py:606-616): where mask[b] != 0 the ADMM duals y[b] (m) <- 0, rho[b] <- 0 (= take the configured default),
+ * has_warm[b] <- 0 (may be NULL: the next solve then starts from the hover guess) and, when U_warm and hover0 are given,
+ * U_warm[b] <- hover (first control component hover0[b], others 0). */
 int gpmpc_reset_scenarios(int B, int N, int nu, int m, const int* mask, const double* hover0, double* U_warm, double* y,
-                          double* rho, void* stream);
+                          double* rho, int* has_warm, void* stream);
 
 /* Unscented propagation (uncertainty_prop.py:179-264), 7-state model, one stage at a time:
  * gpmpc_ut_sigma_3dof: SP[b] (15 x 7) = x_k, x_k + columns, x_k - columns of chol(scale * Sigma_k + 1e-10 I), and the stage
@@ -280,6 +286,106 @@ int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp
                           long ldxref, const double* Qdiag, const double* Qfdiag, const double* Rdiag, double* X,
                           double* U, double* X_prev, double* U_prev, double* cost, int* converged, int* active,
                           int* n_iter, void* stream);
+
+/* ---- fused per-control-step orchestration (SURVEY 8b proposal `gpmpc_solve_batch`) ---------------------------------------
+ *
+ * One call issues the whole device sequence of `GPMPC.solve` (gp_mpc.py:229-369, 7-state specialisation) for B scenarios:
+ *   prologue (reference trajectory from the target, initial controls = warm start | U_ref | hover, gp_mpc.py:266-275)
+ *   -> GP-augmented rollout (:277-281) -> GP variances + covariance chain (:284-289, uncertainty_prop.py:117-177)
+ *   -> max_sqp_iter x [ GP means at the iterate (:309-317) -> QP assembly + primal warm start (osqp_rti.py:203-372,601-614)
+ *                       -> ADMM (osqp_rti.py:464-527) -> unpack / step-size test / cost (:336-345)
+ *                       -> re-propagation of the uncertainty (:347-353) ]
+ *   -> warm start for the next call (:355-357).
+ * 8 kernel launches for max_sqp_iter = 1, no host synchronisation, no allocation: capturable in a CUDA graph.
+ * Every pointer is a device pointer owned by the caller and must stay valid until the stream has run the call. */
+typedef struct GpmpcSolve3 {
+  int B, N;
+  int max_sqp_iter;        /* gp_mpc.py:293 (10); 1 = real-time iteration */
+  int use_gp_mean;         /* GPMPCConfig.use_gp_mean (needs model) */
+  int use_gp_uncertainty;  /* GPMPCConfig.use_gp_uncertainty (needs model, Linv or L/Winv, Ks, covs) */
+  int repropagate;         /* gp_mpc.py:347-353 */
+  int target_mode;         /* 0: x_target (B x 7) given; 1: derived per scenario from the current state as the Monte Carlo
+                              loop does for `.solve` controllers (monte_carlo.py:497-499: x, v = 0, alt = max(0.5, alt - 2)) */
+  int has_model;
+  GpmpcDyn3 dyn;
+  double g0;               /* hover thrust m g0 along axis 0 (nominal_mpc.py:651-657) */
+  GpmpcAdmmSettings admm;
+  GpmpcExactModel model;
+  const double* Linv;      /* n_pad x n_pad explicit inverse factor (gpmpc_tri_inverse) or NULL -> blocked in-place solve */
+  long ldi;
+  double tighten_kappa;    /* > 0: per-stage box tightening (gpmpc_tighten_bounds) with lb_t / ub_t */
+  double tighten_max_variance;
+  /* inputs */
+  const double* x0;        /* B x 7 */
+  const double* x_target;  /* B x 7 (target_mode 0) */
+  const double* X_ref;     /* optional B x (N+1) x 7 reference trajectory (overrides the target), row stride ld_xref_in (0: shared) */
+  long ld_xref_in;
+  const double* U_ref;     /* optional (N x 3), stride ld_uref per scenario (0: shared) */
+  long ld_uref;
+  const int* active_in;    /* optional B */
+  /* shared QP data (n = 10 N + 7) */
+  const double *Pdiag, *lb, *ub, *Qd, *Qfd, *Rd;
+  /* per-scenario state and scratch */
+  double *x_ref;           /* B x (N+1) x 7 */
+  double *X, *U;           /* B x (N+1) x 7, B x N x 3: iterate in / solution out */
+  double *Xs, *dmean, *dmean_s;
+  double *Ks; long ldk; int q_pad;
+  double *var_work, *sumsq, *dvar, *covs;
+  double *lb_t, *ub_t;
+  double *AB, *beq, *q;
+  double *cost; int *converged, *active, *n_iter, *qp_iters;
+  double *z, *y, *rho, *obj, *pri, *dua; int *qp_status, *qp_it;
+  double *U_warm, *X_warm; int* has_warm;   /* per-scenario warm start; has_warm[b] = 0 -> hover / U_ref */
+  /* optional phase timing: events[i] (cudaEvent_t) is recorded after phase event_phase[i] (host arrays written by the call) */
+  void** events; int* event_phase; int event_cap; int* event_count;
+} GpmpcSolve3;
+
+#define GPMPC_PHASE_BEGIN 0
+#define GPMPC_PHASE_PROLOGUE 1
+#define GPMPC_PHASE_ROLLOUT 2
+#define GPMPC_PHASE_GP_VARIANCE 3
+#define GPMPC_PHASE_COV 4
+#define GPMPC_PHASE_GP_MEAN 5
+#define GPMPC_PHASE_ASSEMBLE 6
+#define GPMPC_PHASE_ADMM 7
+#define GPMPC_PHASE_UPDATE 8
+#define GPMPC_PHASE_MC 9
+
+int gpmpc_solve_batch_3dof(const GpmpcSolve3* plan, int* n_launches, void* stream);
+
+/* Closed-loop Monte Carlo advance after a solve (experiments/monte_carlo.py:455-549), one thread per scenario, all on the
+ * device: [fail_policy 1: a scenario whose solve did not succeed ends as DIVERGENCE without a plant step (:507-510, the
+ * branch taken for controllers with `.solve`); 0: the flag is only counted (as for `.step` controllers, :492-494)]
+ * -> plant step (+ drag residual) -> t_step += 1 -> TIMEOUT when t_step reaches max_steps (the for/else at :539-542, the last
+ * state is not classified) else the termination rules :460-488 + check_landing :54-104.  respawn != 0: a finished
+ * scenario restarts from x_init[b] with a fresh controller (has_warm = 0, duals 0, rho unset) so the batch stays full.
+ * classify_only != 0: no solve / plant step, only the termination rules on the current state (the reference applies them
+ * to x0 before the first control). */
+typedef struct GpmpcMcStep3 {
+  int B, N, m;             /* m = rows of the QP (length of y per scenario) */
+  GpmpcDyn3 dyn;
+  double drag_cda;
+  int max_steps, fail_policy, respawn, classify_only;
+  double* x;               /* B x 7 in / out */
+  const double* u;         /* B x ldu: first control of the solution */
+  long ldu;
+  const int* success;      /* B: the solve's success flag (converged) or NULL */
+  const double *m0, *x_init;
+  int *t_step, *active, *outcome, *fail_steps;
+  double* x_final;
+  unsigned long long* counts;   /* 8 counters indexed by outcome code */
+  int* has_warm; double *y, *rho;   /* controller state cleared on respawn (may be NULL) */
+} GpmpcMcStep3;
+int gpmpc_mc_advance_3dof(const GpmpcMcStep3* args, void* stream);
+
+/* sizeof / offsetof probes for the binding tests: which = 0 GpmpcSolve3, 1 GpmpcMcStep3, 2 GpmpcAdmmSettings,
+ * 3 GpmpcExactModel; field < 0 -> sizeof, else the offset of a sentinel field (see csrc/mpc.cu). */
+long gpmpc_struct_layout(int which, int field);
+
+/* CUDA event pool for the phase timers (plain cudaEvent_t behind void*). */
+int gpmpc_events_create(int n, void** events_out);
+int gpmpc_events_destroy(int n, void** events);
+int gpmpc_events_elapsed_ms(void* a, void* b, float* ms_out);   /* synchronises on b */
 
 /* ---- 6-DoF quaternion model (BASELINE configs[3]): 14 states [m, r_I(3), v_I(3), q_BI(4), w_B(3)], 3 controls ----------- */
 

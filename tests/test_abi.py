@@ -31,6 +31,17 @@ def test_struct_layouts_match_header():
     assert ctypes.sizeof(_lib.AdmmSettings) == 8 * 8 + 11 * 4 + 4      # 8 doubles, 11 ints, tail padding to 8 bytes
     assert ctypes.sizeof(_lib.Dyn3) == 5 * 8
     assert ctypes.sizeof(_lib.ExactModel) == 6 * 4 + 8 + 8 * 8
+    # the large plan structs: sizes and sentinel offsets as the C compiler laid them out
+    lay = _lib.lib.gpmpc_struct_layout
+    assert ctypes.sizeof(_lib.AdmmSettings) == lay(2, -1)
+    assert ctypes.sizeof(_lib.ExactModel) == lay(3, -1)
+    assert ctypes.sizeof(_lib.Solve3) == lay(0, -1)
+    for i, f in enumerate(("dyn", "admm", "model", "Linv", "x0", "Ks", "q_pad", "var_work", "U_warm", "events",
+                           "event_count")):
+        assert getattr(_lib.Solve3, f).offset == lay(0, i), f
+    assert ctypes.sizeof(_lib.McStep3) == lay(1, -1)
+    for i, f in enumerate(("dyn", "max_steps", "x", "counts", "rho")):
+        assert getattr(_lib.McStep3, f).offset == lay(1, i), f
 
 
 def test_no_cpu_fallback():
