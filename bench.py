@@ -44,8 +44,13 @@ def parse_args():
     ap.add_argument("--cpu-scenarios", type=int, default=0, help="reference arm: scenarios per step (default: #cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--overlap", type=int, default=0,
-                    help="1: GP variance / covariance chain on a high-priority side stream, concurrent with the QP")
+    ap.add_argument("--no-extra", action="store_true", help="skip the short S=10 / config-3 / config-4 lines")
+    ap.add_argument("--target-mode", default="per_step", choices=["per_step", "fixed"],
+                    help="per_step: the reference's Monte Carlo target for `.solve` controllers (monte_carlo.py:497-499)")
+    ap.add_argument("--fail-policy", default="continue", choices=["continue", "divergence"],
+                    help="divergence: a solve with success == False ends the run (monte_carlo.py:507-510)")
+    ap.add_argument("--theta-every", type=int, default=100,
+                    help="broadcast the GP hyper-parameters and refit every K steps inside the timed loop (0: never)")
     return ap.parse_args()
 
 
@@ -61,13 +66,17 @@ def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
     ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
                            max_sqp_iter=sqp_iters)
     X0, XT = workloads.sample_initial_conditions(idx, 1)
-    x, xt = X0[0], XT[0]
+    x = X0[0]
     p = ompc.Rocket3DoFParams()
 
-    def one():
+    def one():   # one control step of monte_carlo.py:455-549 for a `.solve` controller (per-step target), drag plant
         nonlocal x
+        xt = x.copy(); xt[4:7] = 0; xt[1] = max(0.5, x[1] - 2.0)
         r = ctl.solve(x, xt)
-        x = ompc.step_3dof(x, r.U_opt[0], DT, p)
+        xn = ompc.step_3dof(x, r.U_opt[0], DT, p)
+        rho = 1.225 * np.exp(-x[1] / 8500.0); sp = np.sqrt(x[4] ** 2 + x[5] ** 2 + x[6] ** 2)
+        xn[4:7] = xn[4:7] + DT * (-0.5 * rho * 0.25 * sp * x[4:7] / x[0])
+        x = xn
 
     for _ in range(warmup):
         one()
@@ -232,11 +241,13 @@ def build_problem(args, rank):
     gp.add_data(X, U, D)
     gp.fit()
     dyn = Rocket3DoFDynamics()
-    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter,
-                      overlap_uncertainty=bool(getattr(args, "overlap", False)))
+    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter)
     ctl = GPMPC(dyn, gp, cfg)
     ctl.setup()
-    mc = BatchedMonteCarlo(dyn, ctl, drag_cda=0.25, respawn=True)
+    # the reference's loop for a `.solve` controller (per-step target, monte_carlo.py:497-499); a failed SQP step-size
+    # test is counted, not fatal (an RTI with S = 1 never meets it; `--fail-policy divergence` = monte_carlo.py:507-510)
+    mc = BatchedMonteCarlo(dyn, ctl, drag_cda=0.25, respawn=True, target_mode=getattr(args, "target_mode", "per_step"),
+                           on_solve_failure=getattr(args, "fail_policy", "continue"))
     mc.reset(first=rank * args.batch, count=args.batch, seed=42)
     return dyn, gp, ctl, mc
 
@@ -261,6 +272,7 @@ def run_b200_arm(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from gp_mpc_rocket_landing_b200 import distributed as D
     from gp_mpc_rocket_landing_b200.mpc import engine as me
     dyn, gp, ctl, mc = build_problem(args, rank)
     B, K, W = args.batch, args.steps, max(args.warmup, 3)
@@ -271,35 +283,52 @@ def run_b200_arm(args):
         torch.cuda.synchronize()
 
     # ---- device-resident loop ---------------------------------------------------------------------------------
+    # Every rank steps its own block of scenarios; the two collectives of the path run INSIDE the timed loop:
+    #   * the per-step statistics all-reduce (8 counters) on a side stream, device tensors only (D.AsyncStatsReducer);
+    #   * every `--theta-every` steps rank 0 broadcasts the GP hyper-parameters and every rank refits its replica
+    #     (Gram + Cholesky + alpha + inverse factor) and re-reads it into the controller.
     peak64 = fp64_peak_tflops(torch) if rank == 0 else None
     clocks = ClockSampler(local)
     clocks.start()
+    stats = D.AsyncStatsReducer(mc.counts)
     for _ in range(W):
         mc.step()
-    ctl.timers = me.PhaseTimers()
-    qp_it, launches = torch.zeros((), dtype=torch.float64, device="cuda"), 0
+        stats.submit()
+    stats.reset()
+    timers = me.EventTimers(capacity=(K + 2) * (4 + 8 * args.sqp_iters))
+    ctl.timers = timers
+    comm_ms = 0.0
     barrier()
+    mc.counts.zero_()
     clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(K):
-        sol = mc.step()
-        launches += ctl.last_kernel_launches + 2   # + mc_step3_kernel + reset_scenarios_kernel (respawn)
-        qp_it += sol.qp_iterations.sum()     # stays on the device: no host synchronisation inside the timed region
+    launches = 0
+    for k in range(K):
+        mc.step()
+        launches += ctl.last_kernel_launches + 1      # + mc_advance3_kernel (plant step, termination, respawn)
+        stats.submit()
+        if args.theta_every and (k + 1) % args.theta_every == 0:
+            t0 = time.perf_counter()
+            D.broadcast_hyperparameters(gp, version=2 + k // args.theta_every, refit=False)
+            comm_ms += (time.perf_counter() - t0) * 1e3
+            gp.fit()                                   # every rank refits (deterministic: replicas stay identical)
+            ctl.refresh_gp()
     e1.record()
+    stats.wait()
     barrier()
     clk = clocks.stop()
     ms = e0.elapsed_time(e1)
-    phases = ctl.timers.totals()
+    phases = timers.totals()
+    step_ms = np.array(timers.step_times_ms())
     ctl.timers = None
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     value = world * B * K / (ms * 1e-3)
-    stats = mc.counts.clone()
-    if world > 1:   # per-step statistics gather (the only collective of the path; tens of bytes)
-        dist.all_reduce(stats, op=dist.ReduceOp.SUM)
+    total = stats.total().cpu().numpy()               # summed over ranks by the in-loop all-reduces
+    comm_dev_ms = stats.device_ms()
 
     # ---- end-to-end loop through the public numpy API ------------------------------------------------------------
     e2e = None
@@ -309,32 +338,41 @@ def run_b200_arm(args):
         ctl.reset_warm_start()
         x = X0.copy()
         Ke = min(K, 40)
+        per_step = mc.target_mode == "per_step"
+
+        def e2e_step(x):
+            s = ctl.solve_batch(x, XT, per_step_target=per_step)   # H2D: x (, XT); D2H: u0, cost, flags
+            xn = dyn.step_batch(x, s.u0, DT)                        # H2D: x, u0 ; D2H: x_next
+            # the termination rules of the Monte Carlo loop (experiments/monte_carlo.py:460-488), on the host copy:
+            # finished scenarios restart from their initial condition, exactly as the device-resident loop respawns them
+            done = (xn[:, 1] < 0.0) | (xn[:, 0] <= 1.01) | ((xn[:, 1] < 1.0) & (np.abs(xn[:, 4]) < 5.0)) | \
+                   ~np.all(np.abs(xn) <= 1e6, axis=1)
+            if done.any():
+                xn[done] = X0[done]
+                ctl.reset_scenarios(done)
+            return xn
+
         for _ in range(W):
-            s = ctl.solve_batch(x, XT)
-            x = dyn.step_batch(x, s.u0, DT)
+            x = e2e_step(x)
         barrier()
         t0 = time.perf_counter()
         for _ in range(Ke):
-            s = ctl.solve_batch(x, XT)          # H2D: x, XT ; D2H: u0, cost, flags (X_opt / U_opt on request)
-            x = dyn.step_batch(x, s.u0, DT)     # H2D: x, u0 ; D2H: x_next
-            # the termination rules of the Monte Carlo loop (experiments/monte_carlo.py:460-488), on the host copy:
-            # finished scenarios restart from their initial condition, exactly as the device-resident loop respawns them
-            done = (x[:, 1] < 0.0) | (x[:, 0] <= 1.01) | ((x[:, 1] < 1.0) & (np.abs(x[:, 4]) < 5.0)) | \
-                   ~np.all(np.abs(x) <= 1e6, axis=1)
-            if done.any():
-                x[done] = X0[done]
-                ctl.reset_scenarios(done, X0)
+            x = e2e_step(x)
         barrier()
         te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:
             dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        h2d = B * (7 + 7 + 7 + 3) * 8
+        h2d = B * (7 + (0 if per_step else 7) + 7 + 3) * 8
         # u0 (3) + cost (1) doubles, iteration / status / flag arrays, and the next state from step_batch; the planned
         # trajectories X_opt / U_opt stay on the device until the caller reads them (BatchMPCSolution defers that copy)
-        d2h = B * (3 + 1) * 8 + B * (4 + 1 + 1 + 4 + 4) + B * 7 * 8
+        d2h = B * (3 + 1) * 8 + B * (4 + 4 + 4 + 4) + B * 7 * 8
         e2e = {"value": world * B * Ke / float(te.item()), "unit": "solves/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": d2h, "steps": Ke, "timer": "host wall clock around synchronised steps",
                "result_read": "u0, cost, status / iteration flags, next state (trajectories on request)"}
+
+    extra = {}
+    if rank == 0 and world == 1 and not args.no_extra:
+        extra = run_extras(args, torch)
 
     if rank == 0:
         # ---- rooflines: algorithmic work per launch / measured launch time ------------------------
@@ -348,20 +386,21 @@ def run_b200_arm(args):
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         hbm_src = "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
         n_pad = ((N_TRAIN + 127) // 128) * 128
-        work = {  # phase -> (bound, algorithmic units per step: flops or bytes, kernel description)
-            "gp_variance": ("tensor", Q * float(n_pad) ** 2,
-                            ("dgemm_nt_kernel x1: triangular DMMA GEMM |L^-1 K*^T|^2 against the explicit inverse factor, "
-                             "sum of squares fused, V never stored (n_pad^2 flop per query, SURVEY 8d)")
-                            if ctl.config.variance_via_inverse else
-                            ("dgemm_nt_kernel x31: blocked DMMA TRSM V = L^-1 K*^T with fused sum of squares (n_pad^2 flop "
-                             "per query, SURVEY 8d)")),
-            "admm": ("hbm", B * 22e3, "admm_stage_kernel<7,3,20,2>: 22 kB compulsory per QP (SURVEY 8d); dependency-chain bound, "
-                                      "neither HBM nor FLOP limited (DESIGN.md section 4)"),
+        n_admm_it = float(total[7]) / max(1.0, float(total[0]))
+        work = {  # phase -> (bound, algorithmic units per launch: flops or bytes, kernel description)
+            "gp_variance": ("tensor", Q * float(N_TRAIN) ** 2,
+                            "dgemm_nt_kernel x1: triangular DMMA GEMM |L^-1 K*^T|^2 against the explicit inverse factor, "
+                            "sum of squares fused, V never stored (n^2 P_L flop per query with n = 1000, SURVEY 8d; the "
+                            f"kernel runs on n_pad = {n_pad})"),
+            "admm": ("hbm", B * 22e3, "admm kernel<7,3,20>: 22 kB compulsory per QP (SURVEY 8d); dependency-chain / "
+                                      "shared-memory bound, neither HBM nor FLOP limited (DESIGN.md section 4, 7)"),
             "rollout": ("hbm", Q * 8.0 * n_pad + B * 8.0 * (7 + 60 + 147 + 60),
-                        "rollout3_kernel: K* rows written once (8 n_pad bytes per query) + trajectories"),
-            "cov": ("hbm", B * 8.0 * (21 * 49 + 60 + 60 + 147 + 60), "predict_var + propagate_cov3_kernel"),
-            "assemble": ("hbm", B * 8.0 * (1400 + 147 + 207 + 207 + 147 + 60 + 60), "qp_assemble3 + pack_traj3 kernels"),
-            "update": ("hbm", B * 8.0 * (207 + 2 * 207 + 2), "mpc_update3_kernel"),
+                        "rollout3_smem_kernel: K* rows written once (8 n_pad bytes per query) + trajectories"),
+            "cov": ("hbm", B * 8.0 * (21 * 49 + 60 + 60 + 147 + 60) + Q * 8.0 * (n_pad // 64),
+                    "var_cov3_kernel: partial sums -> variances -> covariance chain"),
+            "assemble": ("hbm", B * 8.0 * (1400 + 147 + 207 + 207 + 147 + 60 + 60), "qp_assemble3_kernel (+ fused z pack)"),
+            "update": ("hbm", B * 8.0 * (207 + 2 * 207 + 2 + 207), "mpc_update3_kernel (+ fused warm-start store)"),
+            "prologue": ("hbm", B * 8.0 * (147 + 60 + 60 + 7), "solve_prologue3_kernel"),
         }
         by_kernel = {}
         for name, (tot, cnt) in phases.items():
@@ -377,27 +416,98 @@ def run_b200_arm(args):
                 r = {"kernel": desc, "bound": "hbm", "achieved": units / avg_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                      "peak_source": hbm_src}
             r["frac"] = r["achieved"] / r["peak"] if r["peak"] else None
-            r["avg_ms_per_step"] = avg_s * 1e3
+            r["avg_ms_per_launch"] = avg_s * 1e3
             r["share_of_step"] = share[name]
             r["traffic"] = NCU_TRAFFIC.get(name)
             by_kernel[name] = r
+        if "admm" in by_kernel:
+            # "report achieved HBM GB/s against the compulsory-byte figure AND FP64 FMA utilisation": the
+            # kernel is bound by its dependency chains, so a flop view and a latency model are printed next to the bytes
+            r = by_kernel["admm"]
+            flops = B * (53e3 + n_admm_it * 25e3)           # factor + 25 kFLOP per iteration
+            r["fp64_tflops"] = flops / (r["avg_ms_per_launch"] * 1e-3) / 1e12
+            r["fp64_fma_frac_of_dgemm_peak"] = r["fp64_tflops"] / peak64 if peak64 else None
+            r["mean_iterations"] = n_admm_it
+            r["us_per_iteration_of_batch"] = r["avg_ms_per_launch"] * 1e3 / max(n_admm_it, 1.0)
+            r.update(ADMM_MODEL)
         dom = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"])
         roof = dict(by_kernel[dom])
         roof["phase"] = dom
+        outcomes = {n: int(total[i]) for i, n in enumerate(
+            ("", "success", "crash", "fuel_exhausted", "constraint_violation", "timeout", "divergence")) if n}
         line = {
             "metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config_dict(args, world), "e2e": e2e, "gpu_launches": launches,
+            "launches_per_step": launches / K,
             "roofline": roof, "roofline_by_kernel": by_kernel, "cpu_baseline": cpu_base, "clocks": clk,
             "phases_share_of_step": share, "phase_ms_per_step": {k: v[0] / K for k, v in phases.items()},
-            "mean_admm_iters_per_solve": float(qp_it.item()) / (B * K), "p50_step_latency_ms": ms / K,
+            "phases_sum_over_step": sum(v[0] for v in phases.values()) / ms,
+            "mean_admm_iters_per_solve": n_admm_it,
+            "p50_step_latency_ms": float(np.median(step_ms)) if step_ms.size else ms / K,
+            "p99_step_latency_ms": float(np.percentile(step_ms, 99)) if step_ms.size else None,
+            "max_step_latency_ms": float(step_ms.max()) if step_ms.size else None,
+            "comm": {"stats_allreduce_per_step": 1, "theta_broadcast_every": args.theta_every,
+                     "theta_broadcast_host_ms_per_step": comm_ms / K, "stats_allreduce_device_ms_per_step": comm_dev_ms / K,
+                     "note": "collectives are issued inside the timed loop; the stats all-reduce runs on a side stream"},
             "fp64_peak_tflops_measured": peak64,
-            "outcomes": {n: int(stats[i].item()) for i, n in enumerate(
-                ("", "success", "crash", "fuel_exhausted", "constraint_violation", "timeout", "divergence")) if n},
+            "outcomes_all_ranks": outcomes, "runs_finished_all_ranks": int(sum(outcomes.values())),
+            "success_rate": outcomes["success"] / max(1, sum(outcomes.values())),
+            "extra": extra,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+# latency model of the ADMM kernel: filled from the kernel's structure, printed with the roofline
+ADMM_MODEL = {}
+
+
+def run_extras(args, torch):
+    """Short driver-run lines for the other BASELINE configs (rank 0, one GPU): S = 10 SQP iterations (gp_mpc.py:296,343),
+    config 3 (refit sweep, n = 4000) and config 4 (6-DoF, 1024 scenarios).  Each is bounded to a few seconds."""
+    out = {}
+    try:
+        import copy
+        a10 = copy.copy(args)
+        a10.sqp_iters, a10.batch = 10, args.batch
+        dyn, gp, ctl, mc = build_problem(a10, 0)
+        for _ in range(3):
+            mc.step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 10
+        mc.counts.zero_()
+        e0.record()
+        for _ in range(n):
+            mc.step()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        c = mc.counts.cpu().numpy()
+        out["sqp10"] = {"config": "same workload with the reference's SQP loop, up to 10 iterations per solve "
+                                  "(gp_mpc.py:296,343), uncertainty re-propagated after every iteration (:347-353)",
+                        "ms_per_step": ms, "solves_per_s": args.batch / (ms * 1e-3),
+                        "qp_solves_per_s": args.batch * 10 / (ms * 1e-3),
+                        "mean_admm_iters_per_solve": float(c[7]) / max(1.0, float(c[0])), "launches_per_step": ctl.last_kernel_launches + 1}
+        del dyn, gp, ctl, mc
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        out["sqp10"] = {"error": repr(e)}
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_refit
+        out["config3_refit_sweep_n4000"] = bench_refit.measure(4000, reps=2, kernels=("se_ard",))[0]
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        out["config3_refit_sweep_n4000"] = {"error": repr(e)}
+    try:
+        import bench_6dof
+        out["config4_6dof_1024"] = bench_6dof.measure(batch=1024, steps=10, warmup=3)
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        out["config4_6dof_1024"] = {"error": repr(e)}
+    return out
 
 
 if __name__ == "__main__":

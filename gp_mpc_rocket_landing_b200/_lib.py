@@ -90,7 +90,7 @@ class McStep3(C.Structure):
         ("max_steps", c_int), ("fail_policy", c_int), ("respawn", c_int), ("classify_only", c_int),
         ("x", c_dp), ("u", c_dp), ("ldu", c_long), ("success", c_dp), ("m0", c_dp), ("x_init", c_dp),
         ("t_step", c_dp), ("active", c_dp), ("outcome", c_dp), ("fail_steps", c_dp), ("x_final", c_dp), ("counts", c_dp),
-        ("has_warm", c_dp), ("y", c_dp), ("rho", c_dp),
+        ("has_warm", c_dp), ("y", c_dp), ("rho", c_dp), ("qp_iters", c_dp),
     ]
 
 

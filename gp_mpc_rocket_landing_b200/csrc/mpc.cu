@@ -930,6 +930,10 @@ __global__ void __launch_bounds__(128) mc_advance3_kernel(GpmpcMcStep3 a) {
   } else {
     const bool ok = a.success == nullptr || a.success[b] != 0;
     if (!ok && a.fail_steps) a.fail_steps[b] += 1;
+    if (a.counts) {  // counts[0]: solves consumed by the loop, counts[7]: their ADMM iterations
+      atomicAdd(a.counts, 1ULL);
+      if (a.qp_iters) atomicAdd(a.counts + 7, (unsigned long long)a.qp_iters[b]);
+    }
     if (!ok && a.fail_policy == 1) {  // monte_carlo.py:507-510: "MPC solve failed" -> DIVERGENCE, no plant step
       code = 6;
 #pragma unroll

@@ -111,6 +111,71 @@ def reduce_stats(counts, sums=None):
     return outs[0] if sums is None else tuple(outs)
 
 
+class AsyncStatsReducer:
+    """The per-step statistics gather of the Monte Carlo path (north_star: "NCCL ... only to gather per-step statistics"):
+    a SUM all-reduce of the rank's cumulative counter vector (8 int64: runs ended per outcome, solves, ADMM iterations),
+    issued every control step on a SIDE stream with device tensors only -- no `.item()`, no numpy round trip, and the
+    main stream never waits for it.  `total()` is the latest global vector (device tensor, valid after `wait()`).
+    With CPU tensors (gloo tests) or without a process group it degrades to a synchronous reduce / a copy."""
+
+    def __init__(self, counts):
+        import torch
+        self.src = counts
+        self.cuda = counts.is_cuda
+        self.buf = torch.zeros_like(counts)
+        self.glob = torch.zeros_like(counts)
+        self.side = torch.cuda.Stream() if self.cuda else None
+        self.n = 0
+        self._timed = []
+
+    def reset(self):
+        self.n = 0
+        self._timed = []
+
+    def submit(self):
+        import torch
+        self.n += 1
+        if not self.cuda:
+            self.buf.copy_(self.src)
+            if is_initialized():
+                _dist().all_reduce(self.buf, op=_dist().ReduceOp.SUM)
+            self.glob.copy_(self.buf)
+            return
+        ev = torch.cuda.Event()
+        ev.record()                                   # after this step's counters were written on the main stream
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(ev)
+            timed = self.n <= 64
+            if timed:
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(self.side)
+            self.buf.copy_(self.src, non_blocking=True)
+            if is_initialized():
+                _dist().all_reduce(self.buf, op=_dist().ReduceOp.SUM)
+            self.glob.copy_(self.buf, non_blocking=True)
+            if timed:
+                b.record(self.side)
+                self._timed.append((a, b))
+
+    def wait(self):
+        if self.cuda:
+            import torch
+            torch.cuda.current_stream().wait_stream(self.side)
+
+    def total(self):
+        self.wait()
+        return self.glob
+
+    def device_ms(self) -> float:
+        """Device time of the side-stream work (copy + all-reduce + copy), extrapolated from the first 64 timed steps."""
+        if not self._timed:
+            return 0.0
+        import torch
+        torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in self._timed)
+        return t / len(self._timed) * self.n
+
+
 def gather_records(local: np.ndarray) -> np.ndarray:
     """All-gather of per-scenario terminal records (rows) in rank order -> the global array on every rank.  Shards may
     have different lengths (remainder ranks)."""

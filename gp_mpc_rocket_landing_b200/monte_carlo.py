@@ -136,12 +136,14 @@ class BatchedMonteCarlo:
             self._u0 = sol.u0.contiguous()
             self._ok = sol.success.to(torch.int32)
             a.u, a.ldu, a.success = ge.ptr(self._u0), self._u0.stride(0), ge.ptr(self._ok)
+            a.qp_iters = None
             a.has_warm = a.y = a.rho = None
         else:
             sol = self.controller.solve_batch(self.x, self.xt, active=self.active,
                                               per_step_target=self.target_mode == "per_step")
             U = sol.U_opt                    # (B,N,3) view of the controller state: u0 = U[:,0]
             a.u, a.ldu, a.success = U.data_ptr(), U.stride(0), ge.ptr(sol.success)
+            a.qp_iters = ge.ptr(sol.qp_iterations)
             st = getattr(self.controller, "_batch", None)
             if self.respawn and st is not None:   # controller state cleared on the device for respawned scenarios
                 a.has_warm, a.y, a.rho, a.m = ge.ptr(st.has_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), st.ws.y.shape[1]

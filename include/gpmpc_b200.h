@@ -373,8 +373,9 @@ typedef struct GpmpcMcStep3 {
   const double *m0, *x_init;
   int *t_step, *active, *outcome, *fail_steps;
   double* x_final;
-  unsigned long long* counts;   /* 8 counters indexed by outcome code */
+  unsigned long long* counts;   /* 8 counters: [1..6] runs ended per outcome code, [0] solves consumed, [7] their ADMM iterations */
   int* has_warm; double *y, *rho;   /* controller state cleared on respawn (may be NULL) */
+  const int* qp_iters;          /* B: ADMM iterations of this step's solve (may be NULL) */
 } GpmpcMcStep3;
 int gpmpc_mc_advance_3dof(const GpmpcMcStep3* args, void* stream);
 

@@ -69,6 +69,67 @@ def query_fixture(X, U, nq, seed):
     return X[idx] + rng.normal(0, 0.05, (nq, 7)), U[idx] + rng.normal(0, 0.05, (nq, 3))
 
 
+def mc_loop_fixture(save):
+    """12. the reference's own closed loop (monte_carlo.py:401-583 `run_single`) around deterministic stub controllers:
+    pins the loop semantics -- termination rules, per-step target for `.solve` controllers, `success == False ->
+    DIVERGENCE`, `.step` controllers whose flag is ignored, the for/else TIMEOUT -- that `gpmpc_mc_advance_3dof` and
+    `oracle.mpc.run_single` restate.  Runs 32 seeds with max_time 20 s (200 steps) so that every outcome class occurs."""
+    import src.experiments.monte_carlo as MC
+    from oracle import mpc as ompc
+    from oracle.mpc import EulerDynamics
+
+    class Sol:
+        def __init__(self, u, ok):
+            self.u0, self.success = u, ok
+
+    class SolveCtl:      # has .solve, no .step: the branch of monte_carlo.py:495-510
+        def __init__(self, gains, fail_step):
+            self.gains, self.fail_step, self.k, self.targets = gains, fail_step, 0, []
+
+        def solve(self, x, x_target):
+            self.targets.append(x_target.copy())
+            ok = self.k != self.fail_step
+            self.k += 1
+            return Sol(ompc.pd_test_law(x, x_target, self.gains), ok)
+
+    class StepCtl:       # has .initialize / .step: the branch of :492-494 (fixed target, flag ignored)
+        def __init__(self, gains, fail_step):
+            self.gains, self.fail_step, self.k = gains, fail_step, 0
+
+        def initialize(self, x0, x_target):
+            self.xt = x_target.copy()
+
+        def step(self, x):
+            ok = self.k != self.fail_step
+            self.k += 1
+            return Sol(ompc.pd_test_law(x, self.xt, self.gains), ok)
+
+    cfg = MC.SimulationConfig(dt=0.1, max_time=20.0, altitude_mean=30.0, altitude_std=5.0, horizontal_std=3.0,
+                              velocity_mean=np.array([-3.0, 0.0, 0.0]), velocity_std=np.array([1.0, 0.5, 0.5]))
+    order = list(MC.LandingOutcome)
+    out = {}
+    for kind, cls in (("solve", SolveCtl), ("step", StepCtl)):
+        oc, xf, nst, fu, x0s, tg = [], [], [], [], [], []
+        for i in range(32):
+            gains, fail_step = ompc.pd_test_gains(i)
+            ctl = cls(gains, fail_step)
+            sim = MC.MonteCarloSimulator(EulerDynamics(), controller=ctl, config=cfg)
+            r = sim.run_single(i, seed=42 + i)
+            oc.append(order.index(r.outcome) + 1)
+            xf.append(r.states[-1]); nst.append(len(r.controls)); fu.append(r.fuel_used); x0s.append(r.initial_state)
+            if kind == "solve":
+                t = np.zeros((3, 7))
+                t[:min(3, len(ctl.targets))] = np.array(ctl.targets[:3]).reshape(-1, 7)
+                tg.append(t)
+        out[kind + "_outcome"] = np.array(oc); out[kind + "_final"] = np.array(xf)
+        out[kind + "_nsteps"] = np.array(nst); out[kind + "_fuel"] = np.array(fu)
+        if kind == "solve":
+            out["x0"] = np.array(x0s); out["solve_targets"] = np.array(tg)
+    print("   mc_loop outcomes (.solve):", np.bincount(out["solve_outcome"], minlength=7)[1:],
+          "(.step):", np.bincount(out["step_outcome"], minlength=7)[1:])
+    save("mc_loop.npz", **out)
+
+
 def online_fixture(G, save):
     """11. online data path (reference src/gp/online_update.py): DataBuffer ring semantics, and the accept / update
     sequence of OnlineGPUpdater around a reference SparseGP with injected inducing points (no RNG dependence)."""
@@ -194,6 +255,22 @@ def main():
     out["Z_train"] = gp.feature_extractor.extract_batch(X, U)
     out["Z_query"] = gp.feature_extractor.extract_batch(Xq, Uq)
     save("simple3dof_exact.npz", **out)
+
+    # ---- 2b. extended-precision arbiter of the same fixture: the posterior in x87 long double
+    # (64-bit mantissa) from the reference's feature matrices, and cond(K + noise I).  NOT a reference output: it is
+    # the yardstick that tells "differs from the reference" apart from "both are within cond*eps of the truth".
+    from oracle import gp as ogp
+    arb = {}
+    for tag, noise in (("n1e-4", 1e-4), ("n1e-2", 1e-2)):
+        K = ogp.gram(ogp.SE, out["Z_train"], out["Z_train"], np.ones(11), 1.0) + noise * np.eye(1000)
+        arb[f"{tag}_cond"] = np.linalg.cond(K)
+        tm = np.zeros((64, 3)); tv = np.zeros((64, 3))
+        for pcol in range(3):
+            f = ogp.exact_fit(ogp.SE, out["Z_train"], Dres[:, pcol], np.ones(11), 1.0, noise)
+            m, v = ogp.longdouble_exact_predict(f, out["Z_query"])
+            tm[:, pcol] = m.astype(np.float64); tv[:, pcol] = v.astype(np.float64)
+        arb[f"{tag}_truth_mean"] = tm; arb[f"{tag}_truth_var"] = tv
+    save("simple3dof_arbiter.npz", **arb)
 
     # ---- 3. ExactGP with each kernel, n=200 (+ return_cov, no-normalise) ------------------
     rng = np.random.default_rng(3)
@@ -344,6 +421,7 @@ def main():
     save("monte_carlo.npz", ics=ics, states=states, landing_ok=ok)
     online_fixture(G, save)
     unscented_fixture(G, save)
+    mc_loop_fixture(save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

@@ -683,3 +683,65 @@ def termination(x, m0):
     if x[1] < 1.0 and abs(x[4]) < 5.0:
         return OUT_SUCCESS if check_landing(x, m0) else OUT_VIOLATION
     return OUT_RUNNING
+
+
+def run_single(solve, x0, dt=0.1, max_time=30.0, params=None, target_mode="per_step", on_solve_failure="divergence",
+               drag_cda=0.0, step_fn=None):
+    """monte_carlo.py:401-583, the closed loop of one run.  `solve(x, x_target) -> (u0, success)`.
+    target_mode "per_step" = the branch for controllers with `.solve` (:495-499), "fixed" = the target of :428-429 that a
+    `.step` controller receives through `initialize`; on_solve_failure "divergence" = :507-510, "continue" = the `.step`
+    branch (:492-494), which never looks at the flag.  Returns (outcome code, final state, number of plant steps,
+    number of failed solves)."""
+    p = params or Rocket3DoFParams()
+    x = np.asarray(x0, float).copy()
+    m0 = x[0]
+    x_fixed = np.zeros(NX); x_fixed[0] = m0                       # :428-429
+    max_steps = int(max_time / dt)                                # :447
+    n_fail = 0
+    for step in range(max_steps):                                 # :455
+        code = termination(x, m0)                                 # :460-488
+        if code != OUT_RUNNING:
+            return code, x, step, n_fail
+        if target_mode == "per_step":                             # :497-499
+            xt = x.copy(); xt[4:7] = 0; xt[1] = max(0.5, x[1] - 2.0)
+        else:
+            xt = x_fixed
+        u, ok = solve(x, xt)
+        if not ok:
+            n_fail += 1
+            if on_solve_failure == "divergence":                  # :507-510
+                return OUT_DIVERGENCE, x, step, n_fail
+        xn = step_fn(x, u, dt) if step_fn is not None else step_3dof(x, u, dt, p)   # :528
+        if drag_cda:
+            rho = 1.225 * np.exp(-x[1] / 8500.0)
+            sp = np.sqrt(x[4] * x[4] + x[5] * x[5] + x[6] * x[6])
+            xn[4:7] = xn[4:7] + dt * (-0.5 * rho * drag_cda * sp * x[4:7] / x[0])
+        x = xn
+    return OUT_TIMEOUT, x, max_steps, n_fail                      # for/else :539-542
+
+
+def pd_test_law(x, xt, gains):
+    """A deterministic stand-in controller for pinning the LOOP (not a reference function): PD towards the target with
+    the reference's control box (osqp_rti.py:200-201).  gains = (kp_alt, kd_alt, kp_lat, kd_lat, bias)."""
+    kp, kd, kpl, kdl, bias = gains
+    m = x[0]
+    u = np.empty(3)
+    u[0] = m * (1.0 + bias + kp * (xt[1] - x[1]) + kd * (xt[4] - x[4]))
+    u[1] = m * (kpl * (xt[2] - x[2]) + kdl * (xt[5] - x[5]))
+    u[2] = m * (kpl * (xt[3] - x[3]) + kdl * (xt[6] - x[6]))
+    return np.minimum(np.maximum(u, U_MIN), U_MAX)
+
+
+def pd_test_gains(i):
+    """Gains / failure step of test run i: a spread that visits every outcome class of monte_carlo.py:24-33."""
+    table = [
+        (0.9, 1.0, 0.3, 0.8, 0.0),     # soft descent at ~1.8 m/s
+        (0.5, 1.0, 0.0, 0.0, 0.0),     # no lateral control
+        (0.05, 0.1, 0.3, 0.8, -0.6),   # under-thrust: arrives fast
+        (0.0, 0.0, 0.0, 0.0, -0.85),   # minimum thrust: crash
+        (0.0, 2.0, 0.0, 0.0, 0.0),     # hover: timeout
+        (0.5, 1.0, 0.3, 0.8, 0.0),     # solve failure at step 10 (fail_step below)
+        (2.0, 0.2, 2.0, 0.1, 1.5),     # aggressive, oscillating: burns fuel
+        (0.8, 1.0, 0.3, 0.8, 0.0),
+    ]
+    return table[i % 8], (10 if i % 8 == 5 else -1)

@@ -43,6 +43,14 @@ def _worker(rank, world_size, port, q):
         c, s = D.reduce_stats(counts, sums)
         out["counts"] = c.numpy().copy()
         out["sums"] = s
+        # --- the per-step statistics reducer the timed loop uses (bench.py): cumulative counters, one reduce per step
+        loc = torch.zeros(8, dtype=torch.int64)
+        red = D.AsyncStatsReducer(loc)
+        for step in range(3):
+            loc[0] += 10 * (rank + 1)
+            loc[1 + rank] += 1
+            red.submit()
+        out["stream_total"] = red.total().numpy().copy()
         # --- hyper-parameter broadcast: rank 0 holds refit values, rank 1 the defaults
         gp = Simple3DoFGP(use_sparse=False, noise_variance=1e-4)
         if rank == 0:
@@ -81,6 +89,7 @@ def test_world_size_2_gloo():
         np.testing.assert_array_equal(res[r]["X0_all"], X0)          # shards concatenate to the unsharded batch
         np.testing.assert_array_equal(res[r]["counts"], [0, 3, 4, 0, 0, 0, 0, 0])
         np.testing.assert_allclose(res[r]["sums"], [4.5, 20.0])
+        np.testing.assert_array_equal(res[r]["stream_total"], [90, 3, 3, 0, 0, 0, 0, 0])
         assert res[r]["version"] == 7
     np.testing.assert_array_equal(res[0]["theta"], res[1]["theta"])  # replicas hold bit-identical hyper-parameters
     assert res[0]["theta"].shape == (3, 13)
@@ -100,3 +109,8 @@ def test_single_process_identity():
     c = D.reduce_stats(np.arange(8))
     np.testing.assert_array_equal(c, np.arange(8))
     np.testing.assert_array_equal(D.gather_records(np.ones((3, 2))), np.ones((3, 2)))
+    import torch
+    loc = torch.arange(8)
+    red = D.AsyncStatsReducer(loc)
+    red.submit()
+    np.testing.assert_array_equal(red.total().numpy(), np.arange(8))

@@ -7,15 +7,13 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--batch", type=int, default=1024)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--sqp-iters", type=int, default=1)
-    ap.add_argument("--inducing", type=int, default=100)
-    ap.add_argument("--cpu", action="store_true")
-    a = ap.parse_args()
+class _A:
+    pass
+
+
+def measure(batch=1024, steps=20, warmup=3, sqp_iters=1, inducing=100, cpu=False):
+    a = _A()
+    a.batch, a.steps, a.warmup, a.sqp_iters, a.inducing, a.cpu = batch, steps, warmup, sqp_iters, inducing, cpu
     import torch
     import gp_mpc_rocket_landing_b200.gp as gp
     import gp_mpc_rocket_landing_b200.mpc as mpc
@@ -73,7 +71,19 @@ def main():
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "solves/s", "cores": os.cpu_count(), "kind": "port",
                                 "sample": "1 solve of 1 scenario (numpy/scipy oracle, dense KKT), %.2f s, %d ADMM iterations" % (dt, r.iters)}
-    print(json.dumps(line), flush=True)
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--sqp-iters", type=int, default=1)
+    ap.add_argument("--inducing", type=int, default=100)
+    ap.add_argument("--cpu", action="store_true")
+    a = ap.parse_args()
+    print(json.dumps(measure(a.batch, a.steps, a.warmup, a.sqp_iters, a.inducing, a.cpu)), flush=True)
 
 
 if __name__ == "__main__":
