@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--cpu-scenarios", type=int, default=0, help="reference arm: scenarios per step (default: #cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--admm-variant", type=int, default=0, help="GpmpcAdmmSettings.kernel_variant (0 newest, 2 / 1 older)")
     ap.add_argument("--no-extra", action="store_true", help="skip the short S=10 / config-3 / config-4 lines")
     ap.add_argument("--target-mode", default="per_step", choices=["per_step", "fixed"],
                     help="per_step: the reference's Monte Carlo target for `.solve` controllers (monte_carlo.py:497-499)")
@@ -241,7 +242,8 @@ def build_problem(args, rank):
     gp.add_data(X, U, D)
     gp.fit()
     dyn = Rocket3DoFDynamics()
-    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter)
+    cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter,
+                      qp_kernel_variant=int(getattr(args, "admm_variant", 0)))
     ctl = GPMPC(dyn, gp, cfg)
     ctl.setup()
     # the reference's loop for a `.solve` controller (per-step target, monte_carlo.py:497-499); a failed SQP step-size

@@ -18,10 +18,11 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libgpmpc_b200.so")
-SOURCES = ["gram.cu", "linalg.cu", "admm.cu", "admm_stage.cu", "mpc.cu", "mpc6.cu", "sparse.cu", "lml_grad.cu"]
+SOURCES = ["gram.cu", "linalg.cu", "admm.cu", "admm_stage.cu", "admm3.cu", "mpc.cu", "mpc6.cu", "sparse.cu", "lml_grad.cu"]
 # element-wise model arithmetic must round like the numpy reference (no FMA contraction); the hot inner products in
 # these files are DMMA inline asm / explicit fma() and are unaffected
-EXTRA_FLAGS = {"gram.cu": ["-fmad=false"], "mpc.cu": ["-fmad=false"], "mpc6.cu": ["-fmad=false"], "sparse.cu": ["-fmad=false"]}
+EXTRA_FLAGS = {"admm3.cu": (["-DADMM3_TRACE"] if os.environ.get("ADMM3_TRACE") else []),
+               "gram.cu": ["-fmad=false"], "mpc.cu": ["-fmad=false"], "mpc6.cu": ["-fmad=false"], "sparse.cu": ["-fmad=false"]}
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-I" + os.path.join(ROOT, "include"), "-I" + CSRC,

@@ -765,6 +765,14 @@ int launch_admm_stage(int N, int B, const double* AB, const double* beq, const d
                       double* scratch, double* x, double* y, double* rho, int* status, int* iters, double* obj,
                       double* pri, double* dua, cudaStream_t stream);
 
+// third-generation kernel (csrc/admm3.cu); returns GPMPC_ERR_ARG without launching when N is not the compiled horizon
+template <int NX, int NU>
+size_t admm3_scratch_doubles(int N);
+template <int NX, int NU>
+int launch_admm3(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag, const double* lb,
+                 const double* ub, const GpmpcAdmmSettings& S, const int* active, double* scratch, double* x, double* y,
+                 double* rho, int* status, int* iters, double* obj, double* pri, double* dua, cudaStream_t stream);
+
 extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const double* beq, const double* q,
                                 const double* Pdiag, const double* lb, const double* ub,
                                 const GpmpcAdmmSettings* settings, const int* active, double* x, double* y, double* rho,
@@ -772,7 +780,24 @@ extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, 
   GPMPC_REQUIRE(settings != nullptr, "gpmpc_admm_solve: settings is NULL");
   GPMPC_REQUIRE(N >= 1 && B >= 0, "gpmpc_admm_solve: bad N or B");
   if (B == 0) return GPMPC_OK;
-  if ((nx == 7 || nx == 14) && nu == 3 && settings->kernel_variant == 0) {
+  // kernel_variant 0: the fastest kernel measured for the shape -- third generation (csrc/admm3.cu: light iterations +
+  // cyclic reduction) for nx = 14 at its compiled horizon N = 30 (ADMM phase of the closed loop 19.5 -> 14.5 ms), second
+  // generation (csrc/admm_stage.cu) otherwise: at nx = 7, N = 20 the third generation wins per light iteration (32.3 vs 39.3
+  // us per iteration of 4096 QPs) but loses it again in its heavier checking iterations and refactorisations (closed loop:
+  // 3.06 vs 2.83 ms).  3 / 2 / 1: force the third / second / first generation.
+  const bool gen3 = settings->kernel_variant == 3 || (settings->kernel_variant == 0 && nx == 14);
+  if ((nx == 7 || nx == 14) && nu == 3 && gen3) {
+    const size_t per = (nx == 7) ? admm3_scratch_doubles<7, 3>(N) : admm3_scratch_doubles<14, 3>(N);
+    double* scratch = alloc_scaling_scratch(per * (size_t)B, (cudaStream_t)stream);
+    if (!scratch) return GPMPC_ERR_CUDA;
+    const int rc = (nx == 7) ? launch_admm3<7, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y, rho,
+                                                  status, iters, obj, pri_res, dua_res, (cudaStream_t)stream)
+                             : launch_admm3<14, 3>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, scratch, x, y, rho,
+                                                   status, iters, obj, pri_res, dua_res, (cudaStream_t)stream);
+    cudaFreeAsync(scratch, (cudaStream_t)stream);
+    if (rc != GPMPC_ERR_ARG) return rc;  // GPMPC_ERR_ARG: not the compiled horizon
+  }
+  if ((nx == 7 || nx == 14) && nu == 3 && settings->kernel_variant != 1) {
     const size_t nv = (size_t)N * (nx + nu) + nx, nm = 2 * nv + (size_t)nx * (N + 1);  // n + m
     double* scratch = alloc_scaling_scratch(nm * (size_t)B, (cudaStream_t)stream);
     if (!scratch) return GPMPC_ERR_CUDA;

@@ -56,6 +56,7 @@ class GPMPCConfig(MPCConfig):
     qp_adaptive_rho_interval: int = 25  # iteration based (OSQP's default is timing based, i.e. not reproducible)
     qp_scaling: int = 3               # osqp_rti.py:477
     qp_keep_rho: bool = True          # the adapted rho persists across solves, as inside one OSQP solver object
+    qp_kernel_variant: int = 0        # GpmpcAdmmSettings.kernel_variant (0 = newest kernel that fits; 2 / 1 = older generations)
     variance_via_inverse: bool = True  # horizon variances |L^-1 k*|^2 as one triangular DMMA GEMM against the explicit
                                        # inverse factor (formed once per fit) instead of the blocked in-place solve
                                        # (31 dependent launches); same quantity, rounding differs by O(cond(L) eps)
@@ -224,7 +225,8 @@ class GPMPC:
         return _lib.AdmmSettings.reference_defaults(
             max_iter=c.qp_max_iter, eps_abs=c.qp_eps_abs, eps_rel=c.qp_eps_rel, check_every=c.qp_check_every,
             adaptive_rho_interval=c.qp_adaptive_rho_interval, scaling=c.qp_scaling,
-            warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1)
+            warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1,
+            kernel_variant=int(c.qp_kernel_variant))
 
     # ------------------------------------------------------------------------------------------------ core
     def _make_plan(self, st: _BatchState) -> "_lib.Solve3":

@@ -57,6 +57,7 @@ class GPMPC6DoFConfig:
     qp_adaptive_rho_interval: int = 25
     qp_scaling: int = 3
     qp_keep_rho: bool = True
+    qp_kernel_variant: int = 0        # GpmpcAdmmSettings.kernel_variant (0 = newest kernel that fits)
 
 
 def _stage_vector(N, xpart, upart):
@@ -138,7 +139,8 @@ class GPMPC6DoF:
         return _lib.AdmmSettings.reference_defaults(
             max_iter=c.qp_max_iter, eps_abs=c.qp_eps_abs, eps_rel=c.qp_eps_rel, check_every=c.qp_check_every,
             adaptive_rho_interval=c.qp_adaptive_rho_interval, scaling=c.qp_scaling,
-            warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1)
+            warm_x=1, warm_y=1, rho_from_input=1 if c.qp_keep_rho else 0, commit_y_solved_only=1,
+            kernel_variant=int(c.qp_kernel_variant))
 
     def _rollout(self, st, x0, U, X, dmean):
         mv, mw = self._models

@@ -182,8 +182,9 @@ typedef struct GpmpcAdmmSettings {
   int warm_x, warm_y;      /* use x / y buffers as warm start (osqp_rti.py:522-524) */
   int rho_from_input;      /* start from rho[b] when > 0 (OSQP keeps its adapted rho between solves) */
   int commit_y_solved_only; /* write y back only when status == SOLVED (GP-MPC SQP loop keeps the last good duals) */
-  int kernel_variant;     /* 0: stage-parallel kernel (csrc/admm_stage.cu) when the problem fits it; 1: force the
-                             first-generation one-chain kernel (csrc/admm.cu) */
+  int kernel_variant;     /* 0: the fastest kernel measured for the shape: csrc/admm3.cu (light iterations + cyclic reduction)
+                             for nx 14 at N 30, csrc/admm_stage.cu (stage-parallel) otherwise; 3: force csrc/admm3.cu (nx 7:
+                             N 20, nx 14: N 30); 2: force csrc/admm_stage.cu; 1: force the first-generation one-chain kernel */
   int bound_stride;       /* 0: lb / ub (n) are shared by all QPs (the reference's fixed box, osqp_rti.py:197-200);
                              > 0: QP b reads lb + b * bound_stride, ub + b * bound_stride (per-scenario tightened boxes) */
 } GpmpcAdmmSettings;

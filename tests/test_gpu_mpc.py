@@ -71,7 +71,7 @@ def _oracle_qp(N, x0, xt, seed=0, perturb=0.0):
     return Pd, q, A, l, u, X_lin, U_lin
 
 
-@pytest.mark.parametrize("variant", [0, 1])  # 0: stage-parallel kernel (admm_stage.cu), 1: first-generation kernel
+@pytest.mark.parametrize("variant", [0, 1, 3])  # 0: stage-parallel kernel (admm_stage.cu), 1: first generation, 3: admm3.cu
 @pytest.mark.parametrize("max_iter", [50, 4000])
 def test_admm_matches_osqp_restatement(E, max_iter, variant):
     """Same algorithm, different linear algebra (block-tridiagonal reduced KKT vs dense LU): statuses, iteration
@@ -162,7 +162,7 @@ def _random_stage_qp(nx, nu, N, rng):
     return AB, beq, Pd, q, lb, ub, A, l, u
 
 
-@pytest.mark.parametrize("nx,N,variant", [(14, 30, 0), (14, 8, 0), (14, 8, 1), (7, 11, 0)])
+@pytest.mark.parametrize("nx,N,variant", [(14, 30, 0), (14, 30, 2), (14, 8, 0), (14, 8, 1), (7, 11, 0), (7, 20, 3)])
 def test_admm_generic_stage_qp(E, nx, N, variant):
     """The solver on random stage-structured QPs of the 6-DoF size (nx = 14, N = 30: BASELINE configs[3]) and on a
     run-time horizon, against the dense CPU restatement: same status / iterations / rho, iterates to 1e-6."""
@@ -191,7 +191,7 @@ def test_admm_generic_stage_qp(E, nx, N, variant):
         assert np.max(np.abs(ws.y[b].cpu().numpy() - r.y)) < 1e-6 * max(1.0, np.max(np.abs(r.y)))
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 3])
 def test_admm_warm_start_and_inactive(E, variant):
     """x/y/rho persist across solves like the OSQP object does (osqp_rti.py:522-527); inactive scenarios are
     untouched."""

@@ -11,7 +11,7 @@ class _A:
     pass
 
 
-def measure(batch=1024, steps=20, warmup=3, sqp_iters=1, inducing=100, cpu=False):
+def measure(batch=1024, steps=20, warmup=3, sqp_iters=1, inducing=100, cpu=False, variant=0):
     a = _A()
     a.batch, a.steps, a.warmup, a.sqp_iters, a.inducing, a.cpu = batch, steps, warmup, sqp_iters, inducing, cpu
     import torch
@@ -24,7 +24,7 @@ def measure(batch=1024, steps=20, warmup=3, sqp_iters=1, inducing=100, cpu=False
     np.random.seed(0)   # the inducing points are drawn from the global numpy RNG (sparse_gp.py:122-148)
     sg.add_data(X, U, Dv, Dw); sg.fit()
     dyn = dynamics.Rocket6DoFDynamics()
-    ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=30, max_sqp_iter=a.sqp_iters))
+    ctl = mpc.GPMPC6DoF(dyn, sg, mpc.GPMPC6DoFConfig(N=30, max_sqp_iter=a.sqp_iters, qp_kernel_variant=variant))
     X0, XT = workloads.sample_initial_conditions_6dof(0, a.batch)
     x = ge.to_dev(X0); xt = ge.to_dev(XT)
     its = []
@@ -82,8 +82,9 @@ def main():
     ap.add_argument("--sqp-iters", type=int, default=1)
     ap.add_argument("--inducing", type=int, default=100)
     ap.add_argument("--cpu", action="store_true")
+    ap.add_argument("--variant", type=int, default=0)
     a = ap.parse_args()
-    print(json.dumps(measure(a.batch, a.steps, a.warmup, a.sqp_iters, a.inducing, a.cpu)), flush=True)
+    print(json.dumps(measure(a.batch, a.steps, a.warmup, a.sqp_iters, a.inducing, a.cpu, a.variant)), flush=True)
 
 
 if __name__ == "__main__":
