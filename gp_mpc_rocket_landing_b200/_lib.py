@@ -94,6 +94,17 @@ class McStep3(C.Structure):
     ]
 
 
+class Safety3(C.Structure):
+    """GpmpcSafety3: set-up of the predictive safety filter (gpmpc_safety_filter_3dof)."""
+    _fields_ = [
+        ("dyn", Dyn3), ("N", c_int), ("n_iters", c_int), ("has_u_limits", c_int), ("reserved", c_int),
+        ("lr", c_double), ("alpha", c_double), ("backup_margin", c_double), ("T_min", c_double), ("T_max", c_double),
+        ("tan_gamma", c_double),
+        ("K", c_double * 21), ("P", c_double * 49), ("x_eq", c_double * 7), ("u_eq", c_double * 3),
+        ("u_min", c_double * 3), ("u_max", c_double * 3),
+    ]
+
+
 PHASE_NAMES = ("begin", "prologue", "rollout", "gp_variance", "cov", "gp_mean", "assemble", "admm", "update", "mc")
 
 
@@ -164,6 +175,7 @@ _PROTOS = {
     "gpmpc_linv_sumsq_parts": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_solve_batch_3dof": (c_int, [C.POINTER(Solve3), C.POINTER(c_int), c_dp]),
     "gpmpc_mc_advance_3dof": (c_int, [C.POINTER(McStep3), c_dp]),
+    "gpmpc_safety_filter_3dof": (c_int, [C.POINTER(Safety3), c_int, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_struct_layout": (c_long, [c_int, c_int]),
     "gpmpc_events_create": (c_int, [c_int, C.POINTER(C.c_void_p)]),
     "gpmpc_events_destroy": (c_int, [c_int, C.POINTER(C.c_void_p)]),

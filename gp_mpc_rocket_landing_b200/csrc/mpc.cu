@@ -981,6 +981,125 @@ __global__ void __launch_bounds__(128) mc_advance3_kernel(GpmpcMcStep3 a) {
     for (int e = 0; e < a.m; ++e) a.y[(long)b * a.m + e] = 0.0;
 }
 
+
+// ------------------------------------------------------------------------------------------------ predictive safety filter
+// src/safety/safety_filter.py:184-361 for the 7-state model, one thread per scenario (see GpmpcSafety3 in the header).
+struct SafetyEval {
+  const GpmpcSafety3& s;
+  __device__ __forceinline__ void backup(const double* x, double* u) const {   // backup_controller.py:231-252
+#pragma unroll
+    for (int r = 0; r < NU; ++r) {
+      double acc = 0.0;
+#pragma unroll
+      for (int c = 0; c < NX; ++c) acc += s.K[r * NX + c] * (x[c] - s.x_eq[c]);
+      double v = s.u_eq[r] - acc;
+      if (s.has_u_limits) v = fmin(fmax(v, s.u_min[r]), s.u_max[r]);
+      u[r] = v;
+    }
+  }
+  __device__ __forceinline__ bool constraints(const double* x, const double* u) const {   // safety_filter.py:315-346
+    const double T = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+    if (T < s.T_min || T > s.T_max) return false;
+    if (x[1] > 0.1) {
+      if ((x[1] * x[1]) * (s.tan_gamma * s.tan_gamma) < x[2] * x[2] + x[3] * x[3]) return false;
+    }
+    return true;
+  }
+  __device__ __forceinline__ double value(const double* x) const {   // invariant_sets.py:178-184
+    double dx[NX], t[NX];
+#pragma unroll
+    for (int c = 0; c < NX; ++c) dx[c] = x[c] - s.x_eq[c];
+#pragma unroll
+    for (int c = 0; c < NX; ++c) {   // dx' P first (row vector times matrix), then . dx -- numpy's  dx.T @ P @ dx
+      double acc = 0.0;
+#pragma unroll
+      for (int r = 0; r < NX; ++r) acc += dx[r] * s.P[r * NX + c];
+      t[c] = acc;
+    }
+    double v = 0.0;
+#pragma unroll
+    for (int c = 0; c < NX; ++c) v += t[c] * dx[c];
+    return v;
+  }
+  // `_predict_with_backup` :281-313 fused with the path-constraint scan of `_check_safety` :265-271; returns V(x_N)
+  __device__ __forceinline__ double predict(const double* x0, const double* u_first, bool* path_ok) const {
+    double x[NX], xn[NX], u[NU];
+#pragma unroll
+    for (int c = 0; c < NX; ++c) x[c] = x0[c];
+    bool ok = true;
+    for (int k = 0; k < s.N; ++k) {
+      if (k == 0) {
+#pragma unroll
+        for (int r = 0; r < NU; ++r) u[r] = u_first[r];
+      } else {
+        backup(x, u);
+      }
+      if (path_ok) ok = ok && constraints(x, u);
+      step3(x, u, s.dyn, xn);
+#pragma unroll
+      for (int c = 0; c < NX; ++c) x[c] = xn[c];
+    }
+    if (path_ok) *path_ok = ok;
+    return value(x);
+  }
+};
+
+__global__ void __launch_bounds__(128) safety_filter3_kernel(GpmpcSafety3 s, int nbatch, const double* __restrict__ X,
+                                                             const double* __restrict__ U_nom, long ldu,
+                                                             double* __restrict__ U_safe, int* __restrict__ flags,
+                                                             double* __restrict__ margin, double* __restrict__ backup_value,
+                                                             const int* __restrict__ active) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nbatch) return;
+  if (active && !active[b]) return;
+  const SafetyEval ev{s};
+  double x[NX], un[NU], u[NU];
+#pragma unroll
+  for (int c = 0; c < NX; ++c) x[c] = X[(long)b * NX + c];
+#pragma unroll
+  for (int r = 0; r < NU; ++r) un[r] = u[r] = U_nom[(long)b * ldu + r];
+  // `_check_safety` of the nominal control
+  bool path_ok;
+  double V = ev.predict(x, un, &path_ok);
+  bool safe = ev.constraints(x, un) && (s.alpha - V > 0.0) && path_ok;
+  int fl = 0;
+  if (!safe) {
+    fl = 1;
+    // `_solve_gradient_qp` :483-531
+    for (int it = 0; it < s.n_iters; ++it) {
+      const double Vt = ev.predict(x, u, nullptr);
+      if (Vt <= s.alpha * s.backup_margin) break;
+      const double eps = 1e-4;
+      double g[NU];
+#pragma unroll
+      for (int r = 0; r < NU; ++r) {
+        double up[NU] = {u[0], u[1], u[2]};
+        up[r] += eps;
+        g[r] = (ev.predict(x, up, nullptr) - Vt) / eps;
+      }
+#pragma unroll
+      for (int r = 0; r < NU; ++r) u[r] = u[r] - s.lr * (g[r] + 2.0 * (u[r] - un[r]));
+      const double T = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+      if (T < s.T_min) {
+        const double d = fmax(T, 1e-6);
+#pragma unroll
+        for (int r = 0; r < NU; ++r) u[r] = u[r] / d * s.T_min;
+      } else if (T > s.T_max) {
+#pragma unroll
+        for (int r = 0; r < NU; ++r) u[r] = u[r] / T * s.T_max;
+      }
+    }
+    V = ev.predict(x, u, &path_ok);
+    safe = ev.constraints(x, u) && (s.alpha - V > 0.0) && path_ok;
+  }
+  if (safe) fl |= 2;
+#pragma unroll
+  for (int r = 0; r < NU; ++r) U_safe[(long)b * NU + r] = u[r];
+  if (flags) flags[b] = fl;
+  if (margin) margin[b] = s.alpha - V;
+  if (backup_value) backup_value[b] = V;
+}
+
 }  // namespace
 
 // ================================================================================================== C ABI
@@ -1183,6 +1302,18 @@ extern "C" int gpmpc_events_elapsed_ms(void* a, void* b, float* ms_out) {
   return GPMPC_OK;
 }
 
+extern "C" int gpmpc_safety_filter_3dof(const GpmpcSafety3* setup, int B, const double* X, const double* U_nom, long ldu,
+                                        double* U_safe, int* flags, double* margin, double* backup_value, const int* active,
+                                        void* stream) {
+  GPMPC_REQUIRE(setup != nullptr && B >= 0 && X && U_nom && U_safe && ldu >= NU, "gpmpc_safety_filter_3dof: bad arguments");
+  GPMPC_REQUIRE(setup->N >= 1 && setup->n_iters >= 0, "gpmpc_safety_filter_3dof: bad horizon / iteration count");
+  if (B == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(safety_filter3_kernel);
+  safety_filter3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*setup, B, X, U_nom, ldu, U_safe, flags, margin,
+                                                                            backup_value, active);
+  return gpmpc_check_launch("safety_filter_3dof");
+}
+
 extern "C" int gpmpc_mc_advance_3dof(const GpmpcMcStep3* a, void* stream) {
   GPMPC_REQUIRE(a != nullptr && a->B >= 0, "gpmpc_mc_advance_3dof: bad arguments");
   GPMPC_REQUIRE(a->x && a->m0 && a->t_step && a->active && a->outcome, "gpmpc_mc_advance_3dof: NULL state buffer");
@@ -1357,6 +1488,13 @@ extern "C" long gpmpc_struct_layout(int which, int field) {
       case 2: return (long)offsetof(GpmpcMcStep3, x);
       case 3: return (long)offsetof(GpmpcMcStep3, counts);
       case 4: return (long)offsetof(GpmpcMcStep3, rho);
+    }
+  } else if (which == 4) {
+    switch (field) {
+      case -1: return (long)sizeof(GpmpcSafety3);
+      case 0: return (long)offsetof(GpmpcSafety3, lr);
+      case 1: return (long)offsetof(GpmpcSafety3, K);
+      case 2: return (long)offsetof(GpmpcSafety3, u_max);
     }
   } else if (which == 2 && field < 0) {
     return (long)sizeof(GpmpcAdmmSettings);

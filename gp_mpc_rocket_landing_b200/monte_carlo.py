@@ -69,16 +69,20 @@ class BatchedMonteCarlo:
     controller: `GPMPC` / `NominalMPC3DoF` (uses `solve_batch`) or `OSQPRTIMPC` / `FastRTI3DoF` (uses `initialize_batch` +
     `step_batch`).  target_mode / on_solve_failure: see the module docstring (None = the reference's behaviour for the
     controller's kind).  drag_cda: C_D*A of the "true" plant's drag residual (0 = the plant is the nominal model).
+    safety_filter: a `safety.PredictiveSafetyFilter` applied to the first control before the plant step.
     respawn: a finished scenario restarts from its initial condition with a fresh controller state, which keeps the
     batch full (throughput runs); the outcome counters keep accumulating."""
 
     def __init__(self, dynamics, controller, sim_config: Optional[SimulationConfig] = None, drag_cda: float = 0.0,
-                 respawn: bool = False, target_mode: Optional[str] = None, on_solve_failure: Optional[str] = None):
+                 respawn: bool = False, target_mode: Optional[str] = None, on_solve_failure: Optional[str] = None,
+                 safety_filter=None):
         self.dynamics = dynamics
         self.controller = controller
         self.cfg = sim_config or SimulationConfig()
         self.drag_cda = float(drag_cda)
         self.respawn = respawn
+        self.safety_filter = safety_filter     # monte_carlo.py:519-525: u <- safety_filter.filter(x, u).u_safe
+        self.last_filter = None
         self.max_steps = int(self.cfg.max_time / self.cfg.dt)    # monte_carlo.py:447
         self._rti = hasattr(controller, "step_batch")
         self.target_mode = target_mode or ("fixed" if self._rti else "per_step")
@@ -149,6 +153,10 @@ class BatchedMonteCarlo:
                 a.has_warm, a.y, a.rho, a.m = ge.ptr(st.has_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), st.ws.y.shape[1]
             else:
                 a.has_warm = a.y = a.rho = None
+        if self.safety_filter is not None:     # filter the first control on the device (safety/safety_filter.py:184-235)
+            u_nom = sol.u0 if self._rti else sol.U_opt[:, 0]
+            self.last_filter = self.safety_filter.filter_batch(self.x, u_nom, active=self.active)
+            a.u, a.ldu = ge.ptr(self.last_filter.u_safe), 3
         ge.call("gpmpc_mc_advance_3dof", _lib.C.byref(a), ge.stream())
         return sol
 

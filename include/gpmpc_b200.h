@@ -380,8 +380,30 @@ typedef struct GpmpcMcStep3 {
 } GpmpcMcStep3;
 int gpmpc_mc_advance_3dof(const GpmpcMcStep3* args, void* stream);
 
+/* Predictive safety filter on the first control (src/safety/safety_filter.py:184-361, the branch that runs without CasADi):
+ * per scenario  (1) `_check_safety` :237-279 -- immediate constraints (:315-346: thrust magnitude in [T_min, T_max], glide
+ * slope r_x^2 tan^2(gamma) >= r_y^2 + r_z^2 above 0.1 m; the 7-state model has identity attitude, so the tilt test always
+ * passes), N-step prediction with u first and the backup law u_eq - K (x - x_eq) afterwards (:281-313,
+ * backup_controller.py:231-252), terminal Lyapunov value (x_N - x_eq)' P (x_N - x_eq) against alpha (invariant_sets.py:178-184),
+ * path constraints;  (2) when unsafe, `_solve_gradient_qp` :483-531 -- <= n_iters steps of  u -= lr (dV/du + 2 (u - u_nom))
+ * with forward-difference gradients (eps 1e-4) through the same prediction, stopped when V <= alpha * backup_margin, each
+ * followed by the projection on the thrust annulus;  (3) the check of the filtered control.
+ * flags[b]: bit 0 = control was modified, bit 1 = the returned control is safe.  U_nom row stride ldu (u0 = U_opt[:, 0]). */
+typedef struct GpmpcSafety3 {
+  GpmpcDyn3 dyn;          /* dt = the filter's step (SafetyFilterConfig.dt) */
+  int N, n_iters;         /* SafetyFilterConfig.N (10); 50 */
+  int has_u_limits;       /* saturate the backup law to [u_min, u_max] (BackupControllerConfig.u_min / u_max) */
+  int reserved;
+  double lr, alpha, backup_margin, T_min, T_max, tan_gamma;
+  double K[21];           /* 3 x 7 backup gain, row-major */
+  double P[49];           /* 7 x 7 Lyapunov matrix */
+  double x_eq[7], u_eq[3], u_min[3], u_max[3];
+} GpmpcSafety3;
+int gpmpc_safety_filter_3dof(const GpmpcSafety3* setup, int B, const double* X, const double* U_nom, long ldu, double* U_safe,
+                             int* flags, double* margin, double* backup_value, const int* active, void* stream);
+
 /* sizeof / offsetof probes for the binding tests: which = 0 GpmpcSolve3, 1 GpmpcMcStep3, 2 GpmpcAdmmSettings,
- * 3 GpmpcExactModel; field < 0 -> sizeof, else the offset of a sentinel field (see csrc/mpc.cu). */
+ * 3 GpmpcExactModel, 4 GpmpcSafety3; field < 0 -> sizeof, else the offset of a sentinel field (see csrc/mpc.cu). */
 long gpmpc_struct_layout(int which, int field);
 
 /* CUDA event pool for the phase timers (plain cudaEvent_t behind void*). */

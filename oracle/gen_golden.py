@@ -130,6 +130,68 @@ def mc_loop_fixture(save):
     save("mc_loop.npz", **out)
 
 
+def safety_fixture(save):
+    """13. the reference's own predictive safety filter (src/safety/safety_filter.py:184-361, the gradient path
+    `_solve_gradient_qp` that runs when CasADi is absent) around a 14-state embedding of the 7-state Euler model: backup
+    gains / Lyapunov matrix as the reference's LQRBackupController produced them, the sampled invariant-set level, and
+    (x, u_nominal) -> (u_safe, is_modified, is_safe, safety_margin, backup_value) for 96 seeded cases."""
+    import io
+    import contextlib
+    import types as _t
+    for name in ("src.safety",):
+        pkg = _t.ModuleType(name)
+        pkg.__path__ = [os.path.join(REF, *name.split(".")[1:])]
+        sys.modules[name] = pkg
+    import src.safety.safety_filter as SF
+    from oracle.mpc import EulerDynamics, Rocket3DoFParams, step_3dof, linearize_3dof
+
+    class Embed14:
+        """14-state view of the 7-state model: [m, r, v | q = (1,0,0,0), w = 0] with inert attitude states."""
+        def __init__(self):
+            self.params = Rocket3DoFParams()
+            self.params.g_I = self.params.g_vec
+
+        def step(self, x, u, dt=0.1):
+            xn = np.asarray(x, float).copy()
+            xn[:7] = step_3dof(xn[:7], np.asarray(u, float), dt, self.params)
+            return xn
+
+        def linearize(self, x, u, dt=0.1):
+            A = np.eye(14); B = np.zeros((14, 3))
+            A7, B7 = linearize_3dof(np.asarray(x, float)[:7], np.asarray(u, float), dt, self.params)
+            A[:7, :7] = A7; B[:7] = B7
+            return A, B
+
+    class CP:
+        T_min, T_max, theta_max, gamma_gs = 0.3, 5.0, 60.0, 30.0
+
+    out = {}
+    for tag, alpha in (("a25", 25.0), ("a100", 100.0)):
+        sf = SF.PredictiveSafetyFilter(Embed14(), SF.SafetyFilterConfig(N=10, dt=0.1), CP())
+        x_eq = np.zeros(14); x_eq[0] = 1.8; x_eq[1] = 5.0; x_eq[7] = 1.0
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            sf.initialize(x_eq, backup_alpha=alpha)
+        out[f"{tag}_init_log"] = np.array(buf.getvalue())
+        rng = np.random.default_rng(17)
+        n = 48
+        X = np.zeros((n, 14)); X[:, 7] = 1.0
+        X[:, 0] = rng.uniform(1.5, 2.0, n); X[:, 1] = rng.uniform(3.0, 8.0, n)
+        X[:, 2:4] = rng.normal(0, 0.8, (n, 2)); X[:, 4] = rng.normal(-0.5, 1.5, n); X[:, 5:7] = rng.normal(0, 0.7, (n, 2))
+        U = np.stack([rng.uniform(0.1, 5.5, n), rng.normal(0, 1.0, n), rng.normal(0, 1.0, n)], 1)
+        res = [sf.filter(X[i], U[i]) for i in range(n)]
+        out[f"{tag}_K"] = sf.backup.K[:, :7].copy(); out[f"{tag}_P"] = sf.backup.P[:7, :7].copy()
+        out[f"{tag}_Kfull_rest"] = np.abs(sf.backup.K[:, 7:]).max(); out[f"{tag}_alpha"] = sf.invariant_set.alpha
+        out[f"{tag}_x_eq"] = sf.backup.x_eq[:7].copy(); out[f"{tag}_u_eq"] = sf.backup.u_eq.copy()
+        out[f"{tag}_X"] = X[:, :7].copy(); out[f"{tag}_U"] = U
+        out[f"{tag}_u_safe"] = np.array([r.u_safe for r in res])
+        out[f"{tag}_modified"] = np.array([r.is_modified for r in res]); out[f"{tag}_safe"] = np.array([r.is_safe for r in res])
+        out[f"{tag}_margin"] = np.array([r.safety_margin for r in res]); out[f"{tag}_backup_value"] = np.array([r.backup_value for r in res])
+        print(f"   safety {tag}: modified {int(out[f'{tag}_modified'].sum())}/{n}, safe after {int(out[f'{tag}_safe'].sum())}, "
+              f"log: {buf.getvalue().strip()[:60]!r}")
+    save("safety_filter.npz", **out)
+
+
 def online_fixture(G, save):
     """11. online data path (reference src/gp/online_update.py): DataBuffer ring semantics, and the accept / update
     sequence of OnlineGPUpdater around a reference SparseGP with injected inducing points (no RNG dependence)."""
@@ -422,6 +484,7 @@ def main():
     online_fixture(G, save)
     unscented_fixture(G, save)
     mc_loop_fixture(save)
+    safety_fixture(save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

@@ -39,6 +39,9 @@ def test_struct_layouts_match_header():
     for i, f in enumerate(("dyn", "admm", "model", "Linv", "x0", "Ks", "q_pad", "var_work", "U_warm", "events",
                            "event_count")):
         assert getattr(_lib.Solve3, f).offset == lay(0, i), f
+    assert ctypes.sizeof(_lib.Safety3) == lay(4, -1)
+    for i, f in enumerate(("lr", "K", "u_max")):
+        assert getattr(_lib.Safety3, f).offset == lay(4, i), f
     assert ctypes.sizeof(_lib.McStep3) == lay(1, -1)
     for i, f in enumerate(("dyn", "max_steps", "x", "counts", "rho")):
         assert getattr(_lib.McStep3, f).offset == lay(1, i), f

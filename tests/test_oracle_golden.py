@@ -222,3 +222,22 @@ def test_reference_and_oracle_within_conditioning_of_longdouble_truth(tag, noise
     m, v = ogp.longdouble_exact_predict(fits[1], g["Z_query"][:4])
     np.testing.assert_array_equal(m.astype(np.float64), tm[:4, 1])
     np.testing.assert_array_equal(v.astype(np.float64), tv[:4, 1])
+
+
+def test_safety_filter_matches_reference():
+    """oracle.safety against the reference's own PredictiveSafetyFilter (safety_filter.py:184-361, gradient path) on 2 x 48
+    seeded cases: same decisions, filtered controls and margins (the reference ran on a 14-state embedding)."""
+    from oracle import safety as osf
+    g = load_golden("safety_filter.npz")
+    for tag in ("a25", "a100"):
+        s = osf.SafetySetup(K=g[f"{tag}_K"], P=g[f"{tag}_P"], x_eq=g[f"{tag}_x_eq"], u_eq=g[f"{tag}_u_eq"],
+                            alpha=float(g[f"{tag}_alpha"]))
+        assert float(g[f"{tag}_Kfull_rest"]) == 0.0          # the inert states never feed back
+        mod = g[f"{tag}_modified"]
+        assert mod.any() and (~mod).any() and (tag != "a25" or (g[f"{tag}_safe"] & mod).any())
+        for i in range(g[f"{tag}_X"].shape[0]):
+            u, m, ok, margin, bv = osf.safety_filter(s, g[f"{tag}_X"][i], g[f"{tag}_U"][i])
+            assert m == bool(mod[i]) and ok == bool(g[f"{tag}_safe"][i]), (tag, i)
+            np.testing.assert_allclose(u, g[f"{tag}_u_safe"][i], rtol=1e-9, atol=1e-12)
+            np.testing.assert_allclose(margin, g[f"{tag}_margin"][i], rtol=1e-8, atol=1e-9)
+            np.testing.assert_allclose(bv, g[f"{tag}_backup_value"][i], rtol=1e-8, atol=1e-9)
