@@ -175,6 +175,7 @@ _PROTOS = {
     "gpmpc_linv_sumsq_parts": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_solve_batch_3dof": (c_int, [C.POINTER(Solve3), C.POINTER(c_int), c_dp]),
     "gpmpc_mc_advance_3dof": (c_int, [C.POINTER(McStep3), c_dp]),
+    "gpmpc_mc_combine_3dof": (c_int, [c_int, c_int, c_dp, c_dp, c_dp, c_double, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_safety_filter_3dof": (c_int, [C.POINTER(Safety3), c_int, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_struct_layout": (c_long, [c_int, c_int]),
     "gpmpc_events_create": (c_int, [c_int, C.POINTER(C.c_void_p)]),

@@ -1100,6 +1100,64 @@ __global__ void __launch_bounds__(128) safety_filter3_kernel(GpmpcSafety3 s, int
   if (backup_value) backup_value[b] = V;
 }
 
+
+// ------------------------------------------------------------------------------------------------ Monte Carlo propagation
+// uncertainty_prop.py:295-315, one warp per scenario (see gpmpc_mc_combine_3dof in the header).
+__global__ void __launch_bounds__(128) mc_combine3_kernel(int nbatch, int S, const double* __restrict__ Xn,
+                                                          const double* __restrict__ var, const double* __restrict__ xi,
+                                                          double dt, double* __restrict__ particles,
+                                                          double* __restrict__ mean, double* __restrict__ cov) {
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (b >= nbatch) return;
+  double sum[NX];
+#pragma unroll
+  for (int c = 0; c < NX; ++c) sum[c] = 0.0;
+  for (int i = lane; i < S; i += 32) {
+    const long pi = (long)b * S + i;
+    const double* img = Xn + pi * 2 * NX + NX;
+    double x[NX];
+#pragma unroll
+    for (int c = 0; c < NX; ++c) x[c] = img[c];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) x[4 + c] = x[4 + c] + (sqrt(var[pi * 3 + c]) * xi[pi * 3 + c]) * dt;
+#pragma unroll
+    for (int c = 0; c < NX; ++c) {
+      particles[pi * NX + c] = x[c];
+      sum[c] += x[c];
+    }
+  }
+  double m[NX];
+#pragma unroll
+  for (int c = 0; c < NX; ++c) m[c] = warp_sum(sum[c]) / (double)S;
+  double acc[NX][NX];
+#pragma unroll
+  for (int r = 0; r < NX; ++r)
+#pragma unroll
+    for (int c = 0; c < NX; ++c) acc[r][c] = 0.0;
+  __syncwarp();
+  for (int i = lane; i < S; i += 32) {
+    const double* x = particles + ((long)b * S + i) * NX;
+    double d[NX];
+#pragma unroll
+    for (int c = 0; c < NX; ++c) d[c] = x[c] - m[c];
+#pragma unroll
+    for (int r = 0; r < NX; ++r)
+#pragma unroll
+      for (int c = r; c < NX; ++c) acc[r][c] += d[r] * d[c];
+  }
+#pragma unroll
+  for (int r = 0; r < NX; ++r)
+#pragma unroll
+    for (int c = r; c < NX; ++c) {
+      const double v = warp_sum(acc[r][c]) / (double)(S - 1);
+      if (lane == 0) {
+        cov[((long)b * NX + r) * NX + c] = v;
+        cov[((long)b * NX + c) * NX + r] = v;
+      }
+    }
+  if (lane < NX) mean[(long)b * NX + lane] = m[lane];
+}
+
 }  // namespace
 
 // ================================================================================================== C ABI
@@ -1300,6 +1358,15 @@ extern "C" int gpmpc_events_elapsed_ms(void* a, void* b, float* ms_out) {
     return GPMPC_ERR_CUDA;
   }
   return GPMPC_OK;
+}
+
+extern "C" int gpmpc_mc_combine_3dof(int B, int S, const double* Xn, const double* var, const double* xi, double dt,
+                                     double* particles, double* mean, double* cov, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && S >= 2 && Xn && var && xi && particles && mean && cov, "gpmpc_mc_combine_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  GPMPC_PREFER_SHARED(mc_combine3_kernel);
+  mc_combine3_kernel<<<(B + 3) / 4, 128, 0, (cudaStream_t)stream>>>(B, S, Xn, var, xi, dt, particles, mean, cov);
+  return gpmpc_check_launch("mc_combine_3dof");
 }
 
 extern "C" int gpmpc_safety_filter_3dof(const GpmpcSafety3* setup, int B, const double* X, const double* U_nom, long ldu,

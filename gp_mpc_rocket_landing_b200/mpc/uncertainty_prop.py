@@ -4,7 +4,10 @@
 the device (`gpmpc_rollout_3dof`, `gpmpc_trsm_sumsq`, `gpmpc_propagate_cov_3dof`).  "unscented"
 (uncertainty_prop.py:179-264) runs stage by stage: sigma points, their images through the N = 1 rollout kernel (step +
 GP mean), the GP variance at the centre, recombination (`gpmpc_ut_sigma_3dof`, `gpmpc_ut_combine_3dof`).
-"monte_carlo" (:266-319, global-RNG particles) is not built and raises.
+"monte_carlo" (:266-319): S particles per scenario, one stage at a time -- the N = 1 rollout kernel images all B*S particles
+(step + GP mean) and writes their cross-covariance rows, one triangular GEMM gives the B*S variances, `gpmpc_mc_combine_3dof`
+draws from the GP posterior and forms the sample mean / covariance.  The reference draws from the global numpy RNG; here the
+initial particles and the standard-normal draws are inputs (for parity tests) or come from torch's Philox generator.
 """
 from __future__ import annotations
 
@@ -56,8 +59,10 @@ class UncertaintyPropagator:
         Sigma_0: scalar s for Sigma_0 = s*I (default 1e-6, uncertainty_prop.py:133-134)."""
         if self.method == "unscented":
             return self._propagate_unscented_batch(X0, U, Sigma_0, dt)
+        if self.method == "monte_carlo":
+            return self._propagate_monte_carlo_batch(X0, U, Sigma_0, dt)
         if self.method != "linear":
-            raise _lib.GpmpcError(f"propagation method {self.method!r} is not built (linear and unscented only)")
+            raise _lib.GpmpcError(f"unknown propagation method {self.method!r} (linear, unscented, monte_carlo)")
         torch = ge.torch_()
         x0, Ud = ge.to_dev(X0), ge.to_dev(U)
         B, N = Ud.shape[0], Ud.shape[1]
@@ -146,6 +151,69 @@ class UncertaintyPropagator:
         if bad:
             raise np.linalg.LinAlgError(f"unscented propagation: (n + lambda) Sigma + 1e-10 I of scenario {bad - 1} is not "
                                         "positive definite")
+        return means, covs, dmean, dvar
+
+    def _propagate_monte_carlo_batch(self, X0, U, Sigma_0, dt, n_samples: int = 100, particles0=None, xi=None, seed=None):
+        """uncertainty_prop.py:266-319 for B scenarios at once; same return as the linear method (dmean / dvar: the GP mean
+        and variance averaged over the particles).  particles0 (B,S,7), xi (B,N,S,3): injected randomness (the reference's
+        draws at :287 and :305); default: x0 + sqrt(Sigma_0) z and standard normals from a Philox generator seeded with
+        `seed` -- a documented deviation from the reference's global numpy RNG, the moments agree within Monte Carlo error."""
+        torch = ge.torch_()
+        x0, Ud = ge.to_dev(X0), ge.to_dev(U)
+        B, N = Ud.shape[0], Ud.shape[1]
+        model = self.gp.device_model() if self.gp is not None else None
+        dyn = self._dyn(dt)
+        f64 = dict(dtype=torch.float64, device=x0.device)
+        s0 = 1e-6 if Sigma_0 is None else float(Sigma_0)
+        gen = None
+        if particles0 is None or xi is None:
+            gen = torch.Generator(device=x0.device)
+            gen.manual_seed(0 if seed is None else int(seed))
+        if particles0 is None:
+            S = int(n_samples)
+            part = x0[:, None, :] + np.sqrt(s0) * torch.randn((B, S, 7), generator=gen, **f64)
+        else:
+            part = ge.to_dev(particles0)
+            S = part.shape[1]
+        part = part.reshape(B * S, 7).contiguous()
+        xi_d = ge.to_dev(xi) if xi is not None else None
+        means = torch.zeros((B, N + 1, 7), **f64)
+        covs = torch.zeros((B, N + 1, 7, 7), **f64)
+        dmean = torch.zeros((B, N, 3), **f64)
+        dvar = torch.zeros((B, N, 3), **f64)
+        means[:, 0] = x0
+        covs[:, 0] = torch.eye(7, **f64) * s0
+        Q = B * S
+        q_pad = ge.pad_to(Q, 128)
+        Xn = torch.empty((Q, 2, 7), **f64)
+        Usp = torch.empty((Q, 1, 3), **f64)
+        dm = torch.zeros((Q, 1, 3), **f64)
+        var = torch.zeros((q_pad, 3), **f64)
+        nxt = torch.empty((Q, 7), **f64)
+        mk = torch.empty((B, 7), **f64)
+        Sk = torch.empty((B, 7, 7), **f64)
+        if model is not None:
+            f = model.f
+            Ks = torch.zeros((q_pad, f.n_pad), **f64)
+            var_work = torch.empty(((f.n_pad // 64) * q_pad,), **f64)
+            ms = model.struct()
+        for k in range(N):
+            Usp[:, 0] = Ud[:, k].repeat_interleave(S, dim=0)
+            if model is None:
+                me.rollout(None, dyn, part, Usp, Xn)
+            else:
+                me.rollout(ms, dyn, part, Usp, Xn, dm, Ks)
+                sumsq = f.sumsq_linv(Ks, var_work)
+                ge.call("gpmpc_predict_var", ge.ptr(sumsq), None, Q, 3, f.sv, 1e-10, ge.ptr(model.ystd), ge.ptr(var), 3, 0,
+                        ge.stream())
+                dmean[:, k] = dm[:, 0].reshape(B, S, 3).mean(dim=1)
+                dvar[:, k] = var[:Q].reshape(B, S, 3).mean(dim=1)
+            z = xi_d[:, k].contiguous() if xi_d is not None else torch.randn((B, S, 3), generator=gen, **f64)
+            ge.call("gpmpc_mc_combine_3dof", B, S, ge.ptr(Xn), ge.ptr(var), ge.ptr(z), float(dt), ge.ptr(nxt), ge.ptr(mk),
+                    ge.ptr(Sk), ge.stream())
+            means[:, k + 1] = mk
+            covs[:, k + 1] = Sk
+            part, nxt = nxt, part
         return means, covs, dmean, dvar
 
     def propagate(self, x0, U, Sigma_0=None, dt: float = 0.1) -> PropagatedUncertainty:

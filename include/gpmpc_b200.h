@@ -267,6 +267,13 @@ int gpmpc_ut_sigma_3dof(int B, double scale, const double* xk, const double* Sk,
 int gpmpc_ut_combine_3dof(int B, int n_inert, double wm0, double wc0, double wi, const double* Xn, const double* var,
                           double dt, double* xnext, double* Snext, void* stream);
 
+/* Particle stage of the Monte Carlo propagation (uncertainty_prop.py:295-315), 7-state model: for scenario b and particle i
+ * particles[b,i] = Xn[b*S+i][1] (the N = 1 rollout image: step + GP mean * dt) with sqrt(var[b*S+i]) * xi[b,i] * dt added to the
+ * velocity (the draw from the GP posterior, :305); mean[b] = sum_i / S (:311), cov[b] = diff' diff / (S - 1) (:312-313).
+ * One warp per scenario.  Xn: (B*S, 2, 7); var: (B*S, 3); xi: (B, S, 3) standard-normal draws; particles: (B*S, 7). */
+int gpmpc_mc_combine_3dof(int B, int S, const double* Xn, const double* var, const double* xi, double dt, double* particles,
+                          double* mean, double* cov, void* stream);
+
 /* Linear covariance propagation (uncertainty_prop.py:117-177, 7-state): Sigma_{k+1} = A_k Sigma_k A_k' + diag(var)dt^2
  * on the velocity block, A_k = analytic discrete Jacobian at (X[b,k],U[b,k]).  covs: B x (N+1) x 7 x 7. */
 int gpmpc_propagate_cov_3dof(const GpmpcDyn3* dyn, int B, int N, const double* X, const double* U, const double* dvar,

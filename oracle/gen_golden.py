@@ -268,6 +268,46 @@ def unscented_fixture(G, save):
          covs=pu.covariances[:, :7, :7], means_inert=pu.means[:, 7:], cov_cross_max=np.abs(pu.covariances[:, :7, 7:]).max())
 
 
+def mc_propagation_fixture(G, save):
+    """14. UncertaintyPropagator(method="monte_carlo") (uncertainty_prop.py:266-319) on the 14-state embedding, with the
+    global numpy RNG seeded and its draw sequence replayed beforehand, so that the particles and the GP-posterior noise the
+    reference consumed are part of the fixture (the device path takes them as inputs for bit-level parity; its default
+    generator is torch's Philox)."""
+    import src.mpc.uncertainty_prop as UP
+    from oracle.mpc import Rocket3DoFParams, step_3dof
+    X, U, Dres = gp_fixture(300, 11)
+    gp = G.Simple3DoFGP(use_sparse=False, noise_variance=1e-3); gp.add_data(X, U, Dres); gp.fit()
+    p = Rocket3DoFParams()
+
+    class Dyn14:
+        params = p
+
+        def step(self, x, u, dt):
+            xn = x.copy(); xn[:7] = step_3dof(x[:7], u, dt, p); return xn
+
+    class GP14:
+        def predict(self, x, u):
+            m, v = gp.predict(x[:7], u); return m, np.zeros(3), v, np.zeros(3)
+
+    x0_14 = np.zeros(14); x0_14[:7] = [1.9, 25, 1, -2, -3.2, 0.3, -0.1]; x0_14[7] = 1.0
+    rng = np.random.default_rng(12)
+    N, S = 8, 100
+    Useq = np.stack([rng.uniform(1.5, 2.5, N), rng.uniform(-.3, .3, N), rng.uniform(-.3, .3, N)], 1)
+    Sigma0 = np.eye(14) * 1e-4
+    seed = 2024
+    np.random.seed(seed)                       # replay of the reference's draw order (:287, :305-306)
+    particles0 = np.random.multivariate_normal(x0_14, Sigma0, S)
+    xi = np.zeros((N, S, 3))
+    for k in range(N):
+        for i in range(S):
+            xi[k, i] = np.random.randn(3)
+            np.random.randn(3)                 # the rotational draw (unused by the 7-state model)
+    np.random.seed(seed)
+    pu = UP.UncertaintyPropagator(Dyn14(), GP14(), method="monte_carlo").propagate(x0_14, Useq, Sigma0, dt=0.1)
+    save("propagation_mc.npz", X=X, U=U, D=Dres, noise=1e-3, x0=x0_14[:7], Useq=Useq, sigma0=1e-4, particles0=particles0[:, :7],
+         xi=xi, means=pu.means[:, :7], covs=pu.covariances[:, :7, :7])
+
+
 def main():
     Stub = install_shim()
     import src.gp as G
@@ -485,6 +525,7 @@ def main():
     unscented_fixture(G, save)
     mc_loop_fixture(save)
     safety_fixture(save)
+    mc_propagation_fixture(G, save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

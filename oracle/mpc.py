@@ -547,6 +547,27 @@ def propagate_unscented(x0, U, Sigma0, dt, p, gp_predict, n_aug=14):
     return means, covs
 
 
+def propagate_monte_carlo(x0, U, Sigma0, dt, p, gp_predict, particles0, xi):
+    """uncertainty_prop.py:266-319 for the 7-state model with the randomness injected: particles0 (S,7) = the draw of
+    :287, xi (N,S,3) = the standard-normal draws of :305 (the reference takes both from the global numpy RNG)."""
+    N, S = len(U), particles0.shape[0]
+    means = np.zeros((N + 1, NX)); covs = np.zeros((N + 1, NX, NX))
+    means[0] = x0; covs[0] = Sigma0
+    particles = np.array(particles0, dtype=float)
+    for k in range(N):
+        nxt = np.zeros_like(particles)
+        for i in range(S):
+            x_nom = step_3dof(particles[i], U[k], dt, p)
+            d, var = gp_predict(particles[i], U[k])
+            nxt[i] = x_nom
+            nxt[i, 4:7] += (d + np.sqrt(var) * xi[k, i]) * dt
+        means[k + 1] = np.mean(nxt, axis=0)
+        diff = nxt - means[k + 1]
+        covs[k + 1] = (diff.T @ diff) / (S - 1)
+        particles = nxt
+    return means, covs
+
+
 # --------------------------------------------------------------------------- GP-MPC (composed 3-DoF path)
 @dataclass
 class MPCSolutionOracle:

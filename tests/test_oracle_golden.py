@@ -241,3 +241,15 @@ def test_safety_filter_matches_reference():
             np.testing.assert_allclose(u, g[f"{tag}_u_safe"][i], rtol=1e-9, atol=1e-12)
             np.testing.assert_allclose(margin, g[f"{tag}_margin"][i], rtol=1e-8, atol=1e-9)
             np.testing.assert_allclose(bv, g[f"{tag}_backup_value"][i], rtol=1e-8, atol=1e-9)
+
+
+def test_monte_carlo_propagation_matches_reference():
+    """uncertainty_prop.py:266-319 through the reference's own class (14-state embedding, seeded global RNG) against the
+    restatement fed with the same particles and posterior noise."""
+    g = load_golden("propagation_mc.npz")
+    o = ogp.Simple3DoFGPOracle(noise_variance=float(g["noise"]))
+    o.add_data(g["X"], g["U"], g["D"]); o.fit()
+    means, covs = ompc.propagate_monte_carlo(g["x0"], g["Useq"], np.eye(7) * float(g["sigma0"]), 0.1, ompc.Rocket3DoFParams(),
+                                             o.predict, g["particles0"], g["xi"])
+    np.testing.assert_allclose(means, g["means"], rtol=1e-12, atol=1e-13)
+    np.testing.assert_allclose(covs, g["covs"], rtol=1e-9, atol=1e-16)
