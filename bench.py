@@ -137,9 +137,8 @@ def run_reference_arm(args):
         return
     cores = os.cpu_count() or 1
     n_scen = args.cpu_scenarios or max(1, min(cores, 64))
-    steps, warmup = max(1, args.steps), max(1, min(args.warmup, 3))
-    # bound the run: one oracle solve costs ~0.3-1 s; keep the whole arm within a few minutes
-    steps = min(steps, 20)
+    # bound the run: one oracle solve costs ~0.25 s per core and step; keep the whole arm within a few minutes
+    steps, warmup = min(max(1, args.steps), 20), min(max(1, args.warmup), 10)
     sps, wall, used = cpu_reference_run(n_scen, warmup, steps, args.sqp_iters, args.qp_max_iter)
     line = {
         "impl": "reference", "metric": METRIC, "value": sps, "unit": "solves/s", "n_gpus": args.gpus, "steps": steps,
@@ -299,7 +298,7 @@ def run_b200_arm(args):
     stats.reset()
     timers = me.EventTimers(capacity=(K + 2) * (4 + 8 * args.sqp_iters))
     ctl.timers = timers
-    comm_ms = 0.0
+    n_theta, theta_events = 0, []
     barrier()
     mc.counts.zero_()
     clocks.mark()
@@ -310,12 +309,16 @@ def run_b200_arm(args):
         mc.step()
         launches += ctl.last_kernel_launches + 1      # + mc_advance3_kernel (plant step, termination, respawn)
         stats.submit()
-        if args.theta_every and (k + 1) % args.theta_every == 0:
-            t0 = time.perf_counter()
+        # hyper-parameter broadcast + local refit every `--theta-every` steps; a run shorter than that does it once, half way
+        if args.theta_every and ((k + 1) % args.theta_every == 0 or (K < args.theta_every and k + 1 == max(1, K // 2))):
+            ta, tb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ta.record()
             D.broadcast_hyperparameters(gp, version=2 + k // args.theta_every, refit=False)
-            comm_ms += (time.perf_counter() - t0) * 1e3
             gp.fit()                                   # every rank refits (deterministic: replicas stay identical)
             ctl.refresh_gp()
+            tb.record()
+            theta_events.append((ta, tb))
+            n_theta += 1
     e1.record()
     stats.wait()
     barrier()
@@ -330,7 +333,21 @@ def run_b200_arm(args):
     ms = float(t.item())
     value = world * B * K / (ms * 1e-3)
     total = stats.total().cpu().numpy()               # summed over ranks by the in-loop all-reduces
-    comm_dev_ms = stats.device_ms()
+    side_ms = stats.device_ms()
+    theta_ms = sum(a.elapsed_time(b) for a, b in theta_events)
+    # the same loop without any collective (no stats reduce, no broadcast / refit): what the collectives cost the step
+    Kn = max(5, min(K, 40))
+    barrier()
+    n0, n1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0.record()
+    for _ in range(Kn):
+        mc.step()
+    n1.record()
+    barrier()
+    tn = torch.tensor([n0.elapsed_time(n1) / Kn], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tn, op=dist.ReduceOp.MAX)
+    ms_nocomm = float(tn.item())
 
     # ---- end-to-end loop through the public numpy API ------------------------------------------------------------
     e2e = None
@@ -450,8 +467,14 @@ def run_b200_arm(args):
             "p99_step_latency_ms": float(np.percentile(step_ms, 99)) if step_ms.size else None,
             "max_step_latency_ms": float(step_ms.max()) if step_ms.size else None,
             "comm": {"stats_allreduce_per_step": 1, "theta_broadcast_every": args.theta_every,
-                     "theta_broadcast_host_ms_per_step": comm_ms / K, "stats_allreduce_device_ms_per_step": comm_dev_ms / K,
-                     "note": "collectives are issued inside the timed loop; the stats all-reduce runs on a side stream"},
+                     "theta_broadcasts_and_refits_in_timed_region": n_theta,
+                     "theta_broadcast_refit_ms_total_on_main_stream": theta_ms,
+                     "ms_per_step_same_loop_without_collectives": ms_nocomm,
+                     "comm_ms_per_step": ms / K - ms_nocomm,
+                     "stats_allreduce_side_stream_elapsed_ms_per_step": side_ms / K,
+                     "note": "collectives are issued inside the timed loop; the stats all-reduce runs on a side stream (its "
+                             "elapsed time includes waiting for a free SM next to the step's kernels and is off the critical "
+                             "path); comm_ms_per_step = timed loop minus the same loop re-run without collectives"},
             "fp64_peak_tflops_measured": peak64,
             "outcomes_all_ranks": outcomes, "runs_finished_all_ranks": int(sum(outcomes.values())),
             "success_rate": outcomes["success"] / max(1, sum(outcomes.values())),

@@ -165,8 +165,6 @@ _PROTOS = {
     "gpmpc_gp_mean_points_3dof": (c_int, [C.POINTER(ExactModel), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long, c_dp,
                                           c_dp]),
     "gpmpc_linearize_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
-    "gpmpc_mc_step_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_double, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
-                                   c_dp, c_dp]),
     "gpmpc_pack_traj_3dof": (c_int, [c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_propagate_cov_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_double, c_dp, c_dp,
                                          c_dp]),

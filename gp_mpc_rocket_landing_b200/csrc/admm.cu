@@ -709,8 +709,8 @@ __global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch
 
 // stream-ordered scratch for the cumulative scaling vectors D (n) and E (m) of every scenario
 double* alloc_scaling_scratch(size_t doubles, cudaStream_t stream) {
-  static bool pool_configured = false;
-  if (!pool_configured) {  // keep freed blocks in the pool: without this every call re-allocates from the driver
+  static GpmpcPerDevice pool_configured;
+  if (!pool_configured.here()) {  // keep freed blocks in the pool: without this every call re-allocates from the driver
     int dev = 0;
     cudaMemPool_t pool;
     if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
@@ -718,7 +718,7 @@ double* alloc_scaling_scratch(size_t doubles, cudaStream_t stream) {
       cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
     }
     cudaGetLastError();
-    pool_configured = true;
+    pool_configured.here() = 1;
   }
   double* scratch = nullptr;
   if (cudaMallocAsync(&scratch, sizeof(double) * doubles, stream) != cudaSuccess) {
@@ -740,11 +740,11 @@ int launch_admm(int N, int B, const double* AB, const double* beq, const double*
     return GPMPC_ERR_ARG;
   }
   auto kern = admm_kernel<NX, NU>;
-  static size_t configured = 0;
-  if (smem > configured) {
+  static GpmpcPerDevice configured;
+  if ((int)smem > configured.here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = smem;
+    configured.here() = (int)smem;
   }
   const size_t n = (size_t)N * NS + NX, m = (size_t)NX * (N + 1) + n;
   double* scratch = alloc_scaling_scratch((n + m) * (size_t)B, stream);

@@ -1090,11 +1090,11 @@ int launch_admm3(int N, int B, const double* AB, const double* beq, const double
   constexpr size_t smem = L::template smem_doubles<H::ABS>() * sizeof(double);
   static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
   auto kern = admm3_kernel<NX, NU, H::NFIX, H::NSLOT, H::NTHR, H::MINB, H::SREG, H::ABS>;
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = true;
+    configured.here() = 1;
   }
   kern<<<B, H::NTHR, smem, stream>>>(B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj, pri,
                                      dua);

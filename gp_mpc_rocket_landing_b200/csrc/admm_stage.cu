@@ -841,11 +841,11 @@ int launch_admm_stage(int N, int B, const double* AB, const double* beq, const d
   const bool fixed = (N == H::NFIX);
   auto kern = fixed ? admm_stage_kernel<NX, NU, H::NFIX, H::NSLOT, H::NTHR, H::MINB>
                     : admm_stage_kernel<NX, NU, 0, H::NSLOT, H::NTHR, H::MINB>;
-  static size_t configured[2] = {0, 0};
-  if (smem > configured[fixed]) {
+  static GpmpcPerDevice configured[2];
+  if ((int)smem > configured[fixed].here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured[fixed] = smem;
+    configured[fixed].here() = (int)smem;
   }
   kern<<<B, H::NTHR, smem, stream>>>(N, B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj,
                                      pri, dua);

@@ -20,15 +20,29 @@ int gpmpc_check_launch(const char* what);
     }                                     \
   } while (0)
 
+// One-time kernel attribute set-up is PER DEVICE (cudaFuncSetAttribute applies to the current device).  The framework runs one
+// process per GPU (distributed.py), but a host that switches devices with cudaSetDevice still gets correct launches: the
+// "already configured" flags are kept per device ordinal.  (Not thread-safe: concurrent first calls from several host threads
+// need external locking, as do the opaque handles -- see include/gpmpc_b200.h.)
+constexpr int GPMPC_MAX_DEVICES = 64;
+struct GpmpcPerDevice {
+  int v[GPMPC_MAX_DEVICES] = {};
+  int& here() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return v[(d >= 0 && d < GPMPC_MAX_DEVICES) ? d : 0];
+  }
+};
+
 // Kernels that may run while a shared-memory heavy kernel (ADMM, DMMA GEMM: carve-out = max shared) is resident on another
 // stream ask for the same L1 / shared-memory split: an SM cannot host CTAs that want different carve-outs, so a
 // default-carve-out kernel would wait for the SM to drain.
 #define GPMPC_PREFER_SHARED(kern)                                                                              \
   do {                                                                                                         \
-    static bool done_ = false;                                                                                 \
-    if (!done_) {                                                                                              \
+    static GpmpcPerDevice done_;                                                                               \
+    if (!done_.here()) {                                                                                       \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared); \
-      done_ = true;                                                                                            \
+      done_.here() = 1;                                                                                        \
     }                                                                                                          \
   } while (0)
 

@@ -225,11 +225,11 @@ int launch_dgemm_nt_persistent(const GemmParams& p, int ctas, int smem_request, 
   if (p.M == 0 || p.N == 0) return GPMPC_OK;
   auto kern = dgemm_nt_persistent_kernel<BM, BN, WARPS_M, WARPS_N>;
   const int smem = smem_request > (int)sizeof(GemmSmem<BM, BN>) ? smem_request : (int)sizeof(GemmSmem<BM, BN>);
-  static int configured = 0;
-  if (smem > configured) {
+  static GpmpcPerDevice configured;
+  if (smem > configured.here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = smem;
+    configured.here() = smem;
   }
   kern<<<ctas, GEMM_THREADS, smem, stream>>>(p);
   return gpmpc_check_launch("dgemm_nt_persistent");
@@ -246,11 +246,11 @@ int launch_dgemm_nt(const GemmParams& p, int batch, cudaStream_t stream, int sme
   // smem_request > sizeof(GemmSmem): ask for more shared memory than the tiles need, to cap the resident CTAs per SM
   // (used to leave room for a co-resident kernel on another stream)
   const int smem = smem_request > (int)sizeof(GemmSmem<BM, BN>) ? smem_request : (int)sizeof(GemmSmem<BM, BN>);
-  static int configured = 0;
-  if (smem > configured) {
+  static GpmpcPerDevice configured;
+  if (smem > configured.here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured = smem;
+    configured.here() = smem;
   }
   dim3 grid(p.N / BN, p.M / BM, batch);
   if (p.m_fast) grid = dim3(p.M / BM, p.N / BN, batch);

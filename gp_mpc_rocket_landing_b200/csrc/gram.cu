@@ -122,11 +122,11 @@ static int launch_gram(int mode, int kind, const double* Xs1, const double* sq1,
   if (n1_pad == 0 || n2_pad == 0) return GPMPC_OK;
   const int pitch = ((DP + 15) / 16) * 16 + 4;
   size_t smem = sizeof(double) * 2 * 128 * pitch;
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(gram_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    configured = true;
+    configured.here() = 1;
   }
   dim3 grid(n2_pad / 128, n1_pad / 128);
   if (mode == 0)

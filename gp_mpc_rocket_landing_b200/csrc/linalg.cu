@@ -125,10 +125,10 @@ extern "C" int gpmpc_trinv64_blocks(const double* L, int n_pad, long lda, double
   GPMPC_REQUIRE(n_pad % 64 == 0 && block_first >= 0 && block_last < n_pad / 64 && block_first <= block_last,
                 "gpmpc_trinv64_blocks: bad block range");
   const size_t smem = sizeof(double) * 2 * 64 * 65;
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(trinv64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = true;
+    configured.here() = 1;
   }
   trinv64_kernel<<<block_last - block_first + 1, 256, smem, (cudaStream_t)stream>>>(L, lda, Winv, block_first);
   return gpmpc_check_launch("trinv64");
@@ -149,10 +149,10 @@ extern "C" int gpmpc_potrf(double* A, int n_pad, long lda, long strideA, int bat
   const long strideW = (long)(n_pad / 64) * 4096;
   cudaMemsetAsync(info, 0, sizeof(int) * batch, stream);
   const size_t diag_smem = sizeof(double) * 2 * 64 * 65;
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(potrf_diag64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem);
-    configured = true;
+    configured.here() = 1;
   }
   // Two-level blocking: 64-wide right-looking steps INSIDE a 256-wide outer panel (their rank-64 updates touch the panel
   // columns only), then ONE rank-256 update of the trailing matrix per outer panel.  The trailing matrix is streamed
@@ -394,10 +394,10 @@ extern "C" int gpmpc_potrs(const double* L, int n_pad, long lda, long strideL, c
     return potrs_blocked(L, n_pad, lda, strideL, Winv, B, nrhs, batch, stream);
   size_t smem = sizeof(double) * (n_pad + 64 + 256);
   GPMPC_REQUIRE(smem <= 200 * 1024, "gpmpc_potrs: n_pad too large for the shared-memory solve");
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(potrs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    configured = true;
+    configured.here() = 1;
   }
   potrs_kernel<<<batch * nrhs, 256, smem, stream>>>(L, n_pad, lda, strideL, Winv, B, nrhs);
   return gpmpc_check_launch("potrs");
@@ -597,13 +597,13 @@ extern "C" int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const d
   // (DMMA runs on the tensor pipe, the ADMM chains on the FP64 FMA pipe: separate units).
   int rc;
   if (one_cta_per_sm) {
-    static int sms = 0;
-    if (!sms) {
+    static GpmpcPerDevice sms;
+    if (!sms.here()) {
       int dev = 0;
       cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      cudaDeviceGetAttribute(&sms.here(), cudaDevAttrMultiProcessorCount, dev);
     }
-    rc = launch_dgemm_nt_persistent<64, 128, 2, 4>(p, sms, 117248, stream);
+    rc = launch_dgemm_nt_persistent<64, 128, 2, 4>(p, sms.here(), 117248, stream);
   } else {
     rc = launch_dgemm_nt<64, 128, 2, 4>(p, 1, stream);
   }
@@ -679,10 +679,10 @@ extern "C" int gpmpc_trsm_small(const double* L, int M, long ldl, double* B, lon
                                 double* sumsq, double sumsq_sign, void* stream) {
   GPMPC_REQUIRE(M > 0 && M <= 144, "gpmpc_trsm_small: M must be in 1..144");
   size_t smem = sizeof(double) * M * (M + 1);
-  static bool configured = false;
-  if (!configured) {
+  static GpmpcPerDevice configured;
+  if (!configured.here()) {
     cudaFuncSetAttribute(trsm_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 180 * 1024);
-    configured = true;
+    configured.here() = 1;
   }
   trsm_small_kernel<<<(ncols + 127) / 128, 128, smem, (cudaStream_t)stream>>>(L, M, ldl, B, ldb, ncols, b_colmajor,
                                                                             sumsq, sumsq_sign);

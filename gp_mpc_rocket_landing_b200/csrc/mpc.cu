@@ -655,43 +655,6 @@ __device__ __forceinline__ int classify3(const double* x, double m0) {
   return 0;
 }
 
-__global__ void __launch_bounds__(128) mc_step3_kernel(GpmpcDyn3 dyn, int nbatch, double drag_cda, int max_steps,
-                                                       double* __restrict__ x, const double* __restrict__ u,
-                                                       const double* __restrict__ m0, int* __restrict__ t_step,
-                                                       int* __restrict__ active, int* __restrict__ outcome,
-                                                       double* __restrict__ x_final,
-                                                       unsigned long long* __restrict__ counts) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= nbatch) return;
-  if (!active[b]) return;
-  double xl[NX], ul[NU], xn[NX];
-#pragma unroll
-  for (int d = 0; d < NX; ++d) xl[d] = x[(long)b * NX + d];
-#pragma unroll
-  for (int d = 0; d < NU; ++d) ul[d] = u[(long)b * NU + d];
-  step3(xl, ul, dyn, xn);
-  if (drag_cda != 0.0) {
-    const double rho = 1.225 * exp(-xl[1] / 8500.0);
-    const double sp = sqrt(xl[4] * xl[4] + xl[5] * xl[5] + xl[6] * xl[6]);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) xn[4 + i] = xn[4 + i] + dyn.dt * (-0.5 * rho * drag_cda * sp * xl[4 + i] / xl[0]);
-  }
-  const int t = t_step[b] + 1;
-  int code = classify3(xn, m0[b]);
-  if (code == 0 && t >= max_steps) code = 5;
-#pragma unroll
-  for (int d = 0; d < NX; ++d) x[(long)b * NX + d] = xn[d];
-  t_step[b] = t;
-  if (code != 0) {
-    active[b] = 0;
-    outcome[b] = code;
-    if (x_final)
-#pragma unroll
-      for (int d = 0; d < NX; ++d) x_final[(long)b * NX + d] = xn[d];
-    if (counts) atomicAdd(counts + code, 1ULL);
-  }
-}
-
 // ------------------------------------------------------------------------------------------------ post-QP update
 // One warp per scenario.  mode 0 = RTI (osqp_rti.py:532-552), mode 1 = GP-MPC SQP iteration (gp_mpc.py:336-345).
 __device__ __forceinline__ void mpc_update3_body(int b, int lane, int N, int mode, const double* __restrict__ z,
@@ -1180,13 +1143,14 @@ extern "C" int gpmpc_rollout_3dof(const GpmpcExactModel* model, const GpmpcDyn3*
   const size_t smem = sizeof(double) * (size_t)M.n_pad * (12 + 1 + 3);
   if (has_model && M.DP == 12 && M.P == 3 && smem <= 200 * 1024) {
     // one wave: one CTA per SM, W warps each, two scenarios per warp
-    static int n_sm = 0;
-    if (n_sm == 0) {
+    static GpmpcPerDevice n_sm_dev;
+    if (n_sm_dev.here() == 0) {
       int dev = 0;
       cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+      cudaDeviceGetAttribute(&n_sm_dev.here(), cudaDevAttrMultiProcessorCount, dev);
       cudaFuncSetAttribute(rollout3_smem_kernel<12, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     }
+    const int n_sm = n_sm_dev.here();
     const int ntask = (B + 1) / 2;
     const int passes = (ntask + n_sm * ROLLS_MAX_WARPS - 1) / (n_sm * ROLLS_MAX_WARPS);
     int W = (ntask + n_sm * passes - 1) / (n_sm * passes);
@@ -1222,16 +1186,6 @@ extern "C" int gpmpc_linearize_3dof(const GpmpcDyn3* dyn, int npts, int lin_mode
   if (npts == 0) return GPMPC_OK;
   linearize3_kernel<<<(npts + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, npts, lin_mode, X, U, AB);
   return gpmpc_check_launch("linearize_3dof");
-}
-
-extern "C" int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_steps, double* x, const double* u,
-                                  const double* m0, int* t_step, int* active, int* outcome, double* x_final,
-                                  unsigned long long* counts, void* stream) {
-  GPMPC_REQUIRE(dyn != nullptr && B >= 0 && x && u && m0 && t_step && active && outcome, "gpmpc_mc_step_3dof: bad arguments");
-  if (B == 0) return GPMPC_OK;
-  mc_step3_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*dyn, B, drag_cda, max_steps, x, u, m0, t_step,
-                                                                      active, outcome, x_final, counts);
-  return gpmpc_check_launch("mc_step_3dof");
 }
 
 extern "C" int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active,

@@ -125,7 +125,12 @@ class ExactGP:
         dev_x = _is_dev(self.X_train)
         Xn = X_new if _is_dev(X_new) else np.atleast_2d(np.asarray(X_new, dtype=np.float64))
         yn = _host(y_new).flatten() if _is_dev(y_new) else np.atleast_1d(np.asarray(y_new, dtype=np.float64)).flatten()
-        y_all = np.concatenate([self.y_train * self._y_std + self._y_mean, yn])
+        # raw targets of the old rows: y_train holds (y - y_mean) / y_std - m(X) / y_std (exact_gp.py:141-154)
+        y_old = self.y_train * self._y_std + self._y_mean
+        if self.mean_function is not None:
+            Xo = _host(self.X_train) if dev_x else self.X_train
+            y_old = y_old + np.asarray(self.mean_function(Xo), dtype=np.float64).flatten()
+        y_all = np.concatenate([y_old, yn])
         if dev_x:
             X_all = E.torch_().cat([self.X_train, E.to_dev(Xn)], dim=0)
         else:

@@ -250,8 +250,13 @@ class OnlineGPUpdater:
         Z, D = self._buffer.get_data()
         y = _targets_1d(D)
         refit = self.should_refit()
-        can_extend = (not refit and hasattr(self.gp, "update") and getattr(self.gp, "_model", None) is not None
-                      and self._fitted_evictions == self._buffer.evictions and 0 < self._fitted_rows <= Z.shape[0])
+        # extension is only valid for an exact GP whose training set is still exactly the front of the buffer: a sparse GP
+        # is refit as in the reference (online_update.py:383-391), and an external gp.fit() on other data in between (its
+        # n_train no longer equals the rows this updater fitted) falls back to a full refit as well
+        from .exact_gp import ExactGP
+        can_extend = (not refit and isinstance(self.gp, ExactGP) and getattr(self.gp, "_model", None) is not None
+                      and self._fitted_evictions == self._buffer.evictions and 0 < self._fitted_rows <= Z.shape[0]
+                      and int(getattr(self.gp, "n_train", -1)) == self._fitted_rows)
         mode = "refit"
         try:
             if can_extend and self._fitted_rows < Z.shape[0]:

@@ -9,6 +9,9 @@
  * the boundary); all pointers are DEVICE pointers to row-major FP64 unless a name ends in `_host`; the caller owns
  * every buffer; the last argument is a cudaStream_t (passed as void*); kernels are stream-ordered and re-entrant
  * on different streams.  "pad" sizes are multiples of 128 (rows) / 4 (feature columns) and padding is zero.
+ * Process model: one process per GPU (the Python side uses torch.distributed that way).  Kernel attributes are configured
+ * lazily per device ordinal, so a host that switches devices with cudaSetDevice works too, but first calls from several
+ * host threads at once need external locking.
  */
 #ifndef GPMPC_B200_H
 #define GPMPC_B200_H
@@ -237,14 +240,6 @@ int gpmpc_gp_mean_points_3dof(const GpmpcExactModel* model, int B, int N, const 
  * protocol consumed at osqp_rti.py:295,340, gp_mpc.py:305, uncertainty_prop.py:147.  lin_mode as in qp_assemble. */
 int gpmpc_linearize_3dof(const GpmpcDyn3* dyn, int npts, int lin_mode, const double* X, const double* U, double* AB,
                          void* stream);
-
-/* One closed-loop Monte Carlo step per scenario (experiments/monte_carlo.py:455-549): x <- step(x,u) (+ optional
- * drag-like true residual -0.5 rho(alt) drag_cda |v| v / m), t_step += 1, then the termination rules :460-488 and
- * check_landing :54-104.  Terminated scenarios get active=0, outcome = LandingOutcome code (1 success, 2 crash, 3 fuel,
- * 4 violation, 5 timeout, 6 divergence), x_final (B x 7, may be NULL) and counts[code] += 1 (8 counters, may be NULL). */
-int gpmpc_mc_step_3dof(const GpmpcDyn3* dyn, int B, double drag_cda, int max_steps, double* x, const double* u,
-                       const double* m0, int* t_step, int* active, int* outcome, double* x_final,
-                       unsigned long long* counts, void* stream);
 
 /* z = [x_0,u_0,...,x_N] from (X, U): OSQPRTIMPC._solution_to_vector, osqp_rti.py:601-614 (primal warm start). */
 int gpmpc_pack_traj_3dof(int B, int N, const double* X, const double* U, double* z, const int* active, void* stream);

@@ -154,6 +154,26 @@ def test_explicit_inverse_variance_path(eng, tag, noise, tol):
     assert relerr(var_trsm, a[f"{tag}_truth_var"]) < bound
 
 
+def test_update_with_mean_function_equals_fit(eng):
+    """ExactGP.update with a prior mean (exact_gp.py:141-154: the stored targets have m(X) / y_std subtracted): extending
+    the model must equal `fit` on the concatenated RAW data -- the old rows' targets are reconstructed with m(X) added back."""
+    from gp_mpc_rocket_landing_b200.gp import ExactGP, SquaredExponentialARD
+    rng = np.random.default_rng(3)
+    D = 4
+    X = rng.normal(size=(90, D)); y = 2.0 + np.sin(X[:, 0]) + 0.5 * X[:, 1] + 0.05 * rng.normal(size=90)
+    Xq = rng.normal(size=(25, D))
+    mean_fn = lambda Z: 2.0 + 0.5 * np.asarray(Z)[:, 1]   # noqa: E731
+    inc = ExactGP(SquaredExponentialARD(D), noise_variance=1e-2, mean_function=mean_fn).fit(X[:60], y[:60])
+    inc.update(X[60:], y[60:])
+    full = ExactGP(SquaredExponentialARD(D), noise_variance=1e-2, mean_function=mean_fn).fit(X, y)
+    assert inc.n_train == full.n_train == 90
+    assert inc._y_mean == pytest.approx(full._y_mean, rel=1e-13) and inc._y_std == pytest.approx(full._y_std, rel=1e-13)
+    np.testing.assert_allclose(inc.y_train, full.y_train, rtol=1e-12, atol=1e-13)
+    pi, pf = inc.predict(Xq), full.predict(Xq)
+    assert relerr(pi.mean, pf.mean) < 1e-10 and relerr(pi.variance, pf.variance) < 1e-9
+    assert abs(inc.log_marginal_likelihood - full.log_marginal_likelihood) < 1e-9 * abs(full.log_marginal_likelihood)
+
+
 def test_predict_batch_equals_singles_and_variance_floor(eng):
     """batch = loop of singles (bitwise: every query row is solved independently), floor 1e-10 * y_std^2."""
     rng = np.random.default_rng(5)
