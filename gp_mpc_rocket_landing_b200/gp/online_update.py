@@ -254,7 +254,8 @@ class OnlineGPUpdater:
         # is refit as in the reference (online_update.py:383-391), and an external gp.fit() on other data in between (its
         # n_train no longer equals the rows this updater fitted) falls back to a full refit as well
         from .exact_gp import ExactGP
-        can_extend = (not refit and isinstance(self.gp, ExactGP) and getattr(self.gp, "_model", None) is not None
+        incremental = isinstance(self.gp, ExactGP) or getattr(self.gp, "supports_incremental_update", False)
+        can_extend = (not refit and incremental and getattr(self.gp, "_model", None) is not None
                       and self._fitted_evictions == self._buffer.evictions and 0 < self._fitted_rows <= Z.shape[0]
                       and int(getattr(self.gp, "n_train", -1)) == self._fitted_rows)
         mode = "refit"

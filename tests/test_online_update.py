@@ -50,15 +50,18 @@ class _FakeGP:
     class kernel:
         signal_variance = 1.0
 
+    supports_incremental_update = True     # the updater extends only ExactGP or a model that declares this
+
     def __init__(self):
         self._model = None
+        self.n_train = 0
         self.calls = []
 
     def fit(self, Z, y):
-        self._model = object(); self.calls.append(("fit", len(y))); return self
+        self._model = object(); self.n_train = len(y); self.calls.append(("fit", len(y))); return self
 
     def update(self, Z, y):
-        self.calls.append(("update", len(y))); return self
+        self.n_train += len(y); self.calls.append(("update", len(y))); return self
 
     def predict(self, Z):
         class P: variance = np.full(len(Z), 0.5)
