@@ -28,7 +28,8 @@ sys.path.insert(0, ROOT)
 
 N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
 # dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` captures (profiles/), B = 4096
-NCU_TRAFFIC = {"admm": 82.6e6, "rollout": 740.5e6, "gp_variance": 689.2e6}  # profiles/r1_step_kernels_v2_full.md
+NCU_TRAFFIC = {"prologue": 2.2e6, "rollout": 740.6e6, "gp_variance": 691.6e6, "cov": 17.7e6, "assemble": 26.8e6,
+               "admm": 83.2e6, "update": 18.5e6}       # profiles/r2_step_kernels_full.md (one closed-loop step)
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 
 
@@ -303,6 +304,9 @@ def run_b200_arm(args):
     mc.counts.zero_()
     clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    prof_range = bool(os.environ.get("GPMPC_PROFILE_RANGE"))    # `ncu --profile-from-start off`: the timed steps only
+    if prof_range:
+        torch.cuda.profiler.start()
     e0.record()
     launches = 0
     for k in range(K):
@@ -320,6 +324,9 @@ def run_b200_arm(args):
             theta_events.append((ta, tb))
             n_theta += 1
     e1.record()
+    if prof_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     stats.wait()
     barrier()
     clk = clocks.stop()
@@ -447,8 +454,13 @@ def run_b200_arm(args):
             r["fp64_tflops"] = flops / (r["avg_ms_per_launch"] * 1e-3) / 1e12
             r["fp64_fma_frac_of_dgemm_peak"] = r["fp64_tflops"] / peak64 if peak64 else None
             r["mean_iterations"] = n_admm_it
-            r["us_per_iteration_of_batch"] = r["avg_ms_per_launch"] * 1e3 / max(n_admm_it, 1.0)
-            r.update(ADMM_MODEL)
+            m = dict(ADMM_MODEL)
+            m["model_ms_per_launch"] = (m["setup_ms"] + n_admm_it * m["us_per_iteration_of_batch"] * 1e-3 * B / 4096.0) \
+                * m["tail_factor"]
+            m["cycles_per_qp_iteration"] = m["us_per_iteration_of_batch"] * 1e-6 * 1.965e9 * m["resident_qps"] / 4096.0
+            m["chain_share_of_iteration"] = (m["dependent_chain_steps_per_iteration"] * m["cycles_per_chain_step"]
+                                             / m["cycles_per_qp_iteration"])
+            r["latency_model"] = m
         dom = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"])
         roof = dict(by_kernel[dom])
         roof["phase"] = dom
@@ -486,7 +498,13 @@ def run_b200_arm(args):
 
 
 # latency model of the ADMM kernel: filled from the kernel's structure, printed with the roofline
-ADMM_MODEL = {}
+# Latency model of the 3-DoF ADMM launch: fixed-iteration runs of the same kernel on the bench QPs
+# (tools/cmp_admm.py, profiles/r2_admm_gen3_vs_gen2_3dof.json) give the set-up and per-iteration cost of a 4096-QP launch;
+# the chain figures are the micro-benchmarks of tools/ubench (LDS -> 5 dependent DFMA -> STS -> warp barrier).
+ADMM_MODEL = {"resident_qps": 444, "setup_ms": 0.64, "us_per_iteration_of_batch": 39.5, "tail_factor": 1.12,
+              "dependent_chain_steps_per_iteration": 21, "cycles_per_chain_step": 190,
+              "note": "launch time = (set-up + mean iterations x per-iteration cost) x tail; adaptive-rho refactorisations "
+                      "are inside the tail factor; the kernel is bound by these dependent steps, not by HBM or FP64 rate"}
 
 
 def run_extras(args, torch):

@@ -1412,7 +1412,9 @@ extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, voi
     }
     rec.mark(GPMPC_PHASE_GP_VARIANCE);
     GPMPC_PREFER_SHARED(var_cov3_kernel);
-    var_cov3_kernel<<<(B + 127) / 128, 128, 0, s>>>(p->dyn, B, N, part, nparts, (long)p->q_pad, p->model.signal_var, 1e-10,
+    // one warp per CTA: the kernel is a latency chain per thread (20 sequential 7x7 products), so the 4096 threads are spread
+    // over 128 SMs instead of 32
+    var_cov3_kernel<<<(B + 31) / 32, 32, 0, s>>>(p->dyn, B, N, part, nparts, (long)p->q_pad, p->model.signal_var, 1e-10,
                                                     p->model.ystd, 1e-6, Xt, p->U, p->dvar, p->covs, p->active);
     if ((r = gpmpc_check_launch("var_cov_3dof"))) return r;
     ++launches;

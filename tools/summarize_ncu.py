@@ -24,8 +24,11 @@ def launches(src, out):
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     ci = {h: i for i, h in enumerate(rows[hi])}
     data = rows[hi + 1:]
+    # the last closed-loop step: from its solve_prologue3_kernel launch (round 2: one C call per solve) to the end;
+    # captures of the round-1 path (no prologue kernel) start after the second-to-last ADMM launch
+    pro = [i for i, r in enumerate(data) if "solve_prologue" in r[ci["Kernel Name"]]]
     adm = [i for i, r in enumerate(data) if "admm" in r[ci["Kernel Name"]]]
-    start = adm[-2] + 1 if len(adm) > 1 else 0
+    start = pro[-1] if pro else (adm[-2] + 1 if len(adm) > 1 else 0)
     agg, tot = collections.OrderedDict(), 0.0
     for r in data[start:]:
         nm = r[ci["Kernel Name"]].split("(")[0]
