@@ -60,6 +60,11 @@ class ExactModel(C.Structure):
     ]
 
 
+class Cone3(C.Structure):
+    """GpmpcCone3: polyhedral thrust / glide-slope rows (gp_mpc.py:417-429 as inner approximations)."""
+    _fields_ = [("enabled", c_int), ("T_max", c_double), ("facet_b", c_double), ("half_tan_gs", c_double)]
+
+
 class Solve3(C.Structure):
     """GpmpcSolve3: the plan of one fused batched solve (gpmpc_solve_batch_3dof); field order = include/gpmpc_b200.h."""
     _fields_ = [
@@ -78,6 +83,8 @@ class Solve3(C.Structure):
         ("z", c_dp), ("y", c_dp), ("rho", c_dp), ("obj", c_dp), ("pri", c_dp), ("dua", c_dp), ("qp_status", c_dp),
         ("qp_it", c_dp),
         ("U_warm", c_dp), ("X_warm", c_dp), ("has_warm", c_dp),
+        ("cone", Cone3), ("AB_c", c_dp), ("beq_c", c_dp), ("q_c", c_dp), ("z_c", c_dp), ("y_c", c_dp),
+        ("Pdiag_c", c_dp), ("lb_c", c_dp), ("ub_c", c_dp),
         ("events", C.POINTER(C.c_void_p)), ("event_phase", C.POINTER(c_int)), ("event_cap", c_int),
         ("event_count", C.POINTER(c_int)),
     ]
@@ -172,6 +179,9 @@ _PROTOS = {
                                        c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linv_sumsq_parts": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_solve_batch_3dof": (c_int, [C.POINTER(Solve3), C.POINTER(c_int), c_dp]),
+    "gpmpc_qp_augment_cone_3dof": (c_int, [C.POINTER(Cone3), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                           c_dp, c_dp, c_dp]),
+    "gpmpc_qp_extract_cone_3dof": (c_int, [c_int, c_int, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_mc_advance_3dof": (c_int, [C.POINTER(McStep3), c_dp]),
     "gpmpc_mc_combine_3dof": (c_int, [c_int, c_int, c_dp, c_dp, c_dp, c_double, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_safety_filter_3dof": (c_int, [C.POINTER(Safety3), c_int, c_dp, c_dp, c_long, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),

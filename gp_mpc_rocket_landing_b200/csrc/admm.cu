@@ -607,8 +607,8 @@ __global__ void __launch_bounds__(ADMM_THREADS, 3) admm_kernel(int N, int nbatch
       P.lbs[r] = v;
       P.ubs[r] = v;
     } else {
-      P.lbs[r] = Er * lb[(size_t)b * S.bound_stride + r - neq];
-      P.ubs[r] = Er * ub[(size_t)b * S.bound_stride + r - neq];
+      P.lbs[r] = Er * fmax(lb[(size_t)b * S.bound_stride + r - neq], -OSQP_INFTY);  // bounds clipped as OSQP's setup does (osqp.h OSQP_INFTY)
+      P.ubs[r] = Er * fmin(ub[(size_t)b * S.bound_stride + r - neq], OSQP_INFTY);
     }
   }
   // ---- iterates (scaled): x = x_in / D ; z = Abar x ; y = c y_in / E -----------------------------------------------------

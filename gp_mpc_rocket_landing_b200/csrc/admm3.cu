@@ -337,8 +337,8 @@ admm3_kernel(int nbatch, const double* __restrict__ ABg, const double* __restric
     for (int s = 0; s < NSLOT; ++s) {
       lbs[s] = ubs[s] = 0.0;
       if (live[s]) {
-        lbs[s] = Eb[s] * lb[(size_t)b * S.bound_stride + JG(s)];
-        ubs[s] = Eb[s] * ub[(size_t)b * S.bound_stride + JG(s)];
+        lbs[s] = Eb[s] * fmax(lb[(size_t)b * S.bound_stride + JG(s)], -OSQP_INFTY);  // bounds clipped as OSQP's setup does (osqp.h OSQP_INFTY)
+        ubs[s] = Eb[s] * fmin(ub[(size_t)b * S.bound_stride + JG(s)], OSQP_INFTY);
         if (lbs[s] < -INF_T && ubs[s] > INF_T) cls[s] = 0;
         else if (ubs[s] - lbs[s] < RHO_TOL) cls[s] = 1;
         if (S.warm_x) x[s] = xg[(size_t)b * n + JG(s)] / Dj[s];

@@ -611,6 +611,139 @@ __global__ void __launch_bounds__(128) qp_assemble3_kernel(GpmpcDyn3 dyn, int nb
   }
 }
 
+// ------------------------------------------------------------------------------------------------ convex rows
+// Polyhedral thrust / glide-slope rows as 7 extra stage "states" (include/gpmpc_b200.h, GpmpcCone3).  One thread per
+// (scenario, stage); stage N writes the initial rows and the terminal entries.
+constexpr int NXC = 2 * NX, NSC = NXC + NU;
+
+// the three normals of the inscribed triangle with a vertex in the radial direction of (y, z)
+__device__ __forceinline__ void glide_normals(double y, double z, double (&ny)[3], double (&nz)[3]) {
+  const double rho = sqrt(y * y + z * z);
+  double cy = 1.0, cz = 0.0;
+  if (rho > 1e-9) {
+    cy = y / rho;
+    cz = z / rho;
+  }
+  const double c60 = 0.5, s60 = 0.8660254037844386;
+  ny[0] = c60 * cy - s60 * cz;
+  nz[0] = s60 * cy + c60 * cz;
+  ny[1] = c60 * cy + s60 * cz;
+  nz[1] = -s60 * cy + c60 * cz;
+  ny[2] = -cy;
+  nz[2] = -cz;
+}
+
+// xi at a nominal point: the four thrust facets of u_prev and the three glide facets of x (oriented by x itself)
+__device__ __forceinline__ void cone_values(const GpmpcCone3& cone, const double* x, const double* u_prev, double* xi) {
+  xi[0] = u_prev[0] + cone.facet_b * u_prev[1];
+  xi[1] = u_prev[0] - cone.facet_b * u_prev[1];
+  xi[2] = u_prev[0] + cone.facet_b * u_prev[2];
+  xi[3] = u_prev[0] - cone.facet_b * u_prev[2];
+  double ny[3], nz[3];
+  glide_normals(x[2], x[3], ny, nz);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) xi[4 + i] = (ny[i] * x[2] + nz[i] * x[3]) - cone.half_tan_gs * x[1];
+}
+
+__global__ void __launch_bounds__(128) qp_augment_cone3_kernel(GpmpcCone3 cone, int nbatch, int N,
+                                                               const double* __restrict__ AB,
+                                                               const double* __restrict__ beq,
+                                                               const double* __restrict__ q,
+                                                               const double* __restrict__ X_nom,
+                                                               const double* __restrict__ U_nom,
+                                                               double* __restrict__ ABc, double* __restrict__ beqc,
+                                                               double* __restrict__ qc, double* __restrict__ zc,
+                                                               const int* __restrict__ active) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nbatch * (N + 1)) return;
+  const int b = idx / (N + 1), k = idx - b * (N + 1);
+  if (active && !active[b]) return;
+  const int n = N * NS + NX, neq = NX * (N + 1), nc = N * NSC + NXC, neqc = NXC * (N + 1);
+  const double* qb = q + (long)b * n + (long)k * NS;
+  double* qcb = qc + (long)b * nc + (long)k * NSC;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) {
+    qcb[i] = qb[i];
+    qcb[NX + i] = 0.0;
+  }
+  const double* xk = X_nom + ((long)b * (N + 1) + k) * NX;
+  if (zc) {
+    double* zb = zc + (long)b * nc + (long)k * NSC;
+#pragma unroll
+    for (int i = 0; i < NX; ++i) zb[i] = xk[i];
+    if (k == 0) {
+#pragma unroll
+      for (int i = 0; i < NX; ++i) zb[NX + i] = 0.0;
+    } else {
+      cone_values(cone, xk, U_nom + ((long)b * N + k - 1) * NU, zb + NX);
+    }
+    if (k < N)
+#pragma unroll
+      for (int i = 0; i < NU; ++i) zb[NXC + i] = U_nom[((long)b * N + k) * NU + i];
+  }
+  if (k == N) {
+#pragma unroll
+    for (int i = 0; i < NX; ++i) {
+      beqc[(long)b * neqc + i] = beq[(long)b * neq + i];
+      beqc[(long)b * neqc + NX + i] = 0.0;
+    }
+    return;
+  }
+#pragma unroll
+  for (int i = 0; i < NU; ++i) qcb[NXC + i] = qb[NX + i];
+  const double* ab = AB + ((long)b * N + k) * NX * NS;
+  const double* be = beq + (long)b * neq + NX + (long)k * NX;
+  double* abc = ABc + ((long)b * N + k) * NXC * NSC;
+  double* bec = beqc + (long)b * neqc + NXC + (long)k * NXC;
+  for (int i = 0; i < NXC * NSC; ++i) abc[i] = 0.0;
+#pragma unroll
+  for (int r = 0; r < NX; ++r) {
+#pragma unroll
+    for (int j = 0; j < NX; ++j) abc[r * NSC + j] = ab[r * NS + j];
+#pragma unroll
+    for (int j = 0; j < NU; ++j) abc[r * NSC + NXC + j] = ab[r * NS + NX + j];
+    bec[r] = be[r];
+  }
+  // thrust facets on u_k
+  const double fb = cone.facet_b;
+  abc[(NX + 0) * NSC + NXC + 0] = 1.0; abc[(NX + 0) * NSC + NXC + 1] = fb;
+  abc[(NX + 1) * NSC + NXC + 0] = 1.0; abc[(NX + 1) * NSC + NXC + 1] = -fb;
+  abc[(NX + 2) * NSC + NXC + 0] = 1.0; abc[(NX + 2) * NSC + NXC + 2] = fb;
+  abc[(NX + 3) * NSC + NXC + 0] = 1.0; abc[(NX + 3) * NSC + NXC + 2] = -fb;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) bec[NX + i] = 0.0;
+  // glide facets on x_{k+1} = A x_k + B u_k - beq_k, oriented by the nominal x_{k+1}
+  const double* xn = X_nom + ((long)b * (N + 1) + k + 1) * NX;
+  double ny[3], nz[3];
+  glide_normals(xn[2], xn[3], ny, nz);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    double* row = abc + (NX + 4 + i) * NSC;
+#pragma unroll
+    for (int j = 0; j < NX; ++j)
+      row[j] = (ny[i] * ab[2 * NS + j] + nz[i] * ab[3 * NS + j]) - cone.half_tan_gs * ab[1 * NS + j];
+#pragma unroll
+    for (int j = 0; j < NU; ++j)
+      row[NXC + j] = (ny[i] * ab[2 * NS + NX + j] + nz[i] * ab[3 * NS + NX + j]) - cone.half_tan_gs * ab[1 * NS + NX + j];
+    bec[NX + 4 + i] = (ny[i] * be[2] + nz[i] * be[3]) - cone.half_tan_gs * be[1];
+  }
+}
+
+__global__ void __launch_bounds__(128) qp_extract_cone3_kernel(int nbatch, int N, const double* __restrict__ zc,
+                                                               double* __restrict__ z, const int* __restrict__ active) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= nbatch * (N + 1)) return;
+  const int b = idx / (N + 1), k = idx - b * (N + 1);
+  if (active && !active[b]) return;
+  const double* zb = zc + (long)b * (N * NSC + NXC) + (long)k * NSC;
+  double* o = z + (long)b * (N * NS + NX) + (long)k * NS;
+#pragma unroll
+  for (int i = 0; i < NX; ++i) o[i] = zb[i];
+  if (k < N)
+#pragma unroll
+    for (int i = 0; i < NU; ++i) o[NX + i] = zb[NXC + i];
+}
+
 // Discrete Jacobians at a list of points (dynamics.linearize protocol: osqp_rti.py:374-401 / :656-710), unfiltered.
 __global__ void __launch_bounds__(128) linearize3_kernel(GpmpcDyn3 dyn, int npts, int lin_mode,
                                                          const double* __restrict__ X, const double* __restrict__ U,
@@ -1361,6 +1494,28 @@ struct PhaseRec {
 };
 }  // namespace
 
+extern "C" int gpmpc_qp_augment_cone_3dof(const GpmpcCone3* cone, int B, int N, const double* AB, const double* beq,
+                                          const double* q, const double* X_nom, const double* U_nom, double* AB_c,
+                                          double* beq_c, double* q_c, double* z_c, const int* active, void* stream) {
+  GPMPC_REQUIRE(cone && B >= 0 && N >= 1 && AB && beq && q && X_nom && U_nom && AB_c && beq_c && q_c,
+                "gpmpc_qp_augment_cone_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  const int total = B * (N + 1);
+  GPMPC_PREFER_SHARED(qp_augment_cone3_kernel);
+  qp_augment_cone3_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(*cone, B, N, AB, beq, q, X_nom, U_nom, AB_c,
+                                                                                 beq_c, q_c, z_c, active);
+  return gpmpc_check_launch("qp_augment_cone_3dof");
+}
+
+extern "C" int gpmpc_qp_extract_cone_3dof(int B, int N, const double* z_c, double* z, const int* active, void* stream) {
+  GPMPC_REQUIRE(B >= 0 && N >= 1 && z_c && z, "gpmpc_qp_extract_cone_3dof: bad arguments");
+  if (B == 0) return GPMPC_OK;
+  const int total = B * (N + 1);
+  GPMPC_PREFER_SHARED(qp_extract_cone3_kernel);
+  qp_extract_cone3_kernel<<<(total + 127) / 128, 128, 0, (cudaStream_t)stream>>>(B, N, z_c, z, active);
+  return gpmpc_check_launch("qp_extract_cone_3dof");
+}
+
 extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, void* stream_) {
   GPMPC_REQUIRE(p != nullptr && p->B >= 0 && p->N >= 1 && p->max_sqp_iter >= 1, "gpmpc_solve_batch_3dof: bad arguments");
   GPMPC_REQUIRE(p->x0 && p->x_ref && p->X && p->U && p->AB && p->beq && p->q && p->z && p->y && p->rho,
@@ -1378,6 +1533,9 @@ extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, voi
   GPMPC_REQUIRE(!p->has_model || p->dmean, "gpmpc_solve_batch_3dof: dmean is NULL");
   const bool tighten = use_unc && p->tighten_kappa > 0.0;
   GPMPC_REQUIRE(!tighten || (p->lb_t && p->ub_t), "gpmpc_solve_batch_3dof: tightened boxes are NULL");
+  GPMPC_REQUIRE(!p->cone.enabled || (p->AB_c && p->beq_c && p->q_c && p->z_c && p->y_c && p->Pdiag_c && p->lb_c && p->ub_c),
+                "gpmpc_solve_batch_3dof: convex-row buffers are NULL");
+  GPMPC_REQUIRE(!p->cone.enabled || !tighten, "gpmpc_solve_batch_3dof: convex rows and per-stage tightening are exclusive");
   PhaseRec rec{p, s};
   const int total = B * (N + 1);
   int rc;
@@ -1455,13 +1613,28 @@ extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, voi
                                                             p->Qfd, p->AB, p->beq, p->q, p->active, p->z);
     if ((rc = gpmpc_check_launch("qp_assemble_3dof"))) return rc;
     ++launches;
-    rec.mark(GPMPC_PHASE_ASSEMBLE);
-    if ((rc = gpmpc_admm_solve(NX, NU, N, B, p->AB, p->beq, p->q, p->Pdiag, tighten ? p->lb_t : p->lb,
-                               tighten ? p->ub_t : p->ub, &S, p->active, p->z, p->y, p->rho, p->qp_status, p->qp_it, p->obj,
-                               p->pri, p->dua, (void*)s)))
-      return rc;
-    ++launches;
-    rec.mark(GPMPC_PHASE_ADMM);
+    if (p->cone.enabled) {  // polyhedral thrust / glide-slope rows: solve in the augmented (14, 3) stage form
+      if ((rc = gpmpc_qp_augment_cone_3dof(&p->cone, B, N, p->AB, p->beq, p->q, p->X, p->U, p->AB_c, p->beq_c, p->q_c, p->z_c,
+                                           p->active, (void*)s)))
+        return rc;
+      ++launches;
+      rec.mark(GPMPC_PHASE_ASSEMBLE);
+      if ((rc = gpmpc_admm_solve(NXC, NU, N, B, p->AB_c, p->beq_c, p->q_c, p->Pdiag_c, p->lb_c, p->ub_c, &S, p->active,
+                                 p->z_c, p->y_c, p->rho, p->qp_status, p->qp_it, p->obj, p->pri, p->dua, (void*)s)))
+        return rc;
+      ++launches;
+      rec.mark(GPMPC_PHASE_ADMM);
+      if ((rc = gpmpc_qp_extract_cone_3dof(B, N, p->z_c, p->z, p->active, (void*)s))) return rc;
+      ++launches;
+    } else {
+      rec.mark(GPMPC_PHASE_ASSEMBLE);
+      if ((rc = gpmpc_admm_solve(NX, NU, N, B, p->AB, p->beq, p->q, p->Pdiag, tighten ? p->lb_t : p->lb,
+                                 tighten ? p->ub_t : p->ub, &S, p->active, p->z, p->y, p->rho, p->qp_status, p->qp_it,
+                                 p->obj, p->pri, p->dua, (void*)s)))
+        return rc;
+      ++launches;
+      rec.mark(GPMPC_PHASE_ADMM);
+    }
     GPMPC_PREFER_SHARED(mpc_update3_kernel);
     mpc_update3_kernel<<<(B + 3) / 4, 128, 0, s>>>(B, N, 1, p->z, p->qp_status, p->x_ref, (long)(N + 1) * NX, p->Qd, p->Qfd,
                                                    p->Rd, p->X, p->U, nullptr, nullptr, p->cost, p->converged, p->active,
@@ -1502,6 +1675,8 @@ extern "C" long gpmpc_struct_layout(int which, int field) {
       case 8: return (long)offsetof(GpmpcSolve3, U_warm);
       case 9: return (long)offsetof(GpmpcSolve3, events);
       case 10: return (long)offsetof(GpmpcSolve3, event_count);
+      case 11: return (long)offsetof(GpmpcSolve3, cone);
+      case 12: return (long)offsetof(GpmpcSolve3, Pdiag_c);
     }
   } else if (which == 1) {
     switch (field) {

@@ -150,7 +150,7 @@ class BatchedMonteCarlo:
             a.qp_iters = ge.ptr(sol.qp_iterations)
             st = getattr(self.controller, "_batch", None)
             if self.respawn and st is not None:   # controller state cleared on the device for respawned scenarios
-                a.has_warm, a.y, a.rho, a.m = ge.ptr(st.has_warm), ge.ptr(st.ws.y), ge.ptr(st.ws.rho), st.ws.y.shape[1]
+                a.has_warm, a.y, a.rho, a.m = ge.ptr(st.has_warm), ge.ptr(st.duals), ge.ptr(st.ws.rho), st.duals.shape[1]
             else:
                 a.has_warm = a.y = a.rho = None
         if self.safety_filter is not None:     # filter the first control on the device (safety/safety_filter.py:184-235)

@@ -49,6 +49,10 @@ class GPMPCConfig(MPCConfig):
     tighten_state_bounds: bool = False
     # numpy-in calls: copy u0 / cost / flags to the host at once and X_opt / U_opt on first access (BatchMPCSolution)
     defer_trajectory_copy: bool = True
+    # Extension (off = the OSQP-form box QP): polyhedral inner approximations of the thrust-norm and
+    # glide-slope constraints the reference's sub-problem hands to IPOPT (gp_mpc.py:417-429) as rows of the ADMM QP,
+    # parameters from `constraint_params` (T_min, T_max, gamma_gs); include/gpmpc_b200.h GpmpcCone3
+    convex_constraints: bool = False
     qp_max_iter: int = 1000           # config/mpc_params.yaml:48 (osqp_rti.py:53 uses 50, which rarely converges)
     qp_eps_abs: float = 1e-4          # osqp_rti.py:54
     qp_eps_rel: float = 1e-4          # osqp_rti.py:55
@@ -103,11 +107,17 @@ class _BatchState:
         self.U_warm = torch.zeros((B, N, NU), **f64)
         self.X_warm = torch.zeros((B, N + 1, NX), **f64)
         self.has_warm = torch.zeros((B,), **i32)     # per scenario: 0 -> hover / U_ref initial guess
+        self.cone = None      # buffers of the augmented (14, 3) stage QP (GPMPCConfig.convex_constraints)
         self.plan = None
         self.generation = 0   # number of solves run on this state (DeferredHostArray checks it)
         self.keep = None      # tensors referenced by the plan for the duration of a call
         self._pinned = [{}, {}]   # two alternating sets of pinned staging buffers for the host results
         self._flip = 0
+
+    @property
+    def duals(self):
+        """The dual state that persists between control steps (y of the QP that is actually solved)."""
+        return self.cone["y"] if self.cone is not None else self.ws.y
 
     def from_host(self, key: str, arr):
         """numpy -> device through a persistent pinned staging buffer (async H2D on the current stream).  Safe to reuse
@@ -203,7 +213,7 @@ class GPMPC:
         for st in (self._single, self._batch):
             if st is not None:
                 st.has_warm.zero_()
-                st.ws.y.zero_()
+                st.duals.zero_()
                 st.ws.rho.zero_()
 
     def reset_scenarios(self, mask, X0=None) -> None:
@@ -217,7 +227,7 @@ class GPMPC:
             mask_d = mask.to(torch.int32).contiguous()
         else:   # host mask: one small pinned H2D copy, one launch
             mask_d = st.from_host("reset_mask", (np.asarray(mask) != 0).astype(np.float64)).to(torch.int32)
-        ge.call("gpmpc_reset_scenarios", st.B, st.N, NU, st.ws.y.shape[1], ge.ptr(mask_d), None, None, ge.ptr(st.ws.y),
+        ge.call("gpmpc_reset_scenarios", st.B, st.N, NU, st.duals.shape[1], ge.ptr(mask_d), None, None, ge.ptr(st.duals),
                 ge.ptr(st.ws.rho), ge.ptr(st.has_warm), ge.stream())
 
     def _settings(self):
@@ -272,7 +282,46 @@ class GPMPC:
                         ("y", ws.y), ("rho", ws.rho), ("obj", ws.obj), ("pri", ws.pri), ("dua", ws.dua),
                         ("qp_status", ws.status), ("qp_it", ws.iters), ("U_warm", st.U_warm), ("X_warm", st.X_warm)):
             setattr(p, name, ge.ptr(t))
+        if c.convex_constraints:
+            self._plan_cone(st, p)
         return p
+
+    def _plan_cone(self, st: _BatchState, p) -> None:
+        """Buffers and shared data of the augmented stage QP [x (7); xi (7); u (3)] (GpmpcCone3)."""
+        torch = ge.torch_()
+        if self.config.tighten_state_bounds:
+            raise _lib.GpmpcError("convex_constraints and tighten_state_bounds are exclusive")
+        cp, N, B = self.constraint_params, st.N, st.B
+        NXC, NSC = 2 * NX, 2 * NX + NU
+        n_c = N * NSC + NXC
+        m_c = NXC * (N + 1) + n_c
+        qp = self._qp
+        if st.cone is None:
+            f64 = dict(dtype=torch.float64, device=st.X.device)
+            Qd, Qfd, Rd = (np.asarray(t.cpu().numpy(), dtype=np.float64) for t in (qp.Qd, qp.Qfd, qp.Rd))
+            lb7, ub7 = qp.lb.cpu().numpy(), qp.ub.cpu().numpy()
+            Pd = np.zeros(n_c); lb = np.full(n_c, -me.INF); ub = np.full(n_c, me.INF)
+            xi_hi = np.array([cp.T_max] * 4 + [0.0] * 3)
+            for k in range(N + 1):
+                o, o7 = k * NSC, k * (NX + NU)
+                Pd[o:o + NX] = Qfd if k == N else Qd
+                lb[o:o + NX], ub[o:o + NX] = lb7[o7:o7 + NX], ub7[o7:o7 + NX]
+                if k > 0:
+                    ub[o + NX:o + NXC] = xi_hi
+                if k < N:
+                    Pd[o + NXC:o + NSC] = Rd
+                    lb[o + NXC:o + NSC], ub[o + NXC:o + NSC] = lb7[o7 + NX:o7 + NX + NU], ub7[o7 + NX:o7 + NX + NU]
+                    lb[o + NXC] = max(lb[o + NXC], cp.T_min)      # |u| >= T_min (non-convex) -> u_x >= T_min
+            st.cone = dict(AB=torch.zeros((B, N, NXC, NSC), **f64), beq=torch.zeros((B, NXC * (N + 1)), **f64),
+                           q=torch.zeros((B, n_c), **f64), z=torch.zeros((B, n_c), **f64), y=torch.zeros((B, m_c), **f64),
+                           Pdiag=ge.to_dev(Pd), lb=ge.to_dev(lb), ub=ge.to_dev(ub))
+        p.cone.enabled = 1
+        p.cone.T_max = float(cp.T_max)
+        p.cone.facet_b = float(np.sqrt(2.0 * (cp.T_max - cp.T_min) / (cp.T_max + cp.T_min)))
+        p.cone.half_tan_gs = float(np.tan(cp.gamma_gs_rad) / 2.0)
+        for name, key in (("AB_c", "AB"), ("beq_c", "beq"), ("q_c", "q"), ("z_c", "z"), ("y_c", "y"), ("Pdiag_c", "Pdiag"),
+                          ("lb_c", "lb"), ("ub_c", "ub")):
+            setattr(p, name, ge.ptr(st.cone[key]))
 
     def _solve_device(self, st: _BatchState, x0, x_target=None, X_ref=None, U_ref=None, active_in=None,
                       per_step_target=False):

@@ -290,6 +290,36 @@ int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp
                           double* U, double* X_prev, double* U_prev, double* cost, int* converged, int* active,
                           int* n_iter, void* stream);
 
+/* ---- convex thrust / glide-slope rows inside the ADMM QP (second half) -----------------------------------
+ *
+ * The reference's sub-problem (gp_mpc.py:417-429) constrains every stage k < N by  T_min^2 <= |u_k|^2 <= T_max^2  and the
+ * glide-slope cone  r_x^2 tan^2(gamma) >= r_y^2 + r_z^2  and hands them to IPOPT.  For the OSQP-form QP they become
+ * polyhedral INNER approximations (every point the QP accepts satisfies the original constraints):
+ *   - |u| >= T_min (non-convex)  ->  u_x >= T_min: the lower box bound of the axial component, set by the host;
+ *   - |u| <= T_max  ->  u_x +- b u_y <= T_max,  u_x +- b u_z <= T_max  with  b = sqrt(2 (T_max - T_min) / (T_max + T_min)):
+ *     a square pyramid with its apex at T_max on the axial direction, inside the ball for u_x >= T_min;
+ *   - the cone at the NEXT stage, sqrt(y^2 + z^2) <= alt tan(gamma): the pyramid over the triangle inscribed in the circle
+ *     with one vertex in the radial direction e of the nominal point,  n_i . (y, z) <= alt tan(gamma) / 2  for the normals
+ *     n_i = R(+60 deg) e, R(-60 deg) e, -e  (e = (1, 0) when the nominal point is on the axis).
+ * To keep the stage structure the ADMM kernels factorise (block tridiagonal, no extra row type), the 7 row values travel as
+ * 7 extra "states":  xi_{k+1} = G_k [x_k; u_k] - g_k  with  -inf < xi <= (T_max x 4, 0 x 3)  as box bounds, i.e. the QP is
+ * solved in the stage form (n_x, n_u) = (14, 3) with stage variables [x (7); xi (7); u (3)] and zero cost on xi;
+ * xi_0 = 0 is fixed by the initial-state rows and unbounded.  n = 17 N + 14, m = 14 (N + 1) + n. */
+typedef struct GpmpcCone3 {
+  int enabled;
+  double T_max;        /* constraints.py:39 */
+  double facet_b;      /* b above */
+  double half_tan_gs;  /* tan(gamma_gs) / 2, constraints.py:50 */
+} GpmpcCone3;
+
+/* (AB, beq, q) of gpmpc_qp_assemble_3dof + the nominal trajectory -> the augmented stage QP (AB_c: B x N x 14 x 17,
+ * beq_c: B x 14 (N + 1), q_c: B x (17 N + 14)) and its primal warm start z_c (may be NULL). */
+int gpmpc_qp_augment_cone_3dof(const GpmpcCone3* cone, int B, int N, const double* AB, const double* beq, const double* q,
+                               const double* X_nom, const double* U_nom, double* AB_c, double* beq_c, double* q_c,
+                               double* z_c, const int* active, void* stream);
+/* z_c (B x (17 N + 14)) -> z (B x (10 N + 7)): the [x; u] part of every stage. */
+int gpmpc_qp_extract_cone_3dof(int B, int N, const double* z_c, double* z, const int* active, void* stream);
+
 /* ---- fused per-control-step orchestration (SURVEY 8b proposal `gpmpc_solve_batch`) ---------------------------------------
  *
  * One call issues the whole device sequence of `GPMPC.solve` (gp_mpc.py:229-369, 7-state specialisation) for B scenarios:
@@ -339,6 +369,11 @@ typedef struct GpmpcSolve3 {
   double *cost; int *converged, *active, *n_iter, *qp_iters;
   double *z, *y, *rho, *obj, *pri, *dua; int *qp_status, *qp_it;
   double *U_warm, *X_warm; int* has_warm;   /* per-scenario warm start; has_warm[b] = 0 -> hover / U_ref */
+  /* optional convex rows (cone.enabled): the QP is solved in the augmented (14, 3) stage form; y_c (B x (31 N + 28)) takes the
+     place of y as the dual state that persists between control steps; Pdiag_c / lb_c / ub_c: shared, length 17 N + 14 */
+  GpmpcCone3 cone;
+  double *AB_c, *beq_c, *q_c, *z_c, *y_c;
+  const double *Pdiag_c, *lb_c, *ub_c;
   /* optional phase timing: events[i] (cudaEvent_t) is recorded after phase event_phase[i] (host arrays written by the call) */
   void** events; int* event_phase; int event_cap; int* event_count;
 } GpmpcSolve3;

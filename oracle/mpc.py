@@ -587,8 +587,9 @@ class GPMPCOracle:
     of osqp_rti.py: box bounds only; GP mean as affine term c_k=[0,0,0,0,d_v*dt]."""
 
     def __init__(self, gp_predict, params=None, N=20, dt=0.1, settings=None, max_sqp_iter=10, use_gp_mean=True,
-                 keep_rho=True):
+                 keep_rho=True, cone: "ConeRows | None" = None):
         self.gp_predict = gp_predict
+        self.cone = cone          # polyhedral thrust / glide-slope rows: the QP is solved in the augmented stage form
         self.p = params or Rocket3DoFParams()
         self.N, self.dt = N, dt
         self.settings = settings or OSQPSettings()
@@ -627,17 +628,28 @@ class GPMPCOracle:
                 for k in range(N):
                     d, _ = self.gp_predict(X[k], U[k]); c_gp[k, 4:7] = d * dt
             A, l, u = build_constraints(N, X, U, x0, dt, p, "analytic", c_gp, mode="gpmpc")
-            qp = OSQPOracle(Pd, q, A, l, u, self.settings)
+            if self.cone is not None:
+                AB = np.stack([A[NX + k * NX:NX + (k + 1) * NX, k * 10:(k + 1) * 10] for k in range(N)])
+                ABc, beqc, qc, zc = augment_cone_qp(N, AB, l[:NX * (N + 1)], q, X, U, self.cone)
+                Pdc, lbc, ubc = cone_shared_data(N, self.cone)
+                Ac, lc, uc = dense_stage_constraints(NXC, NU, N, ABc, beqc, lbc, ubc)
+                qp = OSQPOracle(Pdc, qc, Ac, lc, uc, self.settings)
+            else:
+                qp = OSQPOracle(Pd, q, A, l, u, self.settings)
             if self.keep_rho and self.rho_warm is not None:
                 qp.rho = self.rho_warm
                 qp._set_rho_vec()
                 qp._factor()
-            qp.warm_start(x=traj_to_vec(X, U), y=y)
+            qp.warm_start(x=traj_to_vec(X, U) if self.cone is None else zc, y=y)
             res = qp.solve()
             self.rho_warm = res.rho
             stats.append(res.status); its.append(res.iters)
             if res.status == SOLVED:
-                Xn, Un = vec_to_traj(res.x, N); y = res.y
+                zx = res.x
+                if self.cone is not None:      # [x; xi; u] stages -> [x; u] stages
+                    zx = np.concatenate([np.r_[res.x[k * NSC:k * NSC + NX], res.x[k * NSC + NXC:(k + 1) * NSC]]
+                                         for k in range(N)] + [res.x[N * NSC:N * NSC + NX]])
+                Xn, Un = vec_to_traj(zx, N); y = res.y
                 cost = float(np.sum(Q_DIAG * (Xn[:N] - x_ref[:N]) ** 2) + np.sum(R_DIAG * Un**2)
                              + np.sum(10 * Q_DIAG * (Xn[N] - x_ref[N]) ** 2))
             else:                                                       # gp_mpc.py:478-482: nominal, cost=inf
@@ -652,6 +664,130 @@ class GPMPCOracle:
         self.U_warm = U.copy(); self.y_warm = y
         return MPCSolutionOracle(converged, X, U, cost, it + 1, "Converged" if converged else "Max iterations",
                                  stats, its, covs)
+
+
+# --------------------------------------------------------------------------- convex rows
+@dataclass
+class ConeRows:
+    """Polyhedral INNER approximations of the thrust-norm and glide-slope constraints the reference gives IPOPT
+    (gp_mpc.py:417-429; defaults of ConstraintParams, constraints.py:35-50), see include/gpmpc_b200.h GpmpcCone3:
+    u_x >= T_min (box), u_x +- b u_y <= T_max, u_x +- b u_z <= T_max, and for the next stage's position the pyramid over the
+    triangle inscribed in the glide-slope circle with a vertex in the nominal radial direction."""
+    T_min: float = 0.5
+    T_max: float = 5.0
+    gamma_gs_deg: float = 30.0
+
+    @property
+    def facet_b(self):
+        return float(np.sqrt(2.0 * (self.T_max - self.T_min) / (self.T_max + self.T_min)))
+
+    @property
+    def half_tan(self):
+        return float(np.tan(np.deg2rad(self.gamma_gs_deg)) / 2.0)
+
+
+NXC, NSC = 2 * NX, 2 * NX + NU
+
+
+def glide_normals(y, z):
+    rho = np.sqrt(y * y + z * z)
+    cy, cz = (y / rho, z / rho) if rho > 1e-9 else (1.0, 0.0)
+    c60, s60 = 0.5, 0.8660254037844386
+    return np.array([[c60 * cy - s60 * cz, s60 * cy + c60 * cz], [c60 * cy + s60 * cz, -s60 * cy + c60 * cz], [-cy, -cz]])
+
+
+def cone_values(cone: ConeRows, x, u_prev):
+    b = cone.facet_b
+    n = glide_normals(x[2], x[3])
+    return np.array([u_prev[0] + b * u_prev[1], u_prev[0] - b * u_prev[1], u_prev[0] + b * u_prev[2],
+                     u_prev[0] - b * u_prev[2]] + [(n[i, 0] * x[2] + n[i, 1] * x[3]) - cone.half_tan * x[1] for i in range(3)])
+
+
+def cone_dims(N):
+    n = N * NSC + NXC
+    return n, NXC * (N + 1) + n
+
+
+def augment_cone_qp(N, AB, beq, q, X_nom, U_nom, cone: ConeRows):
+    """Stage data of the 7-state QP -> stage data of the augmented QP with stage variables [x; xi; u] (the arithmetic of
+    qp_augment_cone3_kernel).  AB (N,7,10), beq (7 (N+1),) = [x_init | rhs_0 | ...], q (10 N + 7,)."""
+    n, _ = cone_dims(N)
+    ABc = np.zeros((N, NXC, NSC)); beqc = np.zeros(NXC * (N + 1)); qc = np.zeros(n); zc = np.zeros(n)
+    b, h = cone.facet_b, cone.half_tan
+    beqc[:NX] = beq[:NX]
+    for k in range(N + 1):
+        qc[k * NSC:k * NSC + NX] = q[k * 10:k * 10 + NX]
+        zc[k * NSC:k * NSC + NX] = X_nom[k]
+        if k > 0:
+            zc[k * NSC + NX:k * NSC + NXC] = cone_values(cone, X_nom[k], U_nom[k - 1])
+        if k == N:
+            break
+        qc[k * NSC + NXC:(k + 1) * NSC] = q[k * 10 + NX:(k + 1) * 10]
+        zc[k * NSC + NXC:(k + 1) * NSC] = U_nom[k]
+        ab, be = AB[k], beq[NX + k * NX:NX + (k + 1) * NX]
+        ABc[k, :NX, :NX] = ab[:, :NX]; ABc[k, :NX, NXC:] = ab[:, NX:]
+        r = NXC + k * NXC
+        beqc[r:r + NX] = be
+        for j, (col, sg) in enumerate(((1, b), (1, -b), (2, b), (2, -b))):
+            ABc[k, NX + j, NXC + 0] = 1.0; ABc[k, NX + j, NXC + col] = sg
+        nrm = glide_normals(X_nom[k + 1][2], X_nom[k + 1][3])
+        for i in range(3):
+            row = (nrm[i, 0] * ab[2] + nrm[i, 1] * ab[3]) - h * ab[1]
+            ABc[k, NX + 4 + i, :NX] = row[:NX]; ABc[k, NX + 4 + i, NXC:] = row[NX:]
+            beqc[r + NX + 4 + i] = (nrm[i, 0] * be[2] + nrm[i, 1] * be[3]) - h * be[1]
+    return ABc, beqc, qc, zc
+
+
+def cone_shared_data(N, cone: ConeRows):
+    """Pdiag, lb, ub of the augmented QP (shared by all scenarios): zero cost and the facet bounds on xi, u_x >= T_min."""
+    n, _ = cone_dims(N)
+    Pd = np.zeros(n); lb = np.full(n, -np.inf); ub = np.full(n, np.inf)
+    umin = U_MIN.copy(); umin[0] = max(umin[0], cone.T_min)
+    xi_hi = np.array([cone.T_max] * 4 + [0.0] * 3)
+    for k in range(N + 1):
+        o = k * NSC
+        Pd[o:o + NX] = Q_DIAG * (10 if k == N else 1)
+        lb[o:o + NX] = X_MIN; ub[o:o + NX] = X_MAX
+        if k > 0:
+            ub[o + NX:o + NXC] = xi_hi
+        if k < N:
+            Pd[o + NXC:o + NSC] = R_DIAG
+            lb[o + NXC:o + NSC] = umin; ub[o + NXC:o + NSC] = U_MAX
+    return Pd, lb, ub
+
+
+def dense_stage_constraints(nx, nu, N, AB, beq, lb, ub):
+    """Row order of osqp_rti.py:260-372 for any stage size: [x_0 = x_init | A_k x_k + B_k u_k - x_{k+1} = rhs_k | l <= I z <= u]."""
+    ns = nx + nu
+    n = N * ns + nx; m = nx * (N + 1) + n
+    A = np.zeros((m, n)); l = np.zeros(m); u = np.zeros(m)
+    A[:nx, :nx] = np.eye(nx)
+    for k in range(N):
+        r = nx + k * nx
+        A[r:r + nx, k * ns:(k + 1) * ns] = AB[k]
+        A[r:r + nx, (k + 1) * ns:(k + 1) * ns + nx] = -np.eye(nx)
+    neq = nx * (N + 1)
+    l[:neq] = u[:neq] = beq
+    A[neq:, :] = np.eye(n)
+    l[neq:] = lb; u[neq:] = ub
+    return A, l, u
+
+
+def cone_direct_rows(N, X_nom, cone: ConeRows):
+    """The same polyhedral constraints written directly as inequality rows on z = [x_0,u_0,...,x_N] of the 7-state QP
+    (no auxiliary variables): used by the tests to check that the stage embedding solves the same problem."""
+    n, _ = qp_dims(N)
+    b, h = cone.facet_b, cone.half_tan
+    C = np.zeros((7 * N, n)); hi = np.zeros(7 * N)
+    for k in range(N):
+        for j, (col, sg) in enumerate(((1, b), (1, -b), (2, b), (2, -b))):
+            C[7 * k + j, k * 10 + NX] = 1.0; C[7 * k + j, k * 10 + NX + col] = sg
+            hi[7 * k + j] = cone.T_max
+        nrm = glide_normals(X_nom[k + 1][2], X_nom[k + 1][3])
+        o = (k + 1) * 10
+        for i in range(3):
+            C[7 * k + 4 + i, o + 1] = -h; C[7 * k + 4 + i, o + 2] = nrm[i, 0]; C[7 * k + 4 + i, o + 3] = nrm[i, 1]
+    return C, hi
 
 
 # --------------------------------------------------------------------------- Monte Carlo sampling

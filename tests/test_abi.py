@@ -37,7 +37,7 @@ def test_struct_layouts_match_header():
     assert ctypes.sizeof(_lib.ExactModel) == lay(3, -1)
     assert ctypes.sizeof(_lib.Solve3) == lay(0, -1)
     for i, f in enumerate(("dyn", "admm", "model", "Linv", "x0", "Ks", "q_pad", "var_work", "U_warm", "events",
-                           "event_count")):
+                           "event_count", "cone", "Pdiag_c")):
         assert getattr(_lib.Solve3, f).offset == lay(0, i), f
     assert ctypes.sizeof(_lib.Safety3) == lay(4, -1)
     for i, f in enumerate(("lr", "K", "u_max")):
