@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--qp-max-iter", type=int, default=1000)
     ap.add_argument("--cpu-scenarios", type=int, default=0, help="reference arm: scenarios per step (default: #cores)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--convex-rows", action="store_true",
+                    help="solve the QP with the polyhedral thrust-cone / glide-slope rows (GPMPCConfig.convex_constraints)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--admm-variant", type=int, default=0, help="GpmpcAdmmSettings.kernel_variant (0 newest, 2 / 1 older)")
     ap.add_argument("--no-extra", action="store_true", help="skip the short S=10 / config-3 / config-4 lines")
@@ -243,8 +245,13 @@ def build_problem(args, rank):
     gp.fit()
     dyn = Rocket3DoFDynamics()
     cfg = GPMPCConfig(N=N_HORIZON, dt=DT, max_sqp_iter=args.sqp_iters, qp_max_iter=args.qp_max_iter,
-                      qp_kernel_variant=int(getattr(args, "admm_variant", 0)))
-    ctl = GPMPC(dyn, gp, cfg)
+                      qp_kernel_variant=int(getattr(args, "admm_variant", 0)),
+                      convex_constraints=bool(getattr(args, "convex_rows", False)))
+    cp = None
+    if getattr(args, "gamma_gs", None):
+        from gp_mpc_rocket_landing_b200.mpc import ConstraintParams
+        cp = ConstraintParams(gamma_gs=float(args.gamma_gs))
+    ctl = GPMPC(dyn, gp, cfg, constraint_params=cp)
     ctl.setup()
     # the reference's loop for a `.solve` controller (per-step target, monte_carlo.py:497-499); a failed SQP step-size
     # test is counted, not fatal (an RTI with S = 1 never meets it; `--fail-policy divergence` = monte_carlo.py:507-510)
@@ -537,6 +544,32 @@ def run_extras(args, torch):
         torch.cuda.empty_cache()
     except Exception as e:  # noqa: BLE001
         out["sqp10"] = {"error": repr(e)}
+    try:
+        import copy
+        ac = copy.copy(args)
+        ac.convex_rows = True
+        dyn, gp, ctl, mc = build_problem(ac, 0)
+        for _ in range(3):
+            mc.step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 10
+        mc.counts.zero_()
+        e0.record()
+        for _ in range(n):
+            mc.step()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        c = mc.counts.cpu().numpy()
+        out["convex_rows"] = {"config": "same workload, QP with the polyhedral thrust-cone / glide-slope rows of gp_mpc.py:417-429 "
+                                        "(augmented stage form n = 354, m = 648; DESIGN.md 11g)",
+                              "ms_per_step": ms, "solves_per_s": args.batch / (ms * 1e-3),
+                              "mean_admm_iters_per_solve": float(c[7]) / max(1.0, float(c[0])),
+                              "launches_per_step": ctl.last_kernel_launches + 1}
+        del dyn, gp, ctl, mc
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        out["convex_rows"] = {"error": repr(e)}
     try:
         sys.path.insert(0, os.path.join(ROOT, "tools"))
         import bench_refit

@@ -1059,37 +1059,30 @@ admm3_kernel(int nbatch, const double* __restrict__ ABg, const double* __restric
 #ifndef ADMM3_SREG
 #define ADMM3_SREG false
 #endif
-template <int NX> struct Shape3 {
-  static constexpr int NSLOT = 2, NTHR = 128, MINB = 3, NFIX = 20;
+// Launch shapes, keyed by (n_x, compiled horizon).  n_x = 14 has two: N = 30 (the 6-DoF step, BASELINE configs[3]) and N = 20
+// (the 3-DoF QP with the 7 convex-row states, GpmpcCone3: 21 x 17 = 357 logical slots on 256 threads x 2).
+template <int NX, int NT> struct Shape3 {
+  static constexpr int NSLOT = 2, NTHR = 128, MINB = 3;
   static constexpr bool SREG = ADMM3_SREG, ABS = true;
 };
-template <> struct Shape3<14> {
-  static constexpr int NSLOT = 3, NTHR = 256, MINB = 1, NFIX = 30;
+template <> struct Shape3<14, 30> {
+  static constexpr int NSLOT = 3, NTHR = 256, MINB = 1;
+  static constexpr bool SREG = false, ABS = false;
+};
+template <> struct Shape3<14, 20> {
+  static constexpr int NSLOT = 2, NTHR = 256, MINB = 1;
   static constexpr bool SREG = false, ABS = false;
 };
 
-}  // namespace
-
-// Scratch doubles per QP that launch_admm3 needs (cumulative scalings, + the scaled stage blocks for the 6-DoF shape).
-template <int NX, int NU>
-size_t admm3_scratch_doubles(int N) {
-  using H = Shape3<NX>;
-  const size_t nv = (size_t)N * (NX + NU) + NX, nm = 2 * nv + (size_t)NX * (N + 1);
-  return nm + (H::ABS ? 0 : (size_t)N * NX * (NX + NU));
-}
-
-// Returns GPMPC_ERR_ARG without launching when the horizon is not the compiled one (the caller falls back to the
-// second-generation kernel).
-template <int NX, int NU>
-int launch_admm3(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag, const double* lb,
-                 const double* ub, const GpmpcAdmmSettings& S, const int* active, double* scratch, double* x, double* y,
-                 double* rho, int* status, int* iters, double* obj, double* pri, double* dua, cudaStream_t stream) {
-  using H = Shape3<NX>;
-  using L = Lay<NX, NU, H::NFIX>;
-  if (N != H::NFIX) return GPMPC_ERR_ARG;
+template <int NX, int NU, int NT>
+int launch_admm3_fixed(int B, const double* AB, const double* beq, const double* q, const double* Pdiag, const double* lb,
+                       const double* ub, const GpmpcAdmmSettings& S, const int* active, double* scratch, double* x, double* y,
+                       double* rho, int* status, int* iters, double* obj, double* pri, double* dua, cudaStream_t stream) {
+  using H = Shape3<NX, NT>;
+  using L = Lay<NX, NU, NT>;
   constexpr size_t smem = L::template smem_doubles<H::ABS>() * sizeof(double);
   static_assert(smem <= 227 * 1024, "shared memory budget exceeded");
-  auto kern = admm3_kernel<NX, NU, H::NFIX, H::NSLOT, H::NTHR, H::MINB, H::SREG, H::ABS>;
+  auto kern = admm3_kernel<NX, NU, NT, H::NSLOT, H::NTHR, H::MINB, H::SREG, H::ABS>;
   static GpmpcPerDevice configured;
   if (!configured.here()) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1099,6 +1092,33 @@ int launch_admm3(int N, int B, const double* AB, const double* beq, const double
   kern<<<B, H::NTHR, smem, stream>>>(B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj, pri,
                                      dua);
   return gpmpc_check_launch("admm3");
+}
+
+}  // namespace
+
+// Scratch doubles per QP that launch_admm3 needs (cumulative scalings, + the scaled stage blocks for the n_x = 14 shapes).
+template <int NX, int NU>
+size_t admm3_scratch_doubles(int N) {
+  const size_t nv = (size_t)N * (NX + NU) + NX, nm = 2 * nv + (size_t)NX * (N + 1);
+  return nm + ((NX == 14) ? (size_t)N * NX * (NX + NU) : 0);
+}
+
+// Returns GPMPC_ERR_ARG without launching when the horizon is not a compiled one (the caller falls back to the
+// second-generation kernel).
+template <int NX, int NU>
+int launch_admm3(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag, const double* lb,
+                 const double* ub, const GpmpcAdmmSettings& S, const int* active, double* scratch, double* x, double* y,
+                 double* rho, int* status, int* iters, double* obj, double* pri, double* dua, cudaStream_t stream) {
+  if (NX == 7 && N == 20)
+    return launch_admm3_fixed<7, NU, 20>(B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj, pri,
+                                         dua, stream);
+  if (NX == 14 && N == 30)
+    return launch_admm3_fixed<14, NU, 30>(B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj,
+                                          pri, dua, stream);
+  if (NX == 14 && N == 20)
+    return launch_admm3_fixed<14, NU, 20>(B, AB, beq, q, Pdiag, lb, ub, S, active, scratch, x, y, rho, status, iters, obj,
+                                          pri, dua, stream);
+  return GPMPC_ERR_ARG;
 }
 
 template size_t admm3_scratch_doubles<7, 3>(int);

@@ -307,7 +307,9 @@ class GPMPC:
                 Pd[o:o + NX] = Qfd if k == N else Qd
                 lb[o:o + NX], ub[o:o + NX] = lb7[o7:o7 + NX], ub7[o7:o7 + NX]
                 if k > 0:
-                    ub[o + NX:o + NXC] = xi_hi
+                    ub[o + NX:o + NX + 4] = xi_hi[:4]
+                if k > 1:      # the position of stage 1 is x_0 + dt v_0: no decision enters its rows (redundant or infeasible)
+                    ub[o + NX + 4:o + NXC] = xi_hi[4:]
                 if k < N:
                     Pd[o + NXC:o + NSC] = Rd
                     lb[o + NXC:o + NSC], ub[o + NXC:o + NSC] = lb7[o7 + NX:o7 + NX + NU], ub7[o7 + NX:o7 + NX + NU]

@@ -300,7 +300,9 @@ int gpmpc_mpc_update_3dof(int B, int N, int mode, const double* z, const int* qp
  *     a square pyramid with its apex at T_max on the axial direction, inside the ball for u_x >= T_min;
  *   - the cone at the NEXT stage, sqrt(y^2 + z^2) <= alt tan(gamma): the pyramid over the triangle inscribed in the circle
  *     with one vertex in the radial direction e of the nominal point,  n_i . (y, z) <= alt tan(gamma) / 2  for the normals
- *     n_i = R(+60 deg) e, R(-60 deg) e, -e  (e = (1, 0) when the nominal point is on the axis).
+ *     n_i = R(+60 deg) e, R(-60 deg) e, -e  (e = (1, 0) when the nominal point is on the axis).  The host leaves the glide
+ *     rows of stage 1 unbounded: x_1 = x_0 + dt v_0 whatever the controls, so they are either redundant or make the QP
+ *     infeasible by the solver tolerance of the previous step.
  * To keep the stage structure the ADMM kernels factorise (block tridiagonal, no extra row type), the 7 row values travel as
  * 7 extra "states":  xi_{k+1} = G_k [x_k; u_k] - g_k  with  -inf < xi <= (T_max x 4, 0 x 3)  as box bounds, i.e. the QP is
  * solved in the stage form (n_x, n_u) = (14, 3) with stage variables [x (7); xi (7); u (3)] and zero cost on xi;

@@ -749,7 +749,9 @@ def cone_shared_data(N, cone: ConeRows):
         Pd[o:o + NX] = Q_DIAG * (10 if k == N else 1)
         lb[o:o + NX] = X_MIN; ub[o:o + NX] = X_MAX
         if k > 0:
-            ub[o + NX:o + NXC] = xi_hi
+            ub[o + NX:o + NX + 4] = xi_hi[:4]
+        if k > 1:          # stage 1's position is x_0 + dt v_0 whatever the controls: its glide rows carry no decision
+            ub[o + NX + 4:o + NXC] = xi_hi[4:]
         if k < N:
             Pd[o + NXC:o + NSC] = R_DIAG
             lb[o + NXC:o + NSC] = umin; ub[o + NXC:o + NSC] = U_MAX
@@ -787,6 +789,8 @@ def cone_direct_rows(N, X_nom, cone: ConeRows):
         o = (k + 1) * 10
         for i in range(3):
             C[7 * k + 4 + i, o + 1] = -h; C[7 * k + 4 + i, o + 2] = nrm[i, 0]; C[7 * k + 4 + i, o + 3] = nrm[i, 1]
+            if k == 0:
+                hi[7 * k + 4 + i] = np.inf
     return C, hi
 
 

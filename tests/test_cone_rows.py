@@ -76,6 +76,7 @@ def test_stage_embedding_solves_the_directly_constrained_qp(seed):
     xi = np.stack([r2.x[k * 17 + 7:k * 17 + 14] for k in range(1, N + 1)])
     np.testing.assert_allclose(xi.ravel(), C @ r1.x, rtol=0, atol=5e-6)
     assert np.sum(np.abs(C @ r1.x - hi) < 1e-5) >= 1
+    assert np.isinf(hi[4:7]).all() and np.isfinite(hi[11:14]).all()      # stage 1 carries no glide rows
     # the warm start the device writes is consistent: xi of the nominal trajectory
     assert np.allclose(zc[17 + 7:17 + 14], ompc.cone_values(cone, X[1], U[0]))
 
@@ -147,12 +148,12 @@ def test_controller_with_convex_rows_matches_oracle_and_satisfies_the_cones():
         assert (qs[feas] == 1).all()
         if step == 0:
             assert qs[2] == -3 and np.isinf(sol.cost.cpu().numpy()[2])     # OSQP_PRIMAL_INFEASIBLE -> nominal kept, cost inf
-        # every scenario: thrust inside the ball and above T_min, positions of stages >= 1 inside the glide-slope cone
+        # every scenario: thrust inside the ball and above T_min, positions of stages >= 2 inside the glide-slope cone
         # (to the OSQP primal tolerance eps_abs + eps_rel max(|Ax|, |z|) with |z| up to the 500 m altitude bound)
         tol = 1e-4 + 1e-4 * 500.0
         nrm = np.linalg.norm(Uo[feas], axis=2)
         assert nrm.max() <= cp.T_max + tol and Uo[feas][:, :, 0].min() >= cp.T_min - tol
-        lat = np.hypot(Xo[feas][:, 1:, 2], Xo[feas][:, 1:, 3]); alt = Xo[feas][:, 1:, 1]
+        lat = np.hypot(Xo[feas][:, 2:, 2], Xo[feas][:, 2:, 3]); alt = Xo[feas][:, 2:, 1]
         assert np.all(lat <= alt * np.tan(cp.gamma_gs_rad) + tol)
         assert nrm.max() > cp.T_max - 0.05          # and the thrust facets do bind
         for b in idx:

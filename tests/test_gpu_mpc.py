@@ -162,7 +162,8 @@ def _random_stage_qp(nx, nu, N, rng):
     return AB, beq, Pd, q, lb, ub, A, l, u
 
 
-@pytest.mark.parametrize("nx,N,variant", [(14, 30, 0), (14, 30, 2), (14, 8, 0), (14, 8, 1), (7, 11, 0), (7, 20, 3)])
+@pytest.mark.parametrize("nx,N,variant", [(14, 30, 0), (14, 30, 2), (14, 20, 0), (14, 20, 2), (14, 8, 0), (14, 8, 1), (7, 11, 0),
+                                          (7, 20, 3)])
 def test_admm_generic_stage_qp(E, nx, N, variant):
     """The solver on random stage-structured QPs of the 6-DoF size (nx = 14, N = 30: BASELINE configs[3]) and on a
     run-time horizon, against the dense CPU restatement: same status / iterations / rho, iterates to 1e-6."""
