@@ -167,6 +167,8 @@ _PROTOS = {
                                  c_dp, c_double, c_double, c_int, c_dp, c_dp]),
     "gpmpc_admm_solve": (c_int, [c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
                                  C.POINTER(AdmmSettings), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
+    "gpmpc_admm_solve_noalloc": (c_int, [c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
+                                         C.POINTER(AdmmSettings), c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_rollout_3dof": (c_int, [C.POINTER(ExactModel), C.POINTER(Dyn3), c_int, c_int, c_dp, c_dp, c_dp, c_dp,
                                    c_dp, c_long, c_dp, c_dp]),
     "gpmpc_gp_mean_points_3dof": (c_int, [C.POINTER(ExactModel), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long, c_dp,

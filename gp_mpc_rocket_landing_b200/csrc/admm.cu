@@ -817,3 +817,52 @@ extern "C" int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, 
   gpmpc_set_error("gpmpc_admm_solve: only (nx,nu) = (7,3) and (14,3) are instantiated");
   return GPMPC_ERR_ARG;
 }
+
+// ---- allocation-free variant ---------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate (CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  The Ruiz-scaling scratch of the stage kernel (n + m doubles
+// per QP) lives in a file-scope device array instead of a stream-ordered allocation; every GPU that loads the library holds
+// its GPMPC_NOALLOC_MAX_DOUBLES x 8 bytes (4.6 MB) until exit.  All calls share the array, so calls that overlap on the GPU
+// (different streams, or two host threads) race on it.  It keeps the previous call's contents; nothing has to start at zero:
+// the kernel writes every scaling entry of a QP (admm_stage.cu, D then E) before it reads it.
+static __device__ __align__(256) double g_noalloc_scratch[GPMPC_NOALLOC_MAX_DOUBLES];
+
+extern "C" int gpmpc_admm_solve_noalloc(int N, int B, const double* AB, const double* beq, const double* q,
+                                        const double* Pdiag, const double* lb, const double* ub,
+                                        const GpmpcAdmmSettings* settings, const int* active, double* x, double* y,
+                                        double* rho, int* status, int* iters, double* obj, double* pri_res, double* dua_res,
+                                        void* stream) {
+  GPMPC_REQUIRE(settings != nullptr, "gpmpc_admm_solve_noalloc: settings is NULL");
+  GPMPC_REQUIRE(N >= 1 && B >= 0, "gpmpc_admm_solve_noalloc: bad N or B");
+  if (B == 0) return GPMPC_OK;
+  constexpr int NX = 7, NU = 3;
+  const size_t nv = (size_t)N * (NX + NU) + NX, nm = 2 * nv + (size_t)NX * (N + 1);  // n + m doubles per QP
+  if (nm * (size_t)B > (size_t)GPMPC_NOALLOC_MAX_DOUBLES) {
+    gpmpc_set_error("gpmpc_admm_solve_noalloc: B x (n + m) exceeds GPMPC_NOALLOC_MAX_DOUBLES (574464 doubles = 1024 QPs at "
+                    "N = 20); split the batch or call gpmpc_admm_solve");
+    return GPMPC_ERR_ARG;
+  }
+  // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that
+  // device current.
+  static double* dev_ptr[GPMPC_MAX_DEVICES] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= GPMPC_MAX_DEVICES) {
+    cudaGetLastError();
+    gpmpc_set_error("gpmpc_admm_solve_noalloc: no current CUDA device");
+    return GPMPC_ERR_CUDA;
+  }
+  if (!dev_ptr[dev]) {
+    double* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) {
+      cudaGetLastError();
+      gpmpc_set_error("gpmpc_admm_solve_noalloc: cudaGetSymbolAddress failed for the static scratch");
+      return GPMPC_ERR_CUDA;
+    }
+    dev_ptr[dev] = ptr;
+  }
+  const int rc = launch_admm_stage<NX, NU>(N, B, AB, beq, q, Pdiag, lb, ub, *settings, active, dev_ptr[dev], x, y, rho, status,
+                                           iters, obj, pri_res, dua_res, (cudaStream_t)stream);
+  if (rc == GPMPC_ERR_ARG) gpmpc_set_error("gpmpc_admm_solve_noalloc: horizon too long for the stage kernel");
+  return rc;
+}

@@ -224,6 +224,21 @@ int gpmpc_admm_solve(int nx, int nu, int N, int B, const double* AB, const doubl
                      const int* active, double* x, double* y, double* rho, int* status, int* iters, double* obj,
                      double* pri_res, double* dua_res, void* stream);
 
+/* Allocation-free variant of gpmpc_admm_solve for (nx, nu) = (7, 3), second-generation (stage) kernel.  It has no counterpart
+ * in the reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  It calls no cudaMalloc / cudaFree / allocating library
+ * routine: the per-QP scaling scratch (n + m doubles, 561 at N = 20) lives in a static device array of
+ * GPMPC_NOALLOC_MAX_DOUBLES doubles (4.6 MB, held by every GPU that loads the library until exit), so B x (n + m) beyond that
+ * -- more than 1024 QPs at N = 20 -- is rejected with GPMPC_ERR_ARG and a message.  Same arguments, results, status codes
+ * and iteration counts as gpmpc_admm_solve with kernel_variant 0 / 2.  All calls share the one array: calls that overlap on
+ * the GPU (different streams or host threads) race; calls ordered on one stream do not.  Nothing in it needs clearing between
+ * calls (the kernel writes every entry before reading it). */
+#define GPMPC_NOALLOC_MAX_DOUBLES 574464
+int gpmpc_admm_solve_noalloc(int N, int B, const double* AB, const double* beq, const double* q, const double* Pdiag,
+                             const double* lb, const double* ub, const GpmpcAdmmSettings* settings, const int* active,
+                             double* x, double* y, double* rho, int* status, int* iters, double* obj, double* pri_res,
+                             double* dua_res, void* stream);
+
 /* GP-augmented horizon rollout for B scenarios (gp_mpc.py:277-281 + _predict_with_gp :139-175, 7-state model):
  * X[b,0]=x0[b]; X[b,k+1] = step(X[b,k],U[b,k]) + [0,0,0,0, d_mean*dt].  Also writes the cross-covariance rows
  * Ks[(b*N+k), :] (consumed by gpmpc_trsm_sumsq for the variances) and dmean (B x N x 3).  model==NULL: nominal. */
