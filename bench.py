@@ -31,6 +31,7 @@ N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
 NCU_TRAFFIC = {"prologue": 2.2e6, "rollout": 740.6e6, "gp_variance": 691.6e6, "cov": 17.7e6, "assemble": 26.8e6,
                "admm": 83.2e6, "update": 18.5e6}       # profiles/r2_step_kernels_full.md (one closed-loop step)
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
+CPU_GP_LEG = None     # which GP code the CPU legs ran (set by cpu_reference_run)
 
 
 def parse_args():
@@ -65,8 +66,11 @@ def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
     threadpool_limits(1)   # one BLAS thread per process: the parallelism is one process per scenario
     from gp_mpc_rocket_landing_b200 import workloads
     from oracle import gp as ogp, mpc as ompc
-    gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
-    gp.X, gp.U, gp.D, gp.fits = fits_blob
+    if fits_blob[0] == "reference":     # the reference's own fitted Simple3DoFGP (oracle/_ref), inherited through fork
+        gp = fits_blob[1]
+    else:
+        gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
+        gp.X, gp.U, gp.D, gp.fits = fits_blob[1]
     ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
                            max_sqp_iter=sqp_iters)
     X0, XT = workloads.sample_initial_conditions(idx, 1)
@@ -98,12 +102,22 @@ def cpu_reference_run(n_scen, warmup, steps, sqp_iters, qp_max_iter):
     Returns (solves/s, wall seconds, cores used)."""
     import multiprocessing as mp
     from gp_mpc_rocket_landing_b200 import workloads
-    from oracle import gp as ogp
+    from oracle import gp as ogp, ref_gp
     X, U, D = workloads.residual_dataset(N_TRAIN, seed=0)
-    gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
-    gp.add_data(X, U, D)
-    gp.fit()
-    blob = (gp.X, gp.U, gp.D, gp.fits)
+    ref = ref_gp.load()
+    if ref is not None:     # GP leg = the reference's own src/gp code (exact_gp.py, structured_gp.py), fitted once here
+        gp = ref.Simple3DoFGP(use_sparse=False, noise_variance=NOISE)
+        gp.add_data(X, U, D)
+        gp.fit()
+        blob = ("reference", gp)
+    else:
+        gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
+        gp.add_data(X, U, D)
+        gp.fit()
+        blob = ("port", (gp.X, gp.U, gp.D, gp.fits))
+    global CPU_GP_LEG
+    CPU_GP_LEG = ("reference src/gp (oracle/_ref: Simple3DoFGP / ExactGP, unmodified)" if ref is not None
+                  else "numpy restatement oracle/gp.py (oracle/_ref absent)")
     ctx = mp.get_context("fork")
     procs = []
     for i in range(n_scen):
@@ -150,7 +164,7 @@ def run_reference_arm(args):
         "cpu_baseline": {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
                          "sample": f"{n_scen} scenarios x {steps} closed-loop control steps, one process per scenario "
                                    "(numpy/scipy oracle of the reference algorithm; the reference's own GPMPC needs "
-                                   "CasADi/IPOPT/simdyn, absent)"},
+                                   "CasADi/IPOPT/simdyn, absent)", "gp_leg": CPU_GP_LEG},
         "e2e": {"value": sps, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -273,7 +287,8 @@ def run_b200_arm(args):
         sps, wall, used = cpu_reference_run(n_scen, 1, 6, args.sqp_iters, args.qp_max_iter)
         cpu_base = {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
                     "sample": f"{n_scen} scenarios x 6 closed-loop control steps of the same workload, one process per "
-                              f"scenario, {wall:.1f} s wall (numpy/scipy oracle of the reference algorithm)"}
+                              f"scenario, {wall:.1f} s wall (numpy/scipy oracle of the reference algorithm)",
+                    "gp_leg": CPU_GP_LEG}
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():

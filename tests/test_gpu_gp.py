@@ -217,6 +217,42 @@ def test_refit_sweep_matches_sequential_fits(eng):
     assert relerr(out["lml"].cpu().numpy()[0, 0], g["jit_lml"]) < 1e-6
 
 
+def test_refit_sweep_config3_n4000_matches_scipy(eng):
+    """BASELINE configs[2] at its measured size: n = 4000, D = 11, P = 3 outputs, the 16-candidate grid of SURVEY 8(d)
+    (shared lengthscale log-uniform in [0.1, 10] x noise in {1e-4 .. 1e-1}) -- the batched device sweep against
+    `scipy.linalg.cholesky` LMLs of exact_gp.py:118-204 (same jitter escalation), candidate by candidate.  Tolerance 1e-7
+    relative: cond(K + noise I) reaches 4e7 at lengthscale 10 / noise 1e-4 (two FP64 factorizations differ by cond x eps)."""
+    import scipy.linalg as sla
+    from gp_mpc_rocket_landing_b200.gp import refit
+    from oracle import gp as ogp
+    n, D, P = 4000, 11, 3
+    rng = np.random.default_rng(1)
+    X = rng.normal(0, 0.4, (n, D))
+    Y = np.stack([np.sin(2 * X[:, 0]) + 0.05 * rng.normal(size=n), X[:, 1] * X[:, 2], np.cos(X[:, 3])], axis=1)
+    ls, sv, nz = refit.default_grid(D)
+    assert ls.shape[0] == 16
+    r = refit.refit_sweep(X, Y, ls, sv, nz, kind=0)
+    Yn = (Y - Y.mean(0)) / Y.std(0)
+    want = np.zeros((16, P)); jit = np.zeros(16)
+    for g in range(16):
+        Kn = ogp.gram(ogp.SE, X, None, ls[g], sv[g]) + nz[g] * np.eye(n)
+        j = 0.0
+        while True:
+            try:
+                L = sla.cholesky(Kn + j * np.eye(n) if j else Kn, lower=True, check_finite=False)
+                break
+            except sla.LinAlgError:
+                j = 1e-6 if j == 0.0 else j * 10
+                assert j < 1.0
+        jit[g] = j
+        A = sla.cho_solve((L, True), Yn, check_finite=False)
+        want[g] = -0.5 * np.einsum("np,np->p", Yn, A) - np.sum(np.log(np.diag(L))) - 0.5 * n * np.log(2 * np.pi)
+    np.testing.assert_array_equal(r["jitter"], jit)
+    np.testing.assert_allclose(r["lml"], want, rtol=1e-7, atol=0)
+    assert r["best_shared"] == int(np.argmax(want.sum(1)))
+    np.testing.assert_array_equal(r["best"], np.argmax(want, axis=0))
+
+
 @pytest.mark.parametrize("n,D,noise,tol", [(300, 5, 1e-2, 1e-9), (1000, 11, 1e-2, 1e-8), (130, 17, 1e-3, 1e-8)])
 def test_lml_gradient_matches_closed_form(eng, n, D, noise, tol):
     """gpmpc_lml_grad_se (all D + 2 components, P outputs on one factor) against the oracle's closed form, which

@@ -253,3 +253,24 @@ def test_monte_carlo_propagation_matches_reference():
                                              o.predict, g["particles0"], g["xi"])
     np.testing.assert_allclose(means, g["means"], rtol=1e-12, atol=1e-13)
     np.testing.assert_allclose(covs, g["covs"], rtol=1e-9, atol=1e-16)
+
+
+def test_reference_gp_package_under_oracle_ref_agrees_with_the_restatement():
+    """oracle/_ref (placed by oracle/make_ref.py from /root/reference/src/gp; travels to the GPU box, never committed) is the
+    GP leg of bench.py's CPU arms: the reference's own Simple3DoFGP and the numpy restatement give the same predictions
+    on the bench fixture (bit-compatible operation order; the 1e-4 noise fixture has cond 9e6, hence 1e-8)."""
+    from oracle import ref_gp
+    from gp_mpc_rocket_landing_b200 import workloads
+    ref = ref_gp.load()
+    if ref is None:
+        pytest.skip("oracle/_ref is absent (run python oracle/make_ref.py where /root/reference exists)")
+    X, U, D = workloads.residual_dataset(300, seed=0)
+    g = ref.Simple3DoFGP(use_sparse=False, noise_variance=1e-4); g.add_data(X, U, D); g.fit()
+    o = ogp.Simple3DoFGPOracle(noise_variance=1e-4); o.add_data(X, U, D); o.fit()
+    rng = np.random.default_rng(5)
+    for _ in range(5):
+        x = np.array([2.0, 30, 0, 0, -3, 0, 0]) + rng.normal(size=7) * [0.1, 5, 2, 2, 1, 0.3, 0.3]
+        u = np.array([2.0, 0, 0]) + 0.3 * rng.normal(size=3)
+        (m1, v1), (m2, v2) = g.predict(x, u), o.predict(x, u)
+        np.testing.assert_allclose(m1, m2, rtol=1e-8, atol=1e-12)
+        np.testing.assert_allclose(v1, v2, rtol=1e-8, atol=1e-14)
