@@ -31,6 +31,13 @@ def main():
     ap.add_argument("--max-steps", type=int, default=None)
     ap.add_argument("--drag-cda", type=float, default=0.25)
     ap.add_argument("--rebroadcast-every", type=int, default=0, help="broadcast GP hyper-parameters every K steps")
+    ap.add_argument("--sqp-iters", type=int, default=1, help="SQP iterations per solve (1 = RTI; gp_mpc.py:293 uses 10)")
+    ap.add_argument("--target-mode", default=None, choices=["per_step", "fixed"],
+                    help="default: what monte_carlo.py:492-510 does for the controller type (`.solve` -> per_step)")
+    ap.add_argument("--on-solve-failure", default="continue", choices=["continue", "divergence"],
+                    help="divergence = monte_carlo.py:507-510 (with an RTI every run then ends at step 0, DESIGN 5b)")
+    ap.add_argument("--convex-rows", action="store_true", help="thrust-cone / glide-slope rows in the QP (DESIGN 11g)")
+    ap.add_argument("--safety-filter", action="store_true", help="predictive safety filter on u0 (monte_carlo.py:519-525)")
     a = ap.parse_args()
 
     from gp_mpc_rocket_landing_b200 import distributed as D, workloads
@@ -52,8 +59,16 @@ def main():
     if a.controller == "rti":
         ctl = FastRTI3DoF(dyn, OSQPRTIConfig(N=a.horizon, dt=0.1, osqp_max_iter=1000))
     else:
-        ctl = GPMPC(dyn, gp, GPMPCConfig(N=a.horizon, dt=0.1, max_sqp_iter=1, qp_max_iter=1000))
-    mc = BatchedMonteCarlo(dyn, ctl, drag_cda=a.drag_cda)
+        ctl = GPMPC(dyn, gp, GPMPCConfig(N=a.horizon, dt=0.1, max_sqp_iter=a.sqp_iters, qp_max_iter=1000,
+                                         convex_constraints=a.convex_rows))
+    filt = None
+    if a.safety_filter:
+        from gp_mpc_rocket_landing_b200.safety import PredictiveSafetyFilter, SafetyFilterConfig
+        filt = PredictiveSafetyFilter(dyn, SafetyFilterConfig(N=10, dt=0.1))
+        p = dyn.params
+        filt.initialize(np.array([1.5, 0.5, 0, 0, 0, 0, 0.0]), np.array([1.5 * p.g0, 0, 0.0]), backup_alpha=50.0)
+    mc = BatchedMonteCarlo(dyn, ctl, drag_cda=a.drag_cda, target_mode=a.target_mode,
+                           on_solve_failure=None if a.controller == "rti" else a.on_solve_failure, safety_filter=filt)
     mc.reset(shard.first, shard.count, a.seed)
     limit = mc.max_steps if a.max_steps is None else a.max_steps
     t0 = time.perf_counter()
