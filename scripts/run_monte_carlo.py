@@ -64,7 +64,8 @@ def main():
     filt = None
     if a.safety_filter:
         from gp_mpc_rocket_landing_b200.safety import PredictiveSafetyFilter, SafetyFilterConfig
-        filt = PredictiveSafetyFilter(dyn, SafetyFilterConfig(N=10, dt=0.1))
+        from gp_mpc_rocket_landing_b200.mpc import ConstraintParams
+        filt = PredictiveSafetyFilter(dyn, SafetyFilterConfig(N=10, dt=0.1), constraint_params=ConstraintParams())
         p = dyn.params
         filt.initialize(np.array([1.5, 0.5, 0, 0, 0, 0, 0.0]), np.array([1.5 * p.g0, 0, 0.0]), backup_alpha=50.0)
     mc = BatchedMonteCarlo(dyn, ctl, drag_cda=a.drag_cda, target_mode=a.target_mode,
