@@ -21,6 +21,8 @@ sys.dont_write_bytecode = True
 
 import numpy as np
 
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))   # `from oracle import ...` below
+
 REF = "/root/reference/src"
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
 
@@ -128,6 +130,170 @@ def mc_loop_fixture(save):
     print("   mc_loop outcomes (.solve):", np.bincount(out["solve_outcome"], minlength=7)[1:],
           "(.step):", np.bincount(out["step_outcome"], minlength=7)[1:])
     save("mc_loop.npz", **out)
+
+
+def rti_loop_fixture(save):
+    """13. the reference's own RTI orchestration (osqp_rti.py:403-599: initialize / prepare / feedback / step, the status
+    handling and fall-back of :532-552, the shifted warm start) run END TO END in closed loop, with the absent `osqp` module
+    replaced by a solver-backed stand-in: `osqp.OSQP` = a thin adapter that hands the reference's setup / update / warm_start
+    / solve calls to oracle.mpc.OSQPOracle and answers with OSQP 0.6's result object (x, y, info.status strings, info.iter,
+    info.obj_val).  What this pins is everything AROUND the solver: which matrices the reference builds at every step, what
+    it warm-starts from, what it does with each status -- the solver itself stays the restatement ("parity unpinned").
+    `update(Ax=A.data)` carries only the values; the reference's sparsity pattern changes when a filtered entry (|a| <= 1e-10,
+    :301,309) becomes non-zero, which real OSQP would reject -- the adapter reads the matrix the reference just built from
+    an instrumented `_build_constraint_matrix`, i.e. behaves like a solver that is set up again on a pattern change."""
+    import src.mpc.osqp_rti as R
+    from oracle import mpc as ompc
+    from oracle.mpc import EulerDynamics
+
+    STATUS = {ompc.SOLVED: "solved", ompc.SOLVED_INACCURATE: "solved inaccurate", ompc.MAX_ITER: "maximum iterations reached",
+              ompc.PRIMAL_INFEASIBLE: "primal infeasible", ompc.PRIMAL_INFEASIBLE_INACCURATE: "primal infeasible inaccurate",
+              ompc.DUAL_INFEASIBLE: "dual infeasible", ompc.DUAL_INFEASIBLE_INACCURATE: "dual infeasible inaccurate"}
+    last_A = {}
+
+    class Adapter:
+        def setup(self, P, q, A, l, u, **kw):
+            st = ompc.OSQPSettings(max_iter=kw["max_iter"], eps_abs=kw["eps_abs"], eps_rel=kw["eps_rel"],
+                                   scaling=kw["scaling"], warm_start=kw["warm_start"])
+            self.o = ompc.OSQPOracle(np.asarray(P.todense()).diagonal().copy(), np.asarray(q, float), A.toarray(), l, u, st)
+
+        def update(self, q=None, l=None, u=None, Ax=None):
+            A = None
+            if Ax is not None:
+                A = last_A["A"].toarray()
+                assert np.array_equal(last_A["A"].data, Ax)
+            self.o.update(q=q, l=l, u=u, A=A)
+
+        def warm_start(self, x=None, y=None):
+            self.o.warm_start(x=x, y=y)
+
+        def solve(self):
+            r = self.o.solve()
+            info = types.SimpleNamespace(status=STATUS[r.status], iter=r.iters, obj_val=r.obj_val, status_val=r.status)
+            return types.SimpleNamespace(x=r.x, y=r.y, info=info)
+
+    stub = sys.modules["osqp"].OSQP
+    sys.modules["osqp"].OSQP = Adapter
+    out = {}
+    try:
+        cases = (("vertical_it50", [2.0, 30, 0, 0, -3, 0, 0], 50), ("lateral_it1000", [2.0, 30, 3, -2, -3, 0.5, 0.2], 1000),
+                 ("readme_infeasible_it1000", [2.0, 500, 50, 0, -75, 10, 0], 1000))
+        for tag, x0, max_iter in cases:
+            x0 = np.array(x0, float)
+            xt = np.array([x0[0], 0, 0, 0, 0, 0, 0.0])
+            dyn = EulerDynamics()
+            ctl = R.FastRTI3DoF(dyn, R.OSQPRTIConfig(N=20, osqp_max_iter=max_iter))
+            orig = ctl._build_constraint_matrix
+
+            def rec(X, U, x, _orig=orig):
+                A, l, u = _orig(X, U, x)
+                last_A["A"] = A
+                return A, l, u
+
+            ctl._build_constraint_matrix = rec
+            ctl.initialize(x0, xt)
+            x = x0.copy()
+            rows = {k: [] for k in ("x", "u0", "X_opt", "U_opt", "cost", "iters", "success", "nnzA")}
+            for _ in range(6):
+                sol = ctl.step(x)
+                rows["x"].append(x.copy()); rows["u0"].append(np.array(sol.u0, float)); rows["X_opt"].append(np.array(sol.X_opt))
+                rows["U_opt"].append(np.array(sol.U_opt)); rows["cost"].append(float(sol.cost))
+                rows["iters"].append(int(sol.osqp_iterations)); rows["success"].append(bool(sol.success))
+                rows["nnzA"].append(int(last_A["A"].nnz))
+                x = dyn.step(x, sol.u0, 0.1)
+            for k, v in rows.items():
+                out[f"{tag}_{k}"] = np.array(v)
+            out[f"{tag}_x0"] = x0; out[f"{tag}_xt"] = xt; out[f"{tag}_max_iter"] = max_iter
+            print("rti_loop", tag, rows["success"], rows["iters"], rows["nnzA"])
+    finally:
+        sys.modules["osqp"].OSQP = stub
+    save("rti_loop.npz", **out)
+
+
+def gpmpc_skeleton_fixture(G, save):
+    """14. the reference's own `GPMPC.solve` (gp_mpc.py:229-369) -- initial controls, GP-augmented rollout, uncertainty
+    propagation, per-iteration linearisation list and affine GP terms, the step-size convergence test, warm-start store,
+    `success` / `iterations` / `status` -- run over three consecutive control steps, with ONLY `_solve_qp` (the CasADi/IPOPT
+    sub-problem, absent) replaced: the replacement receives exactly what the reference passes (x0, x_target, X_nom, U_nom,
+    A_list, B_list, c_list, ...) and solves the OSQP-form QP of `north_star` (osqp_rti.py cost and box, deviation-form
+    dynamics rows of gp_mpc.py:402-411 written in absolute variables) with oracle.mpc.OSQPOracle.  `casadi` is an empty
+    stub module so that the reference's modules import.  7-state model inside the reference's 14-state arrays."""
+    sys.modules.setdefault("casadi", types.ModuleType("casadi"))
+    import src.mpc.gp_mpc as GM
+    from oracle import mpc as ompc
+    from oracle.mpc import Rocket3DoFParams, linearize_3dof, step_3dof
+    X, U, Dres = gp_fixture(300, 21)
+    gp = G.Simple3DoFGP(use_sparse=False, noise_variance=1e-3); gp.add_data(X, U, Dres); gp.fit()
+    p = Rocket3DoFParams()
+    N, dt = 20, 0.1
+
+    class Dyn14:
+        params = p
+
+        def step(self, x, u, dt):
+            xn = x.copy(); xn[:7] = step_3dof(x[:7], u, dt, p); return xn
+
+        def linearize(self, x, u, dt=None):
+            A = np.eye(14); B = np.zeros((14, 3)); A[:7, :7], B[:7] = linearize_3dof(x[:7], u, dt, p); return A, B
+
+    class GP14:
+        def predict(self, x, u):
+            m, v = gp.predict(x[:7], u); return m, np.zeros(3), v, np.zeros(3)
+
+    log = []
+    state = {"y": None, "rho": None}
+
+    def solve_qp(x0, x_target, X_nom, U_nom, A_list, B_list, c_list, uncertainty, X_ref, U_ref):
+        n, m = ompc.qp_dims(N)
+        x_ref = np.tile(x_target[:7], (N + 1, 1)) if X_ref is None else X_ref[:N + 1, :7]
+        Pd, q = ompc.build_cost(N, x_ref)
+        A = np.zeros((m, n)); l = np.zeros(m); u = np.zeros(m)
+        A[:7, :7] = np.eye(7); l[:7] = u[:7] = x0[:7]
+        row, idx = 7, 0
+        for k in range(N):
+            Ak, Bk, ck = A_list[k][:7, :7], B_list[k][:7], c_list[k][:7]
+            A[row:row + 7, idx:idx + 7] = np.where(np.abs(Ak) > 1e-10, Ak, 0.0)
+            A[row:row + 7, idx + 7:idx + 10] = np.where(np.abs(Bk) > 1e-10, Bk, 0.0)
+            A[row:row + 7, idx + 10:idx + 17] = -np.eye(7)
+            l[row:row + 7] = u[row:row + 7] = -(X_nom[k + 1, :7] - Ak @ X_nom[k, :7] - Bk @ U_nom[k] + ck)
+            row += 7; idx += 10
+        A[row:, :] = np.eye(n)
+        lo = np.concatenate([np.tile(np.concatenate([ompc.X_MIN, ompc.U_MIN]), N), ompc.X_MIN])
+        hi = np.concatenate([np.tile(np.concatenate([ompc.X_MAX, ompc.U_MAX]), N), ompc.X_MAX])
+        l[row:] = lo; u[row:] = hi
+        qp = ompc.OSQPOracle(Pd, q, A, l, u, ompc.OSQPSettings(max_iter=1000))
+        if state["rho"] is not None:          # one solver object per controller: its adapted rho and duals persist
+            qp.rho = state["rho"]; qp._set_rho_vec(); qp._factor()
+        qp.warm_start(x=ompc.traj_to_vec(X_nom[:, :7], U_nom), y=state["y"])
+        r = qp.solve()
+        state["rho"] = r.rho
+        log.append((r.status, r.iters))
+        if r.status != ompc.SOLVED:            # gp_mpc.py:478-482: nominal trajectory, cost = inf
+            return X_nom, U_nom, np.inf
+        state["y"] = r.y
+        Xs, Us = ompc.vec_to_traj(r.x, N)
+        X_new = X_nom.copy(); X_new[:, :7] = Xs
+        cost = float(np.sum(ompc.Q_DIAG * (Xs[:N] - x_ref[:N]) ** 2) + np.sum(ompc.R_DIAG * Us**2)
+                     + np.sum(10 * ompc.Q_DIAG * (Xs[N] - x_ref[N]) ** 2))
+        return X_new, Us, cost
+
+    ctl = GM.GPMPC(Dyn14(), GP14(), GM.GPMPCConfig(N=N, dt=dt))
+    ctl._solve_qp = solve_qp
+    ctl.setup()
+    x = np.zeros(14); x[:7] = [1.9, 28, 2.0, -1.5, -3.1, 0.2, -0.1]; x[7] = 1.0
+    U_ref = np.tile([x[0] * p.g0, 0.0, 0.0], (N, 1))       # hover along the 3-DoF "up" axis for the first call (:268-269)
+    out = {k: [] for k in ("x", "xt", "success", "iterations", "X_opt", "U_opt", "cost", "qp_n")}
+    for step in range(3):
+        xt = x.copy(); xt[4:7] = 0; xt[1] = max(0.5, x[1] - 2.0)         # monte_carlo.py:497-499
+        n0 = len(log)
+        sol = ctl.solve(x, xt, U_ref=U_ref)
+        out["x"].append(x[:7].copy()); out["xt"].append(xt[:7].copy()); out["success"].append(bool(sol.success))
+        out["iterations"].append(int(sol.iterations)); out["X_opt"].append(sol.X_opt[:, :7].copy())
+        out["U_opt"].append(sol.U_opt.copy()); out["cost"].append(float(sol.cost)); out["qp_n"].append(len(log) - n0)
+        print("gpmpc_skeleton", step, sol.success, sol.iterations, sol.status, log[n0:])
+        x = Dyn14().step(x, sol.U_opt[0], dt)
+    save("gpmpc_skeleton.npz", X=X, U=U, D=Dres, noise=1e-3, U_ref=U_ref, qp_status=np.array([s for s, _ in log]),
+         qp_iters=np.array([i for _, i in log]), **{k: np.array(v) for k, v in out.items()})
 
 
 def safety_fixture(save):
@@ -316,6 +482,12 @@ def main():
     save = lambda name, **kw: np.savez_compressed(os.path.join(OUT, name), **kw)
     if "--only-online" in sys.argv:   # add the newest fixture without rewriting the others
         online_fixture(G, save)
+        return
+    if "--only-rti-loop" in sys.argv:
+        rti_loop_fixture(save)
+        return
+    if "--only-gpmpc-skeleton" in sys.argv:
+        gpmpc_skeleton_fixture(G, save)
         return
     if "--only-unscented" in sys.argv:
         unscented_fixture(G, save)
@@ -524,8 +696,10 @@ def main():
     online_fixture(G, save)
     unscented_fixture(G, save)
     mc_loop_fixture(save)
+    rti_loop_fixture(save)
     safety_fixture(save)
     mc_propagation_fixture(G, save)
+    gpmpc_skeleton_fixture(G, save)
     print("golden fixtures written to", os.path.abspath(OUT))
     for f in sorted(os.listdir(OUT)):
         print(f"  {f}: {os.path.getsize(os.path.join(OUT, f)) / 1024:.1f} KiB")

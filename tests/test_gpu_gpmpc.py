@@ -113,6 +113,61 @@ def test_osqp_rti_step_matches_oracle(setup):
     assert s.u0.shape == (3,) and s.X_opt.shape == (16, 7) and isinstance(s.success, bool)
 
 
+def test_rti_closed_loop_matches_the_reference_orchestration(setup):
+    """a22 on the device: `FastRTI3DoF.step_batch` fed the states of tests/golden/rti_loop.npz -- the reference's own
+    FastRTI3DoF.step loop around a solver-backed `osqp` stand-in -- takes the same branch at every step (max-iter fall-back
+    on the first step at max_iter 50, pattern growth 654 -> 734 non-zeros absorbed by the fixed superset pattern, primal
+    infeasible README state falling back at every step), the same ADMM iteration counts, and returns the same controls /
+    trajectories to the ADMM tolerance."""
+    from conftest import load_golden
+    from gp_mpc_rocket_landing_b200.mpc import FastRTI3DoF, OSQPRTIConfig
+    dyn, _, _ = setup
+    g = load_golden("rti_loop.npz")
+    for tags in (("vertical_it50",), ("lateral_it1000", "readme_infeasible_it1000")):
+        mi = int(g[f"{tags[0]}_max_iter"])
+        ctl = FastRTI3DoF(dyn, OSQPRTIConfig(N=20, osqp_max_iter=mi))
+        ctl.initialize_batch(np.stack([g[f"{t}_x0"] for t in tags]), np.stack([g[f"{t}_xt"] for t in tags]))
+        for k in range(6):
+            sol = ctl.step_batch(np.stack([g[f"{t}_x"][k] for t in tags]))
+            for b, t in enumerate(tags):
+                assert bool(sol.success[b]) == bool(g[f"{t}_success"][k]), (t, k)
+                assert int(sol.osqp_iterations[b]) == int(g[f"{t}_iters"][k]), (t, k)
+                np.testing.assert_allclose(sol.u0[b], g[f"{t}_u0"][k], rtol=0, atol=2e-5)
+                np.testing.assert_allclose(sol.X_opt[b], g[f"{t}_X_opt"][k], rtol=0, atol=5e-5)
+                np.testing.assert_allclose(sol.U_opt[b], g[f"{t}_U_opt"][k], rtol=0, atol=5e-5)
+                assert np.isinf(sol.cost[b]) == np.isinf(g[f"{t}_cost"][k])
+                if np.isfinite(sol.cost[b]):
+                    assert sol.cost[b] == pytest.approx(float(g[f"{t}_cost"][k]), rel=1e-4, abs=1e-3)
+
+
+def test_gpmpc_solve_matches_the_reference_sqp_skeleton():
+    """a17 on the device: tests/golden/gpmpc_skeleton.npz is the reference's own `GPMPC.solve` loop (only `_solve_qp` replaced
+    by the OSQP-form QP, see oracle/gen_golden.py) over three consecutive control steps with the warm start carried.  The
+    device controller with the reference's 10 SQP iterations takes the same path: no convergence (`success` False, 10
+    iterations), the same total ADMM iteration count per solve, the same trajectories to the ADMM tolerance."""
+    from conftest import load_golden
+    from gp_mpc_rocket_landing_b200.dynamics import Rocket3DoFDynamics
+    from gp_mpc_rocket_landing_b200.gp import Simple3DoFGP
+    from gp_mpc_rocket_landing_b200.mpc import GPMPC, GPMPCConfig
+    g = load_golden("gpmpc_skeleton.npz")
+    gp = Simple3DoFGP(noise_variance=float(g["noise"]), use_sparse=False)
+    gp.add_data(g["X"], g["U"], g["D"]); gp.fit()
+    ctl = GPMPC(Rocket3DoFDynamics(), gp, GPMPCConfig(N=20, dt=0.1, max_sqp_iter=10, qp_max_iter=1000))
+    ctl.setup()
+    k0 = 0
+    for s in range(3):
+        sol = ctl.solve(g["x"][s], g["xt"][s], U_ref=g["U_ref"])
+        n = int(g["qp_n"][s])
+        assert sol.success == bool(g["success"][s]) and sol.iterations == int(g["iterations"][s])
+        assert sol.status == "Max iterations"
+        b = ctl._single
+        assert int(b.qp_iters[0].item()) == int(g["qp_iters"][k0:k0 + n].sum())
+        k0 += n
+        np.testing.assert_allclose(sol.U_opt, g["U_opt"][s], rtol=0, atol=2e-5)
+        np.testing.assert_allclose(sol.X_opt, g["X_opt"][s], rtol=0, atol=2e-5)
+        assert sol.cost == pytest.approx(float(g["cost"][s]), rel=1e-5)
+
+
 def test_per_stage_bound_tightening_extension(setup):
     """GPMPCConfig.tighten_state_bounds (extension; the reference prepares the tightening from Sigma_k and applies it at
     k = 0 only, gp_mpc.py:177-215,414): per-scenario boxes lb + kappa sqrt(diag Sigma_k), ub - kappa sqrt(diag Sigma_k) for

@@ -274,3 +274,49 @@ def test_reference_gp_package_under_oracle_ref_agrees_with_the_restatement():
         (m1, v1), (m2, v2) = g.predict(x, u), o.predict(x, u)
         np.testing.assert_allclose(m1, m2, rtol=1e-8, atol=1e-12)
         np.testing.assert_allclose(v1, v2, rtol=1e-8, atol=1e-14)
+
+
+@pytest.mark.parametrize("tag", ["vertical_it50", "lateral_it1000", "readme_infeasible_it1000"])
+def test_rti_orchestration_matches_the_reference_closed_loop(tag):
+    """a22: the reference's own FastRTI3DoF.step loop (osqp_rti.py:403-599) run in closed loop around a solver-backed stand-in
+    for `osqp` (oracle/gen_golden.py::rti_loop_fixture) -- first step at max_iter 50 falls back to the previous trajectory,
+    a lateral scenario whose sparsity pattern grows from 654 to 734 non-zeros, and the README initial state whose QP is
+    primal infeasible at every step (:545-552 fall-back).  `OSQPRTIOracle` must take the same branches with the same iterates."""
+    g = load_golden("rti_loop.npz")
+    oc = ompc.OSQPRTIOracle(ompc.Rocket3DoFParams(), N=20, dt=0.1, lin="analytic",
+                            settings=ompc.OSQPSettings(max_iter=int(g[f"{tag}_max_iter"])))
+    oc.initialize(g[f"{tag}_x0"], g[f"{tag}_xt"])
+    for k in range(6):
+        r = oc.step(g[f"{tag}_x"][k])
+        assert r.success == bool(g[f"{tag}_success"][k]) and r.osqp_iterations == int(g[f"{tag}_iters"][k]), (tag, k)
+        np.testing.assert_allclose(r.u0, g[f"{tag}_u0"][k], rtol=0, atol=1e-11)
+        np.testing.assert_allclose(r.X_opt, g[f"{tag}_X_opt"][k], rtol=0, atol=1e-10)
+        np.testing.assert_allclose(r.U_opt, g[f"{tag}_U_opt"][k], rtol=0, atol=1e-10)
+        if r.success:
+            assert r.cost == pytest.approx(float(g[f"{tag}_cost"][k]), rel=1e-10)
+        else:
+            assert np.isinf(g[f"{tag}_cost"][k]) and np.isinf(r.cost)
+    if tag == "lateral_it1000":
+        assert g[f"{tag}_nnzA"].tolist() == [654] + [734] * 5
+
+
+def test_gpmpc_sqp_skeleton_matches_the_reference_solve():
+    """a17: the reference's own `GPMPC.solve` (gp_mpc.py:229-369) over three consecutive control steps with only `_solve_qp`
+    (CasADi/IPOPT, absent) replaced by the OSQP-form QP built from the A / B / c lists the reference hands over
+    (oracle/gen_golden.py::gpmpc_skeleton_fixture).  `GPMPCOracle` must produce the same sequence: 10 SQP iterations without
+    meeting the 1e-4 step-size test (`success` False, as the reference), the same QP status / iteration count at each of
+    the 30 QPs, the same iterates."""
+    g = load_golden("gpmpc_skeleton.npz")
+    o = ogp.Simple3DoFGPOracle(noise_variance=float(g["noise"])); o.add_data(g["X"], g["U"], g["D"]); o.fit()
+    ctl = ompc.GPMPCOracle(o.predict, N=20, dt=0.1, settings=ompc.OSQPSettings(max_iter=1000), max_sqp_iter=10)
+    k0 = 0
+    for s in range(3):
+        r = ctl.solve(g["x"][s], g["xt"][s])
+        n = int(g["qp_n"][s])
+        assert r.success == bool(g["success"][s]) and r.iterations == int(g["iterations"][s]) == n
+        assert list(r.qp_status) == g["qp_status"][k0:k0 + n].tolist()
+        assert list(r.qp_iters) == g["qp_iters"][k0:k0 + n].tolist()
+        k0 += n
+        np.testing.assert_allclose(r.U_opt, g["U_opt"][s], rtol=0, atol=1e-8)
+        np.testing.assert_allclose(r.X_opt, g["X_opt"][s], rtol=0, atol=1e-8)
+        assert r.cost == pytest.approx(float(g["cost"][s]), rel=1e-9)
