@@ -241,6 +241,7 @@ def gpmpc_skeleton_fixture(G, save):
             m, v = gp.predict(x[:7], u); return m, np.zeros(3), v, np.zeros(3)
 
     log = []
+    first = {}
     state = {"y": None, "rho": None}
 
     def solve_qp(x0, x_target, X_nom, U_nom, A_list, B_list, c_list, uncertainty, X_ref, U_ref):
@@ -261,6 +262,10 @@ def gpmpc_skeleton_fixture(G, save):
         lo = np.concatenate([np.tile(np.concatenate([ompc.X_MIN, ompc.U_MIN]), N), ompc.X_MIN])
         hi = np.concatenate([np.tile(np.concatenate([ompc.X_MAX, ompc.U_MAX]), N), ompc.X_MAX])
         l[row:] = lo; u[row:] = hi
+        if "qp0_A" not in first:               # the first sub-problem as the reference's arguments define it (a18)
+            first.update(qp0_A=A.copy(), qp0_l=l.copy(), qp0_u=u.copy(), qp0_q=q.copy(), qp0_Pd=Pd.copy(),
+                         qp0_X=X_nom[:, :7].copy(), qp0_U=U_nom.copy(), qp0_c=np.stack([c[:7] for c in c_list]),
+                         qp0_x0=x0[:7].copy(), qp0_xref=x_ref.copy())
         qp = ompc.OSQPOracle(Pd, q, A, l, u, ompc.OSQPSettings(max_iter=1000))
         if state["rho"] is not None:          # one solver object per controller: its adapted rho and duals persist
             qp.rho = state["rho"]; qp._set_rho_vec(); qp._factor()
@@ -293,7 +298,7 @@ def gpmpc_skeleton_fixture(G, save):
         print("gpmpc_skeleton", step, sol.success, sol.iterations, sol.status, log[n0:])
         x = Dyn14().step(x, sol.U_opt[0], dt)
     save("gpmpc_skeleton.npz", X=X, U=U, D=Dres, noise=1e-3, U_ref=U_ref, qp_status=np.array([s for s, _ in log]),
-         qp_iters=np.array([i for _, i in log]), **{k: np.array(v) for k, v in out.items()})
+         qp_iters=np.array([i for _, i in log]), **first, **{k: np.array(v) for k, v in out.items()})
 
 
 def safety_fixture(save):

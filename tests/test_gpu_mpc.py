@@ -59,6 +59,25 @@ def test_qp_assembly_matches_reference(E):
         np.testing.assert_array_equal(qp.Pdiag.cpu().numpy(), np.diag(g[f"{tag}_P"]))
 
 
+def test_gpmpc_subproblem_assembly_matches_the_reference_arguments(E):
+    """a18 on the device: `qp_assemble` in the GP-MPC deviation form (rhs_mode 1, gp_mpc.py:402-411) with the affine GP term,
+    against the first sub-problem of tests/golden/gpmpc_skeleton.npz -- built in the fixture from the A_list / B_list / c_list
+    that the reference's own `GPMPC.solve` hands to `_solve_qp`."""
+    ge, me = E
+    g = load_golden("gpmpc_skeleton.npz")
+    N = 20
+    c_gp = g["qp0_c"][:, 4:7] / 0.1            # the kernel takes the GP means d and forms c = [0,0,0,0,d dt] itself
+    qp, AB, beq, q = _assemble(ge, me, N, g["qp0_X"][None], g["qp0_U"][None], g["qp0_x0"][None], g["qp0_xref"], lin_mode=0,
+                               rhs_mode=1, c_gp=c_gp[None])
+    A, l, u = me.dense_constraints(N, AB[0].cpu().numpy(), beq[0].cpu().numpy(), qp.lb.cpu().numpy(), qp.ub.cpu().numpy())
+    assert np.array_equal(A != 0, g["qp0_A"] != 0)
+    np.testing.assert_allclose(A, g["qp0_A"], rtol=3e-16, atol=0)
+    np.testing.assert_allclose(l, np.maximum(g["qp0_l"], -1e30), rtol=0, atol=2e-13)
+    np.testing.assert_allclose(u, np.minimum(g["qp0_u"], 1e30), rtol=0, atol=2e-13)
+    np.testing.assert_array_equal(q[0].cpu().numpy(), g["qp0_q"])
+    np.testing.assert_array_equal(qp.Pdiag.cpu().numpy(), g["qp0_Pd"])
+
+
 def _oracle_qp(N, x0, xt, seed=0, perturb=0.0):
     from oracle import mpc as ompc
     rng = np.random.default_rng(seed)

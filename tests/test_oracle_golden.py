@@ -320,3 +320,18 @@ def test_gpmpc_sqp_skeleton_matches_the_reference_solve():
         np.testing.assert_allclose(r.U_opt, g["U_opt"][s], rtol=0, atol=1e-8)
         np.testing.assert_allclose(r.X_opt, g["X_opt"][s], rtol=0, atol=1e-8)
         assert r.cost == pytest.approx(float(g["cost"][s]), rel=1e-9)
+
+
+def test_gpmpc_subproblem_rows_match_the_reference_arguments():
+    """a18: the first sub-problem of the skeleton fixture, built there from the A_list / B_list / c_list the reference's
+    `GPMPC.solve` passes to `_solve_qp` (deviation form of gp_mpc.py:402-411 in absolute variables) -- against
+    `build_constraints(mode="gpmpc")`, which derives the same rows from (X_nom, U_nom, c) by itself."""
+    g = load_golden("gpmpc_skeleton.npz")
+    p = ompc.Rocket3DoFParams()
+    A, l, u = ompc.build_constraints(20, g["qp0_X"], g["qp0_U"], g["qp0_x0"], 0.1, p, "analytic", g["qp0_c"], mode="gpmpc")
+    np.testing.assert_array_equal(A != 0, g["qp0_A"] != 0)
+    np.testing.assert_allclose(A, g["qp0_A"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(l[:147], g["qp0_l"][:147], rtol=0, atol=1e-13)
+    np.testing.assert_array_equal(l[147:], g["qp0_l"][147:]); np.testing.assert_array_equal(u[147:], g["qp0_u"][147:])
+    Pd, q = ompc.build_cost(20, g["qp0_xref"])
+    np.testing.assert_array_equal(Pd, g["qp0_Pd"]); np.testing.assert_array_equal(q, g["qp0_q"])
