@@ -32,6 +32,7 @@ NCU_TRAFFIC = {"prologue": 2.2e6, "rollout": 740.6e6, "gp_variance": 691.6e6, "c
                "admm": 83.2e6, "update": 18.5e6}       # profiles/r2_step_kernels_full.md (one closed-loop step)
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 CPU_GP_LEG = None     # which GP code the CPU legs ran (set by cpu_reference_run)
+CPU_CTL_LEG = None    # which controller loop the CPU legs ran
 
 
 def parse_args():
@@ -71,8 +72,24 @@ def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
     else:
         gp = ogp.Simple3DoFGPOracle(noise_variance=NOISE)
         gp.X, gp.U, gp.D, gp.fits = fits_blob[1]
-    ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
-                           max_sqp_iter=sqp_iters)
+    gm = None
+    if sqp_iters == 10 and fits_blob[0] == "reference":
+        # the reference's SQP loop (gp_mpc.py:293 hard-codes 10 iterations): run the reference's OWN GPMPC.solve out of
+        # oracle/_ref, with only the absent third-party parts replaced (oracle/ref_controller.py)
+        from oracle import ref_controller, ref_gp
+        gm = ref_gp.load_gpmpc()
+    if gm is not None:
+        rc = ref_controller.ReferenceGPMPC(gm, gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter))
+
+        class _Ctl:
+            @staticmethod
+            def solve(x, xt):
+                u0, _, _ = rc.solve(x, xt)
+                return type("R", (), {"U_opt": u0[None, :]})
+        ctl = _Ctl
+    else:
+        ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
+                               max_sqp_iter=sqp_iters)
     X0, XT = workloads.sample_initial_conditions(idx, 1)
     x = X0[0]
     p = ompc.Rocket3DoFParams()
@@ -115,7 +132,10 @@ def cpu_reference_run(n_scen, warmup, steps, sqp_iters, qp_max_iter):
         gp.add_data(X, U, D)
         gp.fit()
         blob = ("port", (gp.X, gp.U, gp.D, gp.fits))
-    global CPU_GP_LEG
+    global CPU_GP_LEG, CPU_CTL_LEG
+    CPU_CTL_LEG = ("reference GPMPC.solve (oracle/_ref, unmodified; _solve_qp -> OSQP-form QP + OSQP restatement, dynamics -> "
+                   "in-repo Euler statement)" if (sqp_iters == 10 and ref is not None and ref_gp.load_gpmpc() is not None)
+                   else "numpy restatement oracle/mpc.py::GPMPCOracle")
     CPU_GP_LEG = ("reference src/gp (oracle/_ref: Simple3DoFGP / ExactGP, unmodified)" if ref is not None
                   else "numpy restatement oracle/gp.py (oracle/_ref absent)")
     ctx = mp.get_context("fork")
@@ -164,7 +184,7 @@ def run_reference_arm(args):
         "cpu_baseline": {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
                          "sample": f"{n_scen} scenarios x {steps} closed-loop control steps, one process per scenario "
                                    "(numpy/scipy oracle of the reference algorithm; the reference's own GPMPC needs "
-                                   "CasADi/IPOPT/simdyn, absent)", "gp_leg": CPU_GP_LEG},
+                                   "CasADi/IPOPT/simdyn, absent)", "gp_leg": CPU_GP_LEG, "controller_leg": CPU_CTL_LEG},
         "e2e": {"value": sps, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -288,7 +308,17 @@ def run_b200_arm(args):
         cpu_base = {"value": sps, "unit": "solves/s", "cores": used, "kind": "port",
                     "sample": f"{n_scen} scenarios x 6 closed-loop control steps of the same workload, one process per "
                               f"scenario, {wall:.1f} s wall (numpy/scipy oracle of the reference algorithm)",
-                    "gp_leg": CPU_GP_LEG}
+                    "gp_leg": CPU_GP_LEG, "controller_leg": CPU_CTL_LEG}
+        if not args.no_extra and args.sqp_iters != 10:
+            # CPU side of `extra.sqp10`: the reference's own GPMPC.solve (10 SQP iterations), bounded sample
+            try:
+                sps10, wall10, used10 = cpu_reference_run(n_scen, 1, 2, 10, args.qp_max_iter)
+                cpu_base["sqp10"] = {"value": sps10, "unit": "solves/s", "cores": used10, "kind": "port",
+                                     "sample": f"{n_scen} scenarios x 2 closed-loop control steps at 10 SQP iterations per "
+                                               f"solve, {wall10:.1f} s wall", "gp_leg": CPU_GP_LEG,
+                                     "controller_leg": CPU_CTL_LEG}
+            except Exception as e:  # noqa: BLE001
+                cpu_base["sqp10"] = {"error": repr(e)}
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():

@@ -32,3 +32,26 @@ def load():
     finally:
         sys.dont_write_bytecode = old
     return mod
+
+
+def load_gpmpc():
+    """-> the reference's `src.mpc.gp_mpc` module (GPMPC, GPMPCConfig; unmodified) out of oracle/_ref, or None.  The module
+    and its siblings do `import casadi` at the top (nominal_mpc.py:30-36 raises without it); CasADi is absent, so an EMPTY stub
+    module stands in -- everything except `GPMPC._solve_qp` runs without touching it, and the callers replace that one method."""
+    mpc_dir = os.path.join(_ROOT, "mpc")
+    if not os.path.isfile(os.path.join(mpc_dir, "gp_mpc.py")) or load() is None:
+        return None
+    name = _NAME + ".mpc"
+    if name + ".gp_mpc" in sys.modules:
+        return sys.modules[name + ".gp_mpc"]
+    if importlib.util.find_spec("casadi") is None:
+        sys.modules["casadi"] = types.ModuleType("casadi")
+    pkg = types.ModuleType(name)
+    pkg.__path__ = [mpc_dir]          # bypasses src/mpc/__init__.py (osqp, rti_mpc, ...)
+    sys.modules[name] = pkg
+    old = sys.dont_write_bytecode
+    sys.dont_write_bytecode = True
+    try:
+        return importlib.import_module(name + ".gp_mpc")
+    finally:
+        sys.dont_write_bytecode = old

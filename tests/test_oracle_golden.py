@@ -335,3 +335,20 @@ def test_gpmpc_subproblem_rows_match_the_reference_arguments():
     np.testing.assert_array_equal(l[147:], g["qp0_l"][147:]); np.testing.assert_array_equal(u[147:], g["qp0_u"][147:])
     Pd, q = ompc.build_cost(20, g["qp0_xref"])
     np.testing.assert_array_equal(Pd, g["qp0_Pd"]); np.testing.assert_array_equal(q, g["qp0_q"])
+
+
+def test_reference_gpmpc_solve_from_oracle_ref_reproduces_the_skeleton_fixture():
+    """bench.py's CPU leg at S = 10 runs the reference's own `GPMPC.solve` out of oracle/_ref (oracle/ref_controller.py).
+    It is the construction that generated gpmpc_skeleton.npz, so it must reproduce it exactly."""
+    from oracle import ref_controller, ref_gp
+    ref, gm = ref_gp.load(), ref_gp.load_gpmpc()
+    if ref is None or gm is None:
+        pytest.skip("oracle/_ref is absent (run python oracle/make_ref.py where /root/reference exists)")
+    g = load_golden("gpmpc_skeleton.npz")
+    gp = ref.Simple3DoFGP(use_sparse=False, noise_variance=float(g["noise"])); gp.add_data(g["X"], g["U"], g["D"]); gp.fit()
+    c = ref_controller.ReferenceGPMPC(gm, gp.predict)
+    for s in range(3):
+        u0, ok, it = c.solve(g["x"][s], g["xt"][s])
+        assert (ok, it) == (bool(g["success"][s]), int(g["iterations"][s]))
+        np.testing.assert_array_equal(u0, g["U_opt"][s][0])
+    assert [i for _, i in c.qp_log] == g["qp_iters"].tolist()
