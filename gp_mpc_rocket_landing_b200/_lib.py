@@ -180,6 +180,7 @@ _PROTOS = {
     "gpmpc_qp_assemble_3dof": (c_int, [C.POINTER(Dyn3), c_int, c_int, c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_long,
                                        c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp]),
     "gpmpc_linv_sumsq_parts": (c_int, [c_dp, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
+    "gpmpc_linv_sumsq_parts_n": (c_int, [c_dp, c_int, c_int, c_long, c_dp, c_int, c_long, c_dp, c_dp]),
     "gpmpc_solve_batch_3dof": (c_int, [C.POINTER(Solve3), C.POINTER(c_int), c_dp]),
     "gpmpc_qp_augment_cone_3dof": (c_int, [C.POINTER(Cone3), c_int, c_int, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp, c_dp,
                                            c_dp, c_dp, c_dp]),

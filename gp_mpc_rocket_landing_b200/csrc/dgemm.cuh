@@ -39,6 +39,10 @@ struct GemmParams {
   int col_min;      // cols  n < col_min are computed but not stored
   long part_stride; // EPI_SUMSQ_PART: distance between the partial-sum rows of consecutive M tiles
   int m_fast;       // grid = (M tiles, N tiles) with the M tiles of one N tile adjacent and the longest k loops first
+  int tri_skip;     // with k_tri: A is EXACTLY zero above its diagonal, so inside the diagonal block the 8-row MMA strips skip
+                    // the k chunks that lie entirely above them (44 % of that block's DMMAs)
+  int m_valid;      // > 0: rows m >= m_valid of A are padding that contributes nothing (their B columns are zero): the 8-row
+                    // strips made of such rows are skipped altogether
 };
 
 template <int BM, int BN>
@@ -65,6 +69,9 @@ __device__ __forceinline__ void dgemm_nt_tile(const GemmParams& p, int m0, int n
   int K = p.K;
   if (p.k_tri) K = min(K, m0 + BM);
   const int nk = K / GEMM_BK;
+  const int rowbase = m0 + wm * WM;                                            // first row of this warp's strips
+  const int nk_main = (p.k_tri && p.tri_skip) ? min(nk, m0 / GEMM_BK) : nk;    // chunks entirely left of the diagonal block
+  const int i_hi = (p.m_valid > 0) ? max(0, min(MT, (p.m_valid - rowbase + 7) >> 3)) : MT;   // strips with a valid row
 
   double acc[MT][NT][2];
 #pragma unroll
@@ -103,17 +110,40 @@ __device__ __forceinline__ void dgemm_nt_tile(const GemmParams& p, int m0, int n
     }
     const double* as = sm.a[kt % GEMM_STAGES] + (wm * WM + g) * GEMM_PITCH + t;
     const double* bs = sm.b[kt % GEMM_STAGES] + (wn * WN + g) * GEMM_PITCH + t;
+    if (kt < nk_main && i_hi == MT) {   // warp-uniform: every strip of this warp needs every k of the chunk
 #pragma unroll
-    for (int kk = 0; kk < GEMM_BK; kk += 4) {
-      double af[MT], bf[NT];
+      for (int kk = 0; kk < GEMM_BK; kk += 4) {
+        double af[MT], bf[NT];
 #pragma unroll
-      for (int i = 0; i < MT; ++i) af[i] = as[i * 8 * GEMM_PITCH + kk];
+        for (int i = 0; i < MT; ++i) af[i] = as[i * 8 * GEMM_PITCH + kk];
 #pragma unroll
-      for (int j = 0; j < NT; ++j) bf[j] = bs[j * 8 * GEMM_PITCH + kk];
+        for (int j = 0; j < NT; ++j) bf[j] = bs[j * 8 * GEMM_PITCH + kk];
 #pragma unroll
-      for (int i = 0; i < MT; ++i)
+        for (int i = 0; i < MT; ++i)
 #pragma unroll
-        for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+          for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+      }
+    } else {                            // diagonal block of a triangular A and / or padded rows: strip-wise skipping
+      // strip i (rows rowbase + 8 i .. + 7) sees the 16 columns of this chunk iff the chunk starts at or left of its last row.
+      // One branch per (chunk, strip) around 16 DMMAs: a finer test (per 4 columns) is if-converted by ptxas into predicated
+      // DMMAs, and a predicated-off DMMA still occupies the tensor pipe (measured: no gain).
+      const int krel = (kt >= nk_main) ? kt * GEMM_BK - rowbase : -(1 << 20);
+      double bf[GEMM_BK / 4][NT];
+#pragma unroll
+      for (int kk = 0; kk < GEMM_BK; kk += 4)
+#pragma unroll
+        for (int j = 0; j < NT; ++j) bf[kk / 4][j] = bs[j * 8 * GEMM_PITCH + kk];
+#pragma unroll
+      for (int i = 0; i < MT; ++i) {
+        if (i < i_hi && krel <= 8 * i + 7) {
+#pragma unroll
+          for (int kk = 0; kk < GEMM_BK; kk += 4) {
+            const double af = as[i * 8 * GEMM_PITCH + kk];
+#pragma unroll
+            for (int j = 0; j < NT; ++j) dmma884(acc[i][j][0], acc[i][j][1], af, bf[kk / 4][j]);
+          }
+        }
+      }
     }
   }
   cp_async_wait<0>();

@@ -1555,7 +1555,8 @@ extern "C" int gpmpc_solve_batch_3dof(const GpmpcSolve3* p, int* n_launches, voi
     const double* part;
     int nparts;
     if (p->Linv) {
-      if ((r = gpmpc_linv_sumsq_parts(p->Linv, p->model.n_pad, p->ldi, p->Ks, p->q_pad, p->ldk, p->var_work, (void*)s)))
+      if ((r = gpmpc_linv_sumsq_parts_n(p->Linv, p->model.n, p->model.n_pad, p->ldi, p->Ks, p->q_pad, p->ldk, p->var_work,
+                                        (void*)s)))
         return r;
       part = p->var_work;
       nparts = p->model.n_pad / 64;

@@ -121,6 +121,12 @@ int gpmpc_linv_sumsq(const double* Linv, int n_pad, long ldi, const double* Ks, 
  * caller reduces in the order t = 0, 1, ... (gpmpc_solve_batch_3dof does so inside its variance / covariance kernel). */
 int gpmpc_linv_sumsq_parts(const double* Linv, int n_pad, long ldi, const double* Ks, int q_pad, long ldk, double* work,
                            void* stream);
+/* Same, told the number of training points n <= n_pad (0: unknown): the 8-row DMMA strips that consist of padding rows
+ * n..n_pad-1 only (identity rows of Linv against zero columns of Ks) are skipped.  Both forms also skip, inside each diagonal
+ * block, the 16-column chunks that lie entirely above a strip (Linv is exactly zero there): same sums, fewer DMMAs
+ * (branches around whole strips: a predicated-off DMMA still occupies the tensor pipe). */
+int gpmpc_linv_sumsq_parts_n(const double* Linv, int n, int n_pad, long ldi, const double* Ks, int q_pad, long ldk,
+                             double* work, void* stream);
 
 /* Small (M <= 144) lower-triangular solve against many columns, optional sumsq[c] += sign * sum_i x_ic^2:
  * sparse_gp.py:190 (A = L_uu^{-1} K_uf), :293-299 (v, w and their squared norms). */
