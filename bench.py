@@ -29,7 +29,7 @@ sys.path.insert(0, ROOT)
 N_HORIZON, DT, N_TRAIN, NOISE = 20, 0.1, 1000, 1e-4
 # dram__bytes_read.sum + dram__bytes_write.sum per step from the committed `ncu --set full` captures (profiles/), B = 4096
 NCU_TRAFFIC = {"prologue": 2.2e6, "rollout": 740.6e6, "gp_variance": 691.6e6, "cov": 17.7e6, "assemble": 26.8e6,
-               "admm": 83.2e6, "update": 18.5e6}       # profiles/r2_step_kernels_full.md (one closed-loop step)
+               "admm": 83.2e6, "update": 18.5e6}       # profiles/r2_step_kernels_full_v2.md (one closed-loop step)
 METRIC = "GP-MPC solves/sec (3-DoF, N=20, 1000-pt exact GP)"
 CPU_GP_LEG = None     # which GP code the CPU legs ran (set by cpu_reference_run)
 CPU_CTL_LEG = None    # which controller loop the CPU legs ran
