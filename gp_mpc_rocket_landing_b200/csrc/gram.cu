@@ -43,48 +43,52 @@ extern "C" int gpmpc_scale_inputs(const double* X, int n, int D, long ldx, const
 }
 
 // ------------------------------------------------------------------------------------------------ kernel functions
-// 128 x 128 output tile per CTA, 8 warps (2 x 4), warp tile 64 x 32 = 8 x 4 DMMA tiles, K = DP (<= 64).
+// 64 x 128 output tile per CTA, 8 warps (2 x 4), warp tile 32 x 32 = 4 x 4 DMMA tiles, K = DP (<= 64).  (Was 128 x 128 with
+// 64 values per thread: 172 registers, one CTA per SM, and the exp epilogue ran latency-bound at 8 warps per SM -- 203 us per
+// 4096 x 4096 lower triangle; the smaller tile keeps two CTAs resident.)
+constexpr int GRAM_BM = 64;
 template <int MODE>  // 0: Gram ; 1: SE-ARD d/dlog(l_dim) = K * (x1_d - x2_d)^2 / l_d^2 with x/l already scaled
-__global__ void __launch_bounds__(256) gram_kernel(int kind, const double* __restrict__ Xs1,
+__global__ void __launch_bounds__(256, 2) gram_kernel(int kind, const double* __restrict__ Xs1,
                                                    const double* __restrict__ sq1, int n1_valid,
                                                    const double* __restrict__ Xs2, const double* __restrict__ sq2,
                                                    int n2_valid, int DP, double sv, double diag_add, int pad_identity,
                                                    int lower_only, int grad_dim, double* __restrict__ K, long ldk) {
   extern __shared__ double sm[];
   const int pitch = ((DP + 15) / 16) * 16 + 4;
-  double* A = sm;                 // 128 x pitch
-  double* B = sm + 128 * pitch;   // 128 x pitch
-  const int m0 = blockIdx.y * 128, n0 = blockIdx.x * 128;
-  if (lower_only && n0 > m0) return;
+  double* A = sm;                     // GRAM_BM x pitch
+  double* B = sm + GRAM_BM * pitch;   // 128 x pitch
+  const int m0 = blockIdx.y * GRAM_BM, n0 = blockIdx.x * 128;
+  if (lower_only && n0 > m0 + GRAM_BM - 1) return;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int wm = warp >> 2, wn = warp & 3;
   for (int idx = tid; idx < 128 * DP; idx += 256) {
     int r = idx / DP, d = idx - r * DP;
-    A[r * pitch + d] = Xs1[(long)(m0 + r) * DP + d];
+    if (r < GRAM_BM) A[r * pitch + d] = Xs1[(long)(m0 + r) * DP + d];
     B[r * pitch + d] = Xs2[(long)(n0 + r) * DP + d];
   }
   __syncthreads();
-  double acc[8][4][2];
+  constexpr int MT = GRAM_BM / 16;
+  double acc[MT][4][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < MT; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-  const double* as = A + (wm * 64 + g) * pitch + t;
+  const double* as = A + (wm * (GRAM_BM / 2) + g) * pitch + t;
   const double* bs = B + (wn * 32 + g) * pitch + t;
   for (int kk = 0; kk < DP; kk += 4) {
-    double af[8], bf[4];
+    double af[MT], bf[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) af[i] = as[i * 8 * pitch + kk];
+    for (int i = 0; i < MT; ++i) af[i] = as[i * 8 * pitch + kk];
 #pragma unroll
     for (int j = 0; j < 4; ++j) bf[j] = bs[j * 8 * pitch + kk];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < MT; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int ml = wm * 64 + i * 8 + g, m = m0 + ml;
+  for (int i = 0; i < MT; ++i) {
+    const int ml = wm * (GRAM_BM / 2) + i * 8 + g, m = m0 + ml;
     const double s1 = sq1[m];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -121,14 +125,14 @@ static int launch_gram(int mode, int kind, const double* Xs1, const double* sq1,
   GPMPC_REQUIRE(kind >= 0 && kind <= 3, "gpmpc_gram: unknown kernel kind");
   if (n1_pad == 0 || n2_pad == 0) return GPMPC_OK;
   const int pitch = ((DP + 15) / 16) * 16 + 4;
-  size_t smem = sizeof(double) * 2 * 128 * pitch;
+  size_t smem = sizeof(double) * (GRAM_BM + 128) * pitch;
   static GpmpcPerDevice configured;
   if (!configured.here()) {
     cudaFuncSetAttribute(gram_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     cudaFuncSetAttribute(gram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     configured.here() = 1;
   }
-  dim3 grid(n2_pad / 128, n1_pad / 128);
+  dim3 grid(n2_pad / 128, n1_pad / GRAM_BM);
   if (mode == 0)
     gram_kernel<0><<<grid, 256, smem, stream>>>(kind, Xs1, sq1, n1_valid, Xs2, sq2, n2_valid, DP, sv, diag_add,
                                                 pad_identity, lower_only, grad_dim, K, ldk);
