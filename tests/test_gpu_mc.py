@@ -280,3 +280,32 @@ def test_closed_loop_outcomes_match_the_cpu_oracle_on_64_seeds(mode):
     # whose residual sits on the tolerance at a check may stop one check -- 25 iterations -- earlier or later)
     it = int(mc.counts.cpu().numpy()[7])
     assert abs(it - int(g[mode + "_admm_iters"].sum())) <= 0.02 * it
+
+
+def test_reset_scenarios_with_a_host_mask_equals_the_device_mask():
+    """`GPMPC.reset_scenarios` with a numpy mask (the path bench.py's end-to-end loop takes: one pinned H2D copy, one launch)
+    against the same reset with a device mask: warm-start flags, duals and rho of the masked scenarios are cleared, the
+    others untouched, and the next solve is identical either way."""
+    import torch
+    import bench
+    from gp_mpc_rocket_landing_b200 import workloads
+
+    class A:
+        batch, sqp_iters, qp_max_iter = 96, 1, 1000
+    X0, _ = workloads.sample_initial_conditions(0, 96)
+    mask = np.zeros(96, dtype=bool); mask[[0, 5, 31, 32, 95]] = True
+    outs = []
+    for host in (True, False):
+        dyn, gp, ctl, _ = bench.build_problem(A, 0)
+        x = torch.as_tensor(X0, device="cuda")
+        ctl.solve_batch(x, per_step_target=True)
+        st = ctl._batch
+        assert int(st.has_warm.sum().item()) == 96 and float(st.ws.rho.min().item()) > 0.0
+        ctl.reset_scenarios(mask if host else torch.as_tensor(mask, device="cuda"))
+        hw = st.has_warm.cpu().numpy(); rho = st.ws.rho.cpu().numpy(); y = st.ws.y.cpu().numpy()
+        assert np.array_equal(hw == 0, mask) and np.array_equal(rho == 0.0, mask)
+        assert not y[mask].any() and np.abs(y[~mask]).max() > 0
+        sol = ctl.solve_batch(x, per_step_target=True)
+        outs.append((sol.U_opt.cpu().numpy().copy(), sol.qp_iterations.cpu().numpy().copy()))
+    np.testing.assert_array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_array_equal(outs[0][1], outs[1][1])
