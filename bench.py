@@ -79,7 +79,7 @@ def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
         from oracle import ref_controller, ref_gp
         gm = ref_gp.load_gpmpc()
     if gm is not None:
-        rc = ref_controller.ReferenceGPMPC(gm, gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter))
+        rc = ref_controller.ReferenceGPMPC(gm, gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter, linsys="sparse"))
 
         class _Ctl:
             @staticmethod
@@ -88,7 +88,7 @@ def _cpu_worker(idx, conn, fits_blob, warmup, steps, sqp_iters, qp_max_iter):
                 return type("R", (), {"U_opt": u0[None, :]})
         ctl = _Ctl
     else:
-        ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter),
+        ctl = ompc.GPMPCOracle(gp.predict, N=N_HORIZON, dt=DT, settings=ompc.OSQPSettings(max_iter=qp_max_iter, linsys="sparse"),
                                max_sqp_iter=sqp_iters)
     X0, XT = workloads.sample_initial_conditions(idx, 1)
     x = X0[0]

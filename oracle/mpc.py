@@ -205,6 +205,10 @@ class OSQPSettings:
     adaptive_rho_interval: int = 25
     adaptive_rho_tolerance: float = 5.0
     warm_start: bool = True
+    # KKT solver of the restatement: "dense" (LAPACK LU; what every parity test and golden file uses) or "sparse" (SuperLU on
+    # the 0.6 %-dense quasi-definite KKT matrix, closer to the QDLDL factorisation inside the real OSQP; used by bench.py's
+    # CPU legs so that the timed CPU baseline does not pay for a dense 561 x 561 factorisation the library would not do)
+    linsys: str = "dense"
 
 
 @dataclass
@@ -231,7 +235,9 @@ class OSQPOracle:
     is solved by a dense LU; adaptive rho is iteration-count based; across re-scalings (update with new
     A values) the *unscaled* iterates x, y are kept and re-scaled (the C code keeps the scaled ones)."""
 
-    def __init__(self, Pd, q, A, l, u, settings: OSQPSettings | None = None):
+    def __init__(self, Pd, q, A, l, u, settings: OSQPSettings | None = None, rho0: float | None = None):
+        """rho0: start from this rho (the adapted value a persistent solver object carries over) -- same result as setting
+        `rho` after construction and refactorising, without factorising twice."""
         self.s = settings or OSQPSettings()
         self.n, self.m = A.shape[1], A.shape[0]
         self.Pd0 = np.asarray(Pd, float).copy()
@@ -239,7 +245,7 @@ class OSQPOracle:
         self.A0 = np.asarray(A, float).copy()
         self.l0 = np.maximum(np.asarray(l, float), -OSQP_INFTY)
         self.u0 = np.minimum(np.asarray(u, float), OSQP_INFTY)
-        self.rho = self.s.rho
+        self.rho = self.s.rho if rho0 is None else float(rho0)
         self.x = np.zeros(self.n); self.y = np.zeros(self.m); self.z = np.zeros(self.m)  # unscaled
         self._scale()
         self._factor()
@@ -279,7 +285,12 @@ class OSQPOracle:
         K[:n, n:] = self.A.T
         K[n:, :n] = self.A
         K[n:, n:] = -np.diag(1.0 / self.rho_vec)
-        self._lu = sla.lu_factor(K)
+        if self.s.linsys == "sparse":
+            import scipy.sparse as sp
+            import scipy.sparse.linalg as spla
+            self._lu = spla.splu(sp.csc_matrix(K))
+        else:
+            self._lu = sla.lu_factor(K)
 
     # -- updates (osqp python update(): q, then bounds, then Ax -> rescale + refactor)
     def update(self, q=None, l=None, u=None, A=None):
@@ -360,7 +371,7 @@ class OSQPOracle:
         for it in range(1, s.max_iter + 1):
             xp, zp = x, z
             rhs = np.concatenate([s.sigma * xp - self.q, zp - y / self.rho_vec])
-            sol = sla.lu_solve(self._lu, rhs)
+            sol = self._lu.solve(rhs) if self.s.linsys == "sparse" else sla.lu_solve(self._lu, rhs)
             xt, nu = sol[:n], sol[n:]
             zt = zp + (nu - y) / self.rho_vec
             x = s.alpha * xt + (1 - s.alpha) * xp
@@ -628,18 +639,15 @@ class GPMPCOracle:
                 for k in range(N):
                     d, _ = self.gp_predict(X[k], U[k]); c_gp[k, 4:7] = d * dt
             A, l, u = build_constraints(N, X, U, x0, dt, p, "analytic", c_gp, mode="gpmpc")
+            rho0 = self.rho_warm if (self.keep_rho and self.rho_warm is not None) else None
             if self.cone is not None:
                 AB = np.stack([A[NX + k * NX:NX + (k + 1) * NX, k * 10:(k + 1) * 10] for k in range(N)])
                 ABc, beqc, qc, zc = augment_cone_qp(N, AB, l[:NX * (N + 1)], q, X, U, self.cone)
                 Pdc, lbc, ubc = cone_shared_data(N, self.cone)
                 Ac, lc, uc = dense_stage_constraints(NXC, NU, N, ABc, beqc, lbc, ubc)
-                qp = OSQPOracle(Pdc, qc, Ac, lc, uc, self.settings)
+                qp = OSQPOracle(Pdc, qc, Ac, lc, uc, self.settings, rho0=rho0)
             else:
-                qp = OSQPOracle(Pd, q, A, l, u, self.settings)
-            if self.keep_rho and self.rho_warm is not None:
-                qp.rho = self.rho_warm
-                qp._set_rho_vec()
-                qp._factor()
+                qp = OSQPOracle(Pd, q, A, l, u, self.settings, rho0=rho0)
             qp.warm_start(x=traj_to_vec(X, U) if self.cone is None else zc, y=y)
             res = qp.solve()
             self.rho_warm = res.rho

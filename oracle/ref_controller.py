@@ -75,11 +75,7 @@ class ReferenceGPMPC:
             row += 7; idx += 10
         A[row:, :] = np.eye(n)
         l[row:], u[row:] = self._box
-        qp = ompc.OSQPOracle(Pd, q, A, l, u, self.settings)
-        if self._rho is not None:
-            qp.rho = self._rho
-            qp._set_rho_vec()
-            qp._factor()
+        qp = ompc.OSQPOracle(Pd, q, A, l, u, self.settings, rho0=self._rho)
         qp.warm_start(x=ompc.traj_to_vec(X_nom[:, :7], U_nom), y=self._y)
         r = qp.solve()
         self._rho = r.rho
