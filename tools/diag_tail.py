@@ -50,12 +50,25 @@ def three_dof():
     class A: pass
     a = A(); a.batch = 4096; a.sqp_iters = 1; a.qp_max_iter = 1000
     dyn, gp, ctl, mc = bench.build_problem(a, 0)
-    hist = []
-    for k in range(60):
+    hist, cold = [], []
+    for k in range(80):
+        hw = ctl._batch.has_warm.cpu().numpy().copy() if ctl._batch is not None else np.zeros(4096, dtype=np.int32)
         mc.step()
         if k >= 20:
             hist.append(ctl._batch.ws.iters.cpu().numpy().astype(np.float64).copy())
+            cold.append(hw == 0)
     report("3dof B=4096", hist, 444, 15.0)   # set-up 0.6 ms ~ 15 iterations of 39.6 us
+    # cold-started QPs (respawned scenarios: no warm start, default rho) first, the rest in index order
+    res = []
+    for cur, c in zip(hist, cold):
+        order = np.concatenate([np.nonzero(c)[0], np.nonzero(~c)[0]])
+        res.append((makespan(cur, 444, 15.0), makespan(cur[order], 444, 15.0), makespan(np.sort(cur)[::-1], 444, 15.0),
+                    float(cur.sum() + 15.0 * len(cur)) / 444, int(c.sum()), float(cur[c].mean()) if c.any() else 0.0,
+                    float(cur[~c].mean())))
+    a = np.array(res)
+    print(json.dumps({"case": "3dof cold-first order", "makespan_index_order": a[:, 0].mean(), "makespan_cold_first": a[:, 1].mean(),
+                      "makespan_sorted_by_true": a[:, 2].mean(), "perfect_balance": a[:, 3].mean(),
+                      "cold_qps_per_step": a[:, 4].mean(), "mean_iters_cold": a[:, 5].mean(), "mean_iters_warm": a[:, 6].mean()}))
 
 
 def six_dof():
@@ -80,4 +93,5 @@ def six_dof():
 
 if os.environ.get("ONLY6") is None:
     three_dof()
-six_dof()
+if os.environ.get("ONLY3") is None:
+    six_dof()
