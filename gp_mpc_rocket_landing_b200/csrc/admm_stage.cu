@@ -466,7 +466,7 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
     }
     __syncthreads();
   };
-  factorize();
+  bool need_factor = true;   // ONE inlined copy of the factorisation (it is 125 KB of code): run at the top of the loop
 
   // own - sum_c f[c] v[c] with a short dependency chain (4 partial sums, `own` folded into the first)
   auto chain_dot = [&](const double* f, const double* v, int len, double own) -> double {
@@ -699,6 +699,10 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
   }
   __syncthreads();
   for (it = 1; it <= S.max_iter; ++it) {
+    if (need_factor) {
+      factorize();
+      need_factor = false;
+    }
     const bool can_check = S.check_every > 0 && (it % S.check_every) == 0;
     const bool can_adapt = S.adaptive_rho && S.adaptive_rho_interval > 0 && (it % S.adaptive_rho_interval) == 0;
     const bool checking = can_check || can_adapt || it == S.max_iter;
@@ -764,7 +768,7 @@ admm_stage_kernel(int Nrt, int nbatch, const double* __restrict__ ABg, const dou
       if (can_adapt && (co.rho_est > rho * S.adaptive_rho_tolerance || co.rho_est < rho / S.adaptive_rho_tolerance)) {
         rho = co.rho_est;
         rho_eq = RHO_EQ_OVER_INEQ * rho; rei = 1.0 / rho_eq; rhoi = 1.0 / rho;
-        factorize();
+        need_factor = true;
       }
       if (it < S.max_iter) {  // (the block reduction inside check() separates its reads of weq from this write)
 #pragma unroll
