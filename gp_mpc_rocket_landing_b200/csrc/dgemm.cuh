@@ -41,7 +41,6 @@ struct GemmParams {
   int m_fast;       // grid = (M tiles, N tiles) with the M tiles of one N tile adjacent and the longest k loops first
   int tri_skip;     // with k_tri: A is EXACTLY zero above its diagonal, so inside the diagonal block the 8-row MMA strips skip
                     // the k chunks that lie entirely above them (44 % of that block's DMMAs)
-  int no_load;      // EXPERIMENT: skip the operand loads (timing of the DMMA side alone; results are garbage)
   int m_valid;      // > 0: rows m >= m_valid of A are padding that contributes nothing (their B columns are zero): the 8-row
                     // strips made of such rows are skipped altogether
 };
@@ -81,7 +80,6 @@ __device__ __forceinline__ void dgemm_nt_tile(const GemmParams& p, int m0, int n
     for (int j = 0; j < NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
   auto load_tile = [&](int stage, int kt) {
-    if (p.no_load) return;
     const int k0 = kt * GEMM_BK;
     // A: BM rows x 16 doubles = BM*8 chunks of 16 B
 #pragma unroll

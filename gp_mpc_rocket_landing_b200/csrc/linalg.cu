@@ -637,8 +637,6 @@ extern "C" int gpmpc_linv_sumsq_parts_n(const double* Linv, int n, int n_pad, lo
   static const bool no_skip = getenv("GPMPC_NO_TRI_SKIP") != nullptr;   // A/B switch for tools/bench_trigemm.py
   p.tri_skip = no_skip ? 0 : 1;
   p.m_valid = no_skip ? 0 : n;
-  static const bool no_load = getenv("GPMPC_GEMM_NOLOAD") != nullptr;
-  p.no_load = no_load ? 1 : 0;
   return launch_dgemm_nt<64, 128, 2, 4>(p, 1, (cudaStream_t)stream_);
 }
 
