@@ -6,6 +6,7 @@ import bench
 
 class A: pass
 a = A(); a.batch = int(os.environ.get("B", 4096)); a.sqp_iters = int(os.environ.get("S", 1)); a.qp_max_iter = 1000
+a.admm_variant = int(os.environ.get("ADMM_VARIANT", 0))
 dyn, gp, ctl, mc = bench.build_problem(a, 0)
 for k in range(int(os.environ.get("STEPS", 4))):
     mc.step()
